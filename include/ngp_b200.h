@@ -1,0 +1,165 @@
+/* ngp_b200.h -- C ABI of the B200-native instant-NGP NeRF hot path.
+ *
+ * Drop-in boundary for the reference's internal/{sampler,network,render} modules and the tiny-cuda-nn
+ * objects they call (file:line below are relative to the reference tree).  Plain pointers and sizes only:
+ * every pointer named d_* is DEVICE memory owned by the caller, every call is asynchronous on `stream`
+ * (a cudaStream_t passed as void*), nothing allocates, nothing synchronises with the host.
+ * Return value: 0 on success, <0 on error (message via ngp_last_error()).  There is no CPU fallback.
+ */
+#ifndef NGP_B200_H
+#define NGP_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NGP_MAX_LEVELS 32
+#define NGP_MLP_PARAMS 10240u   /* W0[64][32] W1[16][64] V0[64][32] V1[64][64] V2[16][64], row-major [out][in] */
+
+/* Multiresolution hash-grid geometry (tiny-cuda-nn/encodings/grid.h:475-537). Built by ngp_grid_desc_init. */
+typedef struct ngp_grid_desc {
+	uint32_t n_levels;
+	uint32_t offsets[NGP_MAX_LEVELS + 1];  /* prefix sums of per-level entry counts (2 fp16 features / entry) */
+	float    scales[NGP_MAX_LEVELS];       /* exp2f(l*log2(per_level_scale))*base - 1, host float math */
+	uint32_t resolutions[NGP_MAX_LEVELS];  /* ceil(scale)+1 */
+} ngp_grid_desc;
+
+/* Occupancy sampler parameters (internal/sampler/occupancy_sampler.cu:603-631). */
+typedef struct ngp_sampler_cfg {
+	float    aabb_min, aabb_max;     /* cube [min,max]^3 = 0.5 -/+ 0.5*aabb_scale */
+	uint32_t grid_size;              /* 128 */
+	uint32_t n_cascades;             /* >= 2 */
+	uint32_t max_steps;              /* maximum_marching_steps, 1024 */
+	float    cone_angle;             /* cone_angle_constant */
+	float    min_step, max_step;     /* sqrt3/max_steps, sqrt3*2^(C-1)/grid_size */
+	float    near_distance;          /* 0.2 */
+} ngp_sampler_cfg;
+
+/* Pinhole camera set (internal/dataset/nerf_synthetic.h; xforms 3x4 column-major, 12 floats each). */
+typedef struct ngp_camera_cfg {
+	int32_t width, height;
+	float   fx, fy, ppx, ppy;
+} ngp_camera_cfg;
+
+/* Compositing parameters (internal/render/ray_marcher.cu:15-54, internal/utils/common.h:57-94). */
+typedef struct ngp_render_cfg {
+	uint32_t n_cascades;
+	float    min_step;
+	int32_t  rgb_activation, density_activation;   /* EActivation: 0 None 1 ReLU 2 Logistic 3 Exponential */
+	int32_t  loss_type;                            /* ELossType: 0 L2 1 L1 2 Mape 3 Smape 4 SmoothL1 5 LogL1 6 RelativeL2 */
+	int32_t  color_space;                          /* EColorSpace: 0 Linear 1 SRGB */
+	int32_t  train_with_random_bg_color, train_in_linear_color;
+	float    transmittance_threshold;
+	float    min_optical_thickness;
+	float    loss_scale;                           /* 128 */
+	float    background_color[3];
+} ngp_render_cfg;
+
+/* Optimizer chain Ema(ExponentialDecay(Adam)) (tiny-cuda-nn/optimizers/{adam,ema,exponential_decay}.h). */
+typedef struct ngp_optimizer_cfg {
+	float learning_rate, beta1, beta2, epsilon, l2_reg, loss_scale, ema_decay;
+} ngp_optimizer_cfg;
+
+const char* ngp_last_error(void);
+int ngp_abi_version(void);
+
+/* ---- hash grid -------------------------------------------------------------------------------- */
+/* replaces GridEncodingTemplated ctor (grid.h:475-537); returns the number of table entries */
+uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, uint32_t log2_hashmap_size, uint32_t base_resolution, float per_level_scale);
+/* replaces NGPNetwork::auto_determine_grid_parameters (internal/network/ngp_network.h:597-641) */
+float ngp_auto_per_level_scale(float desired_resolution, uint32_t base_resolution, uint32_t n_levels);
+
+/* replaces GridEncodingTemplated::encode (grid.h:539-610): d_out[i*out_stride + 2*l + f], fp16.
+ * d_indices (optional, tests): [n][n_levels][8] u32 entry index of each corner. */
+int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_table,
+                        const ngp_grid_desc* desc, void* d_out, uint32_t out_stride, uint32_t* d_indices);
+/* replaces GridEncodingTemplated::backward (grid.h:612-696): zeroes d_grad (fp16, 2*entries) when zero_first,
+ * then scatters w*dL/dy with warp-aggregated half2 atomics. */
+int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
+                        const ngp_grid_desc* desc, void* d_grad, int zero_first);
+
+/* ---- network ---------------------------------------------------------------------------------- */
+/* d_params: fp16 arena [NGP_MLP_PARAMS | grid table], reference order (ngp_network.h:496-541). */
+size_t ngp_network_workspace_bytes(uint32_t n);
+/* replaces NGPNetwork::inference_mixed_precision (ngp_network.h:217-284): Coordinate[n] (7 floats) -> rgbsigma [n][4] fp16.
+ * d_n_valid (optional): device counter; tiles beyond it are skipped. */
+int ngp_network_inference(void* stream, const float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_params,
+                          const ngp_grid_desc* desc, void* d_rgbsigma, void* d_workspace, size_t workspace_bytes);
+/* replaces NGPNetwork::density (ngp_network.h:286-307): positions (stride floats) -> [n][16] fp16 */
+int ngp_network_density(void* stream, const float* d_positions, uint32_t stride_floats, uint32_t n, const void* d_params,
+                        const ngp_grid_desc* desc, void* d_out, void* d_workspace, size_t workspace_bytes);
+/* replaces NGPNetwork::forward + ::backward (ngp_network.h:325-494) on the compacted batch: writes rgbsigma [n][4]
+ * (optional) and the fp16 gradient arena d_grads [NGP_MLP_PARAMS | grid] (overwritten, not accumulated). */
+int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
+                      const void* d_dloss, void* d_rgbsigma, void* d_grads, void* d_workspace, size_t workspace_bytes);
+/* the two MLPs alone on a precomputed encoding (tests, profiling): enc [n][32] fp16 */
+int ngp_mlp_inference(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, void* d_rgbsigma);
+int ngp_mlp_train(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, const void* d_dloss,
+                  void* d_rgbsigma, void* d_denc, float* d_wgrad_f32 /* [NGP_MLP_PARAMS], accumulated into */);
+
+/* ---- sampler ---------------------------------------------------------------------------------- */
+/* OccupancySampler::init -> mark_untrained_density_grid (occupancy_sampler.cu:18-61) */
+int ngp_mark_untrained_grid(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, uint32_t n_images, const float* d_xforms, float* d_grid);
+/* sample_positions_from_grid -> generate_grid_samples_nerf_nonuniform (:63-105) */
+int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
+                              const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices);
+/* update_grid (:705-735): memset current, splat max, decay max */
+int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,
+                    int density_activation, float decay, float* d_grid_current, float* d_grid);
+/* update_grid_bitfield (:737-760): mean of cascade 0 -> d_mean[0], bits, max-pool */
+int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg, const float* d_grid, float min_optical_thickness, float* d_mean, uint8_t* d_bitfield);
+/* sample_coords_from_dataset -> generate_training_samples_nerf (:310-449).  Compaction is in ray order (deterministic).
+ * d_counters: [0] rays kept, [1] samples counted (both must be zero on entry).  d_scan_ws: >= ngp_scan_workspace_bytes(n_rays), zeroed by the call. */
+size_t ngp_scan_workspace_bytes(uint32_t n);
+int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, uint32_t n_rays, uint32_t n_rays_shift,
+                                  uint32_t n_coords, uint32_t n_images, const float* d_xforms, const void* d_images, const uint8_t* d_bitfield,
+                                  int snap_to_pixel_centers, uint64_t rng_state, uint64_t rng_inc, float* d_rays, float* d_rays_rgba,
+                                  uint32_t* d_numsteps, float* d_coords, uint32_t* d_counters, uint32_t* d_per_ray_n, void* d_scan_ws);
+/* generate_rays_from_camera_matrix (:813-855): init_rays_with_payload_kernel_nerf + advance_pos_nerf; payload = 40 B records */
+int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                  int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads);
+/* generate_coords_from_rays (:857-877) */
+int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps,
+                                  const uint8_t* d_bitfield, void* d_payloads, float* d_coords);
+
+/* ---- render ----------------------------------------------------------------------------------- */
+/* RayMarcher::volume_rendering_with_loss_and_gradient (ray_marcher.cu:15-213, 305-377), compaction in ray order */
+int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
+                        const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
+                        uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,
+                        const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, void* d_scan_ws);
+/* fill_rollover_and_rescale + fill_rollover (tiny-cuda-nn/common_device.h:485-505; testbed.cu:398-404) */
+int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted);
+/* RayMarcher::volume_rendering (ray_marcher.cu:215-295, 379-416); camera_fwd = camera matrix column 2 */
+int ngp_composite_infer(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t n_steps_offset,
+                        void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
+                        float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale);
+/* compact_rays_kernel (testbed.cu:423-446) with warp-aggregated reservation; counters: [0] alive, [1] hit */
+int ngp_compact_rays(void* stream, uint32_t n_rays, const uint32_t* d_n_rays, const void* d_src_payloads, const float* d_src_rgba,
+                     void* d_dst_payloads, float* d_dst_rgba, void* d_hit_payloads, float* d_hit_rgba, uint32_t* d_n_alive, uint32_t* d_n_hit);
+/* shade_kernel (testbed.cu:448-477) */
+int ngp_shade(void* stream, uint32_t n_hit_max, const uint32_t* d_n_hit, const float* d_rgba, const void* d_payloads, float* d_frame, int render_mode, int train_in_linear);
+/* CudaRenderBuffer::accumulate / ::tonemap (render_buffer.cu:51-186) on a linear float4 buffer */
+int ngp_accumulate(void* stream, uint32_t n_pixels, const float* d_frame, float* d_accum, float sample_count, int color_space);
+int ngp_tonemap(void* stream, uint32_t n_pixels, float exposure, const float* background_rgba_host, const float* d_accum, int color_space,
+                int output_color_space, int tonemap_curve, float* d_out);
+
+/* ---- parameters / optimizer ------------------------------------------------------------------- */
+/* Trainer::initialize_params (trainer.h:73-112): xavier MLP (host draws) + grid U(-1e-4,1e-4); fills fp32 master and fp16 params.
+ * rng_state is advanced exactly like the reference's host generator. */
+int ngp_init_params(void* stream, uint64_t* rng_state, uint64_t rng_inc, uint64_t n_grid_params, float* d_params_fp32, void* d_params_fp16);
+/* Trainer::optimizer_step (trainer.h:198) -> ExponentialDecay -> Adam -> EMA, one fused pass.  step = Adam step count BEFORE this step. */
+int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, uint64_t n_params, uint64_t n_matrix_params, uint32_t step, float learning_rate,
+                       float* d_w32, void* d_w16, const void* d_g16, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16);
+/* from_rgba32<__half> (internal/utils/common_device.h:160-175) */
+int ngp_from_rgba32(void* stream, uint64_t n_pixels, const uint8_t* d_rgba8, void* d_out_half);
+/* reduce_sum of the per-ray loss (testbed.cu:288) */
+int ngp_reduce_sum(void* stream, const float* d_in, uint64_t n, float* d_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NGP_B200_H */

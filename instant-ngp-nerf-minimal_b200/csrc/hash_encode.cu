@@ -1,0 +1,190 @@
+// Multiresolution hash-grid encoding, forward gather and backward scatter, for sm_100a.
+// Replaces tiny-cuda-nn/encodings/grid.h: extract_position (:108), kernel_grid (:122), transpose_encoded_position (:371),
+// transpose_gradients (:386), kernel_grid_backward (:259) -- one kernel per direction, no SoA/AoS round trips.
+//
+// Layout: a warp owns 32 consecutive samples and walks the levels; consecutive samples along a ray share cells on the
+// coarse levels, so a warp's gathers hit few cache lines and its scatter can be reduced in-warp before the atomic.
+// The whole table (23 MB at T=2^19) stays resident in B200's 126 MB L2, so levels need not be swept one at a time.
+// Roofline: L2 bandwidth (588 algorithmic bytes / sample).
+#include "common.cuh"
+
+namespace ngp {
+
+struct LevelInfo { uint32_t offset, size, res; float scale; };
+
+__device__ __forceinline__ uint32_t grid_index(uint32_t size, uint32_t res, bool hashed, uint32_t gx, uint32_t gy, uint32_t gz) {
+	// grid.h:84-100 -- dense index while the stride fits the table, spatial hash otherwise
+	uint32_t index;
+	if (hashed) {
+		index = gx ^ (gy * 19349663u) ^ (gz * 83492791u);
+	} else {
+		uint32_t stride = 1; index = 0;
+		index += gx * stride; stride *= res;
+		if (stride <= size) { index += gy * stride; stride *= res; }
+		if (stride <= size) { index += gz * stride; }
+	}
+	return (size & (size - 1)) == 0 ? (index & (size - 1)) : (index % size);
+}
+
+__device__ __forceinline__ bool level_is_hashed(uint32_t size, uint32_t res) {
+	// after the dense loop stride == res^3 unless it stopped early; "size < stride" decides (grid.h:95)
+	uint64_t s = 1;
+	for (int d = 0; d < 3 && s <= size; ++d) s *= res;
+	return size < s;
+}
+
+__device__ __forceinline__ void pos_fract(float x, float scale, uint32_t& g, float& w) {
+	float p = __fmaf_rn(x, scale, 0.5f);
+	float f = floorf(p);
+	g = (uint32_t)(int)f;
+	w = p - f;
+}
+
+template <bool WRITE_INDICES>
+__global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
+	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n, const uint32_t* __restrict__ n_valid,
+	const __half2* __restrict__ table, const __grid_constant__ ngp_grid_desc desc,
+	__half* __restrict__ out, uint32_t out_stride, uint32_t* __restrict__ indices)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (n_valid && blockIdx.x * blockDim.x >= *n_valid) return;
+	if (i >= n) return;
+	const float x = xyz[(size_t)i * stride_floats + 0], y = xyz[(size_t)i * stride_floats + 1], z = xyz[(size_t)i * stride_floats + 2];
+	__half* orow = out + (size_t)i * out_stride;
+
+	#pragma unroll 2
+	for (uint32_t l = 0; l < desc.n_levels; ++l) {
+		const uint32_t off = desc.offsets[l], size = desc.offsets[l + 1] - off, res = desc.resolutions[l];
+		const float scale = desc.scales[l];
+		const bool hashed = level_is_hashed(size, res);
+		const __half2* grid = table + off;
+		uint32_t gx, gy, gz; float wx, wy, wz;
+		pos_fract(x, scale, gx, wx); pos_fract(y, scale, gy, wy); pos_fract(z, scale, gz, wz);
+		uint32_t e[8];
+		#pragma unroll
+		for (int c = 0; c < 8; ++c)
+			e[c] = grid_index(size, res, hashed, gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
+		__half2 v[8];
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) v[c] = __ldg(grid + e[c]);
+		__half2 acc = __floats2half2_rn(0.f, 0.f);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			float w = 1.f;
+			w *= (c & 1) ? wx : 1 - wx;
+			w *= (c & 2) ? wy : 1 - wy;
+			w *= (c & 4) ? wz : 1 - wz;
+			const float2 f = __half22float2(v[c]);
+			// each term rounded to fp16, sum carried in fp16 (grid.h:205-212)
+			acc = __hadd2(__floats2half2_rn(w * f.x, w * f.y), acc);
+			if (WRITE_INDICES) indices[((size_t)i * desc.n_levels + l) * 8 + c] = e[c];
+		}
+		*reinterpret_cast<__half2*>(orow + 2 * l) = acc;
+	}
+}
+
+// Backward: warp = 32 consecutive samples, one level at a time.  Equal entry indices in neighbouring lanes are summed in
+// fp32 with a segmented shuffle reduction and leave the warp as ONE red.global.add.noftz.f16x2.
+__global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
+	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
+	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31;
+	const bool valid = i < n;
+	const uint32_t ii = valid ? i : n - 1;
+	const float x = xyz[(size_t)ii * stride_floats + 0], y = xyz[(size_t)ii * stride_floats + 1], z = xyz[(size_t)ii * stride_floats + 2];
+	const __half* drow = dy + (size_t)ii * dy_stride;
+
+	for (uint32_t l = 0; l < desc.n_levels; ++l) {
+		const uint32_t off = desc.offsets[l], size = desc.offsets[l + 1] - off, res = desc.resolutions[l];
+		const float scale = desc.scales[l];
+		const bool hashed = level_is_hashed(size, res);
+		__half2* grid = grad + off;
+		uint32_t gx, gy, gz; float wx, wy, wz;
+		pos_fract(x, scale, gx, wx); pos_fract(y, scale, gy, wy); pos_fract(z, scale, gz, wz);
+		const float2 g = __half22float2(*reinterpret_cast<const __half2*>(drow + 2 * l));
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			float w = 1.f;
+			w *= (c & 1) ? wx : 1 - wx;
+			w *= (c & 2) ? wy : 1 - wy;
+			w *= (c & 4) ? wz : 1 - wz;
+			const uint32_t e = valid ? grid_index(size, res, hashed, gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1)) : 0xffffffffu - lane;
+			// per-term fp16 rounding as in grid.h:303-306, then exact fp32 sums inside the warp
+			float2 t = __half22float2(__floats2half2_rn(g.x * w, g.y * w));
+			const uint32_t prev = __shfl_up_sync(0xffffffffu, e, 1);
+			const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0 || prev != e);
+			if (heads != 0xffffffffu) {
+				// segment of this lane: [start, end]
+				const uint32_t above = heads & ~((2u << lane) - 1u);           // heads strictly above lane
+				const uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;
+				#pragma unroll
+				for (int o = 1; o < 32; o <<= 1) {
+					const float ax = __shfl_down_sync(0xffffffffu, t.x, o);
+					const float ay = __shfl_down_sync(0xffffffffu, t.y, o);
+					if (lane + o <= end) { t.x += ax; t.y += ay; }
+				}
+			}
+			if (valid && ((heads >> lane) & 1u)) atomicAdd(grid + e, __floats2half2_rn(t.x, t.y));
+		}
+	}
+}
+
+} // namespace ngp
+
+using namespace ngp;
+
+extern "C" float ngp_auto_per_level_scale(float desired_resolution, uint32_t base_resolution, uint32_t n_levels) {
+	return n_levels > 1 ? std::exp(std::log(desired_resolution / (float)base_resolution) / (n_levels - 1)) : 1.0f;
+}
+
+extern "C" uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, uint32_t log2_hashmap_size, uint32_t base_resolution, float per_level_scale) {
+	if (!desc || n_levels == 0 || n_levels > NGP_MAX_LEVELS) { set_error("ngp_grid_desc_init: n_levels must be in [1,%d]", NGP_MAX_LEVELS); return 0; }
+	memset(desc, 0, sizeof(*desc));
+	desc->n_levels = n_levels;
+	uint32_t offset = 0;
+	for (uint32_t i = 0; i < n_levels; ++i) {
+		const float scale = exp2f(i * std::log2(per_level_scale)) * base_resolution - 1.0f;
+		const uint32_t res = (uint32_t)(ceilf(scale)) + 1;
+		const uint32_t max_params = 0xFFFFFFFFu / 2;
+		uint32_t params = std::pow((float)res, 3) > (float)max_params ? max_params : res * res * res;
+		params = ((params + 7u) / 8u) * 8u;
+		params = params < (1u << log2_hashmap_size) ? params : (1u << log2_hashmap_size);
+		desc->offsets[i] = offset; desc->scales[i] = scale; desc->resolutions[i] = res;
+		offset += params;
+	}
+	desc->offsets[n_levels] = offset;
+	return offset;
+}
+
+extern "C" int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_table,
+                                   const ngp_grid_desc* desc, void* d_out, uint32_t out_stride, uint32_t* d_indices) {
+	NGP_REQUIRE(d_xyz && d_table && desc && d_out, "null pointer");
+	NGP_REQUIRE(out_stride >= 2 * desc->n_levels && out_stride % 2 == 0, "out_stride too small or odd");
+	if (n == 0) return 0;
+	const uint32_t grid = div_up(n, 256);
+	if (d_indices) hash_encode_fwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, d_indices);
+	else hash_encode_fwd_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr);
+	return check_launch("hash_encode_fwd");
+}
+
+namespace ngp {
+int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const uint32_t* d_n_valid,
+                            const void* d_table, const ngp_grid_desc* desc, void* d_out, uint32_t out_stride) {
+	if (n == 0) return 0;
+	hash_encode_fwd_kernel<false><<<div_up(n, 256), 256, 0, stream>>>(d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr);
+	return check_launch("hash_encode_fwd");
+}
+}
+
+extern "C" int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
+                                   const ngp_grid_desc* desc, void* d_grad, int zero_first) {
+	NGP_REQUIRE(d_xyz && d_dy && desc && d_grad, "null pointer");
+	if (zero_first) {
+		if (cudaMemsetAsync(d_grad, 0, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half), (cudaStream_t)stream) != cudaSuccess) { set_error("ngp_hash_encode_bwd: memset failed"); return -2; }
+	}
+	if (n == 0) return 0;
+	hash_encode_bwd_kernel<<<div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad);
+	return check_launch("hash_encode_bwd");
+}

@@ -1,0 +1,428 @@
+// Fully fused density + colour MLPs on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM) for sm_100a.
+// Replaces tiny-cuda-nn's kernel_mlp_fused / kernel_mlp_fused_backward (src/fully_fused_mlp.cu:152,480), the five split-K
+// CUTLASS weight-gradient GEMMs and the two FullLayer dgrad GEMMs (:845-897), the SH encoding kernel
+// (encodings/spherical_harmonics.h:48) and NGPNetwork's glue kernels (internal/network/ngp_network.h:44-127).
+//
+// One CTA (4 warps) owns a tile of 128 samples: thread t owns sample t for loads/epilogues, thread 0 issues the MMAs.
+// Weights (20 KB) stay in shared memory for the CTA lifetime; activations pass layer to layer TMEM -> registers -> SMEM
+// and never visit HBM.  In training the same tile runs forward AND backward: dgrad uses the resident weights as MN-major
+// operands, wgrad (dW = dY^T X, K = 128 samples per tile) accumulates in TMEM across all tiles of the persistent CTA
+// and is flushed once with fp32 atomics -- no split-K workspaces, no stored activations.
+#include "common.cuh"
+#include "tcgen05.cuh"
+
+namespace ngp {
+
+using namespace tc;
+
+enum { MODE_INFER = 0, MODE_TRAIN = 1, MODE_DENSITY = 2 };
+
+// weight offsets in the arena (halfs) and in shared memory (bytes)
+constexpr uint32_t kW0 = 0, kW1 = 2048, kV0 = 3072, kV1 = 5120, kV2 = 9216;
+
+struct Smem {
+	// weights, core-matrix tiled, rows = output neuron, F = fan-in
+	static constexpr uint32_t W0 = 0, W1 = 4096, V0 = 6144, V1 = 10240, V2 = 18432, WEND = 20480;
+	// activations, rows = sample
+	static constexpr uint32_t E = WEND, H = E + 8192, X = H + 16384, H1 = X + 8192;
+	static constexpr uint32_t INFER_END = H1 + 16384;                  // H2 reuses H in inference
+	static constexpr uint32_t H2 = INFER_END, GA = H2 + 16384, G16 = GA + 16384, TRAIN_END = G16 + 4096;
+	static constexpr uint32_t CTRL = 64;                               // mbarrier + tmem base, placed after the buffers
+};
+
+// TMEM columns: [0,64) working accumulator; wgrad accumulators (M = 64 rows) follow
+constexpr uint32_t kTmemWork = 0, kTmemW0 = 64, kTmemW1 = 96, kTmemV0 = 112, kTmemV1 = 144, kTmemV2 = 208;
+
+__device__ __forceinline__ void stage_weights(const __half* __restrict__ w, uint8_t* smem, uint32_t off, uint32_t rows, uint32_t F) {
+	// 16-byte chunks: chunk c of row r -> tiled position
+	const uint32_t chunks = F / 8;
+	for (uint32_t i = threadIdx.x; i < rows * chunks; i += blockDim.x) {
+		const uint32_t r = i / chunks, c = i % chunks;
+		*reinterpret_cast<uint4*>(smem + off + tile_off(r, c, F)) = *reinterpret_cast<const uint4*>(w + (size_t)r * F + c * 8);
+	}
+}
+
+__device__ __forceinline__ uint32_t pack2(float a, float b) { const __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<const uint32_t*>(&h); }
+
+// write 8 consecutive features [8*chunk, 8*chunk+8) of this thread's row
+__device__ __forceinline__ void store_chunk(uint8_t* smem, uint32_t buf, uint32_t F, uint32_t row, uint32_t chunk, const float* v, bool relu) {
+	float t[8];
+	#pragma unroll
+	for (int i = 0; i < 8; ++i) t[i] = relu ? fmaxf(v[i], 0.f) : v[i];
+	uint4 o; o.x = pack2(t[0], t[1]); o.y = pack2(t[2], t[3]); o.z = pack2(t[4], t[5]); o.w = pack2(t[6], t[7]);
+	*reinterpret_cast<uint4*>(smem + buf + tile_off(row, chunk, F)) = o;
+}
+
+// degree-4 real spherical harmonics of 2*d-1 (spherical_harmonics.h:63-100)
+__device__ __forceinline__ void sh4(float dx, float dy, float dz, float* out) {
+	const float x = dx * 2.f - 1.f, y = dy * 2.f - 1.f, z = dz * 2.f - 1.f;
+	const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+	out[0] = 0.28209479177387814f;
+	out[1] = -0.48860251190291987f * y;
+	out[2] = 0.48860251190291987f * z;
+	out[3] = -0.48860251190291987f * x;
+	out[4] = 1.0925484305920792f * xy;
+	out[5] = -1.0925484305920792f * yz;
+	out[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
+	out[7] = -1.0925484305920792f * xz;
+	out[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
+	out[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
+	out[10] = 2.8906114426405538f * xy * z;
+	out[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
+	out[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
+	out[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
+	out[14] = 1.4453057213202769f * z * (x2 - y2);
+	out[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+}
+
+struct Pipe {
+	uint32_t bar, parity, tmem;
+	// all threads: publish SMEM writes to the async proxy, order prior TMEM reads, meet
+	__device__ __forceinline__ void publish() { fence_proxy_async(); fence_before_sync(); __syncthreads(); }
+	// thread 0 after issuing: commit; everyone: wait for completion
+	__device__ __forceinline__ void commit_and_wait() {
+		if (threadIdx.x == 0) mma_commit(bar);
+		__syncwarp();
+		mbar_wait(bar, parity);
+		parity ^= 1;
+		fence_after_sync();
+	}
+};
+
+// read this thread's row: n16 groups of 16 fp32 columns starting at column col
+template <int N16>
+__device__ __forceinline__ void read_row(uint32_t tmem, uint32_t col, float* v) {
+	const uint32_t lane_base = (threadIdx.x & ~31u) << 16;
+	#pragma unroll
+	for (int g = 0; g < N16; ++g) tmem_ld16(tmem + lane_base + col + g * 16, v + g * 16);
+}
+
+// zero the gradient where the forward activation (fp16, this thread's row in buf) was not positive
+__device__ __forceinline__ void relu_mask64(const uint8_t* smem, uint32_t buf, uint32_t row, float* g) {
+	#pragma unroll
+	for (int c = 0; c < 8; ++c) {
+		const uint4 a = *reinterpret_cast<const uint4*>(smem + buf + tile_off(row, c, 64));
+		const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+		#pragma unroll
+		for (int i = 0; i < 4; ++i) {
+			const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+			if (!(f.x > 0.f)) g[c * 8 + 2 * i] = 0.f;
+			if (!(f.y > 0.f)) g[c * 8 + 2 * i + 1] = 0.f;
+		}
+	}
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) mlp_kernel(
+	const __half* __restrict__ enc, const float* __restrict__ coords, uint32_t coord_stride, uint32_t n, const uint32_t* __restrict__ n_valid,
+	const __half* __restrict__ weights, const __half* __restrict__ dloss, __half* __restrict__ out, __half* __restrict__ denc, float* __restrict__ wgrad)
+{
+	extern __shared__ __align__(1024) uint8_t smem[];
+	constexpr uint32_t kEnd = MODE == MODE_TRAIN ? Smem::TRAIN_END : Smem::INFER_END;
+	constexpr uint32_t kH2 = MODE == MODE_TRAIN ? Smem::H2 : Smem::H;
+	constexpr uint32_t kTmemCols = MODE == MODE_TRAIN ? 256 : 64;
+	const uint32_t sbase = smem_u32(smem);
+	uint32_t* ctrl = reinterpret_cast<uint32_t*>(smem + kEnd);   // [0..1] mbarrier, [2] tmem base
+	const uint32_t row = threadIdx.x;
+
+	stage_weights(weights + kW0, smem, Smem::W0, 64, 32);
+	stage_weights(weights + kW1, smem, Smem::W1, 16, 64);
+	if (MODE != MODE_DENSITY) {
+		stage_weights(weights + kV0, smem, Smem::V0, 64, 32);
+		stage_weights(weights + kV1, smem, Smem::V1, 64, 64);
+		stage_weights(weights + kV2, smem, Smem::V2, 16, 64);
+	}
+	if (threadIdx.x == 0) { mbar_init(sbase + kEnd, 1); fence_mbar_init(); }
+	if (threadIdx.x < 32) tmem_alloc(sbase + kEnd + 8, kTmemCols);
+	fence_before_sync();
+	__syncthreads();
+	fence_after_sync();
+	Pipe pipe; pipe.bar = sbase + kEnd; pipe.parity = 0; pipe.tmem = ctrl[2];
+	const uint32_t tm = pipe.tmem;
+
+	constexpr uint32_t I_128x64 = instr_desc(128, 64, 0, 0), I_128x16 = instr_desc(128, 16, 0, 0);
+	constexpr uint32_t I_d64 = instr_desc(128, 64, 0, 1), I_d32 = instr_desc(128, 32, 0, 1);          // dgrad: B = W as MN-major
+	constexpr uint32_t I_w64 = instr_desc(64, 64, 1, 1), I_w32 = instr_desc(64, 32, 1, 1), I_w16 = instr_desc(64, 16, 1, 1);
+
+	const uint32_t n_limit = n_valid ? min(*n_valid, n) : n;
+	const uint32_t n_tiles = (n_limit + 127) / 128;
+	uint32_t wg_acc = 0;   // 0 for the CTA's first tile, 1 afterwards
+
+	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+		const uint32_t s = tile * 128 + row;
+		const bool valid = s < n_limit;
+
+		// ---- stage the encoded positions (64 B / sample) and the SH of the direction --------------
+		{
+			const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)s * 32);
+			#pragma unroll
+			for (int c = 0; c < 4; ++c) {
+				const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+				*reinterpret_cast<uint4*>(smem + Smem::E + tile_off(row, c, 32)) = v;
+			}
+			if (MODE != MODE_DENSITY) {
+				float sh[16];
+				if (valid) {
+					const float* cp = coords + (size_t)s * coord_stride + 4;
+					sh4(cp[0], cp[1], cp[2], sh);
+				} else {
+					#pragma unroll
+					for (int i = 0; i < 16; ++i) sh[i] = 0.f;
+				}
+				store_chunk(smem, Smem::X, 32, row, 2, sh, false);
+				store_chunk(smem, Smem::X, 32, row, 3, sh + 8, false);
+			}
+		}
+		pipe.publish();
+
+		float v[64];
+		// ---- density net layer 0: h = relu(W0 e) ---------------------------------------------------
+		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x64, k_major(sbase + Smem::E, 32), k_major(sbase + Smem::W0, 32), 2, 0); }
+		pipe.commit_and_wait();
+		read_row<4>(tm, kTmemWork, v);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::H, 64, row, c, v + 8 * c, true);
+		pipe.publish();
+		// ---- density net layer 1: o = W1 h (16 outputs, no activation) -------------------------------
+		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x16, k_major(sbase + Smem::H, 64), k_major(sbase + Smem::W1, 64), 4, 0); }
+		pipe.commit_and_wait();
+		read_row<1>(tm, kTmemWork, v);
+		if (MODE == MODE_DENSITY) {
+			if (valid) {
+				uint4 o0, o1;
+				o0.x = pack2(v[0], v[1]); o0.y = pack2(v[2], v[3]); o0.z = pack2(v[4], v[5]); o0.w = pack2(v[6], v[7]);
+				o1.x = pack2(v[8], v[9]); o1.y = pack2(v[10], v[11]); o1.z = pack2(v[12], v[13]); o1.w = pack2(v[14], v[15]);
+				reinterpret_cast<uint4*>(out + (size_t)s * 16)[0] = o0;
+				reinterpret_cast<uint4*>(out + (size_t)s * 16)[1] = o1;
+			}
+			fence_before_sync();
+			__syncthreads();
+			continue;
+		}
+		const float sigma_raw = __half2float(__float2half_rn(v[0]));
+		store_chunk(smem, Smem::X, 32, row, 0, v, false);
+		store_chunk(smem, Smem::X, 32, row, 1, v + 8, false);
+		pipe.publish();
+		// ---- rgb net: h1 = relu(V0 x), h2 = relu(V1 h1), c = V2 h2 ---------------------------------
+		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x64, k_major(sbase + Smem::X, 32), k_major(sbase + Smem::V0, 32), 2, 0); }
+		pipe.commit_and_wait();
+		read_row<4>(tm, kTmemWork, v);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::H1, 64, row, c, v + 8 * c, true);
+		pipe.publish();
+		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x64, k_major(sbase + Smem::H1, 64), k_major(sbase + Smem::V1, 64), 4, 0); }
+		pipe.commit_and_wait();
+		read_row<4>(tm, kTmemWork, v);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) store_chunk(smem, kH2, 64, row, c, v + 8 * c, true);
+		pipe.publish();
+		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x16, k_major(sbase + kH2, 64), k_major(sbase + Smem::V2, 64), 4, 0); }
+		pipe.commit_and_wait();
+		read_row<1>(tm, kTmemWork, v);
+		if (valid && out) {
+			uint2 o; o.x = pack2(v[0], v[1]); o.y = pack2(v[2], sigma_raw);
+			*reinterpret_cast<uint2*>(out + (size_t)s * 4) = o;
+		}
+		if (MODE == MODE_INFER) { fence_before_sync(); __syncthreads(); continue; }
+
+		// ======================= backward (MODE_TRAIN) ==============================================
+		float dsigma = 0.f;
+		{
+			float dc[16];
+			#pragma unroll
+			for (int i = 0; i < 16; ++i) dc[i] = 0.f;
+			if (valid) {
+				const uint2 d = __ldg(reinterpret_cast<const uint2*>(dloss + (size_t)s * 4));
+				const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&d.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&d.y));
+				dc[0] = a.x; dc[1] = a.y; dc[2] = b.x; dsigma = b.y;
+			}
+			store_chunk(smem, Smem::G16, 16, row, 0, dc, false);
+			store_chunk(smem, Smem::G16, 16, row, 1, dc + 8, false);
+		}
+		pipe.publish();
+		// dV2^T[64][16] += H2^T dc ; dh2 = dc V2
+		if (threadIdx.x == 0) {
+			fence_after_sync();
+			gemm(tm + kTmemV2, I_w16, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
+			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::G16, 16), mn_major(sbase + Smem::V2, 64), 1, 0);
+		}
+		pipe.commit_and_wait();
+		read_row<4>(tm, kTmemWork, v);
+		relu_mask64(smem, kH2, row, v);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::GA, 64, row, c, v + 8 * c, false);
+		pipe.publish();
+		// dV1[64][64] += dh2^T H1 ; dh1 = dh2 V1
+		if (threadIdx.x == 0) {
+			fence_after_sync();
+			gemm(tm + kTmemV1, I_w64, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::H1, 64), 8, wg_acc);
+			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::V1, 64), 4, 0);
+		}
+		pipe.commit_and_wait();
+		read_row<4>(tm, kTmemWork, v);
+		relu_mask64(smem, Smem::H1, row, v);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) store_chunk(smem, kH2, 64, row, c, v + 8 * c, false);   // dh1 takes H2's place
+		pipe.publish();
+		// dV0[64][32] += dh1^T x ; dx = dh1 V0
+		if (threadIdx.x == 0) {
+			fence_after_sync();
+			gemm(tm + kTmemV0, I_w32, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::X, 32), 8, wg_acc);
+			gemm(tm + kTmemWork, I_d32, k_major(sbase + kH2, 64), mn_major(sbase + Smem::V0, 32), 4, 0);
+		}
+		pipe.commit_and_wait();
+		read_row<1>(tm, kTmemWork, v);      // only dL/d(density_out[0..16)) is needed; the SH half has no parameters
+		v[0] = __half2float(__float2half_rn(v[0])) + dsigma;   // ngp_network.h:119-126
+		store_chunk(smem, Smem::G16, 16, row, 0, v, false);
+		store_chunk(smem, Smem::G16, 16, row, 1, v + 8, false);
+		pipe.publish();
+		// dW1^T[64][16] += H^T do ; dh = do W1
+		if (threadIdx.x == 0) {
+			fence_after_sync();
+			gemm(tm + kTmemW1, I_w16, mn_major(sbase + Smem::H, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
+			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::G16, 16), mn_major(sbase + Smem::W1, 64), 1, 0);
+		}
+		pipe.commit_and_wait();
+		read_row<4>(tm, kTmemWork, v);
+		relu_mask64(smem, Smem::H, row, v);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::GA, 64, row, c, v + 8 * c, false);
+		pipe.publish();
+		// dW0[64][32] += dh^T e ; de = dh W0
+		if (threadIdx.x == 0) {
+			fence_after_sync();
+			gemm(tm + kTmemW0, I_w32, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::E, 32), 8, wg_acc);
+			gemm(tm + kTmemWork, I_d32, k_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::W0, 32), 4, 0);
+		}
+		pipe.commit_and_wait();
+		read_row<2>(tm, kTmemWork, v);
+		if (valid && denc) {
+			uint4* dst = reinterpret_cast<uint4*>(denc + (size_t)s * 32);
+			#pragma unroll
+			for (int c = 0; c < 4; ++c) {
+				uint4 o; o.x = pack2(v[8 * c], v[8 * c + 1]); o.y = pack2(v[8 * c + 2], v[8 * c + 3]); o.z = pack2(v[8 * c + 4], v[8 * c + 5]); o.w = pack2(v[8 * c + 6], v[8 * c + 7]);
+				dst[c] = o;
+			}
+		}
+		wg_acc = 1;
+		fence_before_sync();
+		__syncthreads();
+	}
+
+	// ---- flush the weight-gradient accumulators (M = 64: row m sits in TMEM lane 32*(m/16) + m%16) ------
+	if (MODE == MODE_TRAIN && wg_acc) {
+		fence_after_sync();
+		const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, m = warp * 16 + lane;
+		float v[64];
+		read_row<2>(tm, kTmemW0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kW0 + m * 32 + k, v[k]);
+		read_row<1>(tm, kTmemW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kW1 + o * 64 + m, v[o]);
+		read_row<2>(tm, kTmemV0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kV0 + m * 32 + k, v[k]);
+		read_row<4>(tm, kTmemV1, v);      if (lane < 16) for (int k = 0; k < 64; ++k) atomicAdd(wgrad + kV1 + m * 64 + k, v[k]);
+		read_row<1>(tm, kTmemV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kV2 + o * 64 + m, v[o]);
+	}
+	fence_before_sync();
+	__syncthreads();
+	if (threadIdx.x < 32) tmem_dealloc(tm, kTmemCols);
+}
+
+} // namespace ngp
+
+// =====================================================================================================
+// host side
+// =====================================================================================================
+using namespace ngp;
+
+namespace ngp {
+int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const uint32_t* d_n_valid,
+                            const void* d_table, const ngp_grid_desc* desc, void* d_out, uint32_t out_stride);
+
+__global__ void wgrad_to_half_kernel(const float* __restrict__ w32, __half* __restrict__ w16, uint32_t n) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) w16[i] = __float2half_rn(w32[i]);
+}
+
+template <int MODE>
+static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords, uint32_t coord_stride, uint32_t n, const uint32_t* n_valid,
+                      const void* weights, const void* dloss, void* out, void* denc, float* wgrad) {
+	constexpr uint32_t smem = (MODE == MODE_TRAIN ? Smem::TRAIN_END : Smem::INFER_END) + Smem::CTRL;
+	constexpr uint32_t ctas_per_sm = MODE == MODE_TRAIN ? 2 : 3;
+	static bool configured = false;
+	if (!configured) {
+		if (cudaFuncSetAttribute(mlp_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+			set_error("mlp: cannot reserve %u bytes of shared memory: %s", smem, cudaGetErrorString(cudaGetLastError())); return -2;
+		}
+		configured = true;
+	}
+	const uint32_t n_tiles = div_up(n, 128);
+	const uint32_t grid = n_tiles < kNumSMs * ctas_per_sm ? n_tiles : kNumSMs * ctas_per_sm;
+	mlp_kernel<MODE><<<grid, 128, smem, stream>>>((const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
+		(const __half*)dloss, (__half*)out, (__half*)denc, wgrad);
+	return check_launch("mlp_kernel");
+}
+} // namespace ngp
+
+extern "C" int ngp_mlp_inference(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, void* d_rgbsigma) {
+	NGP_REQUIRE(d_enc && d_coords && d_mlp_params && d_rgbsigma, "null pointer");
+	if (n == 0) return 0;
+	return launch_mlp<MODE_INFER>((cudaStream_t)stream, d_enc, d_coords, 7, n, nullptr, d_mlp_params, nullptr, d_rgbsigma, nullptr, nullptr);
+}
+
+extern "C" int ngp_mlp_train(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, const void* d_dloss,
+                             void* d_rgbsigma, void* d_denc, float* d_wgrad_f32) {
+	NGP_REQUIRE(d_enc && d_coords && d_mlp_params && d_dloss && d_wgrad_f32, "null pointer");
+	if (n == 0) return 0;
+	return launch_mlp<MODE_TRAIN>((cudaStream_t)stream, d_enc, d_coords, 7, n, nullptr, d_mlp_params, d_dloss, d_rgbsigma, d_denc, d_wgrad_f32);
+}
+
+// workspace: [enc n*32 halfs][denc n*32 halfs][wgrad 10240 floats]
+extern "C" size_t ngp_network_workspace_bytes(uint32_t n) {
+	const size_t n_pad = ((size_t)n + 127) / 128 * 128;
+	return n_pad * 32 * 2 * 2 + NGP_MLP_PARAMS * sizeof(float) + 256;
+}
+
+extern "C" int ngp_network_inference(void* stream, const float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_params,
+                                     const ngp_grid_desc* desc, void* d_rgbsigma, void* d_workspace, size_t workspace_bytes) {
+	NGP_REQUIRE(d_coords && d_params && desc && d_rgbsigma && d_workspace, "null pointer");
+	NGP_REQUIRE(desc->n_levels == 16, "the fused network expects 16 levels x 2 features = 32 encoded dims");
+	NGP_REQUIRE(workspace_bytes >= ngp_network_workspace_bytes(n), "workspace too small");
+	if (n == 0) return 0;
+	cudaStream_t s = (cudaStream_t)stream;
+	const __half* params = (const __half*)d_params;
+	int rc = hash_encode_fwd_counted(s, d_coords, 7, n, d_n_valid, params + NGP_MLP_PARAMS, desc, d_workspace, 32);
+	if (rc) return rc;
+	return launch_mlp<MODE_INFER>(s, d_workspace, d_coords, 7, n, d_n_valid, params, nullptr, d_rgbsigma, nullptr, nullptr);
+}
+
+extern "C" int ngp_network_density(void* stream, const float* d_positions, uint32_t stride_floats, uint32_t n, const void* d_params,
+                                   const ngp_grid_desc* desc, void* d_out, void* d_workspace, size_t workspace_bytes) {
+	NGP_REQUIRE(d_positions && d_params && desc && d_out && d_workspace, "null pointer");
+	NGP_REQUIRE(desc->n_levels == 16, "the fused network expects 16 levels x 2 features = 32 encoded dims");
+	NGP_REQUIRE(workspace_bytes >= ngp_network_workspace_bytes(n), "workspace too small");
+	if (n == 0) return 0;
+	cudaStream_t s = (cudaStream_t)stream;
+	const __half* params = (const __half*)d_params;
+	int rc = hash_encode_fwd_counted(s, d_positions, stride_floats, n, nullptr, params + NGP_MLP_PARAMS, desc, d_workspace, 32);
+	if (rc) return rc;
+	return launch_mlp<MODE_DENSITY>(s, d_workspace, nullptr, 0, n, nullptr, params, nullptr, d_out, nullptr, nullptr);
+}
+
+extern "C" int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
+                                 const void* d_dloss, void* d_rgbsigma, void* d_grads, void* d_workspace, size_t workspace_bytes) {
+	NGP_REQUIRE(d_coords && d_params && desc && d_dloss && d_grads && d_workspace, "null pointer");
+	NGP_REQUIRE(desc->n_levels == 16, "the fused network expects 16 levels x 2 features = 32 encoded dims");
+	NGP_REQUIRE(workspace_bytes >= ngp_network_workspace_bytes(n), "workspace too small");
+	if (n == 0) return 0;
+	cudaStream_t s = (cudaStream_t)stream;
+	const __half* params = (const __half*)d_params;
+	const size_t n_pad = ((size_t)n + 127) / 128 * 128;
+	__half* enc = (__half*)d_workspace;
+	__half* denc = enc + n_pad * 32;
+	float* wgrad = (float*)(denc + n_pad * 32);
+	if (cudaMemsetAsync(wgrad, 0, NGP_MLP_PARAMS * sizeof(float), s) != cudaSuccess) { set_error("ngp_network_train: memset failed"); return -2; }
+	int rc = hash_encode_fwd_counted(s, d_coords, 7, n, nullptr, params + NGP_MLP_PARAMS, desc, enc, 32);
+	if (rc) return rc;
+	rc = launch_mlp<MODE_TRAIN>(s, enc, d_coords, 7, n, nullptr, params, d_dloss, d_rgbsigma, denc, wgrad);
+	if (rc) return rc;
+	wgrad_to_half_kernel<<<div_up(NGP_MLP_PARAMS, 256), 256, 0, s>>>(wgrad, (__half*)d_grads, NGP_MLP_PARAMS);
+	return ngp_hash_encode_bwd(stream, d_coords, 7, n, denc, 32, desc, (__half*)d_grads + NGP_MLP_PARAMS, 1);
+}

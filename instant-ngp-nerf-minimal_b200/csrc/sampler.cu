@@ -1,0 +1,160 @@
+// Occupancy grid maintenance and training-ray sample generation for sm_100a.
+// Replaces internal/sampler/occupancy_sampler.cu kernels K1-K8: mark_untrained_density_grid (:18),
+// generate_grid_samples_nerf_nonuniform (:63), splat (:107), ema (:134), reduce_sum mean (:741), grid_to_bitfield (:160),
+// bitfield_max_pool (:182), generate_training_samples_nerf (:310).
+#include "march.cuh"
+
+namespace ngp {
+
+__global__ void mark_untrained_grid_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, uint32_t n_images, const float* __restrict__ xforms, float* __restrict__ grid_out) {
+	const uint32_t G = c.grid_size, cells = G * G * G, total = cells * c.n_cascades;
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+		const uint32_t level = i / cells, pos_idx = i % cells;
+		const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
+		const float s = scalbnf(1.0f, (int)level), g = (float)G;
+		const float px = (((float)x + 0.5f) / g - 0.5f) * s + 0.5f;
+		const float py = (((float)y + 0.5f) / g - 0.5f) * s + 0.5f;
+		const float pz = (((float)z + 0.5f) / g - 0.5f) * s + 0.5f;
+		const float half_resx = cam.width * 0.5f, half_resy = cam.height * 0.5f;
+		const float voxel_radius = 0.5f * 1.73205080757f * s / g;
+		bool seen = false;
+		for (uint32_t j = 0; j < n_images && !seen; ++j) {
+			const float* xf = xforms + (size_t)j * 12;
+			const float lx = px - xf[9], ly = py - xf[10], lz = pz - xf[11];
+			const float cx = __fmaf_rn(lz, xf[2], __fmaf_rn(ly, xf[1], lx * xf[0]));
+			const float cy = __fmaf_rn(lz, xf[5], __fmaf_rn(ly, xf[4], lx * xf[3]));
+			const float cz = __fmaf_rn(lz, xf[8], __fmaf_rn(ly, xf[7], lx * xf[6]));
+			if (cz > 0.f && fabsf(cx) - voxel_radius < cz / cam.fx * half_resx && fabsf(cy) - voxel_radius < cz / cam.fy * half_resy) seen = true;
+		}
+		grid_out[i] = seen ? 0.f : -1.f;
+	}
+}
+
+__global__ void generate_grid_samples_kernel(ngp_sampler_cfg c, uint32_t n, Pcg32 rng0, uint32_t step, const float* __restrict__ grid_in, float thresh,
+                                             float* __restrict__ out_pos, uint32_t* __restrict__ out_idx) {
+	const uint32_t G = c.grid_size, cells = G * G * G;
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		Pcg32 rng = rng0;
+		rng.advance((uint64_t)i * 4);
+		const uint32_t level = (uint32_t)(rng.next_float() * (float)c.n_cascades) % c.n_cascades;
+		uint32_t idx = 0;
+		for (uint32_t j = 0; j < 10; ++j) {
+			idx = ((i + step * n) * 56924617u + j * 19349663u + 96925573u) % cells;
+			idx += level * cells;
+			if (grid_in[idx] > thresh) break;
+		}
+		const uint32_t pos_idx = idx % cells;
+		const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
+		const float rx = rng.next_float(), ry = rng.next_float(), rz = rng.next_float();
+		const float s = scalbnf(1.0f, (int)level), g = (float)G, diag = c.aabb_max - c.aabb_min;
+		const float px = (((float)x + rx) / g - 0.5f) * s + 0.5f;
+		const float py = (((float)y + ry) / g - 0.5f) * s + 0.5f;
+		const float pz = (((float)z + rz) / g - 0.5f) * s + 0.5f;
+		out_pos[(size_t)i * 3 + 0] = (px - c.aabb_min) / diag;
+		out_pos[(size_t)i * 3 + 1] = (py - c.aabb_min) / diag;
+		out_pos[(size_t)i * 3 + 2] = (pz - c.aabb_min) / diag;
+		out_idx[i] = idx;
+	}
+}
+
+__device__ __forceinline__ float density_act(float v, int act) {
+	switch (act) {
+		case 0: return v;
+		case 1: return v > 0.f ? v : 0.f;
+		case 2: return 1.0f / (1.0f + expf(-v));
+		default: return __expf(v);
+	}
+}
+
+__global__ void splat_grid_kernel(uint32_t n, const uint32_t* __restrict__ indices, const __half* __restrict__ density, uint32_t stride, int act, float min_step, float* grid_current) {
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const float thickness = density_act(__half2float(density[(size_t)i * stride]), act) * min_step;
+		atomicMax((uint32_t*)&grid_current[indices[i]], __float_as_uint(thickness));
+	}
+}
+
+__global__ void ema_grid_kernel(uint32_t n, const float* __restrict__ cur, float decay, float* __restrict__ grid) {
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const float prev = grid[i];
+		grid[i] = prev < 0.f ? prev : fmaxf(prev * decay, cur[i]);
+	}
+}
+
+// mean over cascade 0 of max(v,0)/cells.  ONE CTA, fixed order tree => run-to-run deterministic (the reference's
+// float-atomic reduce_sum is not).  2 M floats = 8 MB from L2: a few microseconds, once per train() call.
+__global__ void __launch_bounds__(1024) grid_mean_kernel(const float* __restrict__ grid, uint32_t cells, float* __restrict__ mean_out) {
+	__shared__ float sh[1024];
+	float s = 0.f;
+	const float inv = (float)cells;
+	for (uint32_t i = threadIdx.x; i < cells; i += 1024) s += fmaxf(grid[i], 0.f) / inv;
+	sh[threadIdx.x] = s;
+	__syncthreads();
+	for (int o = 512; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+	if (threadIdx.x == 0) *mean_out = sh[0];
+}
+
+__global__ void grid_to_bitfield_kernel(uint32_t n_bytes, const float* __restrict__ grid, uint8_t* __restrict__ bits, const float* __restrict__ mean, float min_optical_thickness) {
+	const float thresh = fminf(min_optical_thickness, *mean);
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_bytes; i += gridDim.x * blockDim.x) {
+		const float4 a = reinterpret_cast<const float4*>(grid)[(size_t)i * 2], b = reinterpret_cast<const float4*>(grid)[(size_t)i * 2 + 1];
+		uint32_t v = 0;
+		v |= a.x > thresh ? 1u : 0u; v |= a.y > thresh ? 2u : 0u; v |= a.z > thresh ? 4u : 0u; v |= a.w > thresh ? 8u : 0u;
+		v |= b.x > thresh ? 16u : 0u; v |= b.y > thresh ? 32u : 0u; v |= b.z > thresh ? 64u : 0u; v |= b.w > thresh ? 128u : 0u;
+		bits[i] = (uint8_t)v;
+	}
+}
+
+__global__ void bitfield_max_pool_kernel(uint32_t n, uint32_t G, const uint8_t* __restrict__ prev, uint8_t* __restrict__ next) {
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const uint2 p = reinterpret_cast<const uint2*>(prev)[i];
+		uint32_t v = 0;
+		#pragma unroll
+		for (int j = 0; j < 4; ++j) { v |= ((p.x >> (8 * j)) & 0xffu) ? (1u << j) : 0u; v |= ((p.y >> (8 * j)) & 0xffu) ? (16u << j) : 0u; }
+		const uint32_t x = morton3D_invert(i >> 0) + G / 8, y = morton3D_invert(i >> 1) + G / 8, z = morton3D_invert(i >> 2) + G / 8;
+		next[morton3D(x, y, z)] |= (uint8_t)v;
+	}
+}
+
+} // namespace ngp
+
+using namespace ngp;
+
+extern "C" int ngp_mark_untrained_grid(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, uint32_t n_images, const float* d_xforms, float* d_grid) {
+	NGP_REQUIRE(cfg && cam && d_xforms && d_grid, "null pointer");
+	const uint32_t total = cfg->grid_size * cfg->grid_size * cfg->grid_size * cfg->n_cascades;
+	mark_untrained_grid_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, *cam, n_images, d_xforms, d_grid);
+	return check_launch("mark_untrained_grid");
+}
+
+extern "C" int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
+                                         const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices) {
+	NGP_REQUIRE(cfg && d_grid && d_positions && d_indices, "null pointer");
+	if (n == 0) return 0;
+	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
+	generate_grid_samples_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, d_grid, thresh, d_positions, d_indices);
+	return check_launch("generate_grid_samples");
+}
+
+extern "C" int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,
+                               int density_activation, float decay, float* d_grid_current, float* d_grid) {
+	NGP_REQUIRE(cfg && d_indices && d_density && d_grid_current && d_grid, "null pointer");
+	const uint32_t total = cfg->grid_size * cfg->grid_size * cfg->grid_size * cfg->n_cascades;
+	cudaStream_t s = (cudaStream_t)stream;
+	if (cudaMemsetAsync(d_grid_current, 0, (size_t)total * sizeof(float), s) != cudaSuccess) { set_error("ngp_update_grid: memset failed"); return -2; }
+	if (n) splat_grid_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, d_indices, (const __half*)d_density, density_stride, density_activation, cfg->min_step, d_grid_current);
+	ema_grid_kernel<<<grid_for(total, 256), 256, 0, s>>>(total, d_grid_current, decay, d_grid);
+	return check_launch("update_grid");
+}
+
+extern "C" int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg, const float* d_grid, float min_optical_thickness, float* d_mean, uint8_t* d_bitfield) {
+	NGP_REQUIRE(cfg && d_grid && d_mean && d_bitfield, "null pointer");
+	const uint32_t G = cfg->grid_size, cells = G * G * G;
+	NGP_REQUIRE(cells % 64 == 0, "grid_size^3 must be a multiple of 64");
+	cudaStream_t s = (cudaStream_t)stream;
+	grid_mean_kernel<<<1, 1024, 0, s>>>(d_grid, cells, d_mean);
+	const uint32_t n_bytes = cells * cfg->n_cascades / 8;
+	grid_to_bitfield_kernel<<<grid_for(n_bytes, 256), 256, 0, s>>>(n_bytes, d_grid, d_bitfield, d_mean, min_optical_thickness);
+	for (uint32_t level = 1; level < cfg->n_cascades; ++level)
+		bitfield_max_pool_kernel<<<grid_for(cells / 64, 256), 256, 0, s>>>(cells / 64, G, d_bitfield + (size_t)cells * (level - 1) / 8, d_bitfield + (size_t)cells * level / 8);
+	return check_launch("update_grid_bitfield");
+}
