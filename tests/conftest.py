@@ -28,3 +28,11 @@ def orc():
     import oracle
     oracle.lib()
     return oracle
+
+
+@pytest.fixture(autouse=True)
+def _release_device_tensors():
+    yield
+    g = sys.modules.get("gpuutil")
+    if g is not None:
+        g._KEEP.clear()

@@ -5,16 +5,23 @@ import numpy as np
 import torch
 
 
+# device tensors handed out by dev() stay alive until the end of the test (conftest clears this list): a raw pointer
+# taken from a temporary would otherwise dangle as soon as the caching allocator reuses the block
+_KEEP = []
+
+
 def dev(a):
     """numpy -> device tensor (bit-preserving for uint16-viewed fp16)"""
     a = np.ascontiguousarray(a)
-    if a.dtype == np.uint16:
-        return torch.from_numpy(a.view(np.int16)).cuda()
-    if a.dtype == np.uint32:
-        return torch.from_numpy(a.view(np.int32)).cuda()
-    if a.dtype == np.uint64:
-        return torch.from_numpy(a.view(np.int64)).cuda()
-    return torch.from_numpy(a).cuda()
+    if a.dtype in (np.uint16, np.float16):
+        a = a.view(np.int16)
+    elif a.dtype == np.uint32:
+        a = a.view(np.int32)
+    elif a.dtype == np.uint64:
+        a = a.view(np.int64)
+    t = torch.from_numpy(a).cuda()
+    _KEEP.append(t)
+    return t
 
 
 def zeros(n, dtype):
