@@ -156,8 +156,18 @@ int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, uint64_t n_pa
                        float* d_w32, void* d_w16, const void* d_g16, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16);
 /* from_rgba32<__half> (internal/utils/common_device.h:160-175) */
 int ngp_from_rgba32(void* stream, uint64_t n_pixels, const uint8_t* d_rgba8, void* d_out_half);
-/* reduce_sum of the per-ray loss (testbed.cu:288) */
+/* reduce_sum of the per-ray loss (testbed.cu:288).  d_out: 1 result float followed by >= 599 floats of scratch; the word
+ * d_out[1] is a ticket that must be zero before the first use (the kernel resets it). */
 int ngp_reduce_sum(void* stream, const float* d_in, uint64_t n, float* d_out);
+
+/* ---- benchmark fixture ------------------------------------------------------------------------ */
+/* Procedural stand-in for the Blender nerf_synthetic renders (no dataset can be downloaded on the GPU box): ray-marches an
+ * analytic density / colour field inside the unit cube into n_views 8-bit sRGB RGBA images (straight alpha), which then go
+ * through ngp_from_rgba32 like the reference loader's PNGs (internal/dataset/nerf_synthetic.cu:113-127).
+ * d_xforms: n_views 3x4 column-major camera-to-world matrices in the unit-cube frame. */
+#define NGP_SCENE_BLOBS 8
+int ngp_render_procedural_views(void* stream, uint32_t seed, uint32_t n_views, int width, int height, float fx, float fy,
+                                const float* d_xforms, uint8_t* d_rgba8);
 
 #ifdef __cplusplus
 }

@@ -73,6 +73,7 @@ SIGNATURES = {
     "ngp_optimizer_step": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u32, f32, vp, vp, vp, vp, vp, vp, vp]),
     "ngp_from_rgba32": (i32, [vp, u64, vp, vp]),
     "ngp_reduce_sum": (i32, [vp, vp, u64, vp]),
+    "ngp_render_procedural_views": (i32, [vp, u32, u32, i32, i32, f32, f32, vp, vp]),
 }
 
 _lib = None

@@ -1,0 +1,107 @@
+// OccupancySampler host methods: parameter bookkeeping identical to internal/sampler/occupancy_sampler.cu:603-877,
+// kernels behind the C ABI.
+#include "occupancy_sampler.h"
+#include "dataset.h"
+
+namespace ngp {
+
+OccupancySampler::OccupancySampler(const Json& config) {
+	aabb_scale = (uint32_t)config.value("aabb_scale", 1);
+	for (int d = 0; d < 3; ++d) { aabb.min[d] = 0.5f - 0.5f * (float)aabb_scale; aabb.max[d] = 0.5f + 0.5f * (float)aabb_scale; }
+	n_grid_size = (uint32_t)config.value("grid_size", 128);
+	n_grid_elements = n_grid_size * n_grid_size * n_grid_size;
+	n_cascades = 2;
+	while ((1u << (n_cascades - 1)) < aabb_scale) n_cascades++;
+	n_total_elements = n_grid_elements * n_cascades;
+	ema_decay = config.value("ema_decay", 0.95f);
+	density_grid_current.resize(n_total_elements);
+	density_grid.resize(n_total_elements);
+	density_grid_mean.resize(16);
+	density_grid_bitfield.resize(n_total_elements / 8);
+	density_grid_current.memset(0); density_grid.memset(0); density_grid_mean.memset(0); density_grid_bitfield.memset(0);
+	n_max_steps = (uint32_t)config.value("maximum_marching_steps", 1024);
+	cone_angle_constant = config.value("cone_angle_constant", 0.f);
+	const float sqrt3 = 1.73205080757f;
+	min_cone_stepsize = sqrt3 / (float)n_max_steps;
+	max_cone_stepsize = sqrt3 * (float)(1u << (n_cascades - 1)) / (float)n_grid_size;
+	near_distance = config.value("near_distance", 0.2f);
+	far_distance = config.value("far_distance", 100.f);
+	snap_to_pixel_centers_in_training = config.value("snap_to_pixel_centers_in_training", true);
+	snap_to_pixel_centers_in_rendering = config.value("snap_to_pixel_centers_in_rendering", true);
+	min_optical_thickness = config.value("min_optical_thickness", 0.01f);
+}
+
+ngp_sampler_cfg OccupancySampler::cfg() const {
+	ngp_sampler_cfg c;
+	c.aabb_min = aabb.min[0]; c.aabb_max = aabb.max[0];
+	c.grid_size = n_grid_size; c.n_cascades = n_cascades; c.max_steps = n_max_steps;
+	c.cone_angle = cone_angle_constant; c.min_step = min_cone_stepsize; c.max_step = max_cone_stepsize; c.near_distance = near_distance;
+	return c;
+}
+
+void OccupancySampler::init(uint32_t n_images, const int image_resolution[2], const float focal_length[2], const float principal_point[2],
+                            const DeviceBuffer<Mat34>& camera_matrices, default_rng_t& rng_in, cudaStream_t stream) {
+	i_step = 0;
+	rng = default_rng_t{(uint64_t)rng_in.next_uint()};
+	const ngp_sampler_cfg c = cfg();
+	ngp_camera_cfg cam{image_resolution[0], image_resolution[1], focal_length[0], focal_length[1], principal_point[0], principal_point[1]};
+	api_check(ngp_mark_untrained_grid(stream, &c, &cam, n_images, (const float*)camera_matrices.data(), density_grid.data()));
+}
+
+void OccupancySampler::sample_positions_from_grid(uint32_t n_uniform_positions, uint32_t n_nonuniform_positions, DeviceBuffer<Position>& grid_positions,
+                                                  DeviceBuffer<uint32_t>& grid_indices, cudaStream_t stream) {
+	const uint32_t n_total = n_uniform_positions + n_nonuniform_positions;
+	grid_positions.enlarge(n_total);
+	grid_indices.enlarge(n_total);
+	const ngp_sampler_cfg c = cfg();
+	api_check(ngp_generate_grid_samples(stream, &c, n_uniform_positions, rng.state, rng.inc, i_step, density_grid.data(), -0.01f,
+	                                    (float*)grid_positions.data(), grid_indices.data()));
+	rng.advance();
+	api_check(ngp_generate_grid_samples(stream, &c, n_nonuniform_positions, rng.state, rng.inc, i_step, density_grid.data(), min_optical_thickness,
+	                                    (float*)(grid_positions.data() + n_uniform_positions), grid_indices.data() + n_uniform_positions));
+	rng.advance();
+}
+
+void OccupancySampler::update_grid(uint32_t n_total_positions, uint32_t padded_output_width, const DeviceBuffer<precision_t>& grid_densities,
+                                   const DeviceBuffer<uint32_t>& grid_indices, EActivation density_activation, cudaStream_t stream) {
+	const ngp_sampler_cfg c = cfg();
+	api_check(ngp_update_grid(stream, &c, n_total_positions, grid_indices.data(), grid_densities.data(), padded_output_width, (int)density_activation,
+	                          ema_decay, density_grid_current.data(), density_grid.data()));
+	++i_step;
+}
+
+void OccupancySampler::update_grid_bitfield(cudaStream_t stream) {
+	const ngp_sampler_cfg c = cfg();
+	api_check(ngp_update_grid_bitfield(stream, &c, density_grid.data(), min_optical_thickness, density_grid_mean.data(), density_grid_bitfield.data()));
+}
+
+void OccupancySampler::sample_coords_from_dataset(uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_coords, const NeRFSynthetic& dataset, bool,
+                                                  DeviceBuffer<Ray>& rays, DeviceBuffer<float>& rays_rgba, uint32_t* n_rays_counter,
+                                                  DeviceBuffer<uint32_t>& ray_coord_indices, DeviceBuffer<Coordinate>& coords, uint32_t* n_coords_counter,
+                                                  default_rng_t rng_step, cudaStream_t stream) {
+	// the C ABI keeps the two counters adjacent: [0] rays kept, [1] samples counted
+	if (n_coords_counter != n_rays_counter + 1) throw std::runtime_error("sample_coords_from_dataset: counters must be adjacent (rays, samples)");
+	m_scan_ws.enlarge(ngp_scan_workspace_bytes(n_rays));
+	const ngp_sampler_cfg c = cfg();
+	ngp_camera_cfg cam{dataset.image_resolution[0], dataset.image_resolution[1], dataset.focal_length[0], dataset.focal_length[1],
+	                   dataset.principal_point[0], dataset.principal_point[1]};
+	api_check(ngp_generate_training_samples(stream, &c, &cam, n_rays, n_rays_shift, n_coords, dataset.n_images, (const float*)dataset.xforms.data(),
+	                                        dataset.images.data(), density_grid_bitfield.data(), snap_to_pixel_centers_in_training ? 1 : 0,
+	                                        rng_step.state, rng_step.inc, (float*)rays.data(), rays_rgba.data(), ray_coord_indices.data(),
+	                                        (float*)coords.data(), n_rays_counter, nullptr, m_scan_ws.data()));
+}
+
+void OccupancySampler::generate_rays_from_camera_matrix(const int resolution[2], const float focal_length[2], const float principal_point[2],
+                                                        const Mat34& camera_matrix, uint32_t spp, DeviceBuffer<RayPayload>& payload, cudaStream_t stream) {
+	const ngp_sampler_cfg c = cfg();
+	ngp_camera_cfg cam{resolution[0], resolution[1], focal_length[0], focal_length[1], principal_point[0], principal_point[1]};
+	api_check(ngp_init_rays(stream, &c, &cam, camera_matrix.m, spp, snap_to_pixel_centers_in_rendering ? 1 : 0, density_grid_bitfield.data(), payload.data()));
+}
+
+void OccupancySampler::generate_coords_from_rays(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, DeviceBuffer<RayPayload>& payloads,
+                                                 DeviceBuffer<Coordinate>& coords, cudaStream_t stream) {
+	const ngp_sampler_cfg c = cfg();
+	api_check(ngp_generate_coords_from_rays(stream, &c, n_rays, d_n_rays, n_steps, density_grid_bitfield.data(), payloads.data(), (float*)coords.data()));
+}
+
+} // namespace ngp

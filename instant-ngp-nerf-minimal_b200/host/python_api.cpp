@@ -1,0 +1,127 @@
+// pybind11 module `pyngp` -- same classes, enums, method names, argument names and defaults as the reference's
+// internal/python_api.cu:48-138, so experiment/nerf_synthetic/python/run.py runs against it unchanged.  Eigen casters are
+// replaced by numpy / sequence conversions that accept the same Python values ([0.5,0.5,0.5], a 3x4 or 4x4 np.matrix).
+#include <pybind11/pybind11.h>
+#include <pybind11/numpy.h>
+#include <pybind11/stl.h>
+#include "testbed.h"
+
+namespace py = pybind11;
+using namespace ngp;
+
+static Mat34 to_mat34(const py::object& o) {
+	py::array_t<float, py::array::c_style | py::array::forcecast> a = py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(o);
+	if (!a || a.ndim() != 2 || a.shape(0) < 3 || a.shape(1) != 4) throw std::runtime_error("expected a 3x4 (or 4x4) camera matrix");
+	Mat34 m;
+	auto r = a.unchecked<2>();
+	for (int i = 0; i < 3; ++i) for (int j = 0; j < 4; ++j) m.at(i, j) = r(i, j);
+	return m;
+}
+
+static void to_vec(const py::object& o, float* dst, size_t n, const char* what) {
+	py::sequence s = py::reinterpret_borrow<py::sequence>(py::module_::import("numpy").attr("asarray")(o).attr("reshape")(-1).attr("tolist")());
+	if (s.size() != n) throw std::runtime_error(std::string(what) + ": wrong number of elements");
+	for (size_t i = 0; i < n; ++i) dst[i] = s[i].cast<float>();
+}
+
+PYBIND11_MODULE(pyngp, m) {
+	m.doc() = "Instant neural graphics primitives (NeRF) minimal version -- B200-native build";
+
+	py::enum_<EActivation>(m, "Activation")
+		.value("None", EActivation::None).value("ReLU", EActivation::ReLU).value("Logistic", EActivation::Logistic).value("Exponential", EActivation::Exponential)
+		.export_values();
+	py::enum_<ERenderMode>(m, "RenderMode")
+		.value("AO", ERenderMode::AO).value("Shade", ERenderMode::Shade).value("Normals", ERenderMode::Normals).value("Depth", ERenderMode::Depth)
+		.value("Distance", ERenderMode::Distance).value("Stepsize", ERenderMode::Stepsize).value("Cost", ERenderMode::Cost)
+		.export_values();
+	py::enum_<EColorSpace>(m, "ColorSpace").value("Linear", EColorSpace::Linear).value("SRGB", EColorSpace::SRGB).export_values();
+	py::enum_<ETonemapCurve>(m, "TonemapCurve")
+		.value("Identity", ETonemapCurve::Identity).value("ACES", ETonemapCurve::ACES).value("Hable", ETonemapCurve::Hable).value("Reinhard", ETonemapCurve::Reinhard)
+		.export_values();
+	py::enum_<ELossType>(m, "LossType")
+		.value("L2", ELossType::L2).value("L1", ELossType::L1).value("Mape", ELossType::Mape).value("Smape", ELossType::Smape)
+		.value("SmoothL1", ELossType::SmoothL1).value("LogL1", ELossType::LogL1).value("RelativeL2", ELossType::RelativeL2)
+		.export_values();
+
+	py::class_<Testbed> testbed(m, "Testbed");
+	testbed
+		.def(py::init())
+		.def("load_model_config", &Testbed::load_model_config, "Reload the network from a config file.")
+		.def("save_snapshot", &Testbed::save_snapshot, py::arg("snapshot_path"), py::arg("serialize_optimizer") = false, "Save a snapshot of the currently trained model")
+		.def("load_snapshot", &Testbed::load_snapshot, py::arg("snapshot_path"), "Load a previously saved snapshot")
+		.def("load_training_data", [](Testbed& t, const std::string& path, float scale, const py::object& offset) {
+			float off[3]; to_vec(offset, off, 3, "offset");
+			t.load_training_data(path, scale, off);
+		}, "Load training data from a given path.")
+		.def("load_procedural_training_data", [](Testbed& t, uint32_t n_images, int width, int height, uint32_t seed, float scale, const py::object& offset) {
+			float off[3]; to_vec(offset, off, 3, "offset");
+			t.load_procedural_training_data(n_images, width, height, seed, scale, off);
+		}, py::arg("n_images") = 100, py::arg("width") = 800, py::arg("height") = 800, py::arg("seed") = 2024, py::arg("scale") = 0.33f,
+		   py::arg("offset") = std::vector<float>{0.5f, 0.5f, 0.5f}, "Benchmark fixture: procedural nerf_synthetic-shaped scene generated on the device.")
+		.def("train", [](Testbed& t, uint32_t n_steps, uint32_t batch) { py::gil_scoped_release rel; t.train(n_steps, batch); }, "Perform a specified number of training steps.")
+		.def("render", [](Testbed& t, int width, int height, int spp, bool to_srgb) {
+			py::array_t<float> image({height, width, 4});
+			float* ptr = (float*)image.request().ptr;
+			{ py::gil_scoped_release rel; t.render_to_host(width, height, spp, to_srgb, ptr); }
+			return image;
+		}, "Renders an image at the requested resolution.", py::arg("width") = 1920, py::arg("height") = 1080, py::arg("spp") = 1, py::arg("to_srgb") = true)
+		.def_readwrite("loss_type", &Testbed::m_loss_type)
+		.def_readwrite("density_activation", &Testbed::m_density_activation)
+		.def_readwrite("rgb_activation", &Testbed::m_rgb_activation)
+		.def_property("background_color",
+			[](const Testbed& t) { return std::vector<float>(t.m_background_color, t.m_background_color + 4); },
+			[](Testbed& t, const py::object& v) { to_vec(v, t.m_background_color, 4, "background_color"); })
+		.def_readwrite("color_space", &Testbed::m_color_space)
+		.def_readonly("training_buffer", &Testbed::m_training_buffer)
+		.def_readonly("rendering_buffer", &Testbed::m_rendering_buffer)
+		.def_property("fov", &Testbed::fov, &Testbed::set_fov)
+		.def_property("fov_xy",
+			[](const Testbed& t) { return std::vector<float>{focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[0]), focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[1])}; },
+			[](Testbed& t, const py::object& v) { float f[2]; to_vec(v, f, 2, "fov_xy"); for (int k = 0; k < 2; ++k) t.m_rendering_buffer.relative_focal_length[k] = fov_to_focal_length(1, f[k]); })
+		.def("set_nerf_camera_matrix", [](Testbed& t, const py::object& cam) { t.set_nerf_camera_matrix(to_mat34(cam)); })
+		.def("set_camera_to_training_view", &Testbed::set_camera_to_training_view)
+		.def("training_image", [](const Testbed& t, uint32_t i) {
+			const NeRFSynthetic& d = t.m_training_buffer.dataset;
+			py::array_t<float> image({d.image_resolution[1], d.image_resolution[0], 4});
+			t.training_image_to_host(i, (float*)image.request().ptr);
+			return image;
+		})
+		.def_property_readonly("n_training_images", [](const Testbed& t) { return t.m_training_buffer.dataset.n_images; })
+		// ---- additions for data-parallel training (not in the reference) ----
+		.def("set_data_parallel", [](Testbed& t, int rank, int world, uintptr_t comm) { t.set_data_parallel(rank, world, (void*)comm); },
+		     py::arg("rank"), py::arg("world_size"), py::arg("nccl_comm"))
+		.def_property_readonly("gradients_ptr", [](const Testbed& t) { return (uintptr_t)t.gradients(); })
+		.def_property_readonly("n_params", &Testbed::n_params)
+		.def_property_readonly("stream_ptr", [](const Testbed& t) { return (uintptr_t)t.m_stream; })
+		;
+
+	py::class_<Testbed::TrainingBuffer>(testbed, "TrainingBuffer")
+		.def_readonly("n_rays_per_batch", &Testbed::TrainingBuffer::n_rays_per_batch)
+		.def_readonly("measured_batch_size_before_compaction", &Testbed::TrainingBuffer::measured_batch_size_before_compaction)
+		.def_readonly("measured_batch_size", &Testbed::TrainingBuffer::measured_batch_size)
+		.def_readonly("loss", &Testbed::TrainingBuffer::loss_scalar)
+		.def_readonly("training_prep_ms", &Testbed::TrainingBuffer::training_prep_ms)
+		.def_readonly("training_ms", &Testbed::TrainingBuffer::training_ms)
+		.def_readonly("i_step", &Testbed::TrainingBuffer::i_step)
+		;
+
+	py::class_<Testbed::RenderingBuffer>(testbed, "RenderingBuffer")
+		.def_readwrite("render_mode", &Testbed::RenderingBuffer::render_mode)
+		.def_readwrite("tonemap_curve", &Testbed::RenderingBuffer::tonemap_curve)
+		.def_readwrite("exposure", &Testbed::RenderingBuffer::exposure)
+		.def_readwrite("fov_axis", &Testbed::RenderingBuffer::fov_axis)
+		.def_property("relative_focal_length",
+			[](const Testbed::RenderingBuffer& r) { return std::vector<float>{r.relative_focal_length[0], r.relative_focal_length[1]}; },
+			[](Testbed::RenderingBuffer& r, const py::object& v) { to_vec(v, r.relative_focal_length, 2, "relative_focal_length"); })
+		.def_property("principal_point",
+			[](const Testbed::RenderingBuffer& r) { return std::vector<float>{r.principal_point[0], r.principal_point[1]}; },
+			[](Testbed::RenderingBuffer& r, const py::object& v) { to_vec(v, r.principal_point, 2, "principal_point"); })
+		.def_readwrite("MIN_STEPS_INBETWEEN_COMPACTION", &Testbed::RenderingBuffer::MIN_STEPS_INBETWEEN_COMPACTION)
+		.def_readwrite("MAX_STEPS_INBETWEEN_COMPACTION", &Testbed::RenderingBuffer::MAX_STEPS_INBETWEEN_COMPACTION)
+		;
+
+	// NCCL bootstrap helpers for the data-parallel path: rank 0 makes the id, torch.distributed broadcasts the bytes
+	m.def("nccl_unique_id", []() { return py::bytes(ngp_host_nccl_unique_id()); });
+	m.def("nccl_comm_init", [](const py::bytes& id, int rank, int world) { return (uintptr_t)ngp_host_nccl_comm_init(std::string(id), rank, world); });
+	m.def("nccl_comm_destroy", [](uintptr_t comm) { ngp_host_nccl_comm_destroy((void*)comm); });
+}

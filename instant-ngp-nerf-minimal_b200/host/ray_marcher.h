@@ -1,0 +1,45 @@
+// RayMarcher -- the reference's internal/render/ray_marcher.h:18-85 module boundary over the C ABI compositing kernels.
+#pragma once
+#include "common.h"
+#include "json.h"
+#include "occupancy_sampler.h"
+
+namespace ngp {
+
+struct RaysSoA {   // internal/utils/common.h:146-153
+	DeviceBuffer<RayPayload> payload;
+	DeviceBuffer<float> rgba;          // 4 floats per ray
+	void enlarge(size_t n) { payload.enlarge(n); rgba.enlarge(n * 4); }
+};
+
+class RayMarcher {
+public:
+	explicit RayMarcher(const Json& config);
+
+	// ray_marcher.cu:305-377.  n_rays_counter / n_compacted_coords_counter are device counters.
+	void volume_rendering_with_loss_and_gradient(
+		uint32_t n_rays, uint32_t n_max_compacted_coords,
+		const DeviceBuffer<Ray>& rays, const DeviceBuffer<float>& rays_rgba, const uint32_t* n_rays_counter, DeviceBuffer<uint32_t>& ray_coord_indices,
+		const DeviceBuffer<Coordinate>& coords, DeviceBuffer<Coordinate>& compacted_coords, uint32_t* n_compacted_coords_counter,
+		const DeviceBuffer<precision_t>& network_output, DeviceBuffer<precision_t>& dloss_doutput, int padded_output_width,
+		EActivation rgb_activation, EActivation density_activation,
+		float* loss_output, ELossType loss_type, float loss_scale,
+		const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const DeviceBuffer<float>& density_grid_mean, float min_optical_thickness,
+		const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream);
+
+	// ray_marcher.cu:379-416
+	void volume_rendering(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t i_steps_offset, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,
+	                      const DeviceBuffer<precision_t>& rgbsigma, uint32_t padded_output_width, EActivation density_activation, EActivation rgb_activation,
+	                      ERenderMode render_mode, const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const Mat34& camera_matrix,
+	                      float depth_scale, cudaStream_t stream);
+
+public:
+	bool train_with_random_bg_color;
+	bool train_in_linear_color;
+	float transmittance_threshold;
+
+private:
+	DeviceBuffer<uint8_t> m_scan_ws;
+};
+
+} // namespace ngp

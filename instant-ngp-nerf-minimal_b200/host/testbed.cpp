@@ -1,0 +1,128 @@
+// Testbed host orchestration.  Follows the schedule of the reference's internal/testbed.cu (file:line cited per method);
+// all device work is stream-ordered calls into the C ABI, and the only host synchronisations are the ones whose results
+// Python reads (counters + loss at the end of train(), the live-ray count while rendering).
+#include "testbed.h"
+#include <nccl.h>
+#include <algorithm>
+#include <chrono>
+#include <fstream>
+#include <sstream>
+#include <sys/stat.h>
+
+namespace ngp {
+
+static std::string file_extension(const std::string& p) {
+	const size_t k = p.find_last_of('.');
+	std::string e = k == std::string::npos ? "" : p.substr(k + 1);
+	for (auto& c : e) c = (char)tolower(c);
+	return e;
+}
+static bool path_exists(const std::string& p) { struct stat st; return !p.empty() && stat(p.c_str(), &st) == 0; }
+
+Testbed::Testbed() {
+	// testbed.cu:17-37: a CUDA device with tensor cores must be present; here that means sm_100
+	cudaDeviceProp props;
+	int dev = 0;
+	cudaError_t error = cudaGetDevice(&dev);
+	if (error == cudaSuccess) error = cudaGetDeviceProperties(&props, dev);
+	if (error != cudaSuccess) throw std::runtime_error(std::string("cudaGetDeviceProperties() returned an error: ") + cudaGetErrorString(error));
+	if (props.major != 10) throw std::runtime_error("ngp_b200 kernels are built for sm_100a (B200) only; there is no fallback path.");
+	NGP_CUDA_CHECK(cudaStreamCreate(&m_stream));
+	for (auto& e : m_ev) NGP_CUDA_CHECK(cudaEventCreate(&e));
+	NGP_CUDA_CHECK(cudaMallocHost((void**)&m_host_counter, 64 * sizeof(uint32_t)));
+	m_training_buffer.loss_sum.resize(1024);
+	m_training_buffer.loss_sum.memset(0);
+	m_rendering_buffer.n_hit_counter.memset(0);
+	m_rendering_buffer.n_alive_counter.memset(0);
+}
+
+Testbed::~Testbed() {
+	for (auto& e : m_ev) if (e) cudaEventDestroy(e);
+	if (m_host_counter) cudaFreeHost(m_host_counter);
+	if (m_stream) cudaStreamDestroy(m_stream);
+}
+
+// testbed.cu:44-93
+void Testbed::load_model_config(const std::string& config_path) {
+	if (!path_exists(config_path)) throw std::runtime_error("The model config must exist.");
+	std::ifstream f(config_path, std::ios::in | std::ios::binary);
+	std::stringstream ss; ss << f.rdbuf();
+	const std::string ext = file_extension(config_path);
+	if (ext == "json") load_model_config_json(Json::parse(ss.str()));
+	else if (ext == "msgpack") load_model_config_json(Json::from_msgpack(ss.str()));
+	else throw std::runtime_error("The model config must be a .json or .msgpack file.");
+}
+
+void Testbed::load_model_config_json(const Json& config) {
+	m_model_config = config;
+	m_sampler = std::make_shared<OccupancySampler>(m_model_config["samlper"]);   // (sic) the key the reference reads, testbed.cu:67
+	m_network = std::make_shared<NGPNetwork>(m_model_config["network"]);
+	m_render = std::make_shared<RayMarcher>(m_model_config["render"]);
+	m_loss_type = string_to_loss_type(m_model_config["loss"].str());
+	m_trainer = std::make_shared<Trainer>(m_network, OptimizerConfig::from_json(m_model_config["optimizer"]), m_seed, m_stream);
+	m_train_envmap = m_model_config.contains("envmap") ? m_model_config["envmap"].value("train", false) : false;
+	if (m_train_envmap) throw std::runtime_error("envmap training is not implemented in this build (base.json keeps it off)");
+	m_training_buffer.i_step = 0;
+}
+
+// testbed.cu:95-125
+void Testbed::load_training_data(const std::string& data_path, float scale, const float offset[3]) {
+	if (!m_sampler) throw std::runtime_error("load_model_config must be called before load_training_data");
+	if (!path_exists(data_path)) throw std::runtime_error("The data path must exist.");
+	if (file_extension(data_path) != "json") throw std::runtime_error("The data path must be a .json file.");
+	m_training_buffer.dataset.load_from_json(data_path, scale, offset);
+	m_scene_scale = scale;
+	for (int k = 0; k < 3; ++k) m_scene_offset[k] = offset[k];
+	const NeRFSynthetic& d = m_training_buffer.dataset;
+	m_sampler->init(d.n_images, d.image_resolution, d.focal_length, d.principal_point, d.xforms, m_rng, m_stream);
+}
+
+void Testbed::load_procedural_training_data(uint32_t n_images, int width, int height, uint32_t seed, float scale, const float offset[3]) {
+	if (!m_sampler) throw std::runtime_error("load_model_config must be called before load_procedural_training_data");
+	m_training_buffer.dataset.load_procedural(n_images, width, height, 0.6911112f, seed, scale, offset);
+	m_scene_scale = scale;
+	for (int k = 0; k < 3; ++k) m_scene_offset[k] = offset[k];
+	const NeRFSynthetic& d = m_training_buffer.dataset;
+	m_sampler->init(d.n_images, d.image_resolution, d.focal_length, d.principal_point, d.xforms, m_rng, m_stream);
+}
+
+// testbed.cu:127-141
+void Testbed::save_snapshot(const std::string& snapshot_path, bool serialize_optimizer) {
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	m_model_config["snapshot"] = m_trainer->serialize(serialize_optimizer);
+	std::vector<float> grid(m_sampler->n_total_elements);
+	m_sampler->density_grid.copy_to_host(grid.data(), grid.size());
+	m_model_config["snapshot"]["density_grid"] = Json::binary(grid.data(), grid.size() * sizeof(float));
+	m_model_config["snapshot"]["scene_scale"] = Json(m_scene_scale);
+	Json off = Json::array();
+	for (int k = 0; k < 3; ++k) off.push_back(Json(m_scene_offset[k]));
+	m_model_config["snapshot"]["scene_offset"] = off;
+	std::string out;
+	m_model_config.to_msgpack(out);
+	std::ofstream f(snapshot_path, std::ios::out | std::ios::binary);
+	if (!f) throw std::runtime_error("cannot write snapshot: " + snapshot_path);
+	f.write(out.data(), (std::streamsize)out.size());
+}
+
+// testbed.cu:143-163
+void Testbed::load_snapshot(const std::string& snapshot_path) {
+	load_model_config(snapshot_path);
+	if (!m_model_config.contains("snapshot")) throw std::runtime_error("ERROR in loading snapshot.");
+	const Json& snap = m_model_config["snapshot"];
+	m_scene_scale = (float)snap.at("scene_scale").number();
+	for (int k = 0; k < 3; ++k) m_scene_offset[k] = (float)snap.at("scene_offset")[k].number();
+	const Json& grid = snap.at("density_grid");
+	if (grid.type != Json::Binary || grid.s.size() != m_sampler->n_total_elements * sizeof(float)) throw std::runtime_error("snapshot: density_grid has the wrong size");
+	NGP_CUDA_CHECK(cudaMemcpy(m_sampler->density_grid.data(), grid.s.data(), grid.s.size(), cudaMemcpyHostToDevice));
+	m_sampler->update_grid_bitfield(m_stream);
+	m_trainer->deserialize(snap, m_stream);
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+}
+
+void Testbed::set_data_parallel(int rank, int world_size, void* nccl_comm) {
+	if (world_size < 1 || rank < 0 || rank >= world_size) throw std::runtime_error("set_data_parallel: bad rank / world size");
+	if (world_size > 1 && !nccl_comm) throw std::runtime_error("set_data_parallel: a communicator is required for world_size > 1");
+	m_dp_rank = rank; m_dp_world = world_size; m_nccl_comm = nccl_comm;
+}
+
+} // namespace ngp

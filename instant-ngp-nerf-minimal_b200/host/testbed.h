@@ -1,0 +1,132 @@
+// Testbed -- same public surface as the reference's internal/testbed.h:30-204 (load_model_config, load_training_data,
+// save/load_snapshot, train(n_steps, batch), render_frame / render, fov helpers, training_buffer / rendering_buffer views),
+// driving the sampler / network / render modules whose kernels live behind the C ABI.
+#pragma once
+#include <memory>
+#include "common.h"
+#include "json.h"
+#include "dataset.h"
+#include "occupancy_sampler.h"
+#include "ngp_network.h"
+#include "ray_marcher.h"
+#include "render_buffer.h"
+
+namespace ngp {
+
+class Testbed {
+public:
+	Testbed();
+	~Testbed();
+
+	// ---- configuration & I/O (testbed.cu:44-163) ----
+	void load_model_config(const std::string& config_path);
+	void load_model_config_json(const Json& config);
+	void save_snapshot(const std::string& snapshot_path, bool serialize_optimizer);
+	void load_snapshot(const std::string& snapshot_path);
+	void load_training_data(const std::string& data_path, float scale, const float offset[3]);
+	// benchmark fixture (no file I/O): procedural nerf_synthetic-shaped scene generated on the device
+	void load_procedural_training_data(uint32_t n_images, int width, int height, uint32_t seed, float scale, const float offset[3]);
+
+	// ---- training (testbed.cu:168-418) ----
+	void train(uint32_t n_training_steps, uint32_t batch_size);
+	void train_prep_nerf(uint32_t batch_size, uint32_t n_training_steps, cudaStream_t stream);
+	void train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, cudaStream_t stream);
+	void train_nerf_step(uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t* counters /* [2]: rays, samples */, uint32_t* compacted_counter,
+	                     float* loss, cudaStream_t stream);
+
+	// ---- rendering (testbed.cu:479-605, python_api.cu:22-46) ----
+	void render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_buffer, bool to_srgb = true);
+	// renders spp frames and copies the float4 image into `out` ([height][width][4] floats, host memory)
+	void render_to_host(int width, int height, int spp, bool to_srgb, float* out);
+	// tile-sharded inference: this rank renders rows [row_begin, row_end) only (no collective)
+	void set_render_rows(int row_begin, int row_end) { m_render_row_begin = row_begin; m_render_row_end = row_end; }
+
+	float fov() const { return focal_length_to_fov(1, m_rendering_buffer.relative_focal_length[m_rendering_buffer.fov_axis]); }
+	void set_fov(float val) { m_rendering_buffer.relative_focal_length[0] = m_rendering_buffer.relative_focal_length[1] = fov_to_focal_length(1, val); }
+	// evaluation helpers: look through training camera i / fetch its ground-truth image (linear premultiplied RGBA, float)
+	void set_camera_to_training_view(uint32_t i);
+	void training_image_to_host(uint32_t i, float* out) const;
+	void set_nerf_camera_matrix(const Mat34& cam) { m_rendering_buffer.camera_matrix = spec_opengl_to_opencv(cam, m_scene_scale, m_scene_offset); }
+
+	// ---- data-parallel training (new: the reference is single-GPU).  Gradients are summed over ranks with NCCL
+	//      before the optimizer step; each rank draws its own rays.  comm is an ncclComm_t created by the caller. ----
+	void set_data_parallel(int rank, int world_size, void* nccl_comm);
+	precision_t* gradients() const { return m_trainer->gradients(); }
+	size_t n_params() const { return m_trainer->n_params(); }
+
+public:
+	uint32_t m_seed = 43;
+	default_rng_t m_rng = default_rng_t{(uint64_t)43};
+	cudaStream_t m_stream = nullptr;
+
+	Json m_model_config;
+	std::shared_ptr<OccupancySampler> m_sampler;
+	std::shared_ptr<NGPNetwork> m_network;
+	std::shared_ptr<RayMarcher> m_render;
+	ELossType m_loss_type = ELossType::SmoothL1;
+	std::shared_ptr<Trainer> m_trainer;
+	EActivation m_density_activation = EActivation::Exponential;
+	EActivation m_rgb_activation = EActivation::Logistic;
+	float m_background_color[4] = {0.0f, 0.0f, 0.0f, 1.0f};
+	EColorSpace m_color_space = EColorSpace::Linear;
+	bool m_train_envmap = false;
+
+	float m_scene_scale = 1.f;
+	float m_scene_offset[3] = {0.5f, 0.5f, 0.5f};
+
+	struct TrainingBuffer {
+		NeRFSynthetic dataset;
+		uint32_t n_rays_per_batch = 1 << 12;
+		uint32_t n_rays_total = 0;
+		DeviceBuffer<Position> grid_positions;
+		DeviceBuffer<uint32_t> grid_indices;
+		DeviceBuffer<Ray> rays;
+		DeviceBuffer<float> rays_rgba;
+		DeviceBuffer<uint32_t> ray_coord_indices;
+		DeviceBuffer<Coordinate> coords, coords_compacted;
+		DeviceBuffer<precision_t> rgbsigma, dloss_drgbsigma;
+		DeviceBuffer<uint32_t> n_coords_counter;            // [n_steps][2]: rays kept, samples counted
+		DeviceBuffer<uint32_t> n_compacted_coords_counter;  // [n_steps]
+		std::vector<uint32_t> n_coords_counter_cpu, n_compacted_coords_counter_cpu;
+		uint32_t measured_batch_size_before_compaction = 0xffffffffu;
+		uint32_t measured_batch_size = 0xffffffffu;
+		DeviceBuffer<float> loss;
+		DeviceBuffer<float> loss_sum;                       // reduce_sum result + scratch
+		float loss_scalar = 0.f;
+		float training_prep_ms = 0, training_ms = 0;
+		uint32_t i_step = 0;
+	} m_training_buffer;
+
+	struct RenderingBuffer {
+		ERenderMode render_mode = ERenderMode::Shade;
+		ETonemapCurve tonemap_curve = ETonemapCurve::Identity;
+		float exposure = 0.f;
+		CudaRenderBuffer render_buffer;
+		uint32_t fov_axis = 1;
+		float relative_focal_length[2] = {1.f, 1.f};
+		float principal_point[2] = {0.5f, 0.5f};
+		Mat34 camera_matrix;
+		RaysSoA rays[2];
+		RaysSoA rays_hit;
+		DeviceBuffer<uint32_t> n_hit_counter{1};
+		DeviceBuffer<uint32_t> n_alive_counter{64};
+		DeviceBuffer<Coordinate> coords;
+		DeviceBuffer<precision_t> rgbsigma;
+		uint32_t MIN_STEPS_INBETWEEN_COMPACTION = 1;
+		uint32_t MAX_STEPS_INBETWEEN_COMPACTION = 8;
+	} m_rendering_buffer;
+
+private:
+	cudaEvent_t m_ev[3] = {nullptr, nullptr, nullptr};
+	uint32_t* m_host_counter = nullptr;    // pinned
+	int m_dp_rank = 0, m_dp_world = 1;
+	void* m_nccl_comm = nullptr;
+	int m_render_row_begin = 0, m_render_row_end = -1;
+};
+
+} // namespace ngp
+
+// NCCL bootstrap for the data-parallel path (one process per GPU; the id travels through torch.distributed / any channel)
+std::string ngp_host_nccl_unique_id();
+void* ngp_host_nccl_comm_init(const std::string& id_bytes, int rank, int world_size);
+void ngp_host_nccl_comm_destroy(void* comm);

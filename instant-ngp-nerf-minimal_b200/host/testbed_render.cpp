@@ -1,0 +1,98 @@
+// Testbed::render_frame / render_to_host (reference: internal/testbed.cu:479-605, internal/python_api.cu:22-46).
+#include "testbed.h"
+#include <algorithm>
+
+namespace ngp {
+
+void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_buffer, bool to_srgb) {
+	if (!m_trainer) throw std::runtime_error("render: load_model_config or load_snapshot first");
+	RenderingBuffer& rb = m_rendering_buffer;
+	const int* resolution = render_buffer.resolution();
+	const float focal_length[2] = {(float)resolution[rb.fov_axis] * rb.relative_focal_length[0], (float)resolution[rb.fov_axis] * rb.relative_focal_length[1]};
+	const uint32_t n_pixels = (uint32_t)(resolution[0] * resolution[1]);
+	const ERenderMode render_mode = rb.render_mode;
+	if (render_mode == ERenderMode::Normals) throw std::runtime_error("RenderMode::Normals (network input gradients) is not implemented in this build");
+	const uint32_t padded_output_width = m_network->padded_output_width();
+
+	{
+		const uint32_t n_elements = next_multiple(n_pixels, BATCH_SIZE_MULTIPLE);
+		rb.rays[0].enlarge(n_elements); rb.rays[1].enlarge(n_elements); rb.rays_hit.enlarge(n_elements);
+		rb.coords.enlarge((size_t)n_elements * rb.MAX_STEPS_INBETWEEN_COMPACTION);
+		rb.rgbsigma.enlarge((size_t)n_elements * rb.MAX_STEPS_INBETWEEN_COMPACTION * padded_output_width);
+	}
+
+	render_buffer.clear_frame_buffer(m_stream);
+	m_sampler->generate_rays_from_camera_matrix(resolution, focal_length, rb.principal_point, camera_matrix, render_buffer.spp(), rb.rays[0].payload, m_stream);
+	NGP_CUDA_CHECK(cudaMemsetAsync(rb.rays[0].rgba.data(), 0, (size_t)n_pixels * 4 * sizeof(float), m_stream));
+	NGP_CUDA_CHECK(cudaMemsetAsync(rb.n_hit_counter.data(), 0, sizeof(uint32_t), m_stream));
+
+	uint32_t i_steps_offset = 1;
+	uint32_t double_buffer_index = 0;
+	uint32_t n_alive = n_pixels;
+	while (i_steps_offset < MARCH_ITER) {
+		RaysSoA& rays_previous = rb.rays[double_buffer_index % 2];
+		RaysSoA& rays_current = rb.rays[(double_buffer_index + 1) % 2];
+		++double_buffer_index;
+
+		NGP_CUDA_CHECK(cudaMemsetAsync(rb.n_alive_counter.data(), 0, sizeof(uint32_t), m_stream));
+		api_check(ngp_compact_rays(m_stream, n_alive, nullptr, rays_previous.payload.data(), rays_previous.rgba.data(), rays_current.payload.data(), rays_current.rgba.data(),
+		                           rb.rays_hit.payload.data(), rb.rays_hit.rgba.data(), rb.n_alive_counter.data(), rb.n_hit_counter.data()));
+		NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter, rb.n_alive_counter.data(), sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
+		NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+		n_alive = m_host_counter[0];
+		if (n_alive == 0) break;
+
+		const uint32_t n_steps = std::min(std::max(n_pixels / n_alive, rb.MIN_STEPS_INBETWEEN_COMPACTION), rb.MAX_STEPS_INBETWEEN_COMPACTION);
+		m_sampler->generate_coords_from_rays(n_alive, nullptr, n_steps, rays_current.payload, rb.coords, m_stream);
+		// rendering uses the EMA weights (use_inference_matrices = true, testbed.cu:556)
+		m_network->inference_mixed_precision(m_stream, rb.coords.data(), n_alive * n_steps, nullptr, rb.rgbsigma.data(), true);
+		m_render->volume_rendering(n_alive, nullptr, n_steps, i_steps_offset, rays_current, rb.coords, rb.rgbsigma, padded_output_width, m_density_activation,
+		                           m_rgb_activation, render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix,
+		                           1.f / m_scene_scale, m_stream);
+		i_steps_offset += n_steps;
+	}
+
+	NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 1, rb.n_hit_counter.data(), sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	const uint32_t n_hit = m_host_counter[1];
+	api_check(ngp_shade(m_stream, n_hit, nullptr, rb.rays_hit.rgba.data(), rb.rays_hit.payload.data(), render_buffer.frame_buffer(), (int)render_mode,
+	                    m_render->train_in_linear_color ? 1 : 0));
+
+	render_buffer.set_color_space(m_color_space);
+	render_buffer.set_tonemap_curve(rb.tonemap_curve);
+	render_buffer.accumulate(m_stream);
+	render_buffer.tonemap(rb.exposure, m_background_color, to_srgb ? EColorSpace::SRGB : EColorSpace::Linear, m_stream);
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+}
+
+void Testbed::render_to_host(int width, int height, int spp, bool to_srgb, float* out) {
+	RenderingBuffer& rb = m_rendering_buffer;
+	rb.render_buffer.resize(width, height);
+	rb.render_buffer.reset_accumulation();
+	for (int i = 0; i < spp; ++i) render_frame(rb.camera_matrix, rb.render_buffer, to_srgb);
+	NGP_CUDA_CHECK(cudaMemcpy(out, rb.render_buffer.surface(), (size_t)width * height * 4 * sizeof(float), cudaMemcpyDeviceToHost));
+}
+
+void Testbed::set_camera_to_training_view(uint32_t i) {
+	const NeRFSynthetic& d = m_training_buffer.dataset;
+	if (i >= d.n_images) throw std::runtime_error("set_camera_to_training_view: no such view");
+	m_rendering_buffer.camera_matrix = d.xforms_host[i];
+	const int axis = (int)m_rendering_buffer.fov_axis;
+	m_rendering_buffer.relative_focal_length[0] = d.focal_length[0] / (float)d.image_resolution[axis];
+	m_rendering_buffer.relative_focal_length[1] = d.focal_length[1] / (float)d.image_resolution[axis];
+}
+
+void Testbed::training_image_to_host(uint32_t i, float* out) const {
+	const NeRFSynthetic& d = m_training_buffer.dataset;
+	if (i >= d.n_images) throw std::runtime_error("training_image_to_host: no such view");
+	const size_t n = (size_t)d.image_resolution[0] * d.image_resolution[1] * 4;
+	std::vector<uint16_t> h(n);
+	NGP_CUDA_CHECK(cudaMemcpy(h.data(), d.images.data() + n * i, n * 2, cudaMemcpyDeviceToHost));
+	for (size_t k = 0; k < n; ++k) {
+		const uint32_t s = (h[k] >> 15) & 1, e = (h[k] >> 10) & 0x1f, m = h[k] & 0x3ff;
+		float v = e == 0 ? std::ldexp((float)m, -24) : e == 31 ? (m ? NAN : INFINITY) : std::ldexp((float)(m | 0x400), (int)e - 25);
+		out[k] = s ? -v : v;
+	}
+}
+
+} // namespace ngp

@@ -1,0 +1,136 @@
+// Testbed::train and its three stages (reference: internal/testbed.cu:168-418).
+#include "testbed.h"
+#include <nccl.h>
+#include <algorithm>
+
+namespace ngp {
+
+// testbed.cu:168-191.  The reference brackets each stage with a stream synchronise and a wall clock; here the two stages
+// are timed with CUDA events on the stream and the host waits once, at the end, for the counters Python reads.
+void Testbed::train(uint32_t n_training_steps, uint32_t target_batch_size) {
+	if (!m_trainer || m_training_buffer.dataset.n_images == 0) throw std::runtime_error("train: load_model_config and load_training_data first");
+	if (n_training_steps == 0) return;
+	NGP_CUDA_CHECK(cudaEventRecord(m_ev[0], m_stream));
+	train_prep_nerf(target_batch_size, n_training_steps, m_stream);
+	NGP_CUDA_CHECK(cudaEventRecord(m_ev[1], m_stream));
+	train_nerf(target_batch_size, n_training_steps, m_stream);
+}
+
+// testbed.cu:193-229
+void Testbed::train_prep_nerf(uint32_t, uint32_t, cudaStream_t stream) {
+	const uint32_t n_total_elements = m_sampler->n_total_elements;
+	const uint32_t n_uniform_positions = m_training_buffer.i_step >= 256 ? n_total_elements / 4 : n_total_elements;
+	const uint32_t n_nonuniform_positions = m_training_buffer.i_step >= 256 ? n_total_elements / 4 : 0;
+	const uint32_t n_total_positions = n_uniform_positions + n_nonuniform_positions;
+	m_sampler->sample_positions_from_grid(n_uniform_positions, n_nonuniform_positions, m_training_buffer.grid_positions, m_training_buffer.grid_indices, stream);
+	const uint32_t padded_output_width = m_network->padded_density_output_width();
+	m_training_buffer.rgbsigma.enlarge((size_t)padded_output_width * n_total_positions);
+	m_network->density(stream, (const float*)m_training_buffer.grid_positions.data(), sizeof(Position) / sizeof(float), n_total_positions,
+	                   m_training_buffer.rgbsigma.data(), false);
+	m_sampler->update_grid(n_total_positions, padded_output_width, m_training_buffer.rgbsigma, m_training_buffer.grid_indices, m_density_activation, stream);
+	m_sampler->update_grid_bitfield(stream);
+}
+
+// testbed.cu:231-299
+void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, cudaStream_t stream) {
+	uint32_t& n_rays = m_training_buffer.n_rays_per_batch;
+	TrainingBuffer& tb = m_training_buffer;
+
+	tb.n_coords_counter.enlarge((size_t)n_training_steps * 2);
+	NGP_CUDA_CHECK(cudaMemsetAsync(tb.n_coords_counter.data(), 0, sizeof(uint32_t) * 2 * n_training_steps, stream));
+	tb.n_compacted_coords_counter.enlarge(n_training_steps);
+	NGP_CUDA_CHECK(cudaMemsetAsync(tb.n_compacted_coords_counter.data(), 0, sizeof(uint32_t) * n_training_steps, stream));
+	tb.loss.enlarge((size_t)n_rays * n_training_steps);
+	NGP_CUDA_CHECK(cudaMemsetAsync(tb.loss.data(), 0, sizeof(float) * n_rays * n_training_steps, stream));
+
+	for (uint32_t i = 0; i < n_training_steps; ++i)
+		train_nerf_step(target_batch_size, n_rays, tb.n_coords_counter.data() + 2 * i, tb.n_compacted_coords_counter.data() + i, tb.loss.data() + (size_t)n_rays * i, stream);
+
+	api_check(ngp_reduce_sum(stream, tb.loss.data(), (uint64_t)n_rays * n_training_steps, tb.loss_sum.data()));
+	NGP_CUDA_CHECK(cudaEventRecord(m_ev[2], stream));
+
+	// GPU -> CPU: the one synchronisation of a train() call
+	std::vector<uint32_t> pairs((size_t)n_training_steps * 2);
+	tb.n_compacted_coords_counter_cpu.resize(n_training_steps);
+	NGP_CUDA_CHECK(cudaMemcpyAsync(pairs.data(), tb.n_coords_counter.data(), pairs.size() * 4, cudaMemcpyDeviceToHost, stream));
+	NGP_CUDA_CHECK(cudaMemcpyAsync(tb.n_compacted_coords_counter_cpu.data(), tb.n_compacted_coords_counter.data(), n_training_steps * 4, cudaMemcpyDeviceToHost, stream));
+	float loss_sum = 0.f;
+	NGP_CUDA_CHECK(cudaMemcpyAsync(&loss_sum, tb.loss_sum.data(), 4, cudaMemcpyDeviceToHost, stream));
+	NGP_CUDA_CHECK(cudaStreamSynchronize(stream));
+	NGP_CUDA_CHECK(cudaEventElapsedTime(&tb.training_prep_ms, m_ev[0], m_ev[1]));
+	NGP_CUDA_CHECK(cudaEventElapsedTime(&tb.training_ms, m_ev[1], m_ev[2]));
+
+	tb.n_coords_counter_cpu.resize(n_training_steps);
+	tb.measured_batch_size_before_compaction = 0;
+	tb.measured_batch_size = 0;
+	uint64_t before = 0, after = 0;
+	for (uint32_t i = 0; i < n_training_steps; ++i) {
+		tb.n_coords_counter_cpu[i] = pairs[2 * i + 1];
+		if (tb.n_coords_counter_cpu[i] == 0 || tb.n_compacted_coords_counter_cpu[i] == 0) throw std::runtime_error("Training generated 0 samples. Aborting training.");
+		before += tb.n_coords_counter_cpu[i];
+		after += tb.n_compacted_coords_counter_cpu[i];
+	}
+	tb.measured_batch_size_before_compaction = (uint32_t)(before / n_training_steps);
+	tb.measured_batch_size = (uint32_t)(after / n_training_steps);
+
+	tb.loss_scalar = loss_sum / (float)n_training_steps;
+	tb.loss_scalar *= (float)tb.measured_batch_size / (float)target_batch_size;
+
+	// dynamically determine the number of rays for each step (testbed.cu:291-293)
+	n_rays = (uint32_t)((float)n_rays * (float)target_batch_size / (float)tb.measured_batch_size);
+	n_rays = std::min(next_multiple(n_rays, BATCH_SIZE_MULTIPLE), 1u << 18);
+}
+
+// testbed.cu:301-418
+void Testbed::train_nerf_step(uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t* counters, uint32_t* compacted_counter, float* loss, cudaStream_t stream) {
+	TrainingBuffer& tb = m_training_buffer;
+	const uint32_t max_samples = target_batch_size * 16;
+	const uint32_t padded_output_width = m_network->padded_output_width();
+	const uint32_t max_inference = next_multiple(std::min(tb.measured_batch_size_before_compaction, max_samples), BATCH_SIZE_MULTIPLE);
+
+	tb.rays.enlarge(n_rays_per_batch);
+	tb.rays_rgba.enlarge((size_t)n_rays_per_batch * 4);
+	tb.ray_coord_indices.enlarge((size_t)n_rays_per_batch * 2);
+	tb.coords.enlarge(max_samples);
+	tb.coords_compacted.enlarge(target_batch_size);
+	tb.rgbsigma.enlarge((size_t)max_samples * padded_output_width);
+	tb.dloss_drgbsigma.enlarge((size_t)target_batch_size * padded_output_width);
+
+	if (tb.i_step == 0) tb.n_rays_total = 0;
+	const uint32_t n_rays_total = tb.n_rays_total;
+	tb.n_rays_total += n_rays_per_batch;
+
+	// each data-parallel rank draws its own pixels: the per-ray generator is advanced by i*8 draws inside the kernel, so rank r
+	// starts 2^18 * 8 draws further along (2^18 = the cap on rays per batch)
+	default_rng_t ray_rng = m_rng;
+	if (m_dp_rank) ray_rng.advance((int64_t)m_dp_rank * (1ll << 18) * 8);
+
+	// 1. rays + occupancy march + ordered compaction
+	m_sampler->sample_coords_from_dataset(n_rays_per_batch, n_rays_total, max_inference, tb.dataset, m_train_envmap, tb.rays, tb.rays_rgba, counters,
+	                                      tb.ray_coord_indices, tb.coords, counters + 1, ray_rng, stream);
+	// 2. network on every marched sample (training weights); the device-side count bounds the work
+	m_network->inference_mixed_precision(stream, tb.coords.data(), max_inference, counters + 1, tb.rgbsigma.data(), false);
+	// 3. compositing, loss, dL/d(rgb sigma), compaction.  Data parallel: every rank's gradient carries 1/world of the loss scale,
+	//    so the NCCL sum below is the mean over ranks and stays inside fp16 range.
+	m_render->volume_rendering_with_loss_and_gradient(
+		n_rays_per_batch, target_batch_size, tb.rays, tb.rays_rgba, counters, tb.ray_coord_indices, tb.coords, tb.coords_compacted, compacted_counter,
+		tb.rgbsigma, tb.dloss_drgbsigma, (int)padded_output_width, m_rgb_activation, m_density_activation, loss, m_loss_type, LOSS_SCALE / (float)m_dp_world,
+		m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, m_sampler->density_grid_mean, m_sampler->min_optical_thickness,
+		m_background_color, m_color_space, m_rng, stream);
+	// 4. rollover
+	api_check(ngp_rollover(stream, target_batch_size, compacted_counter, tb.dloss_drgbsigma.data(), padded_output_width, (float*)tb.coords_compacted.data()));
+	// 5./6. forward + backward on the compacted batch (one fused launch chain)
+	m_network->forward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data());
+	m_network->backward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data(), tb.dloss_drgbsigma.data());
+	// data parallel: sum the fp16 gradient arena over ranks (NVLink / NVSwitch)
+	if (m_dp_world > 1) {
+		const ncclResult_t r = ncclAllReduce(m_trainer->gradients(), m_trainer->gradients(), m_trainer->n_params(), ncclHalf, ncclSum, (ncclComm_t)m_nccl_comm, stream);
+		if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce failed: ") + ncclGetErrorString(r));
+	}
+	// 7. optimizer
+	m_rng.advance();
+	m_trainer->optimizer_step(stream, LOSS_SCALE);
+	++tb.i_step;
+}
+
+} // namespace ngp
