@@ -126,7 +126,9 @@ int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint
                                   const uint8_t* d_bitfield, void* d_payloads, float* d_coords);
 
 /* ---- render ----------------------------------------------------------------------------------- */
-/* RayMarcher::volume_rendering_with_loss_and_gradient (ray_marcher.cu:15-213, 305-377), compaction in ray order */
+/* RayMarcher::volume_rendering_with_loss_and_gradient (ray_marcher.cu:15-213, 305-377), compaction in ray order.
+ * d_scan_ws: >= ngp_composite_workspace_bytes(n_rays) bytes of scratch. */
+size_t ngp_composite_workspace_bytes(uint32_t n_rays);
 int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
                         const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
                         uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,

@@ -129,6 +129,8 @@ __global__ void rollover_kernel(uint32_t batch, const uint32_t* __restrict__ n_i
 
 using namespace ngp;
 
+extern "C" size_t ngp_composite_workspace_bytes(uint32_t n_rays) { return ngp_scan_workspace_bytes(n_rays); }
+
 extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
                                    const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
                                    uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,

@@ -25,7 +25,7 @@ void RayMarcher::volume_rendering_with_loss_and_gradient(
 	c.train_with_random_bg_color = train_with_random_bg_color ? 1 : 0; c.train_in_linear_color = train_in_linear_color ? 1 : 0;
 	c.transmittance_threshold = transmittance_threshold; c.min_optical_thickness = min_optical_thickness; c.loss_scale = loss_scale;
 	for (int k = 0; k < 3; ++k) c.background_color[k] = background_color[k];
-	m_scan_ws.enlarge(ngp_scan_workspace_bytes(n_rays));
+	m_scan_ws.enlarge(ngp_composite_workspace_bytes(n_rays));
 	api_check(ngp_composite_train(stream, &c, n_rays, n_max_compacted_coords, n_rays_counter, rays_rgba.data(), ray_coord_indices.data(),
 	                              (const float*)coords.data(), (float*)compacted_coords.data(), n_compacted_coords_counter, network_output.data(),
 	                              dloss_doutput.data(), (uint32_t)padded_output_width, density_grid_mean.data(), rng.state, rng.inc, loss_output, m_scan_ws.data()));

@@ -1,0 +1,167 @@
+"""GPU parity: occupancy grid maintenance and ray marching through the C ABI vs the CPU oracle.
+
+Bars (BASELINE.json): occupancy bits and per-ray sample counts bit-exact; sample coordinates bit-exact as well because both
+sides use the same explicit operation order (fmaf where the kernels use __fmaf_rn, nothing else contracted)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from util import rng_uniform, make_cameras, make_density_grid
+
+pytestmark = pytest.mark.gpu
+
+
+def _cam(capi, W, H, fx):
+    c = capi.CameraCfg()
+    c.width, c.height, c.fx, c.fy, c.ppx, c.ppy = W, H, fx, fx, 0.5, 0.5
+    return c
+
+
+@pytest.mark.parametrize("aabb_scale", [1, 4])
+def test_mark_untrained_grid_matches_oracle(capi, orc, aabb_scale):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg, ocfg = capi.make_sampler_cfg(aabb_scale), orc.SamplerCfg(aabb_scale)
+    xf = make_cameras(5)
+    W = H = 100
+    fx = 120.0
+    ref = orc.mark_untrained_grid(ocfg, xf, W, H, fx, fx)
+    out = G.zeros(ref.size, torch.float32)
+    cam = _cam(capi, W, H, fx)
+    capi.check(lib.ngp_mark_untrained_grid(G.stream(), C.byref(cfg), C.byref(cam), 5, G.p(G.dev(xf)), G.p(out)))
+    G.sync()
+    got = G.host(out)
+    assert np.array_equal(got, ref)
+    assert 0 < (ref == 0).mean() < 1 or aabb_scale == 1
+
+
+@pytest.mark.parametrize("thresh,step", [(-0.01, 0), (0.01, 3)])
+def test_generate_grid_samples_matches_oracle(capi, orc, thresh, step):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg, ocfg = capi.make_sampler_cfg(1), orc.SamplerCfg(1)
+    grid = make_density_grid()
+    rng = orc.Pcg32(77)
+    n = 50000
+    rpos, ridx = orc.generate_grid_samples(ocfg, n, rng, step, grid, thresh)
+    pos, idx = G.zeros(n * 3, torch.float32), G.zeros(n, torch.int32)
+    capi.check(lib.ngp_generate_grid_samples(G.stream(), C.byref(cfg), n, rng.state, rng.inc, step, G.p(G.dev(grid)), thresh, G.p(pos), G.p(idx)))
+    G.sync()
+    assert np.array_equal(G.host(idx, np.uint32), ridx)
+    assert np.array_equal(G.host(pos).reshape(n, 3), rpos)
+
+
+def test_update_grid_and_bitfield_match_oracle(capi, orc):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg, ocfg = capi.make_sampler_cfg(1), orc.SamplerCfg(1)
+    grid = make_density_grid()
+    n = 200000
+    g = np.random.Generator(np.random.PCG64(3))
+    indices = g.integers(0, grid.size, n).astype(np.uint32)
+    density = (g.random((n, 16), dtype=np.float32) * 8 - 6).astype(np.float16)
+    ref_grid = grid.copy()
+    orc.update_grid(ocfg, indices, density, 16, 0.95, ref_grid)
+    d_grid, d_cur = G.dev(grid), G.zeros(grid.size, torch.float32)
+    capi.check(lib.ngp_update_grid(G.stream(), C.byref(cfg), n, G.p(G.dev(indices)), G.p(G.dev(density)), 16, 3, 0.95, G.p(d_cur), G.p(d_grid)))
+    G.sync()
+    got = G.host(d_grid)
+    # __expf vs expf: relative 2^-21 or so on the splatted values
+    assert np.allclose(got, ref_grid, rtol=2e-6, atol=0)
+    assert np.array_equal(got < 0, ref_grid < 0)
+    # bitfield from the SAME grid values on both sides: bit-exact
+    mean = orc.grid_mean(ocfg, got)
+    ref_bits = orc.grid_to_bitfield(ocfg, got, mean)
+    d_mean, d_bits = G.zeros(16, torch.float32), G.zeros(grid.size // 8, torch.uint8)
+    capi.check(lib.ngp_update_grid_bitfield(G.stream(), C.byref(cfg), G.p(d_grid), 0.01, G.p(d_mean), G.p(d_bits)))
+    G.sync()
+    assert abs(float(G.host(d_mean)[0]) - mean) <= 1e-6 * abs(mean)
+    bits = G.host(d_bits)
+    if float(G.host(d_mean)[0]) > 0.01 and mean > 0.01:      # threshold = min(0.01, mean): identical on both sides
+        assert np.array_equal(bits, ref_bits)
+    assert np.count_nonzero(bits != ref_bits) <= 2
+    # coarser cascade contains the max-pooled finer one: every set bit of cascade 0 shows up in the centre octant of cascade 1
+    assert bits[grid.size // 16:].any()
+
+
+def _scene(orc, n_images=4, W=64, H=64):
+    xf = make_cameras(n_images, seed=11)
+    images = rng_uniform((n_images, H, W, 4), 21).astype(np.float16)
+    grid = make_density_grid(seed=13)
+    ocfg = orc.SamplerCfg(1)
+    bits = orc.grid_to_bitfield(ocfg, grid, 1.0)
+    return xf, images, bits
+
+
+@pytest.mark.parametrize("n_rays,n_coords", [(4096, 1 << 20), (1000, 1 << 20), (4096, 20000), (1, 1 << 16)])
+def test_generate_training_samples_matches_oracle(capi, orc, n_rays, n_coords):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg, ocfg = capi.make_sampler_cfg(1), orc.SamplerCfg(1)
+    W = H = 64
+    fx = 70.0
+    xf, images, bits = _scene(orc)
+    rng = orc.Pcg32(43)
+    ref = orc.generate_training_samples(ocfg, n_rays, 17, n_coords, xf, images.view(np.uint16), W, H, fx, fx, bits, rng)
+    cam = _cam(capi, W, H, fx)
+    rays, rgba = G.zeros(n_rays * 6, torch.float32), G.zeros(n_rays * 4, torch.float32)
+    numsteps, coords = G.zeros(n_rays * 2, torch.int32), G.zeros(n_coords * 7, torch.float32)
+    counters, per_ray = G.zeros(2, torch.int32), G.zeros(n_rays, torch.int32)
+    ws = G.zeros(lib.ngp_scan_workspace_bytes(n_rays) + 64, torch.uint8)
+    capi.check(lib.ngp_generate_training_samples(G.stream(), C.byref(cfg), C.byref(cam), n_rays, 17, n_coords, 4, G.p(G.dev(xf)), G.p(G.dev(images)),
+                                                 G.p(G.dev(bits)), 1, rng.state, rng.inc, G.p(rays), G.p(rgba), G.p(numsteps), G.p(coords), G.p(counters),
+                                                 G.p(per_ray), G.p(ws)))
+    G.sync()
+    assert np.array_equal(G.host(per_ray, np.uint32), ref["per_ray_n"]), "per-ray sample counts must be bit-exact"
+    cnt = G.host(counters, np.uint32)
+    assert list(cnt) == list(ref["counters"])
+    kept = int(cnt[0])
+    assert kept > 0
+    assert np.array_equal(G.host(numsteps, np.uint32).reshape(-1, 2)[:kept], ref["numsteps"][:kept])
+    assert np.array_equal(G.host(rays).reshape(-1, 6)[:kept], ref["rays"][:kept])
+    assert np.array_equal(G.host(rgba).reshape(-1, 4)[:kept], ref["rgba"][:kept])
+    n_written = int(ref["numsteps"][kept - 1].sum())
+    assert np.array_equal(G.host(coords).reshape(-1, 7)[:n_written], ref["coords"][:n_written]), "sample coordinates differ"
+    if n_coords == 20000:
+        assert cnt[1] > n_coords and kept < n_rays      # the budget really clipped rays
+
+
+@pytest.mark.parametrize("spp,n_steps", [(0, 1), (3, 8)])
+def test_inference_rays_and_coords_match_oracle(capi, orc, spp, n_steps):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg, ocfg = capi.make_sampler_cfg(1), orc.SamplerCfg(1)
+    W, H, fx = 96, 64, 80.0
+    xf, _, bits = _scene(orc)
+    cam_m = xf[1]
+    ref_p = orc.init_rays(ocfg, W, H, fx, fx, cam_m, spp, bits)
+    cam = _cam(capi, W, H, fx)
+    payloads = G.zeros(W * H * 10, torch.int32)
+    d_bits = G.dev(bits)
+    cm = (C.c_float * 12)(*cam_m.tolist())
+    capi.check(lib.ngp_init_rays(G.stream(), C.byref(cfg), C.byref(cam), cm, spp, 1, G.p(d_bits), G.p(payloads)))
+    G.sync()
+    got_p = G.host(payloads, np.uint32).reshape(-1, 10)
+    alive = ref_p[:, 0] != 0
+    assert np.array_equal(got_p[:, 0] != 0, alive)
+    assert alive.any() and not alive.all()
+    assert np.array_equal(got_p[alive], ref_p[alive]), "payloads of live rays must be bit-exact"
+    # per-iteration sample generation on the same payloads
+    ref_coords = orc.generate_coords_from_rays(ocfg, ref_p, n_steps, bits)
+    coords = G.zeros(W * H * n_steps * 7, torch.float32)
+    capi.check(lib.ngp_generate_coords_from_rays(G.stream(), C.byref(cfg), W * H, None, n_steps, G.p(d_bits), G.p(payloads), G.p(coords)))
+    G.sync()
+    got_p2 = G.host(payloads, np.uint32).reshape(-1, 10)
+    assert np.array_equal(got_p2[alive], ref_p[alive]), "n_steps / t after generate_coords must be bit-exact"
+    gc = G.host(coords).reshape(W * H, n_steps, 7)
+    rc = ref_coords.reshape(W * H, n_steps, 7)
+    ns = ref_p[:, 9]
+    for j in range(n_steps):
+        m = alive & (ns > j)
+        assert np.array_equal(gc[m, j], rc[m, j])
