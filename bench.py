@@ -1,0 +1,278 @@
+#!/usr/bin/env python
+"""bench.py -- training samples/s of the instant-NGP NeRF step on a nerf_synthetic-shaped procedural scene
+(BASELINE.json configs[1]: 100 views 800x800, 2^18-sample batches, base.json model), 1..8 B200.
+
+  python bench.py --gpus N --steps K --warmup W            our sm_100a path through the pyngp Testbed (one rank per GPU)
+  python bench.py --impl reference --steps K --warmup W    the reference's algorithm on the host cores (CPU oracle, rank 0)
+
+A "step" is one training step (march -> network -> composite -> forward/backward -> optimizer); occupancy-grid refreshes
+happen every 16 steps as in the reference's run.py loop and are inside the timed region.  One JSON line on stdout."""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "instant-ngp-nerf-minimal_b200"
+METRIC = "nerf_train_samples_per_s"
+UNIT = "samples/s"
+CALL_STEPS = 16                      # run.py:71 trains in calls of 16 steps; the occupancy grid is refreshed once per call
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=256)
+    p.add_argument("--warmup", type=int, default=96)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--batch", type=int, default=1 << 18)
+    p.add_argument("--views", type=int, default=100)
+    p.add_argument("--res", type=int, default=800)
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    return p.parse_args()
+
+
+def config_dict(args, n_gpus):
+    return {"workload": f"configs[1]: nerf_synthetic-shaped procedural scene, {args.views} views {args.res}x{args.res}, base.json model (L=16 F=2 T=2^19, 64-wide MLPs), "
+                        f"{args.batch}-sample batches, occupancy refresh every {CALL_STEPS} steps",
+            "global_batch": args.batch * n_gpus, "per_gpu_batch": args.batch, "parallelism": f"dp{n_gpus}" if n_gpus > 1 else "single",
+            "l2_policy": "inputs larger than L2 (512 MB fp16 image set sampled at random pixels; 37-117 MB of samples streamed per step); "
+                         "the 23 MB hash table is L2-resident by design, as in the real workload"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled while the timed region runs"""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=lambda: [self.rows.append(l) for l in self.proc.stdout], daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        time.sleep(0.05)
+        sm, mx, reasons = [], [], set()
+        for l in self.rows:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 6 or not f[0].isdigit():
+                continue
+            sm.append(int(f[0])); mx.append(int(f[1]))
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops_sustained", 1400.0), "measured"
+    return 6650.0, 1400.0, "fallback"
+
+
+# ALGORITHMIC bytes (or flops) per launch of each hot kernel, from the units one launch processes (DESIGN.md section 4;
+# per-unit figures from SURVEY.md 8d): m = samples marched per step, b = samples in the compacted batch, r = rays, p = params
+def kernel_work(name, m, b, r, p):
+    table = {
+        "composite_train_kernel": ("hbm", m * (8 + 28) + b * (8 + 28) + r * 32),
+        "composite_count_kernel": ("hbm", m * (8 + 4) + r * 40),
+        "composite_grad_kernel": ("hbm", b * (8 + 28 + 8 + 28) + r * 40),
+        "generate_training_samples_kernel": ("hbm", m * 28 + r * (24 + 16 + 8 + 8)),
+        "march_count_kernel": ("hbm", r * 64),
+        "march_emit_kernel": ("hbm", m * 28 + r * 64),
+        "hash_encode_fwd_kernel": ("hbm", 0.5 * (m + b) * 588),          # two launches per step: m points and b points
+        "hash_encode_bwd_kernel": ("hbm", b * 588 + 2 * (p - 10240)),
+        "adam_ema_kernel": ("hbm", p * 42),
+        "mlp_kernel": ("tensor", 0.5 * (m * 18816 + b * 54400)),          # inference launch + training launch
+    }
+    return table.get(name)
+
+
+def run_reference(args):
+    """the reference's algorithm on the host cores: CPU oracle pipeline, all threads, bounded sample per step"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import pipeline
+    cores = os.cpu_count() or 1
+    budget_s = 150.0
+    trainer = pipeline.CpuTrainer(n_views=8, res=200, batch=args.batch)
+    t0 = time.perf_counter()
+    trainer.step(512)
+    per_ray = (time.perf_counter() - t0) / 512
+    total_steps = args.steps + args.warmup
+    n_rays = int(min(8192, max(64, budget_s / total_steps / per_ray)))
+    for _ in range(args.warmup):
+        trainer.step(n_rays)
+    samples, t0 = 0, time.perf_counter()
+    for _ in range(args.steps):
+        samples += trainer.step(n_rays)[1]
+    dt = time.perf_counter() - t0
+    value = samples / dt
+    sample = f"{args.steps} steps of {n_rays} rays ({samples / args.steps:.0f} samples/step) on 8 procedural views 200x200, analytic occupancy grid, same model config"
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+                      "config": config_dict(args, args.gpus),
+                      "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                      "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
+def train_steps(tb, n_steps, batch):
+    """n_steps training steps in calls of CALL_STEPS; returns (post-compaction samples, marched samples, rays, device ms)"""
+    done, samples, marched, rays, dev_ms = 0, 0, 0, 0, 0.0
+    while done < n_steps:
+        k = min(CALL_STEPS, n_steps - done)
+        r = tb.training_buffer.n_rays_per_batch
+        tb.train(k, batch)
+        b = tb.training_buffer
+        samples += sum(min(c, batch) for c in b.n_compacted_coords_counter_cpu)
+        marched += sum(b.n_coords_counter_cpu)
+        rays += r * k
+        dev_ms += b.training_ms + b.training_prep_ms
+        done += k
+    return samples, marched, rays, dev_ms
+
+
+def run_ours(args):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module(PKG)
+    capi, scene = pkg.capi, importlib.import_module(PKG + ".scene")
+    lib = capi.load()                       # raises if the CUDA library is missing: there is no fallback path
+    pyngp = pkg.load_pyngp()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    # ---- scene: rendered once on the device, then parked in PINNED HOST memory like a decoded dataset ----
+    ogl = scene.sphere_cameras(args.views, 2024)
+    xf = torch.from_numpy(scene.opengl_to_ngp(ogl)).cuda()
+    fx = 0.5 * args.res / np.tan(0.5 * scene.CAMERA_ANGLE_X)
+    rgba8 = torch.empty((args.views, args.res, args.res, 4), dtype=torch.uint8, device="cuda")
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    capi.check(lib.ngp_render_procedural_views(s, 2024, args.views, args.res, args.res, fx, fx, C.c_void_p(xf.data_ptr()), C.c_void_p(rgba8.data_ptr())))
+    torch.cuda.synchronize()
+    host_rgba8 = torch.empty(rgba8.shape, dtype=torch.uint8, pin_memory=True)
+    host_rgba8.copy_(rgba8)
+    del rgba8
+    np_rgba8 = host_rgba8.numpy()
+
+    tb = pyngp.Testbed()
+    tb.load_model_config(os.path.join(ROOT, PKG, "configs", "base.json"))
+    comm = 0
+    if world > 1:
+        box = [pyngp.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        comm = pyngp.nccl_comm_init(box[0], rank, world)
+        tb.set_data_parallel(rank, world, comm)
+    # host -> device upload of the dataset through the public API, timed on its second (warm) execution
+    tb.load_training_data_from_memory(np_rgba8, ogl, scene.CAMERA_ANGLE_X, 0.33, [0.5, 0.5, 0.5])
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    tb.load_training_data_from_memory(np_rgba8, ogl, scene.CAMERA_ANGLE_X, 0.33, [0.5, 0.5, 0.5])
+    torch.cuda.synchronize()
+    t_upload = time.perf_counter() - t0
+    h2d_bytes = np_rgba8.nbytes + ogl.nbytes
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    train_steps(tb, args.warmup, args.batch)
+    clocks = ClockSampler(local_rank)
+    barrier()
+    launches0 = lib.ngp_launch_count()
+    clocks.start()
+    t0 = time.perf_counter()
+    samples, marched, rays, dev_ms = train_steps(tb, args.steps, args.batch)
+    barrier()
+    wall = time.perf_counter() - t0
+    clk = clocks.stop()
+    launches = lib.ngp_launch_count() - launches0
+
+    # ---- per-kernel durations, live, with CUDA events on the launching stream (same workload, a further timed region) ----
+    prof_steps = min(args.steps, 64)
+    capi.check(lib.ngp_kernel_timing_enable(1, 64 * prof_steps + 4096))
+    p_samples, p_marched, p_rays, _ = train_steps(tb, prof_steps, args.batch)
+    kt = capi.kernel_timing_collect()
+    capi.check(lib.ngp_kernel_timing_enable(0, 0))
+
+    if world > 1:
+        t = torch.tensor([dev_ms, wall * 1e3, t_upload * 1e3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, wall, t_upload = float(t[0]), float(t[1]) / 1e3, float(t[2]) / 1e3
+        c = torch.tensor([samples, marched, rays], dtype=torch.float64, device="cuda")
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        samples, marched, rays = float(c[0]), float(c[1]), float(c[2])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    hbm_peak, tf_peak, peak_src = measured_peaks()
+    total_kernel_ms = sum(v[0] for v in kt.values())
+    name, (k_ms, k_n) = max(kt.items(), key=lambda kv: kv[1][0])
+    m, b, r = p_marched / prof_steps, p_samples / prof_steps, p_rays / prof_steps
+    work = kernel_work(name, m, b, r, tb.n_params)
+    launches_per_step = k_n / prof_steps
+    roofline = {"kernel": name, "share_of_kernel_time": k_ms / total_kernel_ms, "avg_launch_us": k_ms / k_n * 1e3, "launches_per_step": launches_per_step}
+    if work:
+        bound, per_step = work
+        per_launch = per_step / launches_per_step
+        achieved = per_launch / (k_ms / k_n * 1e-3)
+        peak = hbm_peak if bound == "hbm" else tf_peak
+        achieved = achieved / 1e9 if bound == "hbm" else achieved / 1e12
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(name)
+        roofline.update({"bound": bound, "achieved": achieved, "peak": peak, "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src, "algorithmic_per_launch": per_launch})
+    roofline["kernels_ms_per_step"] = {k: v[0] / prof_steps for k, v in sorted(kt.items(), key=lambda kv: -kv[1][0])}
+
+    out = {"metric": METRIC, "value": samples / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+           "config": config_dict(args, args.gpus), "clocks": clk, "gpu_launches": int(launches),
+           "e2e": {"value": samples / (wall + t_upload), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes / args.steps,
+                   "d2h_bytes_per_step": (3 * 4 * CALL_STEPS + 4) / CALL_STEPS, "wall_ms_per_step": wall / args.steps * 1e3, "dataset_upload_ms": t_upload * 1e3},
+           "roofline": roofline,
+           "samples_marched_per_step": marched / args.steps / max(world, 1), "rays_per_step": rays / args.steps / max(world, 1), "loss": tb.training_buffer.loss}
+    if args.gpus == 1 and not args.no_cpu_baseline:
+        from oracle import pipeline                      # the CPU restatement, timed as the baseline only
+        cb = pipeline.time_cpu_steps(n_steps=4, n_rays=2048, warmup=1, n_views=8, res=200, batch=args.batch)
+        out["cpu_baseline"] = {"value": cb["samples_per_s"], "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+                               "sample": f"4 steps of 2048 rays ({cb['samples_per_step']:.0f} samples/step, {cb['seconds']:.1f} s) on 8 procedural views 200x200, analytic occupancy, same model"}
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

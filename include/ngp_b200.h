@@ -65,6 +65,11 @@ typedef struct ngp_optimizer_cfg {
 
 const char* ngp_last_error(void);
 int ngp_abi_version(void);
+/* measurement hooks: kernels launched by this library so far; optional CUDA-event bracketing of every launch on its own
+ * stream (enable with a capacity, collect = synchronise + per-kernel-name totals, returns the number of names written) */
+unsigned long long ngp_launch_count(void);
+int ngp_kernel_timing_enable(int on, uint32_t max_launches);
+int ngp_kernel_timing_collect(uint32_t max_kernels, char* names /* [max_kernels][64] */, float* total_ms, uint32_t* counts);
 
 /* ---- hash grid -------------------------------------------------------------------------------- */
 /* replaces GridEncodingTemplated ctor (grid.h:475-537); returns the number of table entries */

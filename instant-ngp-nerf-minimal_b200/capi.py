@@ -43,6 +43,9 @@ class OptimizerCfg(C.Structure):
 SIGNATURES = {
     "ngp_last_error": (C.c_char_p, []),
     "ngp_abi_version": (i32, []),
+    "ngp_launch_count": (u64, []),
+    "ngp_kernel_timing_enable": (i32, [i32, u32]),
+    "ngp_kernel_timing_collect": (i32, [u32, vp, vp, vp]),
     "ngp_grid_desc_init": (u32, [C.POINTER(GridDesc), u32, u32, u32, f32]),
     "ngp_auto_per_level_scale": (f32, [f32, u32, u32]),
     "ngp_hash_encode_fwd": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, u32, vp]),
@@ -135,3 +138,16 @@ def make_sampler_cfg(aabb_scale=1, grid_size=128, max_steps=1024, cone_angle=0.0
     c.max_step = float(sqrt3 * np.float32(1 << (n_cascades - 1)) / np.float32(grid_size))
     c.near_distance = near_distance
     return c
+
+
+def kernel_timing_collect(max_kernels=64):
+    """{kernel name: (total ms, launches)} recorded since ngp_kernel_timing_enable(1, n); synchronises the device"""
+    import numpy as np
+    lib = load()
+    names = C.create_string_buffer(max_kernels * 64)
+    ms = np.zeros(max_kernels, np.float32)
+    cnt = np.zeros(max_kernels, np.uint32)
+    k = lib.ngp_kernel_timing_collect(max_kernels, names, ms.ctypes.data_as(vp), cnt.ctypes.data_as(vp))
+    if k < 0:
+        raise NgpError(lib.ngp_last_error().decode())
+    return {names.raw[i * 64:(i + 1) * 64].split(b"\0")[0].decode(): (float(ms[i]), int(cnt[i])) for i in range(k)}

@@ -15,6 +15,17 @@ namespace ngp {
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
 
+// Every kernel launch goes through NGP_LAUNCH: it counts the launch (ngp_launch_count) and, when kernel timing is enabled
+// (ngp_kernel_timing_enable), brackets it with a pair of CUDA events on the launching stream so bench.py can report live
+// per-kernel durations for the roofline without a profiler attached.
+struct KernelTimer {
+	KernelTimer(const char* name, cudaStream_t stream);
+	~KernelTimer();
+	int slot;
+	cudaStream_t stream;
+};
+#define NGP_LAUNCH(name, stream, ...) do { ngp::KernelTimer _kt(name, stream); __VA_ARGS__; } while (0)
+
 #define NGP_REQUIRE(cond, msg) do { if (!(cond)) { ngp::set_error("%s: %s", __func__, msg); return -1; } } while (0)
 
 constexpr uint32_t kNumSMs = 148;

@@ -142,14 +142,14 @@ extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint
 	if (cudaMemsetAsync(d_scan_ws, 0, ngp_scan_workspace_bytes(n_rays), s) != cudaSuccess) { set_error("ngp_composite_train: memset failed"); return -2; }
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
 	ScanState scan{(unsigned long long*)d_scan_ws};
-	composite_train_kernel<<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, n_rays, max_compacted, d_ray_counter, (const float4*)d_rays_rgba, d_numsteps,
+	NGP_LAUNCH("composite_train_kernel", s, composite_train_kernel<<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, n_rays, max_compacted, d_ray_counter, (const float4*)d_rays_rgba, d_numsteps,
 		(const Coordinate*)d_coords, (Coordinate*)d_coords_compacted, d_compacted_counter, (const __half*)d_rgbsigma, (__half*)d_dloss, padded_width,
-		d_mean_density, rng, d_loss, scan);
+		d_mean_density, rng, d_loss, scan));
 	return check_launch("composite_train");
 }
 
 extern "C" int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted) {
 	NGP_REQUIRE(d_compacted_counter && d_dloss && d_coords_compacted, "null pointer");
-	rollover_kernel<<<grid_for(batch, 256), 256, 0, (cudaStream_t)stream>>>(batch, d_compacted_counter, (__half*)d_dloss, padded_width, (Coordinate*)d_coords_compacted);
+	NGP_LAUNCH("rollover_kernel", (cudaStream_t)stream, rollover_kernel<<<grid_for(batch, 256), 256, 0, (cudaStream_t)stream>>>(batch, d_compacted_counter, (__half*)d_dloss, padded_width, (Coordinate*)d_coords_compacted));
 	return check_launch("rollover");
 }

@@ -109,7 +109,7 @@ extern "C" int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp
 	const float offx = fractf_host(0.5f - ax + bx), offy = fractf_host(0.5f - ay + by);
 	const uint32_t n = (uint32_t)cam->width * (uint32_t)cam->height;
 	CamMat cm; memcpy(cm.m, camera_matrix_host, sizeof(cm.m));
-	init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads);
+	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads));
 	return check_launch("init_rays");
 }
 
@@ -117,6 +117,6 @@ extern "C" int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg
                                              const uint8_t* d_bitfield, void* d_payloads, float* d_coords) {
 	NGP_REQUIRE(cfg && d_bitfield && d_payloads && d_coords, "null pointer");
 	if (n_rays == 0) return 0;
-	generate_coords_from_rays_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, d_bitfield, (RayPayload*)d_payloads, (Coordinate*)d_coords);
+	NGP_LAUNCH("generate_coords_from_rays_kernel", (cudaStream_t)stream, generate_coords_from_rays_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, d_bitfield, (RayPayload*)d_payloads, (Coordinate*)d_coords));
 	return check_launch("generate_coords_from_rays");
 }

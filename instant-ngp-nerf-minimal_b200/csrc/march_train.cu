@@ -96,8 +96,8 @@ extern "C" int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg
 	if (cudaMemsetAsync(d_scan_ws, 0, ngp_scan_workspace_bytes(n_rays), s) != cudaSuccess) { set_error("ngp_generate_training_samples: memset failed"); return -2; }
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
 	ScanState scan{(unsigned long long*)d_scan_ws};
-	generate_training_samples_kernel<<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_coords, n_images, d_xforms,
+	NGP_LAUNCH("generate_training_samples_kernel", s, generate_training_samples_kernel<<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_coords, n_images, d_xforms,
 		(const uint2*)d_images, d_bitfield, snap_to_pixel_centers, rng, d_rays, (float4*)d_rays_rgba, d_numsteps, (Coordinate*)d_coords,
-		d_counters, d_per_ray_n, scan);
+		d_counters, d_per_ray_n, scan));
 	return check_launch("generate_training_samples");
 }

@@ -355,8 +355,8 @@ static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords,
 	}
 	const uint32_t n_tiles = div_up(n, 128);
 	const uint32_t grid = n_tiles < kNumSMs * ctas_per_sm ? n_tiles : kNumSMs * ctas_per_sm;
-	mlp_kernel<MODE><<<grid, 128, smem, stream>>>((const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
-		(const __half*)dloss, (__half*)out, (__half*)denc, wgrad);
+	NGP_LAUNCH("mlp_kernel", stream, mlp_kernel<MODE><<<grid, 128, smem, stream>>>((const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
+		(const __half*)dloss, (__half*)out, (__half*)denc, wgrad));
 	return check_launch("mlp_kernel");
 }
 } // namespace ngp
@@ -423,6 +423,6 @@ extern "C" int ngp_network_train(void* stream, const float* d_coords, uint32_t n
 	if (rc) return rc;
 	rc = launch_mlp<MODE_TRAIN>(s, enc, d_coords, 7, n, nullptr, params, d_dloss, d_rgbsigma, denc, wgrad);
 	if (rc) return rc;
-	wgrad_to_half_kernel<<<div_up(NGP_MLP_PARAMS, 256), 256, 0, s>>>(wgrad, (__half*)d_grads, NGP_MLP_PARAMS);
+	NGP_LAUNCH("wgrad_to_half_kernel", s, wgrad_to_half_kernel<<<div_up(NGP_MLP_PARAMS, 256), 256, 0, s>>>(wgrad, (__half*)d_grads, NGP_MLP_PARAMS));
 	return ngp_hash_encode_bwd(stream, d_coords, 7, n, denc, 32, desc, (__half*)d_grads + NGP_MLP_PARAMS, 1);
 }

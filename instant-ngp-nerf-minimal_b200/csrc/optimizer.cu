@@ -113,7 +113,7 @@ extern "C" int ngp_init_params(void* stream, uint64_t* rng_state, uint64_t rng_i
 	    cudaStreamSynchronize(s) != cudaSuccess) { set_error("ngp_init_params: copy failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
 	if (n_grid_params) {
 		const uint64_t n_threads = (n_grid_params + 3) / 4, total_threads = ((n_threads + 127) / 128) * 128;
-		init_grid_kernel<<<grid_for(n_threads, 256), 256, 0, s>>>(n_grid_params, n_threads, total_threads, rnd, d_params_fp32 + NGP_MLP_PARAMS, (__half*)d_params_fp16 + NGP_MLP_PARAMS);
+		NGP_LAUNCH("init_grid_kernel", s, init_grid_kernel<<<grid_for(n_threads, 256), 256, 0, s>>>(n_grid_params, n_threads, total_threads, rnd, d_params_fp32 + NGP_MLP_PARAMS, (__half*)d_params_fp16 + NGP_MLP_PARAMS));
 	}
 	rnd.advance(n_grid_params);
 	*rng_state = rnd.state;
@@ -131,7 +131,7 @@ extern "C" int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, ui
 	h.ema_decay = cfg->ema_decay;
 	h.deb_old = 1 - (float)std::pow(cfg->ema_decay, new_step - 1);
 	h.deb_new = 1.0f / (1 - (float)std::pow(cfg->ema_decay, new_step));
-	adam_ema_kernel<<<grid_for(n_params / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
-		d_m1, d_m2, d_param_steps, (__half*)d_ema16);
+	NGP_LAUNCH("adam_ema_kernel", (cudaStream_t)stream, adam_ema_kernel<<<grid_for(n_params / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
+		d_m1, d_m2, d_param_steps, (__half*)d_ema16));
 	return check_launch("optimizer_step");
 }

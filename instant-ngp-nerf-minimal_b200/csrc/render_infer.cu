@@ -140,9 +140,9 @@ extern "C" int ngp_composite_infer(void* stream, const ngp_render_cfg* cfg, uint
                                    float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale) {
 	NGP_REQUIRE(cfg && d_payloads && d_rgba && d_coords && d_rgbsigma && camera_fwd_host, "null pointer");
 	if (n_rays == 0) return 0;
-	composite_infer_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, n_steps_offset, (RayPayload*)d_payloads,
+	NGP_LAUNCH("composite_infer_kernel", (cudaStream_t)stream, composite_infer_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, n_steps_offset, (RayPayload*)d_payloads,
 		(float4*)d_rgba, (const Coordinate*)d_coords, (const __half*)d_rgbsigma, padded_width, render_mode, aabb_min, aabb_max,
-		camera_fwd_host[0], camera_fwd_host[1], camera_fwd_host[2], depth_scale);
+		camera_fwd_host[0], camera_fwd_host[1], camera_fwd_host[2], depth_scale));
 	return check_launch("composite_infer");
 }
 
@@ -150,22 +150,22 @@ extern "C" int ngp_compact_rays(void* stream, uint32_t n_rays, const uint32_t* d
                                 void* d_dst_payloads, float* d_dst_rgba, void* d_hit_payloads, float* d_hit_rgba, uint32_t* d_n_alive, uint32_t* d_n_hit) {
 	NGP_REQUIRE(d_src_payloads && d_src_rgba && d_dst_payloads && d_dst_rgba && d_hit_payloads && d_hit_rgba && d_n_alive && d_n_hit, "null pointer");
 	if (n_rays == 0) return 0;
-	compact_rays_kernel<<<div_up(n_rays, 256), 256, 0, (cudaStream_t)stream>>>(n_rays, d_n_rays, (const RayPayload*)d_src_payloads, (const float4*)d_src_rgba,
-		(RayPayload*)d_dst_payloads, (float4*)d_dst_rgba, (RayPayload*)d_hit_payloads, (float4*)d_hit_rgba, d_n_alive, d_n_hit);
+	NGP_LAUNCH("compact_rays_kernel", (cudaStream_t)stream, compact_rays_kernel<<<div_up(n_rays, 256), 256, 0, (cudaStream_t)stream>>>(n_rays, d_n_rays, (const RayPayload*)d_src_payloads, (const float4*)d_src_rgba,
+		(RayPayload*)d_dst_payloads, (float4*)d_dst_rgba, (RayPayload*)d_hit_payloads, (float4*)d_hit_rgba, d_n_alive, d_n_hit));
 	return check_launch("compact_rays");
 }
 
 extern "C" int ngp_shade(void* stream, uint32_t n_hit_max, const uint32_t* d_n_hit, const float* d_rgba, const void* d_payloads, float* d_frame, int render_mode, int train_in_linear) {
 	NGP_REQUIRE(d_rgba && d_payloads && d_frame, "null pointer");
 	if (n_hit_max == 0) return 0;
-	shade_kernel<<<div_up(n_hit_max, 256), 256, 0, (cudaStream_t)stream>>>(n_hit_max, d_n_hit, (const float4*)d_rgba, (const RayPayload*)d_payloads, (float4*)d_frame, render_mode, train_in_linear);
+	NGP_LAUNCH("shade_kernel", (cudaStream_t)stream, shade_kernel<<<div_up(n_hit_max, 256), 256, 0, (cudaStream_t)stream>>>(n_hit_max, d_n_hit, (const float4*)d_rgba, (const RayPayload*)d_payloads, (float4*)d_frame, render_mode, train_in_linear));
 	return check_launch("shade");
 }
 
 extern "C" int ngp_accumulate(void* stream, uint32_t n_pixels, const float* d_frame, float* d_accum, float sample_count, int color_space) {
 	NGP_REQUIRE(d_frame && d_accum, "null pointer");
 	if (n_pixels == 0) return 0;
-	accumulate_kernel<<<div_up(n_pixels, 256), 256, 0, (cudaStream_t)stream>>>(n_pixels, (const float4*)d_frame, (float4*)d_accum, sample_count, color_space);
+	NGP_LAUNCH("accumulate_kernel", (cudaStream_t)stream, accumulate_kernel<<<div_up(n_pixels, 256), 256, 0, (cudaStream_t)stream>>>(n_pixels, (const float4*)d_frame, (float4*)d_accum, sample_count, color_space));
 	return check_launch("accumulate");
 }
 
@@ -174,6 +174,6 @@ extern "C" int ngp_tonemap(void* stream, uint32_t n_pixels, float exposure, cons
 	NGP_REQUIRE(background_rgba_host && d_accum && d_out, "null pointer");
 	if (n_pixels == 0) return 0;
 	const float4 bg = make_float4(background_rgba_host[0], background_rgba_host[1], background_rgba_host[2], background_rgba_host[3]);
-	tonemap_kernel<<<div_up(n_pixels, 256), 256, 0, (cudaStream_t)stream>>>(n_pixels, exposure, bg, (const float4*)d_accum, color_space, output_color_space, tonemap_curve_id, (float4*)d_out);
+	NGP_LAUNCH("tonemap_kernel", (cudaStream_t)stream, tonemap_kernel<<<div_up(n_pixels, 256), 256, 0, (cudaStream_t)stream>>>(n_pixels, exposure, bg, (const float4*)d_accum, color_space, output_color_space, tonemap_curve_id, (float4*)d_out));
 	return check_launch("tonemap");
 }

@@ -122,7 +122,7 @@ using namespace ngp;
 extern "C" int ngp_mark_untrained_grid(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, uint32_t n_images, const float* d_xforms, float* d_grid) {
 	NGP_REQUIRE(cfg && cam && d_xforms && d_grid, "null pointer");
 	const uint32_t total = cfg->grid_size * cfg->grid_size * cfg->grid_size * cfg->n_cascades;
-	mark_untrained_grid_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, *cam, n_images, d_xforms, d_grid);
+	NGP_LAUNCH("mark_untrained_grid_kernel", (cudaStream_t)stream, mark_untrained_grid_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, *cam, n_images, d_xforms, d_grid));
 	return check_launch("mark_untrained_grid");
 }
 
@@ -131,7 +131,7 @@ extern "C" int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cf
 	NGP_REQUIRE(cfg && d_grid && d_positions && d_indices, "null pointer");
 	if (n == 0) return 0;
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
-	generate_grid_samples_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, d_grid, thresh, d_positions, d_indices);
+	NGP_LAUNCH("generate_grid_samples_kernel", (cudaStream_t)stream, generate_grid_samples_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, d_grid, thresh, d_positions, d_indices));
 	return check_launch("generate_grid_samples");
 }
 
@@ -141,8 +141,8 @@ extern "C" int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_
 	const uint32_t total = cfg->grid_size * cfg->grid_size * cfg->grid_size * cfg->n_cascades;
 	cudaStream_t s = (cudaStream_t)stream;
 	if (cudaMemsetAsync(d_grid_current, 0, (size_t)total * sizeof(float), s) != cudaSuccess) { set_error("ngp_update_grid: memset failed"); return -2; }
-	if (n) splat_grid_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, d_indices, (const __half*)d_density, density_stride, density_activation, cfg->min_step, d_grid_current);
-	ema_grid_kernel<<<grid_for(total, 256), 256, 0, s>>>(total, d_grid_current, decay, d_grid);
+	if (n) NGP_LAUNCH("splat_grid_kernel", s, splat_grid_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, d_indices, (const __half*)d_density, density_stride, density_activation, cfg->min_step, d_grid_current));
+	NGP_LAUNCH("ema_grid_kernel", s, ema_grid_kernel<<<grid_for(total, 256), 256, 0, s>>>(total, d_grid_current, decay, d_grid));
 	return check_launch("update_grid");
 }
 
@@ -151,10 +151,10 @@ extern "C" int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg
 	const uint32_t G = cfg->grid_size, cells = G * G * G;
 	NGP_REQUIRE(cells % 64 == 0, "grid_size^3 must be a multiple of 64");
 	cudaStream_t s = (cudaStream_t)stream;
-	grid_mean_kernel<<<1, 1024, 0, s>>>(d_grid, cells, d_mean);
+	NGP_LAUNCH("grid_mean_kernel", s, grid_mean_kernel<<<1, 1024, 0, s>>>(d_grid, cells, d_mean));
 	const uint32_t n_bytes = cells * cfg->n_cascades / 8;
-	grid_to_bitfield_kernel<<<grid_for(n_bytes, 256), 256, 0, s>>>(n_bytes, d_grid, d_bitfield, d_mean, min_optical_thickness);
+	NGP_LAUNCH("grid_to_bitfield_kernel", s, grid_to_bitfield_kernel<<<grid_for(n_bytes, 256), 256, 0, s>>>(n_bytes, d_grid, d_bitfield, d_mean, min_optical_thickness));
 	for (uint32_t level = 1; level < cfg->n_cascades; ++level)
-		bitfield_max_pool_kernel<<<grid_for(cells / 64, 256), 256, 0, s>>>(cells / 64, G, d_bitfield + (size_t)cells * (level - 1) / 8, d_bitfield + (size_t)cells * level / 8);
+		NGP_LAUNCH("bitfield_max_pool_kernel", s, bitfield_max_pool_kernel<<<grid_for(cells / 64, 256), 256, 0, s>>>(cells / 64, G, d_bitfield + (size_t)cells * (level - 1) / 8, d_bitfield + (size_t)cells * level / 8));
 	return check_launch("update_grid_bitfield");
 }

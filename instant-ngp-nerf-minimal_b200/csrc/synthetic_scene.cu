@@ -111,6 +111,6 @@ extern "C" int ngp_render_procedural_views(void* stream, uint32_t seed, uint32_t
 	s.shell_col[0] = 0.9f; s.shell_col[1] = 0.8f; s.shell_col[2] = 0.3f;
 	const uint64_t total = (uint64_t)n_views * width * height;
 	NGP_REQUIRE(total < (1ull << 31) * 256ull, "too many pixels");
-	render_procedural_kernel<<<(uint32_t)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(s, n_views, width, height, fx, fy, d_xforms, 1024, (uint32_t*)d_rgba8);
+	NGP_LAUNCH("render_procedural_kernel", (cudaStream_t)stream, render_procedural_kernel<<<(uint32_t)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(s, n_views, width, height, fx, fy, d_xforms, 1024, (uint32_t*)d_rgba8));
 	return check_launch("render_procedural_views");
 }

@@ -53,6 +53,20 @@ PYBIND11_MODULE(pyngp, m) {
 			float off[3]; to_vec(offset, off, 3, "offset");
 			t.load_training_data(path, scale, off);
 		}, "Load training data from a given path.")
+		.def("load_training_data_from_memory", [](Testbed& t, py::array_t<uint8_t, py::array::c_style> rgba8, py::array_t<float, py::array::c_style | py::array::forcecast> xforms,
+		                                          float camera_angle_x, float scale, const py::object& offset) {
+			if (rgba8.ndim() != 4 || rgba8.shape(3) != 4) throw std::runtime_error("rgba8 must be [n][H][W][4] uint8");
+			if (xforms.ndim() != 3 || xforms.shape(0) != rgba8.shape(0) || xforms.shape(1) < 3 || xforms.shape(2) != 4) throw std::runtime_error("xforms must be [n][3|4][4]");
+			float off[3]; to_vec(offset, off, 3, "offset");
+			const uint32_t n = (uint32_t)rgba8.shape(0);
+			std::vector<Mat34> m(n);
+			auto r = xforms.unchecked<3>();
+			for (uint32_t i = 0; i < n; ++i) for (int a = 0; a < 3; ++a) for (int b = 0; b < 4; ++b) m[i].at(a, b) = r(i, a, b);
+			const uint8_t* ptr = rgba8.data();
+			py::gil_scoped_release rel;
+			t.load_training_data_from_memory(n, (int)rgba8.shape(2), (int)rgba8.shape(1), camera_angle_x, m.data(), ptr, scale, off);
+		}, py::arg("rgba8"), py::arg("xforms"), py::arg("camera_angle_x"), py::arg("scale") = 0.33f, py::arg("offset") = std::vector<float>{0.5f, 0.5f, 0.5f},
+		   "Same as load_training_data for images already decoded in host memory.")
 		.def("load_procedural_training_data", [](Testbed& t, uint32_t n_images, int width, int height, uint32_t seed, float scale, const py::object& offset) {
 			float off[3]; to_vec(offset, off, 3, "offset");
 			t.load_procedural_training_data(n_images, width, height, seed, scale, off);
@@ -103,6 +117,9 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readonly("training_prep_ms", &Testbed::TrainingBuffer::training_prep_ms)
 		.def_readonly("training_ms", &Testbed::TrainingBuffer::training_ms)
 		.def_readonly("i_step", &Testbed::TrainingBuffer::i_step)
+		// per-step device counters of the last train() call (exact, for throughput accounting)
+		.def_readonly("n_coords_counter_cpu", &Testbed::TrainingBuffer::n_coords_counter_cpu)
+		.def_readonly("n_compacted_coords_counter_cpu", &Testbed::TrainingBuffer::n_compacted_coords_counter_cpu)
 		;
 
 	py::class_<Testbed::RenderingBuffer>(testbed, "RenderingBuffer")

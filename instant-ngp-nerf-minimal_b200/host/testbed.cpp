@@ -77,6 +77,16 @@ void Testbed::load_training_data(const std::string& data_path, float scale, cons
 	m_sampler->init(d.n_images, d.image_resolution, d.focal_length, d.principal_point, d.xforms, m_rng, m_stream);
 }
 
+void Testbed::load_training_data_from_memory(uint32_t n_images, int width, int height, float camera_angle_x, const Mat34* xforms_ogl, const uint8_t* rgba8,
+                                             float scale, const float offset[3]) {
+	if (!m_sampler) throw std::runtime_error("load_model_config must be called before load_training_data_from_memory");
+	m_training_buffer.dataset.load_from_memory(n_images, width, height, camera_angle_x, xforms_ogl, rgba8, scale, offset);
+	m_scene_scale = scale;
+	for (int k = 0; k < 3; ++k) m_scene_offset[k] = offset[k];
+	const NeRFSynthetic& d = m_training_buffer.dataset;
+	m_sampler->init(d.n_images, d.image_resolution, d.focal_length, d.principal_point, d.xforms, m_rng, m_stream);
+}
+
 void Testbed::load_procedural_training_data(uint32_t n_images, int width, int height, uint32_t seed, float scale, const float offset[3]) {
 	if (!m_sampler) throw std::runtime_error("load_model_config must be called before load_procedural_training_data");
 	m_training_buffer.dataset.load_procedural(n_images, width, height, 0.6911112f, seed, scale, offset);

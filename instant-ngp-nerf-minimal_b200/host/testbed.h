@@ -24,6 +24,10 @@ public:
 	void save_snapshot(const std::string& snapshot_path, bool serialize_optimizer);
 	void load_snapshot(const std::string& snapshot_path);
 	void load_training_data(const std::string& data_path, float scale, const float offset[3]);
+	// images already decoded in HOST memory (rgba8 sRGB straight alpha [n][H][W][4], OpenGL camera-to-world 3x4 per view): the
+	// same upload + from_rgba32 conversion + sampler init as load_training_data, minus the file parsing
+	void load_training_data_from_memory(uint32_t n_images, int width, int height, float camera_angle_x, const Mat34* xforms_ogl, const uint8_t* rgba8,
+	                                    float scale, const float offset[3]);
 	// benchmark fixture (no file I/O): procedural nerf_synthetic-shaped scene generated on the device
 	void load_procedural_training_data(uint32_t n_images, int width, int height, uint32_t seed, float scale, const float offset[3]);
 
