@@ -117,7 +117,7 @@ int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const 
 /* update_grid_bitfield (:737-760): mean of cascade 0 -> d_mean[0], bits, max-pool */
 int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg, const float* d_grid, float min_optical_thickness, float* d_mean, uint8_t* d_bitfield);
 /* sample_coords_from_dataset -> generate_training_samples_nerf (:310-449).  Compaction is in ray order (deterministic).
- * d_counters: [0] rays kept, [1] samples counted (both must be zero on entry).  d_scan_ws: >= ngp_scan_workspace_bytes(n_rays), zeroed by the call. */
+ * d_counters: [0] rays kept, [1] samples counted (overwritten).  d_scan_ws: >= ngp_scan_workspace_bytes(n_rays) bytes of scratch. */
 size_t ngp_scan_workspace_bytes(uint32_t n);
 int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, uint32_t n_rays, uint32_t n_rays_shift,
                                   uint32_t n_coords, uint32_t n_images, const float* d_xforms, const void* d_images, const uint8_t* d_bitfield,

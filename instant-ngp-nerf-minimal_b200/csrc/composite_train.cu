@@ -1,50 +1,118 @@
 // Volume-render compositing for training: forward, loss, analytic backward, ordered compaction.  sm_100a.
 // Replaces volume_rendering_with_loss_and_gradient_kernal (internal/render/ray_marcher.cu:15-213) and the two rollover
-// kernels (tiny-cuda-nn/common_device.h:485-505).  One thread walks one ray (rays are contiguous sample runs); the
-// compacted base of each ray comes from the chained CTA scan in ray order instead of one global atomicAdd per ray, which
-// makes the compacted batch bit-reproducible.  HBM-bound: 8 B rgbsigma + 28 B coord read, 8 B grad + 28 B coord written
-// per sample.
+// kernels (tiny-cuda-nn/common_device.h:485-505).  The reference walks each ray with one thread, three times; here a WARP
+// owns a ray and the running transmittance / prefix colour are per-ray segmented warp scans, so a step's ~8 k rays become
+// ~260 k busy lanes.  The compacted base of each ray is an exclusive scan in ray order (bit-reproducible) instead of one
+// global atomicAdd per ray.  HBM-bound: 12 B / marched sample in the forward launch, 72 B / trained sample in the backward one.
 #include "composite.cuh"
 
 namespace ngp {
 
-__global__ void __launch_bounds__(128) composite_train_kernel(
-	ngp_render_cfg c, uint32_t n_rays, uint32_t max_compacted, const uint32_t* __restrict__ ray_counter,
-	const float4* __restrict__ rays_rgba, uint32_t* __restrict__ numsteps_io, const Coordinate* __restrict__ coords_in,
-	Coordinate* __restrict__ coords_compacted, uint32_t* __restrict__ compacted_counter, const __half* __restrict__ net_out,
-	__half* __restrict__ dloss, uint32_t padded_width, const float* __restrict__ mean_density_ptr, Pcg32 rng,
-	float* __restrict__ loss_out, ScanState scan)
+// per-ray scratch between the three launches
+struct RayTmp { float r, g, b, T; };
+
+__device__ __forceinline__ float warp_scan_mul(float v, uint32_t lane) {
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const float t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v *= t; }
+	return v;
+}
+__device__ __forceinline__ float warp_scan_add(float v, uint32_t lane) {
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const float t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+	return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+
+// Launch 1: forward compositing, ONE WARP PER RAY.  Lanes take 32 consecutive samples; the transmittance in front of each
+// sample is a segmented (per-ray) multiplicative warp scan carried from chunk to chunk; the first sample whose transmittance
+// fell below the threshold ends the ray (ballot + ffs), exactly where the reference's sequential loop breaks.
+__global__ void __launch_bounds__(256) composite_count_kernel(
+	ngp_render_cfg c, uint32_t n_rays, const uint32_t* __restrict__ ray_counter, const uint32_t* __restrict__ numsteps_in,
+	const Coordinate* __restrict__ coords_in, const __half* __restrict__ net_out, RayTmp* __restrict__ tmp, uint32_t* __restrict__ n_used_out)
 {
-	const uint32_t ticket = scan_ticket(scan);
-	const uint32_t i = ticket * blockDim.x + threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const uint32_t n_kept = min(*ray_counter, n_rays);
-	const bool active = i < n_kept;
-
-	uint32_t numst = 0, base = 0, n_used = 0;
-	float T = 1.f, rgb_ray[3] = {0.f, 0.f, 0.f};
-	if (active) {
-		numst = numsteps_io[i * 2]; base = numsteps_io[i * 2 + 1];
-		const Coordinate* cs = coords_in + base;
-		const __half* no = net_out + (size_t)base * 4;
-		for (; n_used < numst; ++n_used) {
-			if (T < c.transmittance_threshold) break;
-			float raw[4];
-			load_rgbsigma(no + (size_t)n_used * 4, raw);
-			const float density = net_to_density(raw[3], c.density_activation);
-			const float dt = unwarp_dt(cs[n_used].dt, c.min_step, c.n_cascades);
-			const float alpha = 1.f - __expf(-density * dt), w = alpha * T;
-			rgb_ray[0] += w * net_to_rgb(raw[0], c.rgb_activation);
-			rgb_ray[1] += w * net_to_rgb(raw[1], c.rgb_activation);
-			rgb_ray[2] += w * net_to_rgb(raw[2], c.rgb_activation);
-			T *= (1.f - alpha);
+	if (i >= n_kept) return;
+	const uint32_t numst = numsteps_in[i * 2], base = numsteps_in[i * 2 + 1];
+	const Coordinate* cs = coords_in + base;
+	const __half* no = net_out + (size_t)base * 4;
+	float T = 1.f, acc[3] = {0.f, 0.f, 0.f};
+	uint32_t n_used = numst;
+	for (uint32_t c0 = 0; c0 < numst; c0 += 32) {
+		const uint32_t k = c0 + lane;
+		const bool valid = k < numst;
+		float raw[4] = {0.f, 0.f, 0.f, 0.f}, alpha = 0.f;
+		if (valid) {
+			load_rgbsigma(no + (size_t)k * 4, raw);
+			const float dt = unwarp_dt(cs[k].dt, c.min_step, c.n_cascades);
+			alpha = 1.f - __expf(-net_to_density(raw[3], c.density_activation) * dt);
 		}
+		const float incl = warp_scan_mul(1.f - alpha, lane);
+		float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+		if (lane == 0) excl = 1.f;
+		const float Tk = T * excl;                               // transmittance in front of sample k
+		const uint32_t stop = __ballot_sync(0xffffffffu, valid && Tk < c.transmittance_threshold);
+		const uint32_t first = stop ? (uint32_t)__ffs(stop) - 1u : 32u;
+		if (valid && lane < first) {
+			const float w = alpha * Tk;
+			acc[0] += w * net_to_rgb(raw[0], c.rgb_activation);
+			acc[1] += w * net_to_rgb(raw[1], c.rgb_activation);
+			acc[2] += w * net_to_rgb(raw[2], c.rgb_activation);
+		}
+		if (stop) { n_used = c0 + first; break; }
+		T *= __shfl_sync(0xffffffffu, incl, 31);
 	}
+	const float r = warp_sum(acc[0]), g = warp_sum(acc[1]), b = warp_sum(acc[2]);
+	if (lane == 0) { tmp[i] = {r, g, b, T}; n_used_out[i] = n_used; }
+}
 
-	const unsigned long long prefix = chained_exclusive_scan(scan, ticket, (unsigned long long)n_used);
-	const uint32_t cbase = (uint32_t)prefix;
-	// final counter value (may exceed max_compacted, like the reference's atomicAdd total)
-	if (i == (n_kept ? n_kept - 1 : 0) && (active || n_kept == 0)) *compacted_counter = n_kept ? cbase + n_used : 0;
-	if (!active) return;
+// Launch 2: exclusive prefix sum of the per-ray sample counts in ray order (one CTA: at most 2^18 rays, a few microseconds).
+// Replaces one global atomicAdd per ray and makes the compacted batch bit-reproducible.
+__global__ void __launch_bounds__(1024) composite_scan_kernel(uint32_t n_rays, const uint32_t* __restrict__ ray_counter, const uint32_t* __restrict__ n_used,
+                                                              uint32_t* __restrict__ cbase, uint32_t* __restrict__ compacted_counter) {
+	__shared__ uint32_t warp_tot[32];
+	const uint32_t n_kept = min(*ray_counter, n_rays);
+	const uint32_t per = (n_kept + 1023) / 1024, lo = min(threadIdx.x * per, n_kept), hi = min(lo + per, n_kept);
+	uint32_t sum = 0;
+	for (uint32_t j = lo; j < hi; ++j) sum += n_used[j];
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint32_t incl = sum;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+	if (lane == 31) warp_tot[warp] = incl;
+	__syncthreads();
+	if (warp == 0) {
+		const uint32_t w = warp_tot[lane];
+		uint32_t wi = w;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+		warp_tot[lane] = wi - w;
+		if (lane == 31) *compacted_counter = wi;      // final value, may exceed the batch like the reference's atomicAdd total
+	}
+	__syncthreads();
+	uint32_t run = warp_tot[warp] + incl - sum;
+	for (uint32_t j = lo; j < hi; ++j) { cbase[j] = run; run += n_used[j]; }
+}
+
+// Launch 3: loss + analytic backward + compaction, one warp per ray.  Prefix colour and transmittance come from warp scans;
+// per-sample gradients are written as coalesced 8-byte records, the ray's Coordinates are copied as one flat float run.
+__global__ void __launch_bounds__(256) composite_grad_kernel(
+	ngp_render_cfg c, uint32_t n_rays, uint32_t max_compacted, const uint32_t* __restrict__ ray_counter, const float4* __restrict__ rays_rgba,
+	uint32_t* __restrict__ numsteps_io, const Coordinate* __restrict__ coords_in, Coordinate* __restrict__ coords_compacted,
+	const __half* __restrict__ net_out, __half* __restrict__ dloss, uint32_t padded_width, const float* __restrict__ mean_density_ptr, Pcg32 rng,
+	float* __restrict__ loss_out, const RayTmp* __restrict__ tmp, const uint32_t* __restrict__ n_used_in, const uint32_t* __restrict__ cbase_in)
+{
+	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const uint32_t n_kept = min(*ray_counter, n_rays);
+	if (i >= n_kept) return;
+	const uint32_t numst = numsteps_io[i * 2], base = numsteps_io[i * 2 + 1];
+	const uint32_t n_used = n_used_in[i], cbase = cbase_in[i];
+	const RayTmp t0 = tmp[i];
+	float rgb_ray[3] = {t0.r, t0.g, t0.b};
 
 	// background: same random colour for every ray of a step (un-advanced generator, ray_marcher.cu:90-93)
 	float bg[3] = {c.background_color[0], c.background_color[1], c.background_color[2]};
@@ -69,48 +137,62 @@ __global__ void __launch_bounds__(128) composite_train_kernel(
 	}
 	if (n_used == numst) {
 		#pragma unroll
-		for (int k = 0; k < 3; ++k) rgb_ray[k] += T * bg[k];
+		for (int k = 0; k < 3; ++k) rgb_ray[k] += t0.T * bg[k];
 	}
 
 	const uint32_t n = min(max_compacted - min(max_compacted, cbase), n_used);
-	numsteps_io[i * 2] = n; numsteps_io[i * 2 + 1] = cbase;
+	__syncwarp();
+	if (lane == 0) { numsteps_io[i * 2] = n; numsteps_io[i * 2 + 1] = cbase; }
 	if (n == 0) return;
 
 	float loss[3], g[3];
 	loss_and_grad(c.loss_type, tgt, rgb_ray, loss, g);
-	if (loss_out) loss_out[i] = ((loss[0] + loss[1] + loss[2]) / 3.f) / (float)n_rays;
+	if (loss_out && lane == 0) loss_out[i] = ((loss[0] + loss[1] + loss[2]) / 3.f) / (float)n_rays;
 	const float ls = c.loss_scale / (float)n_rays;
 	const float l2reg = c.rgb_activation == ACT_EXP ? 1e-4f : 0.f;
 	const float l1reg = *mean_density_ptr < c.min_optical_thickness ? 1e-4f : 0.f;
 
 	const Coordinate* cs = coords_in + base;
 	const __half* no = net_out + (size_t)base * 4;
-	float rgb2[3] = {0.f, 0.f, 0.f};
-	T = 1.f;
-	for (uint32_t j = 0; j < n; ++j) {
-		const Coordinate co = cs[j];
-		coords_compacted[cbase + j] = co;
-		float raw[4];
-		load_rgbsigma(no + (size_t)j * 4, raw);
-		const float dt = unwarp_dt(co.dt, c.min_step, c.n_cascades);
+	float T = 1.f, pre[3] = {0.f, 0.f, 0.f};          // carried: transmittance and colour in front of the chunk
+	for (uint32_t c0 = 0; c0 < n; c0 += 32) {
+		const uint32_t k = c0 + lane;
+		const bool valid = k < n;
+		float raw[4] = {0.f, 0.f, 0.f, 0.f}, alpha = 0.f, dt = 0.f;
+		if (valid) {
+			load_rgbsigma(no + (size_t)k * 4, raw);
+			dt = unwarp_dt(cs[k].dt, c.min_step, c.n_cascades);
+			alpha = 1.f - __expf(-net_to_density(raw[3], c.density_activation) * dt);
+		}
+		const float incl = warp_scan_mul(1.f - alpha, lane);
+		float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+		if (lane == 0) excl = 1.f;
+		const float Tk = T * excl, w = alpha * Tk, T_after = Tk * (1.f - alpha);
 		const float rgb[3] = {net_to_rgb(raw[0], c.rgb_activation), net_to_rgb(raw[1], c.rgb_activation), net_to_rgb(raw[2], c.rgb_activation)};
-		const float density = net_to_density(raw[3], c.density_activation);
-		const float alpha = 1.f - __expf(-density * dt), w = alpha * T;
+		float rgb2[3];
 		#pragma unroll
-		for (int k = 0; k < 3; ++k) rgb2[k] += w * rgb[k];
-		T *= (1.f - alpha);
-		float dl[4];
+		for (int j = 0; j < 3; ++j) rgb2[j] = pre[j] + warp_scan_add(valid ? w * rgb[j] : 0.f, lane);     // colour up to and including sample k
+		if (valid) {
+			float dl[4];
+			#pragma unroll
+			for (int j = 0; j < 3; ++j) dl[j] = ls * (w * g[j] * net_to_rgb_d(raw[j], c.rgb_activation) + fmaxf(0.f, l2reg * raw[j]));
+			float dot = 0.f;
+			#pragma unroll
+			for (int j = 0; j < 3; ++j) dot += g[j] * (T_after * rgb[j] - (rgb_ray[j] - rgb2[j]));
+			const float dmlp = net_to_density_d(raw[3], c.density_activation) * (dt * dot);
+			dl[3] = ls * dmlp + (raw[3] < 0 ? -l1reg : 0.f);
+			const __half2 lo = __floats2half2_rn(dl[0], dl[1]), hi = __floats2half2_rn(dl[2], dl[3]);
+			uint2 pk; pk.x = *reinterpret_cast<const uint32_t*>(&lo); pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+			*reinterpret_cast<uint2*>(dloss + (size_t)(cbase + k) * padded_width) = pk;
+		}
+		T *= __shfl_sync(0xffffffffu, incl, 31);
 		#pragma unroll
-		for (int k = 0; k < 3; ++k) dl[k] = ls * (w * g[k] * net_to_rgb_d(raw[k], c.rgb_activation) + fmaxf(0.f, l2reg * raw[k]));
-		float dot = 0.f;
-		#pragma unroll
-		for (int k = 0; k < 3; ++k) dot += g[k] * (T * rgb[k] - (rgb_ray[k] - rgb2[k]));
-		const float dmlp = net_to_density_d(raw[3], c.density_activation) * (dt * dot);
-		dl[3] = ls * dmlp + (raw[3] < 0 ? -l1reg : 0.f);
-		const __half2 lo = __floats2half2_rn(dl[0], dl[1]), hi = __floats2half2_rn(dl[2], dl[3]);
-		uint2 pk; pk.x = *reinterpret_cast<const uint32_t*>(&lo); pk.y = *reinterpret_cast<const uint32_t*>(&hi);
-		*reinterpret_cast<uint2*>(dloss + (size_t)(cbase + j) * padded_width) = pk;
+		for (int j = 0; j < 3; ++j) pre[j] = __shfl_sync(0xffffffffu, rgb2[j], 31);
 	}
+	// compaction: the ray's n Coordinates are one contiguous run of 7n floats on both sides
+	const float* src = reinterpret_cast<const float*>(cs);
+	float* dst = reinterpret_cast<float*>(coords_compacted + cbase);
+	for (uint32_t j = lane; j < n * 7; j += 32) dst[j] = src[j];
 }
 
 // fill_rollover_and_rescale (grads) + fill_rollover (coords) in one launch
@@ -129,7 +211,8 @@ __global__ void rollover_kernel(uint32_t batch, const uint32_t* __restrict__ n_i
 
 using namespace ngp;
 
-extern "C" size_t ngp_composite_workspace_bytes(uint32_t n_rays) { return ngp_scan_workspace_bytes(n_rays); }
+// workspace: [RayTmp n_rays][n_used n_rays][cbase n_rays]
+extern "C" size_t ngp_composite_workspace_bytes(uint32_t n_rays) { return (size_t)n_rays * (sizeof(RayTmp) + 8) + 256; }
 
 extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
                                    const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
@@ -139,12 +222,17 @@ extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint
 	NGP_REQUIRE(padded_width >= 4 && padded_width % 4 == 0, "padded_width must be a multiple of 4");
 	NGP_REQUIRE(n_rays > 0, "n_rays must be positive");
 	cudaStream_t s = (cudaStream_t)stream;
-	if (cudaMemsetAsync(d_scan_ws, 0, ngp_scan_workspace_bytes(n_rays), s) != cudaSuccess) { set_error("ngp_composite_train: memset failed"); return -2; }
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
-	ScanState scan{(unsigned long long*)d_scan_ws};
-	NGP_LAUNCH("composite_train_kernel", s, composite_train_kernel<<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, n_rays, max_compacted, d_ray_counter, (const float4*)d_rays_rgba, d_numsteps,
-		(const Coordinate*)d_coords, (Coordinate*)d_coords_compacted, d_compacted_counter, (const __half*)d_rgbsigma, (__half*)d_dloss, padded_width,
-		d_mean_density, rng, d_loss, scan));
+	RayTmp* tmp = (RayTmp*)d_scan_ws;
+	uint32_t* n_used = (uint32_t*)(tmp + n_rays);
+	uint32_t* cbase = n_used + n_rays;
+	const uint32_t grid = div_up(n_rays, 8);
+	NGP_LAUNCH("composite_count_kernel", s, composite_count_kernel<<<grid, 256, 0, s>>>(*cfg, n_rays, d_ray_counter, d_numsteps, (const Coordinate*)d_coords,
+		(const __half*)d_rgbsigma, tmp, n_used));
+	NGP_LAUNCH("composite_scan_kernel", s, composite_scan_kernel<<<1, 1024, 0, s>>>(n_rays, d_ray_counter, n_used, cbase, d_compacted_counter));
+	NGP_LAUNCH("composite_grad_kernel", s, composite_grad_kernel<<<grid, 256, 0, s>>>(*cfg, n_rays, max_compacted, d_ray_counter, (const float4*)d_rays_rgba, d_numsteps,
+		(const Coordinate*)d_coords, (Coordinate*)d_coords_compacted, (const __half*)d_rgbsigma, (__half*)d_dloss, padded_width, d_mean_density, rng, d_loss,
+		tmp, n_used, cbase));
 	return check_launch("composite_train");
 }
 

@@ -1,90 +1,170 @@
-// Training ray generation + two-pass occupancy march + ordered compaction, for sm_100a.
+// Training ray generation + occupancy march + ordered compaction, for sm_100a.
 // Replaces generate_training_samples_nerf (internal/sampler/occupancy_sampler.cu:310-449).
 //
-// The reference reserves output space with two global atomicAdds per ray, so its sample order changes from run to run.
-// Here each CTA scans its rays' (sample count, ray-kept flag) pair with warp shuffles and chains the CTA totals with a
-// single-pass decoupled look-back scan: bases come out in ray order, one 64-bit publish per CTA instead of 2 atomics per
-// ray, and the result is bit-reproducible (and equal to the sequential oracle).
+// The reference gives each ray ONE thread that walks the occupancy grid twice (count, then emit) and reserves output space
+// with two global atomicAdds; a training step only has ~8 k rays, so the GPU runs a few hundred divergent warps.  Here a WARP
+// owns a ray.  The key observation is that the ray parameters the reference visits all lie on one lattice
+// t_{k+1} = t_k + calc_dt(t_k) that does not depend on the grid: the occupancy only decides which lattice points are tested.
+// So the warp takes the lattice 32 points at a time, every lane evaluates its point in parallel (position, cascade, bitfield
+// bit, distance to the next voxel), and a ballot-driven resolve replays the reference's control flow exactly:
+//   * an occupied visited point emits a sample and makes the next lattice point visited;
+//   * an empty visited point at t with exit distance s makes the next visited point the first later one with t' >= t + s.
+// Per-ray counts and coordinates therefore stay bit-identical to the sequential march (same expressions, same order), but the
+// bitfield loads and the per-point arithmetic of 32 points overlap, and the resolve costs one ballot per run / per empty voxel.
+// Output bases come from a prefix sum in ray order (deterministic), not from atomics.
 #include "march.cuh"
 
 namespace ngp {
 
-__global__ void __launch_bounds__(128) generate_training_samples_kernel(
-	ngp_sampler_cfg c, ngp_camera_cfg cam, uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_coords, uint32_t n_images,
-	const float* __restrict__ xforms, const uint2* __restrict__ images, const uint8_t* __restrict__ bits, int snap, Pcg32 rng0,
-	float* __restrict__ rays_out, float4* __restrict__ rgba_out, uint32_t* __restrict__ numsteps_out, Coordinate* __restrict__ coords_out,
-	uint32_t* __restrict__ counters, uint32_t* __restrict__ per_ray_n, ScanState scan)
-{
-	const uint32_t ticket = scan_ticket(scan);
-	const uint32_t i = ticket * blockDim.x + threadIdx.x;
-	const bool active = i < n_rays;
+struct RaySetup { V3 o, d, idir; float startt, u, v; uint32_t img; };
 
-	V3 o = {0, 0, 0}, d = {0, 0, 1}, idir = {0, 0, 0};
-	float startt = 0.f, u = 0.f, v = 0.f;
-	uint32_t img = 0, n = 0;
-	if (active) {
-		img = (((n_rays_shift + i) * n_images) / n_rays) % n_images;
-		Pcg32 rng = rng0;
-		rng.advance((uint64_t)i * 8);
-		u = rng.next_float(); v = rng.next_float();
-		if (snap) {
-			u = ((float)min(max((int)(u * (float)cam.width), 0), cam.width - 1) + 0.5f) / (float)cam.width;
-			v = ((float)min(max((int)(v * (float)cam.height), 0), cam.height - 1) + 0.5f) / (float)cam.height;
-		}
-		make_ray(xforms + (size_t)img * 12, u, v, cam, o, d);
-		const float tmin = fmaxf(ray_intersect_tmin(c, o, d), c.near_distance);
-		startt = __fmaf_rn(calc_dt(tmin, c), rng.next_float(), tmin);
-		idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
-		// pass 1: count occupied steps
-		float t = startt; V3 pos;
-		while (aabb_contains(c, pos = ray_at(o, d, t)) && n < c.max_steps) {
-			const float dt = calc_dt(t, c);
-			const uint32_t mip = mip_from_dt(dt, pos, c);
-			if (grid_occupied(pos, bits, mip, c.grid_size)) { ++n; t += dt; }
-			else t = advance_to_next_voxel(t, c, pos, d, idir, c.grid_size >> mip);
-		}
-		if (per_ray_n) per_ray_n[i] = n;
+__device__ __forceinline__ RaySetup setup_ray(const ngp_sampler_cfg& c, const ngp_camera_cfg& cam, uint32_t i, uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_images,
+                                              const float* __restrict__ xforms, int snap, Pcg32 rng) {
+	RaySetup r;
+	r.img = (((n_rays_shift + i) * n_images) / n_rays) % n_images;
+	rng.advance((uint64_t)i * 8);
+	float u = rng.next_float(), v = rng.next_float();
+	if (snap) {
+		u = ((float)min(max((int)(u * (float)cam.width), 0), cam.width - 1) + 0.5f) / (float)cam.width;
+		v = ((float)min(max((int)(v * (float)cam.height), 0), cam.height - 1) + 0.5f) / (float)cam.height;
 	}
+	r.u = u; r.v = v;
+	make_ray(xforms + (size_t)r.img * 12, u, v, cam, r.o, r.d);
+	const float tmin = fmaxf(ray_intersect_tmin(c, r.o, r.d), c.near_distance);
+	r.startt = __fmaf_rn(calc_dt(tmin, c), rng.next_float(), tmin);
+	r.idir = {1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z};
+	return r;
+}
 
-	// (rays with samples, samples) packed hi/lo; exclusive prefix in ray order
-	const unsigned long long packed = ((unsigned long long)(n > 0 ? 1u : 0u) << 32) | n;
-	const unsigned long long prefix = chained_exclusive_scan(scan, ticket, packed);
-	const uint32_t base = (uint32_t)(prefix & 0xffffffffull), ray_idx = (uint32_t)(prefix >> 32);
+// Marches one ray with the whole warp; returns the number of samples (<= n_limit).  EMIT writes them to out[0..n).
+template <bool EMIT>
+__device__ __forceinline__ uint32_t march_ray(const ngp_sampler_cfg& c, const RaySetup& r, const uint8_t* __restrict__ bits, uint32_t lane, uint32_t n_limit,
+                                              Coordinate* __restrict__ out) {
+	float t_base = r.startt;
+	float skip_target = -INFINITY;       // lattice points below it are the ones the reference's do-while steps over
+	uint32_t j = 0;
+	if (n_limit == 0) return 0;
+	for (uint32_t window = 0; window < (1u << 16); ++window) {      // bound: no ray of a sane camera needs 2 M lattice points
+		// this window's 32 lattice points: lane L keeps the value after L steps
+		float t = t_base, my_t = t_base;
+		#pragma unroll
+		for (int s = 0; s < 32; ++s) { if (s == (int)lane) my_t = t; t += calc_dt(t, c); }
+		t_base = t;
+		const V3 pos = ray_at(r.o, r.d, my_t);
+		const bool inside = aabb_contains(c, pos);
+		const float dt = calc_dt(my_t, c);
+		bool occ = false;
+		float t_target = 0.f;
+		if (inside) {
+			const uint32_t mip = mip_from_dt(dt, pos, c);
+			occ = grid_occupied(pos, bits, mip, c.grid_size);
+			if (!occ) t_target = my_t + distance_to_next_voxel(pos, r.d, r.idir, c.grid_size >> mip);
+		}
+		const uint32_t inside_mask = __ballot_sync(0xffffffffu, inside);
+		const uint32_t run_mask = __ballot_sync(0xffffffffu, inside && occ);     // points that emit when visited
+		uint32_t p = 0;
+		while (p < 32) {
+			const uint32_t cand = __ballot_sync(0xffffffffu, lane >= p && !(my_t < skip_target));
+			if (!cand) break;                                      // rest of the window is skipped; the target carries over
+			const uint32_t q = (uint32_t)__ffs(cand) - 1u;
+			if (!((inside_mask >> q) & 1u)) return j;              // the ray left the box: while (contains(pos) ...) ends
+			if ((run_mask >> q) & 1u) {
+				const uint32_t rest = ~run_mask >> q;              // first later point that does not emit (bit 0 is clear)
+				const uint32_t run = rest ? (uint32_t)__ffs(rest) - 1u : 32u - q;
+				const uint32_t take = min(run, n_limit - j);
+				if (EMIT && lane >= q && lane < q + take) out[j + (lane - q)] = make_coord(pos, r.d, dt, c);
+				j += take;
+				if (j >= n_limit) return j;
+				p = q + run;
+				skip_target = -INFINITY;                           // after a sample the very next lattice point is visited
+			} else {
+				skip_target = __shfl_sync(0xffffffffu, t_target, q);
+				p = q + 1;                                         // the do-while advances at least once
+			}
+		}
+	}
+	return j;
+}
 
-	// the last ray publishes the totals (the sample counter includes dropped rays, like the reference's atomicAdd)
-	if (active && i == n_rays - 1) { counters[1] = base + n; }
-	const bool kept = active && n > 0 && (uint64_t)base + n <= n_coords;
-	// rays kept = number of kept rays; kept rays form a prefix of the rays with samples, so the count is ray_idx+1 of the last kept one
-	if (kept) atomicMax(&counters[0], ray_idx + 1);
-	if (!kept) return;
+__global__ void __launch_bounds__(256) march_count_kernel(
+	ngp_sampler_cfg c, ngp_camera_cfg cam, uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_images, const float* __restrict__ xforms,
+	const uint8_t* __restrict__ bits, int snap, Pcg32 rng, uint32_t* __restrict__ n_out, uint32_t* __restrict__ per_ray_n)
+{
+	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (i >= n_rays) return;
+	const RaySetup r = setup_ray(c, cam, i, n_rays, n_rays_shift, n_images, xforms, snap, rng);
+	const uint32_t n = march_ray<false>(c, r, bits, lane, c.max_steps, nullptr);
+	if (lane == 0) { n_out[i] = n; if (per_ray_n) per_ray_n[i] = n; }
+}
 
-	float* ro = rays_out + (size_t)ray_idx * 6;
-	ro[0] = o.x; ro[1] = o.y; ro[2] = o.z; ro[3] = d.x; ro[4] = d.y; ro[5] = d.z;
-	{
-		const int px = max(min((int)(u * (float)cam.width), cam.width - 1), 0), py = max(min((int)(v * (float)cam.height), cam.height - 1), 0);
-		const uint2 pix = __ldg(images + ((size_t)px + (size_t)py * cam.width + (size_t)img * cam.width * cam.height));
+// exclusive scan in ray order of (ray has samples, sample count); one CTA.  counters[0] = rays kept, counters[1] = samples
+// counted including dropped rays (what the reference's atomicAdd would have reached).
+__global__ void __launch_bounds__(1024) march_scan_kernel(uint32_t n_rays, uint32_t n_coords, const uint32_t* __restrict__ n_in, uint32_t* __restrict__ base_out,
+                                                          uint32_t* __restrict__ ridx_out, uint32_t* __restrict__ counters) {
+	__shared__ unsigned long long warp_tot[32];
+	__shared__ uint32_t kept_total;
+	if (threadIdx.x == 0) kept_total = 0;
+	const uint32_t per = (n_rays + 1023) / 1024, lo = min(threadIdx.x * per, n_rays), hi = min(lo + per, n_rays);
+	unsigned long long sum = 0;
+	for (uint32_t j = lo; j < hi; ++j) { const uint32_t n = n_in[j]; sum += ((unsigned long long)(n > 0) << 32) | n; }
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	unsigned long long incl = sum;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+	if (lane == 31) warp_tot[warp] = incl;
+	__syncthreads();
+	if (warp == 0) {
+		const unsigned long long w = warp_tot[lane];
+		unsigned long long wi = w;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const unsigned long long t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+		warp_tot[lane] = wi - w;
+		if (lane == 31) counters[1] = (uint32_t)wi;
+	}
+	__syncthreads();
+	unsigned long long run = warp_tot[warp] + incl - sum;
+	uint32_t kept = 0;
+	for (uint32_t j = lo; j < hi; ++j) {
+		const uint32_t n = n_in[j], base = (uint32_t)run;
+		base_out[j] = base; ridx_out[j] = (uint32_t)(run >> 32);
+		if (n > 0 && (uint64_t)base + n <= n_coords) ++kept;
+		run += ((unsigned long long)(n > 0) << 32) | n;
+	}
+	if (kept) atomicAdd(&kept_total, kept);
+	__syncthreads();
+	if (threadIdx.x == 0) counters[0] = kept_total;
+}
+
+__global__ void __launch_bounds__(256) march_emit_kernel(
+	ngp_sampler_cfg c, ngp_camera_cfg cam, uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_coords, uint32_t n_images,
+	const float* __restrict__ xforms, const uint2* __restrict__ images, const uint8_t* __restrict__ bits, int snap, Pcg32 rng,
+	const uint32_t* __restrict__ n_in, const uint32_t* __restrict__ base_in, const uint32_t* __restrict__ ridx_in,
+	float* __restrict__ rays_out, float4* __restrict__ rgba_out, uint32_t* __restrict__ numsteps_out, Coordinate* __restrict__ coords_out)
+{
+	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (i >= n_rays) return;
+	const uint32_t n = n_in[i], base = base_in[i], ray_idx = ridx_in[i];
+	if (n == 0 || (uint64_t)base + n > n_coords) return;      // no samples, or over budget: dropped like the reference does
+	const RaySetup r = setup_ray(c, cam, i, n_rays, n_rays_shift, n_images, xforms, snap, rng);
+	if (lane == 0) {
+		float* ro = rays_out + (size_t)ray_idx * 6;
+		ro[0] = r.o.x; ro[1] = r.o.y; ro[2] = r.o.z; ro[3] = r.d.x; ro[4] = r.d.y; ro[5] = r.d.z;
+		const int px = max(min((int)(r.u * (float)cam.width), cam.width - 1), 0), py = max(min((int)(r.v * (float)cam.height), cam.height - 1), 0);
+		const uint2 pix = __ldg(images + ((size_t)px + (size_t)py * cam.width + (size_t)r.img * cam.width * cam.height));
 		const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&pix.x)), ba = __half22float2(*reinterpret_cast<const __half2*>(&pix.y));
 		rgba_out[ray_idx] = make_float4(rg.x, rg.y, ba.x, ba.y);
+		numsteps_out[(size_t)ray_idx * 2 + 0] = n;
+		numsteps_out[(size_t)ray_idx * 2 + 1] = base;
 	}
-	numsteps_out[(size_t)ray_idx * 2 + 0] = n;
-	numsteps_out[(size_t)ray_idx * 2 + 1] = base;
-
-	// pass 2: emit
-	Coordinate* out = coords_out + base;
-	uint32_t j = 0; float t = startt; V3 pos;
-	while (aabb_contains(c, pos = ray_at(o, d, t)) && j < n) {
-		const float dt = calc_dt(t, c);
-		const uint32_t mip = mip_from_dt(dt, pos, c);
-		if (grid_occupied(pos, bits, mip, c.grid_size)) { out[j] = make_coord(pos, d, dt, c); ++j; t += dt; }
-		else t = advance_to_next_voxel(t, c, pos, d, idir, c.grid_size >> mip);
-	}
+	march_ray<true>(c, r, bits, lane, n, coords_out + base);
 }
 
 } // namespace ngp
 
 using namespace ngp;
 
-extern "C" size_t ngp_scan_workspace_bytes(uint32_t n) { return (size_t)(div_up(n, 128) + 2) * sizeof(unsigned long long); }
+// scratch of ngp_generate_training_samples: per ray (count, base, compacted ray index)
+extern "C" size_t ngp_scan_workspace_bytes(uint32_t n) { return (size_t)n * 12 + 256; }
 
 extern "C" int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, uint32_t n_rays, uint32_t n_rays_shift,
                                              uint32_t n_coords, uint32_t n_images, const float* d_xforms, const void* d_images, const uint8_t* d_bitfield,
@@ -93,11 +173,15 @@ extern "C" int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg
 	NGP_REQUIRE(cfg && cam && d_xforms && d_images && d_bitfield && d_rays && d_rays_rgba && d_numsteps && d_coords && d_counters && d_scan_ws, "null pointer");
 	NGP_REQUIRE(n_rays > 0 && n_images > 0, "n_rays and n_images must be positive");
 	cudaStream_t s = (cudaStream_t)stream;
-	if (cudaMemsetAsync(d_scan_ws, 0, ngp_scan_workspace_bytes(n_rays), s) != cudaSuccess) { set_error("ngp_generate_training_samples: memset failed"); return -2; }
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
-	ScanState scan{(unsigned long long*)d_scan_ws};
-	NGP_LAUNCH("generate_training_samples_kernel", s, generate_training_samples_kernel<<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_coords, n_images, d_xforms,
-		(const uint2*)d_images, d_bitfield, snap_to_pixel_centers, rng, d_rays, (float4*)d_rays_rgba, d_numsteps, (Coordinate*)d_coords,
-		d_counters, d_per_ray_n, scan));
+	uint32_t* n_tmp = (uint32_t*)d_scan_ws;
+	uint32_t* base_tmp = n_tmp + n_rays;
+	uint32_t* ridx_tmp = base_tmp + n_rays;
+	const uint32_t grid = div_up(n_rays, 8);
+	NGP_LAUNCH("march_count_kernel", s, march_count_kernel<<<grid, 256, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_images, d_xforms, d_bitfield,
+		snap_to_pixel_centers, rng, n_tmp, d_per_ray_n));
+	NGP_LAUNCH("march_scan_kernel", s, march_scan_kernel<<<1, 1024, 0, s>>>(n_rays, n_coords, n_tmp, base_tmp, ridx_tmp, d_counters));
+	NGP_LAUNCH("march_emit_kernel", s, march_emit_kernel<<<grid, 256, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_coords, n_images, d_xforms, (const uint2*)d_images,
+		d_bitfield, snap_to_pixel_centers, rng, n_tmp, base_tmp, ridx_tmp, d_rays, (float4*)d_rays_rgba, d_numsteps, (Coordinate*)d_coords));
 	return check_launch("generate_training_samples");
 }
