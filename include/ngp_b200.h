@@ -90,7 +90,8 @@ int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t stride_floats
 /* d_params: fp16 arena [NGP_MLP_PARAMS | grid table], reference order (ngp_network.h:496-541). */
 size_t ngp_network_workspace_bytes(uint32_t n);
 /* replaces NGPNetwork::inference_mixed_precision (ngp_network.h:217-284): Coordinate[n] (7 floats) -> rgbsigma [n][4] fp16.
- * d_n_valid (optional): device counter; tiles beyond it are skipped. */
+ * d_n_valid (optional): device counter; tiles beyond it are skipped.  On return the first n*64 bytes of d_workspace hold
+ * the encoded positions [n][32] fp16. */
 int ngp_network_inference(void* stream, const float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_params,
                           const ngp_grid_desc* desc, void* d_rgbsigma, void* d_workspace, size_t workspace_bytes);
 /* replaces NGPNetwork::density (ngp_network.h:286-307): positions (stride floats) -> [n][16] fp16 */
@@ -100,6 +101,12 @@ int ngp_network_density(void* stream, const float* d_positions, uint32_t stride_
  * (optional) and the fp16 gradient arena d_grads [NGP_MLP_PARAMS | grid] (overwritten, not accumulated). */
 int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
                       const void* d_dloss, void* d_rgbsigma, void* d_grads, void* d_workspace, size_t workspace_bytes);
+/* Same result as ngp_network_train, without encoding the batch again: sample i takes row d_src_index[i] of d_encoded
+ * ([m][32] fp16 -- the first m*64 bytes ngp_network_inference left in ITS workspace for the marched samples, of which the
+ * compacted batch is a subset).  The table must not have changed in between.  d_workspace must not alias d_encoded. */
+int ngp_network_train_reuse(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
+                            const void* d_dloss, void* d_rgbsigma, void* d_grads, const void* d_encoded, uint32_t n_encoded /* = m; indices are clamped to it */,
+                            const uint32_t* d_src_index, void* d_workspace, size_t workspace_bytes);
 /* the two MLPs alone on a precomputed encoding (tests, profiling): enc [n][32] fp16 */
 int ngp_mlp_inference(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, void* d_rgbsigma);
 int ngp_mlp_train(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, const void* d_dloss,
@@ -114,7 +121,7 @@ int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cfg, uint32_t
 /* update_grid (:705-735): memset current, splat max, decay max */
 int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,
                     int density_activation, float decay, float* d_grid_current, float* d_grid);
-/* update_grid_bitfield (:737-760): mean of cascade 0 -> d_mean[0], bits, max-pool */
+/* update_grid_bitfield (:737-760): mean of cascade 0 -> d_mean[0] (d_mean: 1 result + 128 floats of scratch), bits, max-pool */
 int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg, const float* d_grid, float min_optical_thickness, float* d_mean, uint8_t* d_bitfield);
 /* sample_coords_from_dataset -> generate_training_samples_nerf (:310-449).  Compaction is in ray order (deterministic).
  * d_counters: [0] rays kept, [1] samples counted (overwritten).  d_scan_ws: >= ngp_scan_workspace_bytes(n_rays) bytes of scratch. */
@@ -132,14 +139,17 @@ int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint
 
 /* ---- render ----------------------------------------------------------------------------------- */
 /* RayMarcher::volume_rendering_with_loss_and_gradient (ray_marcher.cu:15-213, 305-377), compaction in ray order.
- * d_scan_ws: >= ngp_composite_workspace_bytes(n_rays) bytes of scratch. */
+ * d_scan_ws: >= ngp_composite_workspace_bytes(n_rays) bytes of scratch.
+ * d_src_index (optional, [max_compacted]): for every compacted sample, its index in d_coords -- lets
+ * ngp_network_train_reuse pick up the encodings ngp_network_inference already computed for it. */
 size_t ngp_composite_workspace_bytes(uint32_t n_rays);
 int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
                         const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
                         uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,
-                        const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, void* d_scan_ws);
+                        const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, void* d_scan_ws, uint32_t* d_src_index);
 /* fill_rollover_and_rescale + fill_rollover (tiny-cuda-nn/common_device.h:485-505; testbed.cu:398-404) */
-int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted);
+int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted,
+                 uint32_t* d_src_index /* optional, rolled over like the coordinates */);
 /* RayMarcher::volume_rendering (ray_marcher.cu:215-295, 379-416); camera_fwd = camera matrix column 2 */
 int ngp_composite_infer(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t n_steps_offset,
                         void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,

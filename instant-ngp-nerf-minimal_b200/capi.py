@@ -54,6 +54,7 @@ SIGNATURES = {
     "ngp_network_inference": (i32, [vp, vp, u32, vp, vp, C.POINTER(GridDesc), vp, vp, sz]),
     "ngp_network_density": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, vp, sz]),
     "ngp_network_train": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, sz]),
+    "ngp_network_train_reuse": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, u32, vp, vp, sz]),
     "ngp_mlp_inference": (i32, [vp, vp, vp, u32, vp, vp]),
     "ngp_mlp_train": (i32, [vp, vp, vp, u32, vp, vp, vp, vp, vp]),
     "ngp_mark_untrained_grid": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), u32, vp, vp]),
@@ -66,8 +67,8 @@ SIGNATURES = {
     "ngp_init_rays": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), C.POINTER(f32), u32, i32, vp, vp]),
     "ngp_generate_coords_from_rays": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, u32, vp, vp, vp]),
     "ngp_composite_workspace_bytes": (sz, [u32]),
-    "ngp_composite_train": (i32, [vp, C.POINTER(RenderCfg), u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, u64, u64, vp, vp]),
-    "ngp_rollover": (i32, [vp, u32, vp, vp, u32, vp]),
+    "ngp_composite_train": (i32, [vp, C.POINTER(RenderCfg), u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, u64, u64, vp, vp, vp]),
+    "ngp_rollover": (i32, [vp, u32, vp, vp, u32, vp, vp]),
     "ngp_composite_infer": (i32, [vp, C.POINTER(RenderCfg), u32, vp, u32, u32, vp, vp, vp, vp, u32, i32, f32, f32, C.POINTER(f32), f32]),
     "ngp_compact_rays": (i32, [vp, u32, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "ngp_shade": (i32, [vp, u32, vp, vp, vp, vp, i32, i32]),

@@ -104,7 +104,8 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 	ngp_render_cfg c, uint32_t n_rays, uint32_t max_compacted, const uint32_t* __restrict__ ray_counter, const float4* __restrict__ rays_rgba,
 	uint32_t* __restrict__ numsteps_io, const Coordinate* __restrict__ coords_in, Coordinate* __restrict__ coords_compacted,
 	const __half* __restrict__ net_out, __half* __restrict__ dloss, uint32_t padded_width, const float* __restrict__ mean_density_ptr, Pcg32 rng,
-	float* __restrict__ loss_out, const RayTmp* __restrict__ tmp, const uint32_t* __restrict__ n_used_in, const uint32_t* __restrict__ cbase_in)
+	float* __restrict__ loss_out, const RayTmp* __restrict__ tmp, const uint32_t* __restrict__ n_used_in, const uint32_t* __restrict__ cbase_in,
+	uint32_t* __restrict__ src_index)
 {
 	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const uint32_t n_kept = min(*ray_counter, n_rays);
@@ -193,15 +194,19 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 	const float* src = reinterpret_cast<const float*>(cs);
 	float* dst = reinterpret_cast<float*>(coords_compacted + cbase);
 	for (uint32_t j = lane; j < n * 7; j += 32) dst[j] = src[j];
+	// where each compacted sample came from, so the training pass can reuse the encodings of the inference pass
+	if (src_index) for (uint32_t j = lane; j < n; j += 32) src_index[cbase + j] = base + j;
 }
 
 // fill_rollover_and_rescale (grads) + fill_rollover (coords) in one launch
-__global__ void rollover_kernel(uint32_t batch, const uint32_t* __restrict__ n_in_ptr, __half* __restrict__ grads, uint32_t stride, Coordinate* __restrict__ coords) {
+__global__ void rollover_kernel(uint32_t batch, const uint32_t* __restrict__ n_in_ptr, __half* __restrict__ grads, uint32_t stride, Coordinate* __restrict__ coords,
+                                uint32_t* __restrict__ src_index) {
 	const uint32_t n_in = *n_in_ptr;
 	if (n_in == 0 || n_in >= batch) return;
 	for (uint32_t i = n_in + blockIdx.x * blockDim.x + threadIdx.x; i < batch; i += gridDim.x * blockDim.x) {
 		const uint32_t src = i % n_in;
 		coords[i] = coords[src];
+		if (src_index) src_index[i] = src_index[src];
 		for (uint32_t k = 0; k < stride; ++k)
 			grads[(size_t)i * stride + k] = __float2half_rn(__half2float(grads[(size_t)src * stride + k]) * (float)n_in / (float)batch);
 	}
@@ -217,7 +222,7 @@ extern "C" size_t ngp_composite_workspace_bytes(uint32_t n_rays) { return (size_
 extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
                                    const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
                                    uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,
-                                   const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, void* d_scan_ws) {
+                                   const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, void* d_scan_ws, uint32_t* d_src_index) {
 	NGP_REQUIRE(cfg && d_ray_counter && d_rays_rgba && d_numsteps && d_coords && d_coords_compacted && d_compacted_counter && d_rgbsigma && d_dloss && d_mean_density && d_scan_ws, "null pointer");
 	NGP_REQUIRE(padded_width >= 4 && padded_width % 4 == 0, "padded_width must be a multiple of 4");
 	NGP_REQUIRE(n_rays > 0, "n_rays must be positive");
@@ -232,12 +237,12 @@ extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint
 	NGP_LAUNCH("composite_scan_kernel", s, composite_scan_kernel<<<1, 1024, 0, s>>>(n_rays, d_ray_counter, n_used, cbase, d_compacted_counter));
 	NGP_LAUNCH("composite_grad_kernel", s, composite_grad_kernel<<<grid, 256, 0, s>>>(*cfg, n_rays, max_compacted, d_ray_counter, (const float4*)d_rays_rgba, d_numsteps,
 		(const Coordinate*)d_coords, (Coordinate*)d_coords_compacted, (const __half*)d_rgbsigma, (__half*)d_dloss, padded_width, d_mean_density, rng, d_loss,
-		tmp, n_used, cbase));
+		tmp, n_used, cbase, d_src_index));
 	return check_launch("composite_train");
 }
 
-extern "C" int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted) {
+extern "C" int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted, uint32_t* d_src_index) {
 	NGP_REQUIRE(d_compacted_counter && d_dloss && d_coords_compacted, "null pointer");
-	NGP_LAUNCH("rollover_kernel", (cudaStream_t)stream, rollover_kernel<<<grid_for(batch, 256), 256, 0, (cudaStream_t)stream>>>(batch, d_compacted_counter, (__half*)d_dloss, padded_width, (Coordinate*)d_coords_compacted));
+	NGP_LAUNCH("rollover_kernel", (cudaStream_t)stream, rollover_kernel<<<grid_for(batch, 256), 256, 0, (cudaStream_t)stream>>>(batch, d_compacted_counter, (__half*)d_dloss, padded_width, (Coordinate*)d_coords_compacted, d_src_index));
 	return check_launch("rollover");
 }

@@ -115,7 +115,8 @@ __device__ __forceinline__ void relu_mask64(const uint8_t* smem, uint32_t buf, u
 template <int MODE>
 __global__ void __launch_bounds__(128) mlp_kernel(
 	const __half* __restrict__ enc, const float* __restrict__ coords, uint32_t coord_stride, uint32_t n, const uint32_t* __restrict__ n_valid,
-	const __half* __restrict__ weights, const __half* __restrict__ dloss, __half* __restrict__ out, __half* __restrict__ denc, float* __restrict__ wgrad)
+	const __half* __restrict__ weights, const __half* __restrict__ dloss, __half* __restrict__ out, __half* __restrict__ denc, float* __restrict__ wgrad,
+	float* __restrict__ wgrad_partials, const uint32_t* __restrict__ enc_rows, uint32_t n_enc_rows)
 {
 	extern __shared__ __align__(1024) uint8_t smem[];
 	constexpr uint32_t kEnd = MODE == MODE_TRAIN ? Smem::TRAIN_END : Smem::INFER_END;
@@ -154,7 +155,8 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 
 		// ---- stage the encoded positions (64 B / sample) and the SH of the direction --------------
 		{
-			const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)s * 32);
+			const uint32_t enc_row = (MODE == MODE_TRAIN && enc_rows && valid) ? min(__ldg(enc_rows + s), n_enc_rows - 1u) : s;   // reuse of the inference pass's encodings
+			const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)enc_row * 32);
 			#pragma unroll
 			for (int c = 0; c < 4; ++c) {
 				const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
@@ -310,15 +312,26 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 	}
 
 	// ---- flush the weight-gradient accumulators (M = 64: row m sits in TMEM lane 32*(m/16) + m%16) ------
+	// wgrad_partials != nullptr: this CTA owns one [NGP_MLP_PARAMS] fp32 slot and stores plainly (a small second kernel sums
+	// the slots in a fixed order); otherwise fp32 atomics into wgrad (the stand-alone ngp_mlp_train entry point).
 	if (MODE == MODE_TRAIN && wg_acc) {
 		fence_after_sync();
 		const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, m = warp * 16 + lane;
 		float v[64];
-		read_row<2>(tm, kTmemW0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kW0 + m * 32 + k, v[k]);
-		read_row<1>(tm, kTmemW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kW1 + o * 64 + m, v[o]);
-		read_row<2>(tm, kTmemV0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kV0 + m * 32 + k, v[k]);
-		read_row<4>(tm, kTmemV1, v);      if (lane < 16) for (int k = 0; k < 64; ++k) atomicAdd(wgrad + kV1 + m * 64 + k, v[k]);
-		read_row<1>(tm, kTmemV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kV2 + o * 64 + m, v[o]);
+		if (wgrad_partials) {
+			float* slot = wgrad_partials + (size_t)blockIdx.x * NGP_MLP_PARAMS;
+			read_row<2>(tm, kTmemW0, v);      if (lane < 16) for (int k = 0; k < 32; k += 4) *reinterpret_cast<float4*>(slot + kW0 + m * 32 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+			read_row<1>(tm, kTmemW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) slot[kW1 + o * 64 + m] = v[o];
+			read_row<2>(tm, kTmemV0, v);      if (lane < 16) for (int k = 0; k < 32; k += 4) *reinterpret_cast<float4*>(slot + kV0 + m * 32 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+			read_row<4>(tm, kTmemV1, v);      if (lane < 16) for (int k = 0; k < 64; k += 4) *reinterpret_cast<float4*>(slot + kV1 + m * 64 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+			read_row<1>(tm, kTmemV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) slot[kV2 + o * 64 + m] = v[o];
+		} else {
+			read_row<2>(tm, kTmemW0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kW0 + m * 32 + k, v[k]);
+			read_row<1>(tm, kTmemW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kW1 + o * 64 + m, v[o]);
+			read_row<2>(tm, kTmemV0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kV0 + m * 32 + k, v[k]);
+			read_row<4>(tm, kTmemV1, v);      if (lane < 16) for (int k = 0; k < 64; ++k) atomicAdd(wgrad + kV1 + m * 64 + k, v[k]);
+			read_row<1>(tm, kTmemV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kV2 + o * 64 + m, v[o]);
+		}
 	}
 	fence_before_sync();
 	__syncthreads();
@@ -336,14 +349,19 @@ namespace ngp {
 int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const uint32_t* d_n_valid,
                             const void* d_table, const ngp_grid_desc* desc, void* d_out, uint32_t out_stride);
 
-__global__ void wgrad_to_half_kernel(const float* __restrict__ w32, __half* __restrict__ w16, uint32_t n) {
+// sums the per-CTA weight-gradient slots in CTA order (deterministic) and rounds to the fp16 gradient arena
+__global__ void wgrad_reduce_kernel(const float* __restrict__ partials, uint32_t n_slots, __half* __restrict__ w16, uint32_t n) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i < n) w16[i] = __float2half_rn(w32[i]);
+	if (i >= n) return;
+	float s = 0.f;
+	for (uint32_t c = 0; c < n_slots; ++c) s += partials[(size_t)c * n + i];
+	w16[i] = __float2half_rn(s);
 }
 
 template <int MODE>
 static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords, uint32_t coord_stride, uint32_t n, const uint32_t* n_valid,
-                      const void* weights, const void* dloss, void* out, void* denc, float* wgrad) {
+                      const void* weights, const void* dloss, void* out, void* denc, float* wgrad, float* wgrad_partials = nullptr, uint32_t* grid_out = nullptr,
+                      const uint32_t* enc_rows = nullptr, uint32_t n_enc_rows = 0) {
 	constexpr uint32_t smem = (MODE == MODE_TRAIN ? Smem::TRAIN_END : Smem::INFER_END) + Smem::CTRL;
 	constexpr uint32_t ctas_per_sm = MODE == MODE_TRAIN ? 2 : 3;
 	static bool configured = false;
@@ -356,7 +374,8 @@ static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords,
 	const uint32_t n_tiles = div_up(n, 128);
 	const uint32_t grid = n_tiles < kNumSMs * ctas_per_sm ? n_tiles : kNumSMs * ctas_per_sm;
 	NGP_LAUNCH("mlp_kernel", stream, mlp_kernel<MODE><<<grid, 128, smem, stream>>>((const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
-		(const __half*)dloss, (__half*)out, (__half*)denc, wgrad));
+		(const __half*)dloss, (__half*)out, (__half*)denc, wgrad, wgrad_partials, enc_rows, n_enc_rows));
+	if (grid_out) *grid_out = grid;
 	return check_launch("mlp_kernel");
 }
 } // namespace ngp
@@ -374,10 +393,11 @@ extern "C" int ngp_mlp_train(void* stream, const void* d_enc, const float* d_coo
 	return launch_mlp<MODE_TRAIN>((cudaStream_t)stream, d_enc, d_coords, 7, n, nullptr, d_mlp_params, d_dloss, d_rgbsigma, d_denc, d_wgrad_f32);
 }
 
-// workspace: [enc n*32 halfs][denc n*32 halfs][wgrad 10240 floats]
+// workspace: [enc n*32 halfs][denc n*32 halfs][per-CTA weight-gradient slots, kMaxTrainCtas x 10240 floats]
+constexpr uint32_t kMaxTrainCtas = kNumSMs * 2;
 extern "C" size_t ngp_network_workspace_bytes(uint32_t n) {
 	const size_t n_pad = ((size_t)n + 127) / 128 * 128;
-	return n_pad * 32 * 2 * 2 + NGP_MLP_PARAMS * sizeof(float) + 256;
+	return n_pad * 32 * 2 * 2 + (size_t)kMaxTrainCtas * NGP_MLP_PARAMS * sizeof(float) + 256;
 }
 
 extern "C" int ngp_network_inference(void* stream, const float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_params,
@@ -406,8 +426,8 @@ extern "C" int ngp_network_density(void* stream, const float* d_positions, uint3
 	return launch_mlp<MODE_DENSITY>(s, d_workspace, nullptr, 0, n, nullptr, params, nullptr, d_out, nullptr, nullptr);
 }
 
-extern "C" int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
-                                 const void* d_dloss, void* d_rgbsigma, void* d_grads, void* d_workspace, size_t workspace_bytes) {
+static int network_train_impl(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc, const void* d_dloss,
+                              void* d_rgbsigma, void* d_grads, const void* d_encoded, uint32_t n_encoded, const uint32_t* d_src_index, void* d_workspace, size_t workspace_bytes) {
 	NGP_REQUIRE(d_coords && d_params && desc && d_dloss && d_grads && d_workspace, "null pointer");
 	NGP_REQUIRE(desc->n_levels == 16, "the fused network expects 16 levels x 2 features = 32 encoded dims");
 	NGP_REQUIRE(workspace_bytes >= ngp_network_workspace_bytes(n), "workspace too small");
@@ -417,12 +437,27 @@ extern "C" int ngp_network_train(void* stream, const float* d_coords, uint32_t n
 	const size_t n_pad = ((size_t)n + 127) / 128 * 128;
 	__half* enc = (__half*)d_workspace;
 	__half* denc = enc + n_pad * 32;
-	float* wgrad = (float*)(denc + n_pad * 32);
-	if (cudaMemsetAsync(wgrad, 0, NGP_MLP_PARAMS * sizeof(float), s) != cudaSuccess) { set_error("ngp_network_train: memset failed"); return -2; }
-	int rc = hash_encode_fwd_counted(s, d_coords, 7, n, nullptr, params + NGP_MLP_PARAMS, desc, enc, 32);
+	float* wgrad_slots = (float*)(denc + n_pad * 32);
+	int rc = 0;
+	if (!d_encoded) rc = hash_encode_fwd_counted(s, d_coords, 7, n, nullptr, params + NGP_MLP_PARAMS, desc, enc, 32);
 	if (rc) return rc;
-	rc = launch_mlp<MODE_TRAIN>(s, enc, d_coords, 7, n, nullptr, params, d_dloss, d_rgbsigma, denc, wgrad);
+	uint32_t n_slots = 0;
+	rc = launch_mlp<MODE_TRAIN>(s, d_encoded ? d_encoded : enc, d_coords, 7, n, nullptr, params, d_dloss, d_rgbsigma, denc, nullptr, wgrad_slots, &n_slots, d_src_index, n_encoded);
 	if (rc) return rc;
-	NGP_LAUNCH("wgrad_to_half_kernel", s, wgrad_to_half_kernel<<<div_up(NGP_MLP_PARAMS, 256), 256, 0, s>>>(wgrad, (__half*)d_grads, NGP_MLP_PARAMS));
+	NGP_LAUNCH("wgrad_reduce_kernel", s, wgrad_reduce_kernel<<<div_up(NGP_MLP_PARAMS, 128), 128, 0, s>>>(wgrad_slots, n_slots, (__half*)d_grads, NGP_MLP_PARAMS));
 	return ngp_hash_encode_bwd(stream, d_coords, 7, n, denc, 32, desc, (__half*)d_grads + NGP_MLP_PARAMS, 1);
+}
+
+extern "C" int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
+                                 const void* d_dloss, void* d_rgbsigma, void* d_grads, void* d_workspace, size_t workspace_bytes) {
+	return network_train_impl(stream, d_coords, n, d_params, desc, d_dloss, d_rgbsigma, d_grads, nullptr, 0, nullptr, d_workspace, workspace_bytes);
+}
+
+extern "C" int ngp_network_train_reuse(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
+                                       const void* d_dloss, void* d_rgbsigma, void* d_grads, const void* d_encoded, uint32_t n_encoded, const uint32_t* d_src_index,
+                                       void* d_workspace, size_t workspace_bytes) {
+	NGP_REQUIRE(d_encoded && d_src_index, "null pointer");
+	NGP_REQUIRE(n_encoded > 0, "n_encoded must be positive");
+	NGP_REQUIRE(d_encoded != d_workspace, "the training workspace must not alias the encodings it reads");
+	return network_train_impl(stream, d_coords, n, d_params, desc, d_dloss, d_rgbsigma, d_grads, d_encoded, n_encoded, d_src_index, d_workspace, workspace_bytes);
 }

@@ -24,10 +24,31 @@ __global__ void init_grid_kernel(uint64_t n, uint64_t n_threads, uint64_t total_
 	}
 }
 
-struct AdamHyper { float lr, beta1, beta2, eps, l2_reg, loss_scale, ema_decay, deb_old, deb_new; };
+struct AdamHyper {
+	float lr, beta1, beta2, eps, l2_reg, loss_scale, ema_decay, deb_old, deb_new;
+	float inv_loss_scale;                   // exact reciprocal when loss_scale is a power of two, else 0 (then the kernel divides)
+	float l2b1_hi, l2b1_lo, l2b2_hi, l2b2_lo; // log2(beta) as an unevaluated fp32 sum, for beta^steps = exp2(steps * log2 beta)
+};
 
-__device__ __forceinline__ void adam_one(const AdamHyper& h, bool matrix, float gh, float& w, float& m1, float& m2, uint32_t& steps, __half& w16, bool& touched) {
-	float g = gh / h.loss_scale;
+// beta^c for an integer-valued c: the product c*log2(beta) is formed to ~48 bits (exact head product via fma, plus the
+// tail), so the result is as accurate as powf (a few ulp) at a tenth of its instruction count.
+__device__ __forceinline__ float pow_steps(float c, float hi, float lo) {
+	const float p = c * hi;
+	const float e = __fmaf_rn(c, hi, -p) + c * lo;
+	const float r = exp2f(p);
+	return __fmaf_rn(r, e * 0.693147180559945f, r);
+}
+
+// lr * sqrt(1 - beta2^cs) / (1 - beta1^cs): the per-parameter bias correction of adam.h:85-90
+__device__ __forceinline__ float bias_corrected_lr(const AdamHyper& h, uint32_t cs) {
+	const float c = (float)cs;
+	return h.lr * (sqrtf(1 - pow_steps(c, h.l2b2_hi, h.l2b2_lo)) / (1 - pow_steps(c, h.l2b1_hi, h.l2b1_lo)));
+}
+
+// cached_steps / cached_lr: neighbouring parameters usually share their step count, so the correction is computed once per run
+__device__ __forceinline__ void adam_one(const AdamHyper& h, bool matrix, float gh, float& w, float& m1, float& m2, uint32_t& steps, __half& w16, bool& touched,
+                                         uint32_t& cached_steps, float& cached_lr) {
+	float g = h.inv_loss_scale != 0.f ? gh * h.inv_loss_scale : gh / h.loss_scale;
 	touched = matrix || g != 0.f;
 	if (!touched) return;
 	if (matrix) g += h.l2_reg * w;
@@ -35,57 +56,74 @@ __device__ __forceinline__ void adam_one(const AdamHyper& h, bool matrix, float 
 	m1 = h.beta1 * m1 + (1 - h.beta1) * g;
 	m2 = h.beta2 * m2 + (1 - h.beta2) * gsq;
 	const uint32_t cs = ++steps;
-	const float lr = h.lr * (sqrtf(1 - powf(h.beta2, (float)cs)) / (1 - powf(h.beta1, (float)cs)));
+	if (cs != cached_steps) { cached_steps = cs; cached_lr = bias_corrected_lr(h, cs); }
+	const float lr = cached_lr;
 	const float eff = fminf(fmaxf(lr / (sqrtf(m2) + h.eps), 0.f), 3.402823466e38f);
 	w = w - eff * m1;
 	w16 = __float2half_rn(w);
 }
 
-// 4 parameters per thread (n is padded up by the caller's allocation to a multiple of 4 only logically: the tail is scalar)
+__device__ __forceinline__ void unpack8(const uint4& p, float* f) {
+	const uint32_t w[4] = {p.x, p.y, p.z, p.w};
+	#pragma unroll
+	for (int i = 0; i < 4; ++i) { const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&w[i])); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+	uint32_t w[4];
+	#pragma unroll
+	for (int i = 0; i < 4; ++i) { const __half2 h = __floats2half2_rn(f[2 * i], f[2 * i + 1]); w[i] = *reinterpret_cast<const uint32_t*>(&h); }
+	return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// 8 parameters per thread: three 16-byte loads (gradient, fp16 weight, EMA) are issued together; the 64 bytes of fp32
+// state are only touched when one of the 8 gradients is non-zero (or the group belongs to the MLP matrices).
 __global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t n, uint64_t n_matrix, AdamHyper h, float* __restrict__ w32, __half* __restrict__ w16,
                                                         const __half* __restrict__ g16, float* __restrict__ m1, float* __restrict__ m2,
                                                         uint32_t* __restrict__ steps, __half* __restrict__ ema16) {
-	const uint64_t n4 = n / 4;
-	for (uint64_t q = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < n4; q += (uint64_t)gridDim.x * blockDim.x) {
-		const uint64_t i = q * 4;
-		const uint2 gp = reinterpret_cast<const uint2*>(g16)[q];
-		uint2 wp = reinterpret_cast<const uint2*>(w16)[q];
-		const uint2 ep = reinterpret_cast<const uint2*>(ema16)[q];
-		float gh[4]; __half wh[4]; float eh[4];
-		{
-			const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&gp.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&gp.y));
-			gh[0] = a.x; gh[1] = a.y; gh[2] = b.x; gh[3] = b.y;
-			const __half2 w0 = *reinterpret_cast<const __half2*>(&wp.x), w1 = *reinterpret_cast<const __half2*>(&wp.y);
-			wh[0] = __low2half(w0); wh[1] = __high2half(w0); wh[2] = __low2half(w1); wh[3] = __high2half(w1);
-			const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&ep.x)), d = __half22float2(*reinterpret_cast<const __half2*>(&ep.y));
-			eh[0] = c.x; eh[1] = c.y; eh[2] = d.x; eh[3] = d.y;
-		}
-		const bool any_matrix = i < n_matrix;
-		const bool any = any_matrix || gh[0] != 0.f || gh[1] != 0.f || gh[2] != 0.f || gh[3] != 0.f;
+	const uint64_t n8 = n / 8;
+	for (uint64_t q = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < n8; q += (uint64_t)gridDim.x * blockDim.x) {
+		const uint64_t i = q * 8;
+		const uint4 gp = __ldg(reinterpret_cast<const uint4*>(g16) + q);
+		const uint4 wp = reinterpret_cast<const uint4*>(w16)[q];
+		const uint4 ep = reinterpret_cast<const uint4*>(ema16)[q];
+		const bool any = i < n_matrix || ((gp.x | gp.y | gp.z | gp.w) & 0x7fff7fffu) != 0u;      // any gradient that is not +-0
+		float wh[8];
+		unpack8(wp, wh);
 		if (any) {
-			float4 w = reinterpret_cast<float4*>(w32)[q], a = reinterpret_cast<float4*>(m1)[q], b = reinterpret_cast<float4*>(m2)[q];
-			uint4 s = reinterpret_cast<uint4*>(steps)[q];
-			float* wv = &w.x; float* av = &a.x; float* bv = &b.x; uint32_t* sv = &s.x;
+			float gh[8];
+			unpack8(gp, gh);
+			float4 w[2], a[2], b[2]; uint4 st[2];
 			#pragma unroll
-			for (int k = 0; k < 4; ++k) { bool t; adam_one(h, i + k < n_matrix, gh[k], wv[k], av[k], bv[k], sv[k], wh[k], t); }
-			reinterpret_cast<float4*>(w32)[q] = w; reinterpret_cast<float4*>(m1)[q] = a; reinterpret_cast<float4*>(m2)[q] = b;
-			reinterpret_cast<uint4*>(steps)[q] = s;
-			const __half2 w0 = __halves2half2(wh[0], wh[1]), w1 = __halves2half2(wh[2], wh[3]);
-			wp.x = *reinterpret_cast<const uint32_t*>(&w0); wp.y = *reinterpret_cast<const uint32_t*>(&w1);
-			reinterpret_cast<uint2*>(w16)[q] = wp;
+			for (int v = 0; v < 2; ++v) {
+				w[v] = reinterpret_cast<const float4*>(w32)[q * 2 + v]; a[v] = reinterpret_cast<const float4*>(m1)[q * 2 + v];
+				b[v] = reinterpret_cast<const float4*>(m2)[q * 2 + v]; st[v] = reinterpret_cast<const uint4*>(steps)[q * 2 + v];
+			}
+			float* wv = &w[0].x; float* av = &a[0].x; float* bv = &b[0].x; uint32_t* sv = &st[0].x;
+			uint32_t cached_steps = 0; float cached_lr = 0.f;
+			#pragma unroll
+			for (int k = 0; k < 8; ++k) {
+				bool t; __half nh = __float2half_rn(wh[k]);
+				adam_one(h, i + k < n_matrix, gh[k], wv[k], av[k], bv[k], sv[k], nh, t, cached_steps, cached_lr);
+				if (t) wh[k] = __half2float(nh);
+			}
+			#pragma unroll
+			for (int v = 0; v < 2; ++v) {
+				reinterpret_cast<float4*>(w32)[q * 2 + v] = w[v]; reinterpret_cast<float4*>(m1)[q * 2 + v] = a[v];
+				reinterpret_cast<float4*>(m2)[q * 2 + v] = b[v]; reinterpret_cast<uint4*>(steps)[q * 2 + v] = st[v];
+			}
+			reinterpret_cast<uint4*>(w16)[q] = pack8(wh);
 		}
-		float e[4];
+		float eh[8], e[8];
+		unpack8(ep, eh);
 		#pragma unroll
-		for (int k = 0; k < 4; ++k) e[k] = (eh[k] * h.ema_decay * h.deb_old + __half2float(wh[k]) * (1 - h.ema_decay)) * h.deb_new;
-		const __half2 e0 = __floats2half2_rn(e[0], e[1]), e1 = __floats2half2_rn(e[2], e[3]);
-		uint2 eo; eo.x = *reinterpret_cast<const uint32_t*>(&e0); eo.y = *reinterpret_cast<const uint32_t*>(&e1);
-		reinterpret_cast<uint2*>(ema16)[q] = eo;
+		for (int k = 0; k < 8; ++k) e[k] = (eh[k] * h.ema_decay * h.deb_old + wh[k] * (1 - h.ema_decay)) * h.deb_new;
+		reinterpret_cast<uint4*>(ema16)[q] = pack8(e);
 	}
 	// scalar tail
-	if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
-		const uint64_t i = n4 * 4 + threadIdx.x;
-		__half wh = w16[i]; bool t;
-		adam_one(h, i < n_matrix, __half2float(g16[i]), w32[i], m1[i], m2[i], steps[i], wh, t);
+	if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+		const uint64_t i = n8 * 8 + threadIdx.x;
+		__half wh = w16[i]; bool t; uint32_t cs = 0; float clr = 0.f;
+		adam_one(h, i < n_matrix, __half2float(g16[i]), w32[i], m1[i], m2[i], steps[i], wh, t, cs, clr);
 		w16[i] = wh;
 		ema16[i] = __float2half_rn((__half2float(ema16[i]) * h.ema_decay * h.deb_old + __half2float(wh) * (1 - h.ema_decay)) * h.deb_new);
 	}
@@ -123,15 +161,27 @@ extern "C" int ngp_init_params(void* stream, uint64_t* rng_state, uint64_t rng_i
 extern "C" int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, uint64_t n_params, uint64_t n_matrix_params, uint32_t step, float learning_rate,
                                   float* d_w32, void* d_w16, const void* d_g16, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16) {
 	NGP_REQUIRE(cfg && d_w32 && d_w16 && d_g16 && d_m1 && d_m2 && d_param_steps && d_ema16, "null pointer");
-	NGP_REQUIRE(n_matrix_params % 4 == 0, "n_matrix_params must be a multiple of 4");
+	NGP_REQUIRE(n_matrix_params % 8 == 0, "n_matrix_params must be a multiple of 8");
 	if (n_params == 0) return 0;
 	const uint32_t new_step = step + 1;
 	AdamHyper h;
 	h.lr = learning_rate; h.beta1 = cfg->beta1; h.beta2 = cfg->beta2; h.eps = cfg->epsilon; h.l2_reg = cfg->l2_reg; h.loss_scale = cfg->loss_scale;
 	h.ema_decay = cfg->ema_decay;
+	{
+		int ex = 0;
+		const bool pow2 = cfg->loss_scale > 0.f && std::isfinite(cfg->loss_scale) && std::frexp(cfg->loss_scale, &ex) == 0.5f && ex > -120 && ex < 120;
+		h.inv_loss_scale = pow2 ? 1.0f / cfg->loss_scale : 0.f;
+		auto split = [](float beta, float& hi, float& lo) {
+			if (!(beta > 0.f)) { hi = -1e20f; lo = 0.f; return; }       // beta^cs == 0 for cs >= 1
+			const double l = std::log2((double)beta);
+			hi = (float)l; lo = (float)(l - (double)hi);
+		};
+		split(cfg->beta1, h.l2b1_hi, h.l2b1_lo);
+		split(cfg->beta2, h.l2b2_hi, h.l2b2_lo);
+	}
 	h.deb_old = 1 - (float)std::pow(cfg->ema_decay, new_step - 1);
 	h.deb_new = 1.0f / (1 - (float)std::pow(cfg->ema_decay, new_step));
-	NGP_LAUNCH("adam_ema_kernel", (cudaStream_t)stream, adam_ema_kernel<<<grid_for(n_params / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
+	NGP_LAUNCH("adam_ema_kernel", (cudaStream_t)stream, adam_ema_kernel<<<grid_for(n_params / 8 + 1, 256, 6), 256, 0, (cudaStream_t)stream>>>(n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
 		d_m1, d_m2, d_param_steps, (__half*)d_ema16));
 	return check_launch("optimizer_step");
 }

@@ -80,16 +80,25 @@ __global__ void ema_grid_kernel(uint32_t n, const float* __restrict__ cur, float
 	}
 }
 
-// mean over cascade 0 of max(v,0)/cells.  ONE CTA, fixed order tree => run-to-run deterministic (the reference's
-// float-atomic reduce_sum is not).  2 M floats = 8 MB from L2: a few microseconds, once per train() call.
-__global__ void __launch_bounds__(1024) grid_mean_kernel(const float* __restrict__ grid, uint32_t cells, float* __restrict__ mean_out) {
-	__shared__ float sh[1024];
-	float s = 0.f;
+// mean over cascade 0 of max(v,0)/cells in two fixed-shape stages (128 CTAs of contiguous slices, then one tree over the
+// partials): run-to-run deterministic, unlike the reference's float-atomic reduce_sum.
+constexpr uint32_t kMeanParts = 128;
+__global__ void __launch_bounds__(256) grid_mean_partial_kernel(const float* __restrict__ grid, uint32_t cells, float* __restrict__ partials) {
+	__shared__ float sh[256];
+	const uint32_t per = (cells + kMeanParts - 1) / kMeanParts, lo = blockIdx.x * per, hi = min(lo + per, cells);
 	const float inv = (float)cells;
-	for (uint32_t i = threadIdx.x; i < cells; i += 1024) s += fmaxf(grid[i], 0.f) / inv;
+	float s = 0.f;
+	for (uint32_t i = lo + threadIdx.x; i < hi; i += 256) s += fmaxf(grid[i], 0.f) / inv;
 	sh[threadIdx.x] = s;
 	__syncthreads();
-	for (int o = 512; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+	for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+	if (threadIdx.x == 0) partials[blockIdx.x] = sh[0];
+}
+__global__ void __launch_bounds__(kMeanParts) grid_mean_final_kernel(const float* __restrict__ partials, float* __restrict__ mean_out) {
+	__shared__ float sh[kMeanParts];
+	sh[threadIdx.x] = partials[threadIdx.x];
+	__syncthreads();
+	for (int o = kMeanParts / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
 	if (threadIdx.x == 0) *mean_out = sh[0];
 }
 
@@ -151,7 +160,8 @@ extern "C" int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg
 	const uint32_t G = cfg->grid_size, cells = G * G * G;
 	NGP_REQUIRE(cells % 64 == 0, "grid_size^3 must be a multiple of 64");
 	cudaStream_t s = (cudaStream_t)stream;
-	NGP_LAUNCH("grid_mean_kernel", s, grid_mean_kernel<<<1, 1024, 0, s>>>(d_grid, cells, d_mean));
+	NGP_LAUNCH("grid_mean_partial_kernel", s, grid_mean_partial_kernel<<<kMeanParts, 256, 0, s>>>(d_grid, cells, d_mean + 1));
+	NGP_LAUNCH("grid_mean_final_kernel", s, grid_mean_final_kernel<<<1, kMeanParts, 0, s>>>(d_mean + 1, d_mean));
 	const uint32_t n_bytes = cells * cfg->n_cascades / 8;
 	NGP_LAUNCH("grid_to_bitfield_kernel", s, grid_to_bitfield_kernel<<<grid_for(n_bytes, 256), 256, 0, s>>>(n_bytes, d_grid, d_bitfield, d_mean, min_optical_thickness));
 	for (uint32_t level = 1; level < cfg->n_cascades; ++level)

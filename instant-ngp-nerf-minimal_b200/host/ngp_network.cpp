@@ -54,10 +54,17 @@ void NGPNetwork::density(cudaStream_t stream, const float* positions, uint32_t s
 
 void NGPNetwork::forward(cudaStream_t, const Coordinate*, uint32_t, precision_t* output) { m_forward_output = output; }
 
-void NGPNetwork::backward(cudaStream_t stream, const Coordinate* input, uint32_t n, const precision_t* output, const precision_t* dL_doutput) {
-	ensure_workspace(n);
+void NGPNetwork::backward(cudaStream_t stream, const Coordinate* input, uint32_t n, const precision_t* output, const precision_t* dL_doutput,
+                          const uint32_t* src_index, uint32_t n_encoded) {
 	precision_t* out = m_forward_output == output ? m_forward_output : nullptr;
-	api_check(ngp_network_train(stream, (const float*)input, n, m_params, &m_grid, dL_doutput, out, m_gradients, m_workspace.data(), m_workspace.get_bytes()));
+	m_train_workspace.enlarge(ngp_network_workspace_bytes(n));
+	if (src_index) {
+		// the batch is a subset of the samples inference_mixed_precision just encoded into m_workspace: gather instead of re-encoding
+		api_check(ngp_network_train_reuse(stream, (const float*)input, n, m_params, &m_grid, dL_doutput, out, m_gradients, m_workspace.data(), n_encoded, src_index,
+		                                  m_train_workspace.data(), m_train_workspace.get_bytes()));
+	} else {
+		api_check(ngp_network_train(stream, (const float*)input, n, m_params, &m_grid, dL_doutput, out, m_gradients, m_train_workspace.data(), m_train_workspace.get_bytes()));
+	}
 	m_forward_output = nullptr;
 }
 

@@ -21,7 +21,10 @@ public:
 	// ngp_network.h:325-398 / 400-494.  forward() only notes its arguments: the fused kernel recomputes the activations in
 	// shared memory during backward() instead of storing them in HBM, and writes `output` there.
 	void forward(cudaStream_t stream, const Coordinate* input, uint32_t n, precision_t* output);
-	void backward(cudaStream_t stream, const Coordinate* input, uint32_t n, const precision_t* output, const precision_t* dL_doutput);
+	// src_index (optional): row of the last inference_mixed_precision() batch (n_encoded rows) each input came from; the encodings
+	// computed there are then gathered instead of recomputed (same values: the table has not changed in between).
+	void backward(cudaStream_t stream, const Coordinate* input, uint32_t n, const precision_t* output, const precision_t* dL_doutput,
+	              const uint32_t* src_index = nullptr, uint32_t n_encoded = 0);
 
 	size_t n_params() const { return (size_t)NGP_MLP_PARAMS + (size_t)m_n_grid_entries * 2; }
 	size_t n_matrix_params() const { return NGP_MLP_PARAMS; }
@@ -38,7 +41,8 @@ private:
 	precision_t* m_params = nullptr;
 	precision_t* m_inference_params = nullptr;
 	precision_t* m_gradients = nullptr;
-	DeviceBuffer<uint8_t> m_workspace;
+	DeviceBuffer<uint8_t> m_workspace;          // inference / density scratch; starts with the encodings of the last batch
+	DeviceBuffer<uint8_t> m_train_workspace;    // backward() scratch, separate so it can read m_workspace's encodings
 	precision_t* m_forward_output = nullptr;
 };
 

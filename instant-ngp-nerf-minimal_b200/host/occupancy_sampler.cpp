@@ -16,7 +16,7 @@ OccupancySampler::OccupancySampler(const Json& config) {
 	ema_decay = config.value("ema_decay", 0.95f);
 	density_grid_current.resize(n_total_elements);
 	density_grid.resize(n_total_elements);
-	density_grid_mean.resize(16);
+	density_grid_mean.resize(256);
 	density_grid_bitfield.resize(n_total_elements / 8);
 	density_grid_current.memset(0); density_grid.memset(0); density_grid_mean.memset(0); density_grid_bitfield.memset(0);
 	n_max_steps = (uint32_t)config.value("maximum_marching_steps", 1024);

@@ -16,7 +16,7 @@ void RayMarcher::volume_rendering_with_loss_and_gradient(
 	EActivation rgb_activation, EActivation density_activation,
 	float* loss_output, ELossType loss_type, float loss_scale,
 	const BoundingBox&, uint32_t n_cascades, float min_cone_stepsize, const DeviceBuffer<float>& density_grid_mean, float min_optical_thickness,
-	const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream)
+	const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream, uint32_t* compacted_src_index)
 {
 	ngp_render_cfg c;
 	c.n_cascades = n_cascades; c.min_step = min_cone_stepsize;
@@ -28,7 +28,7 @@ void RayMarcher::volume_rendering_with_loss_and_gradient(
 	m_scan_ws.enlarge(ngp_composite_workspace_bytes(n_rays));
 	api_check(ngp_composite_train(stream, &c, n_rays, n_max_compacted_coords, n_rays_counter, rays_rgba.data(), ray_coord_indices.data(),
 	                              (const float*)coords.data(), (float*)compacted_coords.data(), n_compacted_coords_counter, network_output.data(),
-	                              dloss_doutput.data(), (uint32_t)padded_output_width, density_grid_mean.data(), rng.state, rng.inc, loss_output, m_scan_ws.data()));
+	                              dloss_doutput.data(), (uint32_t)padded_output_width, density_grid_mean.data(), rng.state, rng.inc, loss_output, m_scan_ws.data(), compacted_src_index));
 }
 
 void RayMarcher::volume_rendering(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t i_steps_offset, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,

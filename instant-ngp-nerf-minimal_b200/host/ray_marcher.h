@@ -25,7 +25,7 @@ public:
 		EActivation rgb_activation, EActivation density_activation,
 		float* loss_output, ELossType loss_type, float loss_scale,
 		const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const DeviceBuffer<float>& density_grid_mean, float min_optical_thickness,
-		const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream);
+		const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream, uint32_t* compacted_src_index = nullptr);
 
 	// ray_marcher.cu:379-416
 	void volume_rendering(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t i_steps_offset, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,

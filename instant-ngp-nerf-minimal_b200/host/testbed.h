@@ -88,6 +88,7 @@ public:
 		DeviceBuffer<float> rays_rgba;
 		DeviceBuffer<uint32_t> ray_coord_indices;
 		DeviceBuffer<Coordinate> coords, coords_compacted;
+		DeviceBuffer<uint32_t> compacted_src_index;   // marched-sample index of every compacted sample
 		DeviceBuffer<precision_t> rgbsigma, dloss_drgbsigma;
 		DeviceBuffer<uint32_t> n_coords_counter;            // [n_steps][2]: rays kept, samples counted
 		DeviceBuffer<uint32_t> n_compacted_coords_counter;  // [n_steps]

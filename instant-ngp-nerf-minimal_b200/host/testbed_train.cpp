@@ -93,6 +93,7 @@ void Testbed::train_nerf_step(uint32_t target_batch_size, uint32_t n_rays_per_ba
 	tb.ray_coord_indices.enlarge((size_t)n_rays_per_batch * 2);
 	tb.coords.enlarge(max_samples);
 	tb.coords_compacted.enlarge(target_batch_size);
+	tb.compacted_src_index.enlarge(target_batch_size);
 	tb.rgbsigma.enlarge((size_t)max_samples * padded_output_width);
 	tb.dloss_drgbsigma.enlarge((size_t)target_batch_size * padded_output_width);
 
@@ -116,12 +117,15 @@ void Testbed::train_nerf_step(uint32_t target_batch_size, uint32_t n_rays_per_ba
 		n_rays_per_batch, target_batch_size, tb.rays, tb.rays_rgba, counters, tb.ray_coord_indices, tb.coords, tb.coords_compacted, compacted_counter,
 		tb.rgbsigma, tb.dloss_drgbsigma, (int)padded_output_width, m_rgb_activation, m_density_activation, loss, m_loss_type, LOSS_SCALE / (float)m_dp_world,
 		m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, m_sampler->density_grid_mean, m_sampler->min_optical_thickness,
-		m_background_color, m_color_space, m_rng, stream);
+		m_background_color, m_color_space, m_rng, stream, tb.compacted_src_index.data());
 	// 4. rollover
-	api_check(ngp_rollover(stream, target_batch_size, compacted_counter, tb.dloss_drgbsigma.data(), padded_output_width, (float*)tb.coords_compacted.data()));
-	// 5./6. forward + backward on the compacted batch (one fused launch chain)
+	api_check(ngp_rollover(stream, target_batch_size, compacted_counter, tb.dloss_drgbsigma.data(), padded_output_width, (float*)tb.coords_compacted.data(),
+	                       tb.compacted_src_index.data()));
+	// 5./6. forward + backward on the compacted batch (one fused launch chain).  The compacted samples are a subset of the ones
+	//       step 2 encoded with the same table, so their encodings are gathered from there instead of being computed again.
 	m_network->forward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data());
-	m_network->backward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data(), tb.dloss_drgbsigma.data());
+	m_network->backward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data(), tb.dloss_drgbsigma.data(),
+	                    tb.compacted_src_index.data(), max_inference);
 	// data parallel: sum the fp16 gradient arena over ranks (NVLink / NVSwitch)
 	if (m_dp_world > 1) {
 		const ncclResult_t r = ncclAllReduce(m_trainer->gradients(), m_trainer->gradients(), m_trainer->n_params(), ncclHalf, ncclSum, (ncclComm_t)m_nccl_comm, stream);

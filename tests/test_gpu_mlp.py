@@ -139,3 +139,41 @@ def test_network_density_and_inference_chain(capi, orc):
     g2 = G.host(out2, np.int16).reshape(n, 4)
     assert np.array_equal(g2[:1000], G.host(out, np.int16).reshape(n, 4)[:1000])
     assert np.all(g2[1024:] == 0x7E00)
+
+
+def test_network_train_reuse_equals_network_train(capi, orc):
+    """gathering the encodings the inference pass left behind gives the same step as encoding the compacted batch again"""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    m, n = 9000, 4096 + 17
+    L = orc.GridLevels(16, 19, 16)
+    d, _ = capi.make_grid_desc()
+    w = _weights(15)
+    table = rng_uniform(L.n_params, 43, -1, 1).astype(np.float16)
+    params = np.concatenate([w, table])
+    _, coords = _inputs(m, 44)
+    idx = (rng_uniform(n, 45, 0, 1) * m).astype(np.uint32) % m
+    idx[:64] = idx[0]                                       # repeated rows, as the rollover produces
+    sub = np.ascontiguousarray(coords.reshape(m, 7)[idx])
+    dl = (rng_uniform((n, 4), 46, -1, 1) * 0.01).astype(np.float16)
+    dp, dc, dsub, ddl, didx = G.dev(params.view(np.uint16)), G.dev(coords), G.dev(sub), G.dev(dl.view(np.uint16)), G.dev(idx)
+    ws_inf_bytes, ws_bytes = lib.ngp_network_workspace_bytes(m), lib.ngp_network_workspace_bytes(n)
+    ws_inf, ws_a, ws_b = G.zeros(ws_inf_bytes, torch.uint8), G.zeros(ws_bytes, torch.uint8), G.zeros(ws_bytes, torch.uint8)
+    out_inf = G.zeros(m * 4, torch.int16)
+    capi.check(lib.ngp_network_inference(G.stream(), G.p(dc), m, None, G.p(dp), C.byref(d), G.p(out_inf), G.p(ws_inf), ws_inf_bytes))
+    n_params = params.size
+    ga, gb = G.zeros(n_params, torch.int16), G.zeros(n_params, torch.int16)
+    oa, ob = G.zeros(n * 4, torch.int16), G.zeros(n * 4, torch.int16)
+    capi.check(lib.ngp_network_train(G.stream(), G.p(dsub), n, G.p(dp), C.byref(d), G.p(ddl), G.p(oa), G.p(ga), G.p(ws_a), ws_bytes))
+    capi.check(lib.ngp_network_train_reuse(G.stream(), G.p(dsub), n, G.p(dp), C.byref(d), G.p(ddl), G.p(ob), G.p(gb), G.p(ws_inf), m, G.p(didx),
+                                           G.p(ws_b), ws_bytes))
+    G.sync()
+    assert np.array_equal(G.host(oa, np.int16), G.host(ob, np.int16)), "forward outputs must be bit-identical"
+    a, b = G.host(ga, np.float16).astype(np.float32), G.host(gb, np.float16).astype(np.float32)
+    assert np.array_equal(a[:10240], b[:10240]), "MLP weight gradients must be bit-identical (deterministic slot reduction)"
+    assert np.abs(a[10240:]).max() > 0
+    # the grid gradient is scattered with fp16 atomics whose order is not fixed: equal up to fp16 rounding of the partial sums
+    assert np.allclose(a[10240:], b[10240:], rtol=2e-2, atol=2e-3 * np.abs(a[10240:]).max())
+    # aliasing the two workspaces is refused
+    assert lib.ngp_network_train_reuse(G.stream(), G.p(dsub), n, G.p(dp), C.byref(d), G.p(ddl), G.p(ob), G.p(gb), G.p(ws_b), m, G.p(didx), G.p(ws_b), ws_bytes) != 0

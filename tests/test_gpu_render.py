@@ -70,14 +70,18 @@ def test_composite_train_matches_oracle(capi, orc, n_rays, max_compacted, kw):
     ray_counter = G.dev(np.array([n_rays], np.uint32))
     d_mean = G.dev(np.array([mean], np.float32))
     ws = G.zeros(lib.ngp_composite_workspace_bytes(n_rays + 100) + 64, torch.uint8)
+    src_index = G.zeros(max_compacted, torch.int32)
     capi.check(lib.ngp_composite_train(G.stream(), C.byref(c), n_rays + 100, max_compacted, G.p(ray_counter), G.p(G.dev(rgba)), G.p(d_ns), G.p(G.dev(coords)),
-                                       G.p(cc), G.p(counter), G.p(G.dev(net)), G.p(dloss), 4, G.p(d_mean), rng.state, rng.inc, G.p(loss), G.p(ws)))
+                                       G.p(cc), G.p(counter), G.p(G.dev(net)), G.p(dloss), 4, G.p(d_mean), rng.state, rng.inc, G.p(loss), G.p(ws), G.p(src_index)))
     G.sync()
     got_counter = int(G.host(counter, np.uint32)[0])
     assert got_counter == ref["counter"]
     assert np.array_equal(G.host(d_ns, np.uint32).reshape(-1, 2), ref_ns), "compacted (count, base) per ray must be exact"
     n_comp = min(got_counter, max_compacted)
     assert np.array_equal(G.host(cc).reshape(-1, 7)[:n_comp], ref["coords_compacted"][:n_comp])
+    # the source index of every compacted sample points at the very coordinate that was copied
+    si = G.host(src_index, np.uint32)[:n_comp]
+    assert np.array_equal(coords.reshape(-1, 7)[si], ref["coords_compacted"][:n_comp])
     gl, rl = G.host(loss)[:n_rays], ref["loss"][:n_rays]
     assert np.allclose(gl, rl, rtol=2e-3, atol=1e-8)
     gd = G.host(dloss, np.float16).reshape(-1, 4)[:n_comp].astype(np.float32)
@@ -100,13 +104,17 @@ def test_rollover_matches_oracle(capi, orc):
     ref_c = coords.copy()
     ref_g = orc.rollover(B, n_in, grads.copy(), ref_c)
     dg, dc = G.dev(grads), G.dev(coords)
-    capi.check(lib.ngp_rollover(G.stream(), B, G.p(G.dev(np.array([n_in], np.uint32))), G.p(dg), 4, G.p(dc)))
+    si = np.arange(B, dtype=np.uint32) * 3 + 1
+    dsi = G.dev(si)
+    capi.check(lib.ngp_rollover(G.stream(), B, G.p(G.dev(np.array([n_in], np.uint32))), G.p(dg), 4, G.p(dc), G.p(dsi)))
     G.sync()
     assert np.array_equal(G.host(dg, np.uint16), ref_g.view(np.uint16).reshape(-1, 4))
     assert np.array_equal(G.host(dc), ref_c)
+    k = np.arange(B)
+    assert np.array_equal(G.host(dsi, np.uint32), si[np.where(k < n_in, k, k % n_in)])
     # a full (or overfull) batch is left untouched
     dg2 = G.dev(grads)
-    capi.check(lib.ngp_rollover(G.stream(), B, G.p(G.dev(np.array([B + 5], np.uint32))), G.p(dg2), 4, G.p(dc)))
+    capi.check(lib.ngp_rollover(G.stream(), B, G.p(G.dev(np.array([B + 5], np.uint32))), G.p(dg2), 4, G.p(dc), None))
     G.sync()
     assert np.array_equal(G.host(dg2, np.uint16), grads.view(np.uint16))
 

@@ -76,7 +76,7 @@ def test_update_grid_and_bitfield_match_oracle(capi, orc):
     # bitfield from the SAME grid values on both sides: bit-exact
     mean = orc.grid_mean(ocfg, got)
     ref_bits = orc.grid_to_bitfield(ocfg, got, mean)
-    d_mean, d_bits = G.zeros(16, torch.float32), G.zeros(grid.size // 8, torch.uint8)
+    d_mean, d_bits = G.zeros(256, torch.float32), G.zeros(grid.size // 8, torch.uint8)
     capi.check(lib.ngp_update_grid_bitfield(G.stream(), C.byref(cfg), G.p(d_grid), 0.01, G.p(d_mean), G.p(d_bits)))
     G.sync()
     assert abs(float(G.host(d_mean)[0]) - mean) <= 1e-6 * abs(mean)
@@ -97,12 +97,14 @@ def _scene(orc, n_images=4, W=64, H=64):
     return xf, images, bits
 
 
-@pytest.mark.parametrize("n_rays,n_coords", [(4096, 1 << 20), (1000, 1 << 20), (4096, 20000), (1, 1 << 16)])
-def test_generate_training_samples_matches_oracle(capi, orc, n_rays, n_coords):
+# cone 1/256: variable step (sequential lattice path); max_steps 4096: rays of >64 windows (emit pass marches again)
+@pytest.mark.parametrize("n_rays,n_coords,cone,max_steps", [(4096, 1 << 20, 0.0, 1024), (1000, 1 << 20, 0.0, 1024), (4096, 20000, 0.0, 1024),
+                                                            (1, 1 << 16, 0.0, 1024), (2048, 1 << 20, 1.0 / 256, 1024), (1024, 1 << 21, 0.0, 4096)])
+def test_generate_training_samples_matches_oracle(capi, orc, n_rays, n_coords, cone, max_steps):
     import gpuutil as G
     import torch
     lib = capi.load()
-    cfg, ocfg = capi.make_sampler_cfg(1), orc.SamplerCfg(1)
+    cfg, ocfg = capi.make_sampler_cfg(1, max_steps=max_steps, cone_angle=cone), orc.SamplerCfg(1, max_steps=max_steps, cone_angle=cone)
     W = H = 64
     fx = 70.0
     xf, images, bits = _scene(orc)
