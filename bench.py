@@ -87,20 +87,19 @@ def measured_peaks():
     return 6650.0, 1400.0, "fallback"
 
 
-# ALGORITHMIC bytes (or flops) per launch of each hot kernel, from the units one launch processes (DESIGN.md section 4;
-# per-unit figures from SURVEY.md 8d): m = samples marched per step, b = samples in the compacted batch, r = rays, p = params
-def kernel_work(name, m, b, r, p):
+# ALGORITHMIC bytes (or flops) per STEP of each hot kernel, from the units it processes (per-unit figures
+# from SURVEY.md 8d): m = samples marched per step, b = samples in the compacted batch, r = rays, p = params,
+# g = occupancy-refresh positions per step (one refresh of 2^22 / 2^21 positions every 16 steps)
+def kernel_work(name, m, b, r, p, g=0.0):
     table = {
-        "composite_train_kernel": ("hbm", m * (8 + 28) + b * (8 + 28) + r * 32),
         "composite_count_kernel": ("hbm", m * (8 + 4) + r * 40),
-        "composite_grad_kernel": ("hbm", b * (8 + 28 + 8 + 28) + r * 40),
-        "generate_training_samples_kernel": ("hbm", m * 28 + r * (24 + 16 + 8 + 8)),
-        "march_count_kernel": ("hbm", r * 64),
-        "march_emit_kernel": ("hbm", m * 28 + r * 64),
-        "hash_encode_fwd_kernel": ("hbm", 0.5 * (m + b) * 588),          # two launches per step: m points and b points
+        "composite_grad_kernel": ("hbm", b * (8 + 28 + 8 + 28 + 4) + r * 40),
+        "march_count_kernel": ("hbm", r * (64 + 256)),
+        "march_emit_kernel": ("hbm", m * 28 + r * (64 + 256)),
+        "hash_encode_fwd_kernel": ("hbm", (m + g) * 588),                 # the marched samples + the refresh positions; the batch reuses pass 1
         "hash_encode_bwd_kernel": ("hbm", b * 588 + 2 * (p - 10240)),
         "adam_ema_kernel": ("hbm", p * 42),
-        "mlp_kernel": ("tensor", 0.5 * (m * 18816 + b * 54400)),          # inference launch + training launch
+        "mlp_kernel": ("tensor", m * 18816 + b * 54400 + g * 6144),       # inference launch + training launch + density-only refresh
     }
     return table.get(name)
 
@@ -236,7 +235,9 @@ def run_ours(args):
     total_kernel_ms = sum(v[0] for v in kt.values())
     name, (k_ms, k_n) = max(kt.items(), key=lambda kv: kv[1][0])
     m, b, r = p_marched / prof_steps, p_samples / prof_steps, p_rays / prof_steps
-    work = kernel_work(name, m, b, r, tb.n_params)
+    first = args.warmup + args.steps                                     # index of the first profiled step
+    g = sum((1 << 22) if (first + k) < 256 else (1 << 21) for k in range(0, prof_steps, CALL_STEPS)) / prof_steps
+    work = kernel_work(name, m, b, r, tb.n_params, g)
     launches_per_step = k_n / prof_steps
     roofline = {"kernel": name, "share_of_kernel_time": k_ms / total_kernel_ms, "avg_launch_us": k_ms / k_n * 1e3, "launches_per_step": launches_per_step}
     if work:
