@@ -97,10 +97,12 @@ __device__ __forceinline__ Coordinate make_coord(V3 pos, V3 dir, float dt, const
 __device__ __forceinline__ void make_ray(const float* __restrict__ xf, float u, float v, const ngp_camera_cfg& cam, V3& o, V3& d) {
 	const float cx = (u - cam.ppx) * (float)cam.width / cam.fx, cy = (v - cam.ppy) * (float)cam.height / cam.fy, cz = 1.0f;
 	o = {xf[9], xf[10], xf[11]};
-	float dx = __fmaf_rn(xf[6], cz, __fmaf_rn(xf[3], cy, xf[0] * cx));
-	float dy = __fmaf_rn(xf[7], cz, __fmaf_rn(xf[4], cy, xf[1] * cx));
-	float dz = __fmaf_rn(xf[8], cz, __fmaf_rn(xf[5], cy, xf[2] * cx));
-	const float n2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+	// Eigen's fixed-size reductions associate as p0 + (p1 + p2) and nvcc contracts both sums (cz == 1: p2 is exact);
+	// verified bit-for-bit against rays dumped from the reference's own sm_100 build
+	float dx = __fmaf_rn(xf[0], cx, __fmaf_rn(xf[3], cy, xf[6] * cz));
+	float dy = __fmaf_rn(xf[1], cx, __fmaf_rn(xf[4], cy, xf[7] * cz));
+	float dz = __fmaf_rn(xf[2], cx, __fmaf_rn(xf[5], cy, xf[8] * cz));
+	const float n2 = __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, dz * dz));
 	if (n2 > 0.f) { const float n = sqrtf(n2); dx /= n; dy /= n; dz /= n; }
 	d = {dx, dy, dz};
 }

@@ -9,15 +9,16 @@
 
 namespace ngp {
 
-// reference pattern: thread i advances the generator by 4*i and writes elements i + total_threads*j, j < 4
-__global__ void init_grid_kernel(uint64_t n, uint64_t n_threads, uint64_t total_threads, Pcg32 rng0, float* __restrict__ w32, __half* __restrict__ w16) {
-	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_threads; i += (uint64_t)gridDim.x * blockDim.x) {
+// reference pattern: thread i advances the generator by 4*i and writes elements i + total_threads*j, j < 4; ALL launched
+// threads take part (total_threads = div_round_up(n, 4) rounded up to whole 128-thread blocks), verified against a dump
+__global__ void init_grid_kernel(uint64_t n, uint64_t total_threads, Pcg32 rng0, float* __restrict__ w32, __half* __restrict__ w16) {
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total_threads; i += (uint64_t)gridDim.x * blockDim.x) {
 		Pcg32 rng = rng0;
 		rng.advance(i * 4);
 		for (uint64_t j = 0; j < 4; ++j) {
 			const uint64_t idx = i + total_threads * j;
 			if (idx >= n) break;
-			const float v = rng.next_float() * (1e-4f - (-1e-4f)) + (-1e-4f);
+			const float v = __fmaf_rn(rng.next_float(), 1e-4f - (-1e-4f), -1e-4f);     // the reference's lambda is contracted to one FFMA
 			w32[idx] = v;
 			w16[idx] = __float2half_rn(v);
 		}
@@ -151,7 +152,7 @@ extern "C" int ngp_init_params(void* stream, uint64_t* rng_state, uint64_t rng_i
 	    cudaStreamSynchronize(s) != cudaSuccess) { set_error("ngp_init_params: copy failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
 	if (n_grid_params) {
 		const uint64_t n_threads = (n_grid_params + 3) / 4, total_threads = ((n_threads + 127) / 128) * 128;
-		NGP_LAUNCH("init_grid_kernel", s, init_grid_kernel<<<grid_for(n_threads, 256), 256, 0, s>>>(n_grid_params, n_threads, total_threads, rnd, d_params_fp32 + NGP_MLP_PARAMS, (__half*)d_params_fp16 + NGP_MLP_PARAMS));
+		NGP_LAUNCH("init_grid_kernel", s, init_grid_kernel<<<grid_for(total_threads, 256), 256, 0, s>>>(n_grid_params, total_threads, rnd, d_params_fp32 + NGP_MLP_PARAMS, (__half*)d_params_fp16 + NGP_MLP_PARAMS));
 	}
 	rnd.advance(n_grid_params);
 	*rng_state = rnd.state;

@@ -21,9 +21,10 @@ __global__ void mark_untrained_grid_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam
 		for (uint32_t j = 0; j < n_images && !seen; ++j) {
 			const float* xf = xforms + (size_t)j * 12;
 			const float lx = px - xf[9], ly = py - xf[10], lz = pz - xf[11];
-			const float cx = __fmaf_rn(lz, xf[2], __fmaf_rn(ly, xf[1], lx * xf[0]));
-			const float cy = __fmaf_rn(lz, xf[5], __fmaf_rn(ly, xf[4], lx * xf[3]));
-			const float cz = __fmaf_rn(lz, xf[8], __fmaf_rn(ly, xf[7], lx * xf[6]));
+			// Eigen dot(): p0 + (p1 + p2), both sums contracted by nvcc
+			const float cx = __fmaf_rn(lx, xf[0], __fmaf_rn(ly, xf[1], lz * xf[2]));
+			const float cy = __fmaf_rn(lx, xf[3], __fmaf_rn(ly, xf[4], lz * xf[5]));
+			const float cz = __fmaf_rn(lx, xf[6], __fmaf_rn(ly, xf[7], lz * xf[8]));
 			if (cz > 0.f && fabsf(cx) - voxel_radius < cz / cam.fx * half_resx && fabsf(cy) - voxel_radius < cz / cam.fy * half_resy) seen = true;
 		}
 		grid_out[i] = seen ? 0.f : -1.f;

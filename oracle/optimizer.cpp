@@ -44,13 +44,13 @@ void orc_init_params(uint64_t* state, uint64_t inc, const uint32_t* layer_shapes
 	const uint64_t total_threads = ((n_threads + 127) / 128) * 128;
 	float* grid = params + pos;
 	#pragma omp parallel for schedule(static)
-	for (int64_t i = 0; i < (int64_t)n_threads; ++i) {
+	for (int64_t i = 0; i < (int64_t)total_threads; ++i) {      // every launched thread writes, also those past div_round_up(n, 4) (random.h:69-84)
 		Pcg32 r = rnd;
 		r.advance((int64_t)i * 4);
 		for (uint64_t j = 0; j < 4; ++j) {
 			uint64_t idx = (uint64_t)i + total_threads * j;
 			if (idx >= n_grid) break;
-			grid[idx] = r.next_float() * (1e-4f - (-1e-4f)) + (-1e-4f);
+			grid[idx] = fmaf(r.next_float(), 1e-4f - (-1e-4f), -1e-4f);   // val * (upper - lower) + lower, contracted by nvcc (random.h:99)
 		}
 	}
 	rnd.advance((int64_t)n_grid);

@@ -1,0 +1,221 @@
+// TEST INFRASTRUCTURE ONLY -- a small driver around the UNMODIFIED reference (Testbed and its module classes, compiled from
+// /root/reference by oracle/build_ref.sh).  It feeds the reference the same synthetic dataset our path gets, runs the
+// reference's own Testbed::train_prep_nerf / train_nerf / train, and either dumps the buffers the parity tests compare
+// against (dump) or prints the training throughput (bench).  Nothing of the product links or includes this file.
+//
+//   ref_harness dump  <dir> [batch] [n_rays]   reads <dir>/{config.json,meta.txt,xforms.f32,images.f16}, writes <dir>/ref_*.bin
+//   ref_harness bench <dir> <calls> <warmup>   train(16, batch) loop as experiment/run.py:71 drives it; one JSON line
+#include "internal/testbed.h"
+
+#include <chrono>
+#include <cstdio>
+#include <fstream>
+#include <iostream>
+#include <string>
+#include <vector>
+
+using namespace Eigen;
+
+template <typename T>
+static std::vector<T> read_file(const std::string& path) {
+	std::ifstream f(path, std::ios::binary | std::ios::ate);
+	if (!f) throw std::runtime_error("cannot open " + path);
+	const size_t bytes = (size_t)f.tellg();
+	std::vector<T> v(bytes / sizeof(T));
+	f.seekg(0);
+	f.read((char*)v.data(), (std::streamsize)(v.size() * sizeof(T)));
+	return v;
+}
+
+static void write_device(const std::string& path, const void* dptr, size_t bytes) {
+	std::vector<char> h(bytes);
+	if (bytes) CUDA_CHECK_THROW(cudaMemcpy(h.data(), dptr, bytes, cudaMemcpyDeviceToHost));
+	std::ofstream f(path, std::ios::binary);
+	f.write(h.data(), (std::streamsize)bytes);
+}
+
+static void write_host(const std::string& path, const void* p, size_t bytes) {
+	std::ofstream f(path, std::ios::binary);
+	f.write((const char*)p, (std::streamsize)bytes);
+}
+
+// what Testbed::load_training_data does (internal/testbed.cu:95-125) with the decoded images handed over directly
+static void load_dataset(Testbed& tb, const std::string& dir) {
+	std::ifstream meta(dir + "/meta.txt");
+	size_t n_images; int W, H; float fx, fy, scale;
+	meta >> n_images >> W >> H >> fx >> fy >> scale;
+	if (!meta) throw std::runtime_error("bad meta.txt");
+	auto xf = read_file<float>(dir + "/xforms.f32");            // [n][12] column-major, already in the NGP frame
+	auto img = read_file<uint16_t>(dir + "/images.f16");        // [n][H][W][4] linear premultiplied fp16
+	if (xf.size() != n_images * 12 || img.size() != n_images * (size_t)W * H * 4) throw std::runtime_error("dataset size mismatch");
+	NeRFSynthetic& d = tb.m_training_buffer.dataset;
+	d.scale = scale; d.offset = Vector3f::Constant(0.5f);
+	d.n_images = n_images;
+	d.image_resolution = Vector2i(W, H);
+	d.focal_length = Vector2f(fx, fy);
+	d.principal_point = Vector2f::Constant(0.5f);
+	d.xforms.resize(n_images);
+	CUDA_CHECK_THROW(cudaMemcpy(d.xforms.data(), xf.data(), xf.size() * sizeof(float), cudaMemcpyHostToDevice));
+	d.images.resize(img.size());
+	CUDA_CHECK_THROW(cudaMemcpy(d.images.data(), img.data(), img.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+	tb.m_scene_scale = scale;
+	tb.m_scene_offset = Vector3f::Constant(0.5f);
+	tb.m_sampler->init((uint32_t)d.n_images, d.image_resolution, d.focal_length, d.principal_point, d.xforms, d.images, tb.m_rng, tb.m_stream);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(tb.m_stream));
+}
+
+static int run_dump(const std::string& dir, uint32_t batch, uint32_t n_rays_override) {
+	Testbed tb;
+	if (n_rays_override) tb.m_training_buffer.n_rays_per_batch = n_rays_override;
+	tb.load_model_config(dir + "/config.json");
+	const size_t n = tb.m_network->n_params();
+	float* p32 = tb.m_trainer->params();
+	const __half* p16 = (const __half*)(p32 + n);               // arena order of Trainer::initialize_params (trainer.h:79-85)
+	const __half* grads = p16 + 2 * n;
+	CUDA_CHECK_THROW(cudaDeviceSynchronize());
+	write_device(dir + "/ref_params_init_f32.bin", p32, n * 4);  // what Trainer::initialize_params produced (seed 43)
+	{
+		// optional: start from given fp16 parameters instead (Trainer::set_params), so the numerics are exercised at O(1) values
+		std::ifstream probe(dir + "/params_init.f16", std::ios::binary);
+		if (probe.good()) {
+			auto h = read_file<uint16_t>(dir + "/params_init.f16");
+			if (h.size() != n) throw std::runtime_error("params_init.f16 has the wrong size");
+			tb.m_trainer->set_params((const precision_t*)h.data(), n);
+			CUDA_CHECK_THROW(cudaDeviceSynchronize());
+		}
+	}
+	write_device(dir + "/ref_params0_f32.bin", p32, n * 4);
+
+	load_dataset(tb, dir);
+	OccupancySampler& s = *tb.m_sampler;
+	write_device(dir + "/ref_grid0_f32.bin", s.density_grid.data(), (size_t)s.n_total_elements * 4);
+	write_device(dir + "/ref_bitfield0_u8.bin", s.density_grid_bitfield.data(), s.density_grid_bitfield.size());
+
+	// occupancy refresh (internal/testbed.cu:193-229); the sampler's own generator going in is recorded
+	const uint64_t sampler_rng[2] = {s.rng.state, s.rng.inc};
+	tb.train_prep_nerf(batch, 1, tb.m_stream);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(tb.m_stream));
+	auto& b = tb.m_training_buffer;
+	write_device(dir + "/ref_grid_positions_f32.bin", b.grid_positions.data(), (size_t)s.n_total_elements * sizeof(Position));
+	write_device(dir + "/ref_grid_indices_u32.bin", b.grid_indices.data(), (size_t)s.n_total_elements * 4);
+	write_device(dir + "/ref_grid_density_f16.bin", b.rgbsigma.data(), (size_t)s.n_total_elements * tb.m_network->padded_density_output_width() * 2);
+	write_device(dir + "/ref_grid1_f32.bin", s.density_grid.data(), (size_t)s.n_total_elements * 4);
+	write_device(dir + "/ref_grid_mean_f32.bin", s.density_grid_mean.data(), 4);
+	write_device(dir + "/ref_bitfield1_u8.bin", s.density_grid_bitfield.data(), s.density_grid_bitfield.size());
+
+	// One training step, stage by stage, through the reference's own module methods in the order Testbed::train_nerf_step
+	// issues them (internal/testbed.cu:301-418), with the buffers dumped between stages.  (bench mode below calls the
+	// reference's Testbed::train itself.)
+	cudaStream_t stream = tb.m_stream;
+	const uint64_t rng_in[2] = {tb.m_rng.state, tb.m_rng.inc};
+	const uint32_t n_rays = b.n_rays_per_batch, max_samples = batch * 16, w = tb.m_network->padded_output_width();
+	b.rays.enlarge(n_rays); b.rays_rgba.enlarge(n_rays); b.ray_counter.enlarge(1); b.ray_coord_indices.enlarge(n_rays * 2);
+	b.coords.enlarge(max_samples); b.coords_compacted.enlarge(batch);
+	b.rgbsigma.enlarge((size_t)max_samples * w); b.dloss_drgbsigma.enlarge((size_t)batch * w);
+	b.n_coords_counter.enlarge(1); b.n_compacted_coords_counter.enlarge(1); b.loss.enlarge(n_rays);
+	CUDA_CHECK_THROW(cudaMemsetAsync(b.ray_counter.data(), 0, 4, stream));
+	CUDA_CHECK_THROW(cudaMemsetAsync(b.n_coords_counter.data(), 0, 4, stream));
+	CUDA_CHECK_THROW(cudaMemsetAsync(b.n_compacted_coords_counter.data(), 0, 4, stream));
+	CUDA_CHECK_THROW(cudaMemsetAsync(b.loss.data(), 0, (size_t)n_rays * 4, stream));
+	CUDA_CHECK_THROW(cudaMemsetAsync(b.coords_compacted.data(), 0, (size_t)batch * sizeof(Coordinate), stream));
+	CUDA_CHECK_THROW(cudaMemsetAsync(b.dloss_drgbsigma.data(), 0, (size_t)batch * w * 2, stream));
+	const uint32_t max_inference = tcnn::next_multiple(max_samples, BATCH_SIZE_MULTIPLE);
+
+	tb.m_sampler->sample_coords_from_dataset(n_rays, 0, max_inference, b.dataset, false, b.rays, b.rays_rgba, b.ray_counter.data(), b.ray_coord_indices, b.coords,
+	                                         b.n_coords_counter.data(), tb.m_rng, stream);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	uint32_t n_kept = 0, n_marched = 0, n_comp = 0;
+	CUDA_CHECK_THROW(cudaMemcpy(&n_kept, b.ray_counter.data(), 4, cudaMemcpyDeviceToHost));
+	CUDA_CHECK_THROW(cudaMemcpy(&n_marched, b.n_coords_counter.data(), 4, cudaMemcpyDeviceToHost));
+	const uint32_t n_used = std::min(n_marched, max_inference);
+	write_device(dir + "/ref_rays_f32.bin", b.rays.data(), (size_t)n_kept * sizeof(Ray));
+	write_device(dir + "/ref_rays_rgba_f32.bin", b.rays_rgba.data(), (size_t)n_kept * 16);
+	write_device(dir + "/ref_numsteps_u32.bin", b.ray_coord_indices.data(), (size_t)n_kept * 8);
+	write_device(dir + "/ref_coords_f32.bin", b.coords.data(), (size_t)n_used * sizeof(Coordinate));
+
+	tcnn::GPUMatrix<float> coords_matrix((float*)b.coords.data(), sizeof(Coordinate) / sizeof(float), max_inference);
+	tcnn::GPUMatrix<precision_t> rgbsigma_matrix(b.rgbsigma.data(), w, max_inference);
+	tb.m_network->inference_mixed_precision(stream, coords_matrix, rgbsigma_matrix, false);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_device(dir + "/ref_rgbsigma_f16.bin", b.rgbsigma.data(), (size_t)n_used * w * 2);
+
+	tb.m_render->volume_rendering_with_loss_and_gradient(
+		n_rays, batch, b.rays, b.rays_rgba, b.ray_counter, b.ray_coord_indices, b.coords, b.coords_compacted, b.n_compacted_coords_counter.data(),
+		b.rgbsigma, b.dloss_drgbsigma, w, tb.m_rgb_activation, tb.m_density_activation, b.loss.data(), tb.m_loss_type, LOSS_SCALE,
+		tb.m_sampler->aabb, tb.m_sampler->n_cascades, tb.m_sampler->min_cone_stepsize, tb.m_sampler->density_grid_mean, tb.m_sampler->min_optical_thickness,
+		tb.m_envmap.envmap->params(), nullptr, tb.m_envmap.resolution, tb.m_envmap.loss_type,
+		tb.m_background_color.head<3>(), tb.m_color_space, tb.m_rng, stream);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	CUDA_CHECK_THROW(cudaMemcpy(&n_comp, b.n_compacted_coords_counter.data(), 4, cudaMemcpyDeviceToHost));
+	write_device(dir + "/ref_numsteps_compacted_u32.bin", b.ray_coord_indices.data(), (size_t)n_kept * 8);
+	write_device(dir + "/ref_coords_compacted_f32.bin", b.coords_compacted.data(), (size_t)batch * sizeof(Coordinate));
+	write_device(dir + "/ref_dloss_f16.bin", b.dloss_drgbsigma.data(), (size_t)batch * w * 2);
+	write_device(dir + "/ref_loss_f32.bin", b.loss.data(), (size_t)n_rays * 4);
+
+	tcnn::fill_rollover_and_rescale<precision_t><<<tcnn::n_blocks_linear(batch * w), tcnn::n_threads_linear, 0, stream>>>(
+		batch, w, b.n_compacted_coords_counter.data(), b.dloss_drgbsigma.data());
+	tcnn::fill_rollover<Coordinate><<<tcnn::n_blocks_linear(batch), tcnn::n_threads_linear, 0, stream>>>(batch, 1, b.n_compacted_coords_counter.data(), b.coords_compacted.data());
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_device(dir + "/ref_coords_rolled_f32.bin", b.coords_compacted.data(), (size_t)batch * sizeof(Coordinate));
+	write_device(dir + "/ref_dloss_rolled_f16.bin", b.dloss_drgbsigma.data(), (size_t)batch * w * 2);
+
+	tcnn::GPUMatrix<float> cc_matrix((float*)b.coords_compacted.data(), sizeof(Coordinate) / sizeof(float), batch);
+	tcnn::GPUMatrix<precision_t> out_matrix(b.rgbsigma.data(), w, batch);
+	tcnn::GPUMatrix<precision_t> grad_matrix(b.dloss_drgbsigma.data(), w, batch);
+	tb.m_network->forward(stream, cc_matrix, &out_matrix);
+	tb.m_network->backward(stream, cc_matrix, out_matrix, grad_matrix);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_device(dir + "/ref_rgbsigma_compacted_f16.bin", b.rgbsigma.data(), (size_t)batch * w * 2);
+	write_device(dir + "/ref_grads_f16.bin", grads, n * 2);
+
+	tb.m_rng.advance();
+	tb.m_trainer->optimizer_step(stream, LOSS_SCALE);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_device(dir + "/ref_params1_f32.bin", p32, n * 4);
+	write_device(dir + "/ref_params1_f16.bin", p16, n * 2);
+	{
+		std::ofstream f(dir + "/ref_step.txt");
+		f << "rng_state " << rng_in[0] << "\nrng_inc " << rng_in[1] << "\nsampler_rng_state " << sampler_rng[0] << "\nsampler_rng_inc " << sampler_rng[1]
+		  << "\nn_rays " << n_rays << "\nn_kept " << n_kept << "\nn_marched " << n_marched << "\nn_compacted " << n_comp << "\nbatch " << batch
+		  << "\npadded_output_width " << w << "\nn_params " << n << "\nn_total_elements " << s.n_total_elements << "\n";
+	}
+	std::cout << "dumped: n_rays " << n_rays << " kept " << n_kept << " marched " << n_marched << " compacted " << n_comp << std::endl;
+	return 0;
+}
+
+static int run_bench(const std::string& dir, uint32_t calls, uint32_t warmup, uint32_t batch) {
+	Testbed tb;
+	tb.load_model_config(dir + "/config.json");
+	load_dataset(tb, dir);
+	auto& b = tb.m_training_buffer;
+	for (uint32_t i = 0; i < warmup; ++i) tb.train(16, batch);
+	CUDA_CHECK_THROW(cudaDeviceSynchronize());
+	double ms = 0, samples = 0, marched = 0, rays = 0;
+	const auto t0 = std::chrono::steady_clock::now();
+	for (uint32_t i = 0; i < calls; ++i) {
+		const uint32_t r = b.n_rays_per_batch;
+		tb.train(16, batch);
+		ms += b.training_ms + b.training_prep_ms;                 // the reference's own timers (internal/testbed.cu:170-190)
+		for (uint32_t k = 0; k < 16; ++k) { samples += std::min(b.n_compacted_coords_counter_cpu[k], batch); marched += b.n_coords_counter_cpu[k]; }
+		rays += 16.0 * r;
+	}
+	CUDA_CHECK_THROW(cudaDeviceSynchronize());
+	const double wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+	const double steps = 16.0 * calls;
+	printf("{\"impl\": \"reference-cuda-sm100\", \"samples_per_s\": %.1f, \"ms_per_step\": %.5f, \"wall_ms_per_step\": %.5f, \"steps\": %.0f, \"warmup_steps\": %u, "
+	       "\"samples_per_step\": %.1f, \"marched_per_step\": %.1f, \"rays_per_step\": %.1f, \"loss\": %.6g}\n",
+	       samples / (ms * 1e-3), ms / steps, wall_ms / steps, steps, warmup * 16, samples / steps, marched / steps, rays / steps, (double)b.loss_scalar);
+	return 0;
+}
+
+int main(int argc, char** argv) {
+	try {
+		if (argc >= 3 && std::string(argv[1]) == "dump") return run_dump(argv[2], argc > 3 ? (uint32_t)atoi(argv[3]) : (1u << 18), argc > 4 ? (uint32_t)atoi(argv[4]) : 0u);
+		if (argc >= 5 && std::string(argv[1]) == "bench") return run_bench(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argc > 5 ? (uint32_t)atoi(argv[5]) : (1u << 18));
+		std::cerr << "usage: ref_harness dump <dir> [batch] [n_rays] | bench <dir> <calls> <warmup_calls> [batch]" << std::endl;
+		return 2;
+	} catch (const std::exception& e) {
+		std::cerr << "ref_harness: " << e.what() << std::endl;
+		return 1;
+	}
+}

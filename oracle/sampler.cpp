@@ -112,10 +112,12 @@ static inline Coordinate make_coord(V3 pos, V3 dir, float dt, const SamplerCfg& 
 static inline void make_ray(const float* xf, float u, float v, float ppx, float ppy, int W, int H, float fx, float fy, V3& o, V3& d) {
 	float cx = (u - ppx) * (float)W / fx, cy = (v - ppy) * (float)H / fy, cz = 1.0f;
 	o = {xf[9], xf[10], xf[11]};
-	float dx = fmaf(xf[6], cz, fmaf(xf[3], cy, xf[0] * cx));
-	float dy = fmaf(xf[7], cz, fmaf(xf[4], cy, xf[1] * cx));
-	float dz = fmaf(xf[8], cz, fmaf(xf[5], cy, xf[2] * cx));
-	float n2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+	// Eigen's fixed-size reductions associate as p0 + (p1 + p2) and nvcc contracts both sums; cz == 1 makes p2 exact.
+	// Confirmed bit-for-bit against rays dumped from the reference's sm_100 build (tests/test_gpu_reference_cuda.py).
+	float dx = fmaf(xf[0], cx, fmaf(xf[3], cy, xf[6] * cz));
+	float dy = fmaf(xf[1], cx, fmaf(xf[4], cy, xf[7] * cz));
+	float dz = fmaf(xf[2], cx, fmaf(xf[5], cy, xf[8] * cz));
+	float n2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
 	if (n2 > 0.f) { float n = sqrtf(n2); dx /= n; dy /= n; dz /= n; }
 	d = {dx, dy, dz};
 }

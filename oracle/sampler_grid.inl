@@ -21,9 +21,10 @@ void orc_mark_untrained_grid(uint32_t n_cascades, uint32_t G, uint32_t n_images,
 		for (uint32_t j = 0; j < n_images; ++j) {
 			const float* xf = xforms + (size_t)j * 12;
 			float lx = px - xf[9], ly = py - xf[10], lz = pz - xf[11];
-			float cx = fmaf(lz, xf[2], fmaf(ly, xf[1], lx * xf[0]));
-			float cy = fmaf(lz, xf[5], fmaf(ly, xf[4], lx * xf[3]));
-			float cz = fmaf(lz, xf[8], fmaf(ly, xf[7], lx * xf[6]));
+			// Eigen dot(): p0 + (p1 + p2), both sums contracted by nvcc
+			float cx = fmaf(lx, xf[0], fmaf(ly, xf[1], lz * xf[2]));
+			float cy = fmaf(lx, xf[3], fmaf(ly, xf[4], lz * xf[5]));
+			float cz = fmaf(lx, xf[6], fmaf(ly, xf[7], lz * xf[8]));
 			if (cz > 0.f) {
 				if (fabsf(cx) - voxel_radius < cz / fx * half_resx && fabsf(cy) - voxel_radius < cz / fy * half_resy) { count++; break; }
 			}
