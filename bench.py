@@ -36,6 +36,9 @@ def parse():
     p.add_argument("--views", type=int, default=100)
     p.add_argument("--res", type=int, default=800)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference's own CUDA build (oracle/_ref/ref_harness) beside ours")
+    p.add_argument("--reference-kind", default="auto", choices=["auto", "cuda", "cpu"],
+                   help="--impl reference: the reference's CUDA build when oracle/_ref/ref_harness exists (auto/cuda), or the CPU oracle port")
     return p.parse_args()
 
 
@@ -104,13 +107,99 @@ def kernel_work(name, m, b, r, p, g=0.0):
     return table.get(name)
 
 
+REF_HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+
+
+def make_scene_on_device(args, capi, scene, lib):
+    """procedural views rendered once by the fixture renderer (never timed): (ogl matrices, ngp-frame matrices, device rgba8)"""
+    import ctypes as C
+    import torch
+    ogl = scene.sphere_cameras(args.views, 2024)
+    xf_np = scene.opengl_to_ngp(ogl)
+    xf = torch.from_numpy(xf_np).cuda()
+    fx = 0.5 * args.res / np.tan(0.5 * scene.CAMERA_ANGLE_X)
+    rgba8 = torch.empty((args.views, args.res, args.res, 4), dtype=torch.uint8, device="cuda")
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    capi.check(lib.ngp_render_procedural_views(s, 2024, args.views, args.res, args.res, fx, fx, C.c_void_p(xf.data_ptr()), C.c_void_p(rgba8.data_ptr())))
+    torch.cuda.synchronize()
+    return ogl, xf_np, fx, rgba8
+
+
+def time_reference_cuda(args, capi, lib, xf_np, fx, rgba8, steps, warmup):
+    """The UNMODIFIED reference (Testbed::train compiled for sm_100 by oracle/build_ref.sh) on the same scene, same base.json,
+    same train(16, batch) loop, timed by its own training_ms + training_prep_ms.  Returns its JSON dict, or a reason string."""
+    import ctypes as C
+    import shutil
+    import tempfile
+    import torch
+    if not (os.path.exists(REF_HARNESS) and os.access(REF_HARNESS, os.X_OK)):
+        return "oracle/_ref/ref_harness not built"
+    d = tempfile.mkdtemp(prefix="ngp_refbench_")
+    try:
+        half = torch.empty(rgba8.shape, dtype=torch.int16, device="cuda")
+        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        capi.check(lib.ngp_from_rgba32(s, rgba8.numel() // 4, C.c_void_p(rgba8.data_ptr()), C.c_void_p(half.data_ptr())))
+        torch.cuda.synchronize()
+        half.cpu().numpy().tofile(os.path.join(d, "images.f16"))
+        del half
+        np.ascontiguousarray(xf_np, np.float32).tofile(os.path.join(d, "xforms.f32"))
+        with open(os.path.join(d, "meta.txt"), "w") as f:
+            f.write(f"{args.views} {args.res} {args.res} {float(np.float32(fx))!r} {float(np.float32(fx))!r} 0.33\n")
+        shutil.copy(os.path.join(ROOT, PKG, "configs", "base.json"), os.path.join(d, "config.json"))
+        calls, wcalls = max(1, -(-steps // CALL_STEPS)), max(1, -(-warmup // CALL_STEPS))
+        r = subprocess.run([REF_HARNESS, "bench", d, str(calls), str(wcalls), str(args.batch)], capture_output=True, text=True, timeout=900)
+        if r.returncode != 0:
+            return f"ref_harness failed ({r.returncode}): {r.stderr[-300:]}"
+        line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+        return json.loads(line)
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
+def run_reference_cuda(args):
+    """--impl reference, CUDA kind: rank 0 times the reference's own CUDA build on GPU 0"""
+    import torch
+    pkg = importlib.import_module(PKG)
+    capi, scene = pkg.capi, importlib.import_module(PKG + ".scene")
+    lib = capi.load()
+    torch.cuda.set_device(0)
+    _, xf_np, fx, rgba8 = make_scene_on_device(args, capi, scene, lib)
+    clocks = ClockSampler(0)
+    clocks.start()
+    r = time_reference_cuda(args, capi, lib, xf_np, fx, rgba8, args.steps, args.warmup)
+    clk = clocks.stop()
+    if not isinstance(r, dict):
+        return None, r
+    out = {"impl": "reference", "reference_kind": "cuda: unmodified reference (Testbed::train, tiny-cuda-nn) compiled for sm_100 by oracle/build_ref.sh, run as oracle/_ref/ref_harness",
+           "metric": METRIC, "value": r["samples_per_s"], "unit": UNIT, "n_gpus": 1, "steps": int(r["steps"]), "warmup": int(r["warmup_steps"]),
+           "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+           "config": config_dict(args, 1), "clocks": clk,
+           "e2e": {"value": r["samples_per_s"] * r["ms_per_step"] / r["wall_ms_per_step"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 12,
+                   "wall_ms_per_step": r["wall_ms_per_step"]},
+           "samples_marched_per_step": r["marched_per_step"], "rays_per_step": r["rays_per_step"], "loss": r["loss"]}
+    return out, None
+
+
 def run_reference(args):
     """the reference's algorithm on the host cores: CPU oracle pipeline, all threads, bounded sample per step"""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    cuda_line, why = None, "cpu kind requested"
+    if args.reference_kind in ("auto", "cuda"):
+        try:
+            cuda_line, why = run_reference_cuda(args)
+        except Exception as e:                                    # no GPU / library missing: fall back to the CPU port below
+            cuda_line, why = None, f"{type(e).__name__}: {e}"
     from oracle import pipeline
     cores = os.cpu_count() or 1
+    if cuda_line is not None:
+        # the CPU port is still reported beside it, on a bounded sample
+        cb = pipeline.time_cpu_steps(n_steps=4, n_rays=2048, warmup=1, n_views=8, res=200, batch=args.batch)
+        cuda_line["cpu_baseline"] = {"value": cb["samples_per_s"], "unit": UNIT, "cores": cores, "kind": "port",
+                                     "sample": f"4 steps of 2048 rays ({cb['samples_per_step']:.0f} samples/step, {cb['seconds']:.1f} s) on 8 procedural views 200x200, analytic occupancy, same model"}
+        print(json.dumps(cuda_line), flush=True)
+        return
     budget_s = 150.0
     trainer = pipeline.CpuTrainer(n_views=8, res=200, batch=args.batch)
     t0 = time.perf_counter()
@@ -126,7 +215,7 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = samples / dt
     sample = f"{args.steps} steps of {n_rays} rays ({samples / args.steps:.0f} samples/step) on 8 procedural views 200x200, analytic occupancy grid, same model config"
-    print(json.dumps({"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+    print(json.dumps({"impl": "reference", "reference_kind": f"cpu port (oracle/); cuda build not used: {why}", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                       "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
                       "config": config_dict(args, args.gpus),
                       "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
@@ -166,16 +255,11 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     # ---- scene: rendered once on the device, then parked in PINNED HOST memory like a decoded dataset ----
-    ogl = scene.sphere_cameras(args.views, 2024)
-    xf = torch.from_numpy(scene.opengl_to_ngp(ogl)).cuda()
-    fx = 0.5 * args.res / np.tan(0.5 * scene.CAMERA_ANGLE_X)
-    rgba8 = torch.empty((args.views, args.res, args.res, 4), dtype=torch.uint8, device="cuda")
-    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    capi.check(lib.ngp_render_procedural_views(s, 2024, args.views, args.res, args.res, fx, fx, C.c_void_p(xf.data_ptr()), C.c_void_p(rgba8.data_ptr())))
-    torch.cuda.synchronize()
+    ogl, xf_np, fx, rgba8 = make_scene_on_device(args, capi, scene, lib)
     host_rgba8 = torch.empty(rgba8.shape, dtype=torch.uint8, pin_memory=True)
     host_rgba8.copy_(rgba8)
-    del rgba8
+    if not (args.gpus == 1 and not args.no_ref_cuda):
+        del rgba8
     np_rgba8 = host_rgba8.numpy()
 
     tb = pyngp.Testbed()
@@ -261,6 +345,12 @@ def run_ours(args):
                    "d2h_bytes_per_step": (3 * 4 * CALL_STEPS + 4) / CALL_STEPS, "wall_ms_per_step": wall / args.steps * 1e3, "dataset_upload_ms": t_upload * 1e3},
            "roofline": roofline,
            "samples_marched_per_step": marched / args.steps / max(world, 1), "rays_per_step": rays / args.steps / max(world, 1), "loss": tb.training_buffer.loss}
+    if args.gpus == 1 and not args.no_ref_cuda:
+        # the reference's own CUDA build on the same GPU, same scene, right after ours (reported, not part of any timed region)
+        r = time_reference_cuda(args, capi, lib, xf_np, fx, rgba8, args.steps, args.warmup)
+        out["reference_cuda"] = r if isinstance(r, dict) else {"unavailable": r}
+        if isinstance(r, dict):
+            out["reference_cuda"]["speedup"] = out["value"] / r["samples_per_s"]
     if args.gpus == 1 and not args.no_cpu_baseline:
         from oracle import pipeline                      # the CPU restatement, timed as the baseline only
         cb = pipeline.time_cpu_steps(n_steps=4, n_rays=2048, warmup=1, n_views=8, res=200, batch=args.batch)

@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- ctypes front end of the CPU oracle (oracle/*.cpp).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
-Parity unpinned: see oracle/oracle_common.h.
+Pinned to golden vectors from the reference's own CUDA build (tests/golden/, see oracle/oracle_common.h).
 """
 import ctypes as C
 import os

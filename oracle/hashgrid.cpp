@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Parity unpinned.
+// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Pinned to golden vectors from the reference's CUDA build (tests/golden/).
 // CPU restatement of the multiresolution hash-grid encoding.
 //   offsets / resolutions : tiny-cuda-nn/encodings/grid.h:475-537
 //   forward               : grid.h:122-215 (kernel_grid), pos_fract common_device.h:396-413

@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Parity unpinned.
+// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Pinned to golden vectors from the reference's CUDA build (tests/golden/).
 // CPU restatement of the NeRF network dataflow:
 //   spherical harmonics degree 4 : tiny-cuda-nn/encodings/spherical_harmonics.h:63-100
 //   fully fused MLPs             : tiny-cuda-nn/src/fully_fused_mlp.cu:480-533 (fwd), :152-248 (bwd),

@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Parity unpinned.
+// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Pinned to golden vectors from the reference's CUDA build (tests/golden/).
 // CPU restatement of parameter initialisation and the optimizer chain:
 //   Trainer ctor / initialize_params : tiny-cuda-nn/trainer.h:54-112
 //   xavier uniform                   : tiny-cuda-nn/gpu_matrix.h:147-164

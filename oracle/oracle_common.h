@@ -5,11 +5,13 @@
 // __graft_entry__.smoke() and by bench.py's cpu_baseline / --impl reference
 // legs, always as the checker or the timed CPU baseline, never by the product.
 //
-// PARITY UNPINNED: the reference ships no golden vectors, known-answer tests or
-// fixtures for this path and its implementation is
-// GPU-only, so it cannot be executed in the build container.  The oracle is
-// pinned only by analytic known answers in tests/ (hand-computed hashes,
-// Morton round trips, closed-form compositing, SH at axis directions).
+// PARITY PINNED to the reference's own CUDA build: the reference ships no golden
+// vectors or tests of its own and is GPU-only, so
+// oracle/build_ref.sh compiles the unmodified reference for sm_100 into
+// oracle/_ref/ref_harness, scripts/make_golden_from_ref.py ran it on a B200 and
+// wrote tests/golden/ref_cuda_step.npz, and tests/test_oracle_vs_reference_golden.py
+// checks this restatement against those vectors (integer outcomes and sample
+// coordinates bit-exact).  Analytic known answers in tests/ cover the rest.
 //
 // Conventions shared with the CUDA kernels (documented in DESIGN.md):
 //  * no implicit FMA contraction (-ffp-contract=off here, -fmad=false there);

@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE ONLY -- the reference's training step (internal/testbed.cu:301-418) executed on the host cores by
 chaining the oracle's restatements of its kernels.  Used by bench.py's cpu_baseline / --impl reference legs (timed) and by
-tests/ (as the checker of the whole step).  Never imported by the product.  Parity unpinned (see oracle_common.h)."""
+tests/ (as the checker of the whole step).  Never imported by the product.  Pinned to the reference's CUDA build through tests/golden/ (see oracle_common.h)."""
 import ctypes as C
 import time
 

@@ -5,6 +5,7 @@
 //
 //   ref_harness dump  <dir> [batch] [n_rays]   reads <dir>/{config.json,meta.txt,xforms.f32,images.f16}, writes <dir>/ref_*.bin
 //   ref_harness bench <dir> <calls> <warmup>   train(16, batch) loop as experiment/run.py:71 drives it; one JSON line
+//   ref_harness trainrender <dir> <calls> <W> <H> <spp> <fov>   train, then render <dir>/test_xforms.f32 -> ref_render_<i>.f32
 #include "internal/testbed.h"
 
 #include <chrono>
@@ -208,11 +209,54 @@ static int run_bench(const std::string& dir, uint32_t calls, uint32_t warmup, ui
 	return 0;
 }
 
+// train n_calls x 16 steps, then render the poses of <dir>/test_xforms.f32 the way Testbed::render (internal/python_api.cu:22-46) does
+static int run_trainrender(const std::string& dir, uint32_t calls, int W, int H, int spp, float fov_value, uint32_t batch) {
+	Testbed tb;
+	tb.load_model_config(dir + "/config.json");
+	load_dataset(tb, dir);
+	auto& b = tb.m_training_buffer;
+	std::ofstream lf(dir + "/ref_loss_curve.txt");
+	double ms = 0;
+	for (uint32_t i = 0; i < calls; ++i) {
+		tb.train(16, batch);
+		ms += b.training_ms + b.training_prep_ms;
+		lf << (i + 1) * 16 << " " << b.loss_scalar << " " << b.measured_batch_size << " " << b.n_rays_per_batch << "\n";
+	}
+	auto poses = read_file<float>(dir + "/test_xforms.f32");
+	const size_t n_poses = poses.size() / 12;
+	tb.set_fov(fov_value);
+	auto& rb = tb.m_rendering_buffer;
+	std::vector<float> image((size_t)W * H * 4);
+	double render_ms = 0;
+	for (size_t p = 0; p < n_poses; ++p) {
+		Eigen::Matrix<float, 3, 4> cam;
+		for (int k = 0; k < 12; ++k) cam.data()[k] = poses[p * 12 + k];          // column-major, already in the NGP frame
+		rb.camera_matrix = cam;
+		CUDA_CHECK_THROW(cudaDeviceSynchronize());
+		const auto t0 = std::chrono::steady_clock::now();
+		rb.render_buffer.resize({W, H});
+		rb.render_buffer.reset_accumulation();
+		for (int i = 0; i < spp; ++i) tb.render_frame(rb.camera_matrix, rb.render_buffer, true);
+		CUDA_CHECK_THROW(cudaDeviceSynchronize());
+		if (p > 0) render_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();   // pose 0 warms up
+		CUDA_CHECK_THROW(cudaMemcpy2DFromArray(image.data(), (size_t)W * 4 * sizeof(float), rb.render_buffer.surface_provider().array(), 0, 0,
+		                                       (size_t)W * 4 * sizeof(float), H, cudaMemcpyDeviceToHost));
+		write_host(dir + "/ref_render_" + std::to_string(p) + ".f32", image.data(), image.size() * 4);
+	}
+	const double mrays = n_poses > 1 ? (double)W * H * spp * (n_poses - 1) / (render_ms * 1e-3) / 1e6 : 0.0;
+	printf("{\"impl\": \"reference-cuda-sm100\", \"train_steps\": %u, \"train_ms_per_step\": %.5f, \"loss\": %.6g, \"render_mrays_per_s\": %.3f, \"render_ms_per_frame\": %.3f, "
+	       "\"n_poses\": %zu, \"width\": %d, \"height\": %d, \"spp\": %d}\n",
+	       calls * 16, ms / (16.0 * calls), (double)b.loss_scalar, mrays, n_poses > 1 ? render_ms / (n_poses - 1) : 0.0, n_poses, W, H, spp);
+	return 0;
+}
+
 int main(int argc, char** argv) {
 	try {
 		if (argc >= 3 && std::string(argv[1]) == "dump") return run_dump(argv[2], argc > 3 ? (uint32_t)atoi(argv[3]) : (1u << 18), argc > 4 ? (uint32_t)atoi(argv[4]) : 0u);
 		if (argc >= 5 && std::string(argv[1]) == "bench") return run_bench(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argc > 5 ? (uint32_t)atoi(argv[5]) : (1u << 18));
-		std::cerr << "usage: ref_harness dump <dir> [batch] [n_rays] | bench <dir> <calls> <warmup_calls> [batch]" << std::endl;
+		if (argc >= 8 && std::string(argv[1]) == "trainrender")
+			return run_trainrender(argv[2], (uint32_t)atoi(argv[3]), atoi(argv[4]), atoi(argv[5]), atoi(argv[6]), (float)atof(argv[7]), argc > 8 ? (uint32_t)atoi(argv[8]) : (1u << 18));
+		std::cerr << "usage: ref_harness dump <dir> [batch] [n_rays] | bench <dir> <calls> <warmup_calls> [batch] | trainrender <dir> <calls> <W> <H> <spp> <fov> [batch]" << std::endl;
 		return 2;
 	} catch (const std::exception& e) {
 		std::cerr << "ref_harness: " << e.what() << std::endl;

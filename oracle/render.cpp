@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Parity unpinned.
+// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Pinned to golden vectors from the reference's CUDA build (tests/golden/).
 // CPU restatement of volume-render compositing:
 //   training fwd + loss + bwd + compaction : internal/render/ray_marcher.cu:15-213
 //   losses                                 : internal/utils/loss.cu:23-103

@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Parity unpinned.
+// TEST INFRASTRUCTURE ONLY (see oracle_common.h).  Pinned to golden vectors from the reference's CUDA build (tests/golden/).
 // CPU restatement of the occupancy sampler (internal/sampler/occupancy_sampler.cu):
 //   mark_untrained_density_grid :18-61     generate_grid_samples_nerf_nonuniform :63-105
 //   splat / ema                 :107-158   grid_to_bitfield / bitfield_max_pool  :160-205
