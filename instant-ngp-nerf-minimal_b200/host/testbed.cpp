@@ -29,6 +29,12 @@ Testbed::Testbed() {
 	if (props.major != 10) throw std::runtime_error("ngp_b200 kernels are built for sm_100a (B200) only; there is no fallback path.");
 	NGP_CUDA_CHECK(cudaStreamCreate(&m_stream));
 	for (auto& e : m_ev) NGP_CUDA_CHECK(cudaEventCreate(&e));
+	NGP_CUDA_CHECK(cudaStreamCreateWithFlags(&m_march_stream, cudaStreamNonBlocking));
+	NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_march_go, cudaEventDisableTiming));
+	for (int k = 0; k < 2; ++k) {
+		NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_march_ready[k], cudaEventDisableTiming));
+		NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_slot_free[k], cudaEventDisableTiming));
+	}
 	NGP_CUDA_CHECK(cudaMallocHost((void**)&m_host_counter, 64 * sizeof(uint32_t)));
 	m_training_buffer.loss_sum.resize(1024);
 	m_training_buffer.loss_sum.memset(0);
@@ -38,6 +44,8 @@ Testbed::Testbed() {
 
 Testbed::~Testbed() {
 	for (auto& e : m_ev) if (e) cudaEventDestroy(e);
+	for (cudaEvent_t e : {m_ev_march_go, m_ev_march_ready[0], m_ev_march_ready[1], m_ev_slot_free[0], m_ev_slot_free[1]}) if (e) cudaEventDestroy(e);
+	if (m_march_stream) cudaStreamDestroy(m_march_stream);
 	if (m_host_counter) cudaFreeHost(m_host_counter);
 	if (m_stream) cudaStreamDestroy(m_stream);
 }

@@ -84,10 +84,15 @@ public:
 		uint32_t n_rays_total = 0;
 		DeviceBuffer<Position> grid_positions;
 		DeviceBuffer<uint32_t> grid_indices;
-		DeviceBuffer<Ray> rays;
-		DeviceBuffer<float> rays_rgba;
-		DeviceBuffer<uint32_t> ray_coord_indices;
-		DeviceBuffer<Coordinate> coords, coords_compacted;
+		// Rays and marched samples are double-buffered: the march of step i+1 only depends on the occupancy bitfield and the host
+		// generator, so it runs on a second stream underneath step i's network / optimizer kernels.
+		struct MarchSlot {
+			DeviceBuffer<Ray> rays;
+			DeviceBuffer<float> rays_rgba;
+			DeviceBuffer<uint32_t> ray_coord_indices;
+			DeviceBuffer<Coordinate> coords;
+		} march[2];
+		DeviceBuffer<Coordinate> coords_compacted;
 		DeviceBuffer<uint32_t> compacted_src_index;   // marched-sample index of every compacted sample
 		DeviceBuffer<precision_t> rgbsigma, dloss_drgbsigma;
 		DeviceBuffer<uint32_t> n_coords_counter;            // [n_steps][2]: rays kept, samples counted
@@ -123,6 +128,11 @@ public:
 
 private:
 	cudaEvent_t m_ev[3] = {nullptr, nullptr, nullptr};
+	cudaStream_t m_march_stream = nullptr;
+	cudaEvent_t m_ev_march_go = nullptr, m_ev_march_ready[2] = {nullptr, nullptr}, m_ev_slot_free[2] = {nullptr, nullptr};
+	void march_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t n_rays_total, default_rng_t rng, uint32_t* counters, cudaStream_t stream);
+	void learn_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_rays_per_batch, default_rng_t rng, uint32_t* counters, uint32_t* compacted_counter, float* loss,
+	                cudaStream_t stream);
 	uint32_t* m_host_counter = nullptr;    // pinned
 	int m_dp_rank = 0, m_dp_world = 1;
 	void* m_nccl_comm = nullptr;

@@ -43,8 +43,44 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 	tb.loss.enlarge((size_t)n_rays * n_training_steps);
 	NGP_CUDA_CHECK(cudaMemsetAsync(tb.loss.data(), 0, sizeof(float) * n_rays * n_training_steps, stream));
 
-	for (uint32_t i = 0; i < n_training_steps; ++i)
-		train_nerf_step(target_batch_size, n_rays, tb.n_coords_counter.data() + 2 * i, tb.n_compacted_coords_counter.data() + i, tb.loss.data() + (size_t)n_rays * i, stream);
+	// Buffers grow before anything is enqueued (a reallocation would synchronise the device in the middle of the pipeline).
+	const uint32_t max_samples = target_batch_size * 16;
+	for (auto& slot : tb.march) {
+		slot.rays.enlarge(n_rays); slot.rays_rgba.enlarge((size_t)n_rays * 4); slot.ray_coord_indices.enlarge((size_t)n_rays * 2); slot.coords.enlarge(max_samples);
+	}
+	tb.coords_compacted.enlarge(target_batch_size);
+	tb.compacted_src_index.enlarge(target_batch_size);
+	tb.rgbsigma.enlarge((size_t)max_samples * m_network->padded_output_width());
+	tb.dloss_drgbsigma.enlarge((size_t)target_batch_size * m_network->padded_output_width());
+
+	// Software pipeline over the steps of this call.  The march of step i needs only the bitfield (fixed for the whole call) and
+	// host-side generator state, so it is issued one step ahead on m_march_stream and hides under step i-1's network and
+	// optimizer kernels; the main stream picks its output up through an event.  Results are identical to the serial schedule.
+	if (tb.i_step == 0) tb.n_rays_total = 0;
+	NGP_CUDA_CHECK(cudaEventRecord(m_ev_march_go, stream));               // after the refresh and the counter memsets
+	NGP_CUDA_CHECK(cudaStreamWaitEvent(m_march_stream, m_ev_march_go, 0));
+	default_rng_t rng_step = m_rng;
+	auto issue_march = [&](uint32_t i) {
+		const uint32_t slot = i & 1;
+		default_rng_t r = m_rng;
+		for (uint32_t k = 0; k < i; ++k) r.advance();
+		if (i >= 2) NGP_CUDA_CHECK(cudaStreamWaitEvent(m_march_stream, m_ev_slot_free[slot], 0));   // step i-2 has consumed this slot
+		march_step(slot, target_batch_size, n_rays, tb.n_rays_total + n_rays * i, r, tb.n_coords_counter.data() + 2 * i, m_march_stream);
+		NGP_CUDA_CHECK(cudaEventRecord(m_ev_march_ready[slot], m_march_stream));
+	};
+	issue_march(0);
+	for (uint32_t i = 0; i < n_training_steps; ++i) {
+		const uint32_t slot = i & 1;
+		if (i + 1 < n_training_steps) issue_march(i + 1);
+		NGP_CUDA_CHECK(cudaStreamWaitEvent(stream, m_ev_march_ready[slot], 0));
+		learn_step(slot, target_batch_size, n_rays, rng_step, tb.n_coords_counter.data() + 2 * i, tb.n_compacted_coords_counter.data() + i,
+		           tb.loss.data() + (size_t)n_rays * i, stream);
+		NGP_CUDA_CHECK(cudaEventRecord(m_ev_slot_free[slot], stream));
+		rng_step.advance();
+		++tb.i_step;
+	}
+	m_rng = rng_step;
+	tb.n_rays_total += n_rays * n_training_steps;
 
 	api_check(ngp_reduce_sum(stream, tb.loss.data(), (uint64_t)n_rays * n_training_steps, tb.loss_sum.data()));
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev[2], stream));
@@ -81,43 +117,39 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 	n_rays = std::min(next_multiple(n_rays, BATCH_SIZE_MULTIPLE), 1u << 18);
 }
 
-// testbed.cu:301-418
-void Testbed::train_nerf_step(uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t* counters, uint32_t* compacted_counter, float* loss, cudaStream_t stream) {
+// testbed.cu:301-344: rays + occupancy march + ordered compaction of one step, into march slot `slot`
+void Testbed::march_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t n_rays_total, default_rng_t rng, uint32_t* counters,
+                         cudaStream_t stream) {
 	TrainingBuffer& tb = m_training_buffer;
+	TrainingBuffer::MarchSlot& ms = tb.march[slot];
+	const uint32_t max_samples = target_batch_size * 16;
+	const uint32_t max_inference = next_multiple(std::min(tb.measured_batch_size_before_compaction, max_samples), BATCH_SIZE_MULTIPLE);
+	// each data-parallel rank draws its own pixels: the per-ray generator is advanced by i*8 draws inside the kernel, so rank r
+	// starts 2^18 * 8 draws further along (2^18 = the cap on rays per batch)
+	default_rng_t ray_rng = rng;
+	if (m_dp_rank) ray_rng.advance((int64_t)m_dp_rank * (1ll << 18) * 8);
+	m_sampler->sample_coords_from_dataset(n_rays_per_batch, n_rays_total, max_inference, tb.dataset, m_train_envmap, ms.rays, ms.rays_rgba, counters,
+	                                      ms.ray_coord_indices, ms.coords, counters + 1, ray_rng, stream);
+}
+
+// testbed.cu:346-418: everything of one step that depends on the current weights
+void Testbed::learn_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_rays_per_batch, default_rng_t rng, uint32_t* counters, uint32_t* compacted_counter,
+                         float* loss, cudaStream_t stream) {
+	TrainingBuffer& tb = m_training_buffer;
+	TrainingBuffer::MarchSlot& ms = tb.march[slot];
 	const uint32_t max_samples = target_batch_size * 16;
 	const uint32_t padded_output_width = m_network->padded_output_width();
 	const uint32_t max_inference = next_multiple(std::min(tb.measured_batch_size_before_compaction, max_samples), BATCH_SIZE_MULTIPLE);
 
-	tb.rays.enlarge(n_rays_per_batch);
-	tb.rays_rgba.enlarge((size_t)n_rays_per_batch * 4);
-	tb.ray_coord_indices.enlarge((size_t)n_rays_per_batch * 2);
-	tb.coords.enlarge(max_samples);
-	tb.coords_compacted.enlarge(target_batch_size);
-	tb.compacted_src_index.enlarge(target_batch_size);
-	tb.rgbsigma.enlarge((size_t)max_samples * padded_output_width);
-	tb.dloss_drgbsigma.enlarge((size_t)target_batch_size * padded_output_width);
-
-	if (tb.i_step == 0) tb.n_rays_total = 0;
-	const uint32_t n_rays_total = tb.n_rays_total;
-	tb.n_rays_total += n_rays_per_batch;
-
-	// each data-parallel rank draws its own pixels: the per-ray generator is advanced by i*8 draws inside the kernel, so rank r
-	// starts 2^18 * 8 draws further along (2^18 = the cap on rays per batch)
-	default_rng_t ray_rng = m_rng;
-	if (m_dp_rank) ray_rng.advance((int64_t)m_dp_rank * (1ll << 18) * 8);
-
-	// 1. rays + occupancy march + ordered compaction
-	m_sampler->sample_coords_from_dataset(n_rays_per_batch, n_rays_total, max_inference, tb.dataset, m_train_envmap, tb.rays, tb.rays_rgba, counters,
-	                                      tb.ray_coord_indices, tb.coords, counters + 1, ray_rng, stream);
 	// 2. network on every marched sample (training weights); the device-side count bounds the work
-	m_network->inference_mixed_precision(stream, tb.coords.data(), max_inference, counters + 1, tb.rgbsigma.data(), false);
+	m_network->inference_mixed_precision(stream, ms.coords.data(), max_inference, counters + 1, tb.rgbsigma.data(), false);
 	// 3. compositing, loss, dL/d(rgb sigma), compaction.  Data parallel: every rank's gradient carries 1/world of the loss scale,
 	//    so the NCCL sum below is the mean over ranks and stays inside fp16 range.
 	m_render->volume_rendering_with_loss_and_gradient(
-		n_rays_per_batch, target_batch_size, tb.rays, tb.rays_rgba, counters, tb.ray_coord_indices, tb.coords, tb.coords_compacted, compacted_counter,
+		n_rays_per_batch, target_batch_size, ms.rays, ms.rays_rgba, counters, ms.ray_coord_indices, ms.coords, tb.coords_compacted, compacted_counter,
 		tb.rgbsigma, tb.dloss_drgbsigma, (int)padded_output_width, m_rgb_activation, m_density_activation, loss, m_loss_type, LOSS_SCALE / (float)m_dp_world,
 		m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, m_sampler->density_grid_mean, m_sampler->min_optical_thickness,
-		m_background_color, m_color_space, m_rng, stream, tb.compacted_src_index.data());
+		m_background_color, m_color_space, rng, stream, tb.compacted_src_index.data());
 	// 4. rollover
 	api_check(ngp_rollover(stream, target_batch_size, compacted_counter, tb.dloss_drgbsigma.data(), padded_output_width, (float*)tb.coords_compacted.data(),
 	                       tb.compacted_src_index.data()));
@@ -132,8 +164,25 @@ void Testbed::train_nerf_step(uint32_t target_batch_size, uint32_t n_rays_per_ba
 		if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce failed: ") + ncclGetErrorString(r));
 	}
 	// 7. optimizer
-	m_rng.advance();
 	m_trainer->optimizer_step(stream, LOSS_SCALE);
+}
+
+// the reference's single-step entry point (testbed.cu:301-418), kept for callers that drive steps themselves: serial schedule
+void Testbed::train_nerf_step(uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t* counters, uint32_t* compacted_counter, float* loss, cudaStream_t stream) {
+	TrainingBuffer& tb = m_training_buffer;
+	const uint32_t max_samples = target_batch_size * 16;
+	TrainingBuffer::MarchSlot& ms = tb.march[0];
+	ms.rays.enlarge(n_rays_per_batch); ms.rays_rgba.enlarge((size_t)n_rays_per_batch * 4); ms.ray_coord_indices.enlarge((size_t)n_rays_per_batch * 2);
+	ms.coords.enlarge(max_samples);
+	tb.coords_compacted.enlarge(target_batch_size);
+	tb.compacted_src_index.enlarge(target_batch_size);
+	tb.rgbsigma.enlarge((size_t)max_samples * m_network->padded_output_width());
+	tb.dloss_drgbsigma.enlarge((size_t)target_batch_size * m_network->padded_output_width());
+	if (tb.i_step == 0) tb.n_rays_total = 0;
+	march_step(0, target_batch_size, n_rays_per_batch, tb.n_rays_total, m_rng, counters, stream);
+	tb.n_rays_total += n_rays_per_batch;
+	learn_step(0, target_batch_size, n_rays_per_batch, m_rng, counters, compacted_counter, loss, stream);
+	m_rng.advance();
 	++tb.i_step;
 }
 
