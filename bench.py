@@ -23,6 +23,7 @@ sys.path.insert(0, ROOT)
 PKG = "instant-ngp-nerf-minimal_b200"
 METRIC = "nerf_train_samples_per_s"
 UNIT = "samples/s"
+ENQUEUE_MS = 0.0                     # host time spent issuing work, summed over train() calls (diagnostic)
 CALL_STEPS = 16                      # run.py:71 trains in calls of 16 steps; the occupancy grid is refreshed once per call
 
 
@@ -51,13 +52,41 @@ def config_dict(args, n_gpus):
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled while the timed region runs"""
+    """SM clock + throttle reasons sampled WHILE the timed region runs.  NVML in a thread (pyngp releases the GIL inside train());
+    spawning nvidia-smi every 100 ms measurably disturbs a step that lasts 0.7 ms, so it is only the fallback."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.sm, self.mx, self.reasons, self.stop_flag, self.thread, self.nvml = [], [], set(), False, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml, self.handle = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+        except Exception:
+            self.nvml = None
+
+    def _poll(self):
+        n = self.nvml
+        names = {n.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", n.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 n.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", n.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.sm.append(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+                self.mx.append(n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM))
+                r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
 
     def start(self):
+        if self.nvml is not None:
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -66,6 +95,11 @@ class ClockSampler:
             self.proc = None
 
     def stop(self):
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=1.0)
+            return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": float(max(self.mx)) if self.mx else None,
+                    "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -79,7 +113,8 @@ class ClockSampler:
             for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[2:6]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvidia-smi"}
 
 
 def measured_peaks():
@@ -224,6 +259,7 @@ def run_reference(args):
 
 def train_steps(tb, n_steps, batch):
     """n_steps training steps in calls of CALL_STEPS; returns (post-compaction samples, marched samples, rays, device ms)"""
+    global ENQUEUE_MS
     done, samples, marched, rays, dev_ms = 0, 0, 0, 0, 0.0
     while done < n_steps:
         k = min(CALL_STEPS, n_steps - done)
@@ -234,6 +270,7 @@ def train_steps(tb, n_steps, batch):
         marched += sum(b.n_coords_counter_cpu)
         rays += r * k
         dev_ms += b.training_ms + b.training_prep_ms
+        ENQUEUE_MS += b.enqueue_ms
         done += k
     return samples, marched, rays, dev_ms
 
@@ -290,7 +327,9 @@ def run_ours(args):
     launches0 = lib.ngp_launch_count()
     clocks.start()
     t0 = time.perf_counter()
+    enq0 = ENQUEUE_MS
     samples, marched, rays, dev_ms = train_steps(tb, args.steps, args.batch)
+    enqueue_ms = ENQUEUE_MS - enq0
     barrier()
     wall = time.perf_counter() - t0
     clk = clocks.stop()
@@ -299,7 +338,9 @@ def run_ours(args):
     # ---- per-kernel durations, live, with CUDA events on the launching stream (same workload, a further timed region) ----
     prof_steps = min(args.steps, 64)
     capi.check(lib.ngp_kernel_timing_enable(1, 64 * prof_steps + 4096))
+    tb.pipeline_march = False             # kernels one after another on one stream, so each duration is the kernel's own
     p_samples, p_marched, p_rays, _ = train_steps(tb, prof_steps, args.batch)
+    tb.pipeline_march = True
     kt = capi.kernel_timing_collect()
     capi.check(lib.ngp_kernel_timing_enable(0, 0))
 
@@ -342,7 +383,8 @@ def run_ours(args):
            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
            "config": config_dict(args, args.gpus), "clocks": clk, "gpu_launches": int(launches),
            "e2e": {"value": samples / (wall + t_upload), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes / args.steps,
-                   "d2h_bytes_per_step": (3 * 4 * CALL_STEPS + 4) / CALL_STEPS, "wall_ms_per_step": wall / args.steps * 1e3, "dataset_upload_ms": t_upload * 1e3},
+                   "d2h_bytes_per_step": (3 * 4 * CALL_STEPS + 4) / CALL_STEPS, "wall_ms_per_step": wall / args.steps * 1e3, "dataset_upload_ms": t_upload * 1e3,
+                   "host_enqueue_ms_per_step": enqueue_ms / args.steps},
            "roofline": roofline,
            "samples_marched_per_step": marched / args.steps / max(world, 1), "rays_per_step": rays / args.steps / max(world, 1), "loss": tb.training_buffer.loss}
     if args.gpus == 1 and not args.no_ref_cuda:

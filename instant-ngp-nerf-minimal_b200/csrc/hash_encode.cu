@@ -40,7 +40,7 @@ __device__ __forceinline__ void pos_fract(float x, float scale, uint32_t& g, flo
 	w = p - f;
 }
 
-template <bool WRITE_INDICES>
+template <bool WRITE_INDICES, bool PAIRS = true>
 __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n, const uint32_t* __restrict__ n_valid,
 	const __half2* __restrict__ table, const __grid_constant__ ngp_grid_desc desc,
@@ -64,9 +64,25 @@ __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 		#pragma unroll
 		for (int c = 0; c < 8; ++c)
 			e[c] = grid_index(size, res, hashed, gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
+		// The two x-neighbours of a corner pair are adjacent table entries whenever the lower one has an even index (hashed:
+		// gx ^ h and (gx+1) ^ h differ in bit 0 only when gx is even; dense: e and e+1).  One aligned 8-byte load then brings
+		// both, and only the other half of the lanes issue a second gather: a quarter fewer L1 wavefronts per level.
 		__half2 v[8];
+		if (!PAIRS) {
+			#pragma unroll
+			for (int c = 0; c < 8; ++c) v[c] = __ldg(grid + e[c]);
+		} else {
+		uint2 pr[4];
 		#pragma unroll
-		for (int c = 0; c < 8; ++c) v[c] = __ldg(grid + e[c]);
+		for (int c = 0; c < 8; c += 2) pr[c >> 1] = __ldg(reinterpret_cast<const uint2*>(grid) + (e[c] >> 1));
+		#pragma unroll
+		for (int c = 0; c < 8; c += 2) {
+			const uint32_t lo = (e[c] & 1u) ? pr[c >> 1].y : pr[c >> 1].x, buddy = (e[c] & 1u) ? pr[c >> 1].x : pr[c >> 1].y;
+			v[c] = *reinterpret_cast<const __half2*>(&lo);
+			if (e[c + 1] == (e[c] ^ 1u)) v[c + 1] = *reinterpret_cast<const __half2*>(&buddy);
+			else v[c + 1] = __ldg(grid + e[c + 1]);
+		}
+		}
 		__half2 acc = __floats2half2_rn(0.f, 0.f);
 		#pragma unroll
 		for (int c = 0; c < 8; ++c) {
@@ -83,8 +99,39 @@ __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 	}
 }
 
-// Backward: warp = 32 consecutive samples, one level at a time.  Equal entry indices in neighbouring lanes are summed in
-// fp32 with a segmented shuffle reduction and leave the warp as ONE red.global.add.noftz.f16x2.
+// segmented sum over runs of equal keys in neighbouring lanes; returns true on the first lane of each run (which then holds the run's sums)
+template <int N>
+__device__ __forceinline__ bool warp_run_sum(uint32_t key, uint32_t lane, float (&v)[N]) {
+	const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+	const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0 || prev != key);
+	if (heads != 0xffffffffu) {
+		const uint32_t above = heads & ~((2u << lane) - 1u);           // heads strictly above this lane
+		const uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;   // last lane of this lane's run
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			float a[N];
+			#pragma unroll
+			for (int k = 0; k < N; ++k) a[k] = __shfl_down_sync(0xffffffffu, v[k], o);
+			if (lane + o <= end) {
+				#pragma unroll
+				for (int k = 0; k < N; ++k) v[k] += a[k];
+			}
+		}
+	}
+	return (heads >> lane) & 1u;
+}
+
+__device__ __forceinline__ void red_half2(__half2* p, float x, float y) { atomicAdd(p, __floats2half2_rn(x, y)); }
+// one 8-byte reduction onto two adjacent half2 entries (p 8-byte aligned): REDG.E.ADD.F16x4
+__device__ __forceinline__ void red_half2x2(__half2* p, float x0, float y0, float x1, float y1) {
+	const __half2 a = __floats2half2_rn(x0, y0), b = __floats2half2_rn(x1, y1);
+	asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" :: "l"(p), "r"(*reinterpret_cast<const uint32_t*>(&a)), "r"(*reinterpret_cast<const uint32_t*>(&b)) : "memory");
+}
+
+// Backward: warp = 32 consecutive samples, one level at a time.  Per corner pair along x: when the two entries are adjacent in
+// the table (lower index even, see the forward kernel) they leave as ONE 8-byte reduction.  Before that, equal targets in
+// neighbouring lanes (samples of one ray inside one cell) are summed in fp32 with a segmented shuffle reduction, so the
+// contended coarse levels issue one reduction per run instead of one per sample.
 __global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
 	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad)
@@ -105,28 +152,36 @@ __global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
 		pos_fract(x, scale, gx, wx); pos_fract(y, scale, gy, wy); pos_fract(z, scale, gz, wz);
 		const float2 g = __half22float2(*reinterpret_cast<const __half2*>(drow + 2 * l));
 		#pragma unroll
-		for (int c = 0; c < 8; ++c) {
-			float w = 1.f;
-			w *= (c & 1) ? wx : 1 - wx;
-			w *= (c & 2) ? wy : 1 - wy;
-			w *= (c & 4) ? wz : 1 - wz;
-			const uint32_t e = valid ? grid_index(size, res, hashed, gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1)) : 0xffffffffu - lane;
+		for (int c = 0; c < 8; c += 2) {
+			// same product order as the forward pass: (wx' * wy') * wz'
+			const float w0 = ((1 - wx) * ((c & 2) ? wy : 1 - wy)) * ((c & 4) ? wz : 1 - wz);
+			const float w1 = (wx * ((c & 2) ? wy : 1 - wy)) * ((c & 4) ? wz : 1 - wz);
+			const uint32_t e0 = grid_index(size, res, hashed, gx, gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
+			const uint32_t e1 = grid_index(size, res, hashed, gx + 1, gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
+			const bool paired = e1 == (e0 ^ 1u);
 			// per-term fp16 rounding as in grid.h:303-306, then exact fp32 sums inside the warp
-			float2 t = __half22float2(__floats2half2_rn(g.x * w, g.y * w));
-			const uint32_t prev = __shfl_up_sync(0xffffffffu, e, 1);
-			const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0 || prev != e);
-			if (heads != 0xffffffffu) {
-				// segment of this lane: [start, end]
-				const uint32_t above = heads & ~((2u << lane) - 1u);           // heads strictly above lane
-				const uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;
-				#pragma unroll
-				for (int o = 1; o < 32; o <<= 1) {
-					const float ax = __shfl_down_sync(0xffffffffu, t.x, o);
-					const float ay = __shfl_down_sync(0xffffffffu, t.y, o);
-					if (lane + o <= end) { t.x += ax; t.y += ay; }
+			const float2 t0 = __half22float2(__floats2half2_rn(g.x * w0, g.y * w0)), t1 = __half22float2(__floats2half2_rn(g.x * w1, g.y * w1));
+			// round A: entry e0 of every lane, together with e1 where the two are adjacent
+			{
+				float v[4] = {t0.x, t0.y, paired ? t1.x : 0.f, paired ? t1.y : 0.f};
+				const uint32_t key = valid ? (e0 | (paired ? 0x80000000u : 0u)) : 0x7fffffffu - lane;
+				const bool head = warp_run_sum<4>(key, lane, v);
+				if (valid && head) {
+					if (paired) {
+						if (e0 & 1u) red_half2x2(grid + (e0 ^ 1u), v[2], v[3], v[0], v[1]);
+						else red_half2x2(grid + e0, v[0], v[1], v[2], v[3]);
+					} else {
+						red_half2(grid + e0, v[0], v[1]);
+					}
 				}
 			}
-			if (valid && ((heads >> lane) & 1u)) atomicAdd(grid + e, __floats2half2_rn(t.x, t.y));
+			// round B: entry e1 of the lanes whose pair is not adjacent
+			if (__any_sync(0xffffffffu, valid && !paired)) {
+				float v[2] = {t1.x, t1.y};
+				const uint32_t key = (valid && !paired) ? e1 : 0x7fffffffu - lane;
+				const bool head = warp_run_sum<2>(key, lane, v);
+				if (valid && !paired && head) red_half2(grid + e1, v[0], v[1]);
+			}
 		}
 	}
 }
@@ -161,6 +216,7 @@ extern "C" uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, u
 extern "C" int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_table,
                                    const ngp_grid_desc* desc, void* d_out, uint32_t out_stride, uint32_t* d_indices) {
 	NGP_REQUIRE(d_xyz && d_table && desc && d_out, "null pointer");
+	NGP_REQUIRE(((uintptr_t)d_table & 7u) == 0, "d_table must be 8-byte aligned");
 	NGP_REQUIRE(out_stride >= 2 * desc->n_levels && out_stride % 2 == 0, "out_stride too small or odd");
 	if (n == 0) return 0;
 	const uint32_t grid = div_up(n, 256);
@@ -173,7 +229,9 @@ namespace ngp {
 int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const uint32_t* d_n_valid,
                             const void* d_table, const ngp_grid_desc* desc, void* d_out, uint32_t out_stride) {
 	if (n == 0) return 0;
-	NGP_LAUNCH("hash_encode_fwd_kernel", stream, hash_encode_fwd_kernel<false><<<div_up(n, 256), 256, 0, stream>>>(d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	static const bool pairs = !(getenv("NGP_HASH_PAIRS") && getenv("NGP_HASH_PAIRS")[0] == '0');
+	if (pairs) NGP_LAUNCH("hash_encode_fwd_kernel", stream, hash_encode_fwd_kernel<false><<<div_up(n, 256), 256, 0, stream>>>(d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	else NGP_LAUNCH("hash_encode_fwd_kernel", stream, hash_encode_fwd_kernel<false, false><<<div_up(n, 256), 256, 0, stream>>>(d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
 	return check_launch("hash_encode_fwd");
 }
 }
@@ -181,6 +239,7 @@ int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t st
 extern "C" int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
                                    const ngp_grid_desc* desc, void* d_grad, int zero_first) {
 	NGP_REQUIRE(d_xyz && d_dy && desc && d_grad, "null pointer");
+	NGP_REQUIRE(((uintptr_t)d_grad & 7u) == 0, "d_grad must be 8-byte aligned");
 	if (zero_first) {
 		if (cudaMemsetAsync(d_grad, 0, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half), (cudaStream_t)stream) != cudaSuccess) { set_error("ngp_hash_encode_bwd: memset failed"); return -2; }
 	}

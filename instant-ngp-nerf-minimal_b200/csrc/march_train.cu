@@ -138,15 +138,16 @@ __global__ void __launch_bounds__(256) march_count_kernel(
 	const uint8_t* __restrict__ bits, int snap, Pcg32 rng, uint32_t* __restrict__ n_out, uint32_t* __restrict__ per_ray_n,
 	uint32_t* __restrict__ n_windows_out, uint32_t* __restrict__ masks_out)
 {
-	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	if (i >= n_rays) return;
-	const RaySetup r = setup_ray(c, cam, i, n_rays, n_rays_shift, n_images, xforms, snap, rng);
-	uint32_t rec_lo, rec_hi, nw;
-	const uint32_t n = march_ray<false, true>(c, r, bits, lane, c.max_steps, nullptr, rec_lo, rec_hi, nw);
-	if (lane == 0) { n_out[i] = n; n_windows_out[i] = nw; if (per_ray_n) per_ray_n[i] = n; }
-	if (n > 0 && nw <= kMaskWindows) {
-		if (lane < nw) masks_out[(size_t)i * kMaskWindows + lane] = rec_lo;
-		if (lane + 32 < nw) masks_out[(size_t)i * kMaskWindows + 32 + lane] = rec_hi;
+	const uint32_t lane = threadIdx.x & 31, warps = gridDim.x * (blockDim.x >> 5);
+	for (uint32_t i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n_rays; i += warps) {
+		const RaySetup r = setup_ray(c, cam, i, n_rays, n_rays_shift, n_images, xforms, snap, rng);
+		uint32_t rec_lo, rec_hi, nw;
+		const uint32_t n = march_ray<false, true>(c, r, bits, lane, c.max_steps, nullptr, rec_lo, rec_hi, nw);
+		if (lane == 0) { n_out[i] = n; n_windows_out[i] = nw; if (per_ray_n) per_ray_n[i] = n; }
+		if (n > 0 && nw <= kMaskWindows) {
+			if (lane < nw) masks_out[(size_t)i * kMaskWindows + lane] = rec_lo;
+			if (lane + 32 < nw) masks_out[(size_t)i * kMaskWindows + 32 + lane] = rec_hi;
+		}
 	}
 }
 
@@ -194,10 +195,10 @@ __global__ void __launch_bounds__(256) march_emit_kernel(
 	const uint32_t* __restrict__ n_in, const uint32_t* __restrict__ base_in, const uint32_t* __restrict__ ridx_in,
 	const uint32_t* __restrict__ n_windows_in, const uint32_t* __restrict__ masks_in, float* __restrict__ rays_out, float4* __restrict__ rgba_out, uint32_t* __restrict__ numsteps_out, Coordinate* __restrict__ coords_out)
 {
-	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	if (i >= n_rays) return;
+	const uint32_t lane = threadIdx.x & 31, warps = gridDim.x * (blockDim.x >> 5);
+	for (uint32_t i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n_rays; i += warps) {
 	const uint32_t n = n_in[i], base = base_in[i], ray_idx = ridx_in[i];
-	if (n == 0 || (uint64_t)base + n > n_coords) return;      // no samples, or over budget: dropped like the reference does
+	if (n == 0 || (uint64_t)base + n > n_coords) continue;    // no samples, or over budget: dropped like the reference does
 	const RaySetup r = setup_ray(c, cam, i, n_rays, n_rays_shift, n_images, xforms, snap, rng);
 	if (lane == 0) {
 		float* ro = rays_out + (size_t)ray_idx * 6;
@@ -217,6 +218,7 @@ __global__ void __launch_bounds__(256) march_emit_kernel(
 	} else {
 		uint32_t a, b, w;
 		march_ray<true, false>(c, r, bits, lane, n, coords_out + base, a, b, w);   // very long rays: march again
+	}
 	}
 }
 
@@ -240,7 +242,9 @@ extern "C" int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg
 	uint32_t* ridx_tmp = base_tmp + n_rays;
 	uint32_t* nwin_tmp = ridx_tmp + n_rays;
 	uint32_t* mask_tmp = nwin_tmp + n_rays;
-	const uint32_t grid = div_up(n_rays, 8);
+	// at most 4 CTAs (32 warps) per SM: the march is latency-bound and usually runs underneath another stream's kernels
+	static const uint32_t ctas_per_sm = getenv("NGP_MARCH_CTAS") ? (uint32_t)atoi(getenv("NGP_MARCH_CTAS")) : 4u;
+	const uint32_t grid = std::min(div_up(n_rays, 8), kNumSMs * ctas_per_sm);
 	NGP_LAUNCH("march_count_kernel", s, march_count_kernel<<<grid, 256, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_images, d_xforms, d_bitfield,
 		snap_to_pixel_centers, rng, n_tmp, d_per_ray_n, nwin_tmp, mask_tmp));
 	NGP_LAUNCH("march_scan_kernel", s, march_scan_kernel<<<1, 1024, 0, s>>>(n_rays, n_coords, n_tmp, base_tmp, ridx_tmp, d_counters));

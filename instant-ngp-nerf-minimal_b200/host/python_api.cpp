@@ -88,6 +88,7 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readwrite("color_space", &Testbed::m_color_space)
 		.def_readonly("training_buffer", &Testbed::m_training_buffer)
 		.def_readonly("rendering_buffer", &Testbed::m_rendering_buffer)
+		.def_readwrite("pipeline_march", &Testbed::m_pipeline_march, "march step i+1 on a second stream underneath step i (default on)")
 		.def_property("fov", &Testbed::fov, &Testbed::set_fov)
 		.def_property("fov_xy",
 			[](const Testbed& t) { return std::vector<float>{focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[0]), focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[1])}; },
@@ -116,6 +117,7 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readonly("loss", &Testbed::TrainingBuffer::loss_scalar)
 		.def_readonly("training_prep_ms", &Testbed::TrainingBuffer::training_prep_ms)
 		.def_readonly("training_ms", &Testbed::TrainingBuffer::training_ms)
+		.def_readonly("enqueue_ms", &Testbed::TrainingBuffer::enqueue_ms)
 		.def_readonly("i_step", &Testbed::TrainingBuffer::i_step)
 		// per-step device counters of the last train() call (exact, for throughput accounting)
 		.def_readonly("n_coords_counter_cpu", &Testbed::TrainingBuffer::n_coords_counter_cpu)

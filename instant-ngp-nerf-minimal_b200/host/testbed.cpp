@@ -27,9 +27,12 @@ Testbed::Testbed() {
 	if (error == cudaSuccess) error = cudaGetDeviceProperties(&props, dev);
 	if (error != cudaSuccess) throw std::runtime_error(std::string("cudaGetDeviceProperties() returned an error: ") + cudaGetErrorString(error));
 	if (props.major != 10) throw std::runtime_error("ngp_b200 kernels are built for sm_100a (B200) only; there is no fallback path.");
-	NGP_CUDA_CHECK(cudaStreamCreate(&m_stream));
+	// the training stream outranks the look-ahead march stream: when both have blocks pending, the step's own kernels go first
+	int prio_lo = 0, prio_hi = 0;
+	NGP_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+	NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_stream, cudaStreamNonBlocking, prio_hi));
 	for (auto& e : m_ev) NGP_CUDA_CHECK(cudaEventCreate(&e));
-	NGP_CUDA_CHECK(cudaStreamCreateWithFlags(&m_march_stream, cudaStreamNonBlocking));
+	NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_march_stream, cudaStreamNonBlocking, prio_lo));
 	NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_march_go, cudaEventDisableTiming));
 	for (int k = 0; k < 2; ++k) {
 		NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_march_ready[k], cudaEventDisableTiming));

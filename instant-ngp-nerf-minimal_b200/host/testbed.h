@@ -2,6 +2,7 @@
 // save/load_snapshot, train(n_steps, batch), render_frame / render, fov helpers, training_buffer / rendering_buffer views),
 // driving the sampler / network / render modules whose kernels live behind the C ABI.
 #pragma once
+#include <chrono>
 #include <memory>
 #include "common.h"
 #include "json.h"
@@ -104,6 +105,7 @@ public:
 		DeviceBuffer<float> loss_sum;                       // reduce_sum result + scratch
 		float loss_scalar = 0.f;
 		float training_prep_ms = 0, training_ms = 0;
+		float enqueue_ms = 0;                               // host time spent issuing the last train() call's work (before the one sync)
 		uint32_t i_step = 0;
 	} m_training_buffer;
 
@@ -128,6 +130,10 @@ public:
 
 private:
 	cudaEvent_t m_ev[3] = {nullptr, nullptr, nullptr};
+public:
+	bool m_pipeline_march = true;      // false: issue the march on the main stream (serial schedule; used when timing kernels one by one)
+private:
+	std::chrono::steady_clock::time_point m_enqueue_start;
 	cudaStream_t m_march_stream = nullptr;
 	cudaEvent_t m_ev_march_go = nullptr, m_ev_march_ready[2] = {nullptr, nullptr}, m_ev_slot_free[2] = {nullptr, nullptr};
 	void march_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t n_rays_total, default_rng_t rng, uint32_t* counters, cudaStream_t stream);

@@ -2,6 +2,7 @@
 #include "testbed.h"
 #include <nccl.h>
 #include <algorithm>
+#include <chrono>
 
 namespace ngp {
 
@@ -10,6 +11,7 @@ namespace ngp {
 void Testbed::train(uint32_t n_training_steps, uint32_t target_batch_size) {
 	if (!m_trainer || m_training_buffer.dataset.n_images == 0) throw std::runtime_error("train: load_model_config and load_training_data first");
 	if (n_training_steps == 0) return;
+	m_enqueue_start = std::chrono::steady_clock::now();
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev[0], m_stream));
 	train_prep_nerf(target_batch_size, n_training_steps, m_stream);
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev[1], m_stream));
@@ -57,16 +59,17 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 	// host-side generator state, so it is issued one step ahead on m_march_stream and hides under step i-1's network and
 	// optimizer kernels; the main stream picks its output up through an event.  Results are identical to the serial schedule.
 	if (tb.i_step == 0) tb.n_rays_total = 0;
+	cudaStream_t march_stream = m_pipeline_march ? m_march_stream : stream;
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev_march_go, stream));               // after the refresh and the counter memsets
-	NGP_CUDA_CHECK(cudaStreamWaitEvent(m_march_stream, m_ev_march_go, 0));
+	NGP_CUDA_CHECK(cudaStreamWaitEvent(march_stream, m_ev_march_go, 0));
 	default_rng_t rng_step = m_rng;
 	auto issue_march = [&](uint32_t i) {
 		const uint32_t slot = i & 1;
 		default_rng_t r = m_rng;
 		for (uint32_t k = 0; k < i; ++k) r.advance();
-		if (i >= 2) NGP_CUDA_CHECK(cudaStreamWaitEvent(m_march_stream, m_ev_slot_free[slot], 0));   // step i-2 has consumed this slot
-		march_step(slot, target_batch_size, n_rays, tb.n_rays_total + n_rays * i, r, tb.n_coords_counter.data() + 2 * i, m_march_stream);
-		NGP_CUDA_CHECK(cudaEventRecord(m_ev_march_ready[slot], m_march_stream));
+		if (i >= 2) NGP_CUDA_CHECK(cudaStreamWaitEvent(march_stream, m_ev_slot_free[slot], 0));   // step i-2 has consumed this slot
+		march_step(slot, target_batch_size, n_rays, tb.n_rays_total + n_rays * i, r, tb.n_coords_counter.data() + 2 * i, march_stream);
+		NGP_CUDA_CHECK(cudaEventRecord(m_ev_march_ready[slot], march_stream));
 	};
 	issue_march(0);
 	for (uint32_t i = 0; i < n_training_steps; ++i) {
@@ -85,6 +88,7 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 	api_check(ngp_reduce_sum(stream, tb.loss.data(), (uint64_t)n_rays * n_training_steps, tb.loss_sum.data()));
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev[2], stream));
 
+	tb.enqueue_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - m_enqueue_start).count();
 	// GPU -> CPU: the one synchronisation of a train() call
 	std::vector<uint32_t> pairs((size_t)n_training_steps * 2);
 	tb.n_compacted_coords_counter_cpu.resize(n_training_steps);
