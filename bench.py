@@ -37,6 +37,8 @@ def parse():
     p.add_argument("--views", type=int, default=100)
     p.add_argument("--res", type=int, default=800)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--dp-mode", default="peer", choices=["peer", "nccl"],
+                   help="N > 1: fused reduce-scatter + Adam + all-gather over NVLink peer memory (default), or NCCL all-reduce + replicated optimizer")
     p.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference's own CUDA build (oracle/_ref/ref_harness) beside ours")
     p.add_argument("--reference-kind", default="auto", choices=["auto", "cuda", "cpu"],
                    help="--impl reference: the reference's CUDA build when oracle/_ref/ref_harness exists (auto/cuda), or the CPU oracle port")
@@ -46,7 +48,7 @@ def parse():
 def config_dict(args, n_gpus):
     return {"workload": f"configs[1]: nerf_synthetic-shaped procedural scene, {args.views} views {args.res}x{args.res}, base.json model (L=16 F=2 T=2^19, 64-wide MLPs), "
                         f"{args.batch}-sample batches, occupancy refresh every {CALL_STEPS} steps",
-            "global_batch": args.batch * n_gpus, "per_gpu_batch": args.batch, "parallelism": f"dp{n_gpus}" if n_gpus > 1 else "single",
+            "global_batch": args.batch * n_gpus, "per_gpu_batch": args.batch, "parallelism": (f"dp{n_gpus} ({'peer-memory sharded optimizer' if args.dp_mode == 'peer' else 'nccl all-reduce'})") if n_gpus > 1 else "single",
             "l2_policy": "inputs larger than L2 (512 MB fp16 image set sampled at random pixels; 37-117 MB of samples streamed per step); "
                          "the 23 MB hash table is L2-resident by design, as in the real workload"}
 
@@ -306,7 +308,7 @@ def run_ours(args):
         box = [pyngp.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)
         comm = pyngp.nccl_comm_init(box[0], rank, world)
-        tb.set_data_parallel(rank, world, comm)
+        tb.set_data_parallel(rank, world, comm, args.dp_mode == "peer")
     # host -> device upload of the dataset through the public API, timed on its second (warm) execution
     tb.load_training_data_from_memory(np_rgba8, ogl, scene.CAMERA_ANGLE_X, 0.33, [0.5, 0.5, 0.5])
     torch.cuda.synchronize()

@@ -171,6 +171,31 @@ int ngp_init_params(void* stream, uint64_t* rng_state, uint64_t rng_inc, uint64_
 /* Trainer::optimizer_step (trainer.h:198) -> ExponentialDecay -> Adam -> EMA, one fused pass.  step = Adam step count BEFORE this step. */
 int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, uint64_t n_params, uint64_t n_matrix_params, uint32_t step, float learning_rate,
                        float* d_w32, void* d_w16, const void* d_g16, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16);
+/* ---- data-parallel optimizer over NVLink peer memory ------------------------------------------------
+ * One process per GPU.  Instead of "all-reduce the gradient arena, then every rank runs the whole optimizer", rank r owns the
+ * parameter range [shard_begin, shard_end): ONE kernel waits until every rank has published its gradients, sums the shard's
+ * gradients straight out of the peers' arenas (P2P loads, fixed rank order, fp32), applies the same Adam + EMA update as
+ * ngp_optimizer_step to the shard's state, and stores the new fp16 weights into every rank's parameter arena (P2P stores):
+ * reduce-scatter + optimizer + all-gather without staging buffers, and 1/world of the optimizer work per GPU.
+ * Pointers in ngp_peer_set are addresses valid ON THIS DEVICE (own allocations, and peers' opened through CUDA IPC).
+ * flags: per rank, 2*NGP_MAX_PEERS uint32 in that rank's memory, zero-initialised; [p] = last epoch whose gradients rank p
+ * published to me, [NGP_MAX_PEERS + p] = last epoch whose weights rank p finished storing into my arena. */
+#define NGP_MAX_PEERS 8
+typedef struct ngp_peer_set {
+	uint32_t world, rank;
+	const void* grads[NGP_MAX_PEERS];     /* fp16 gradient arena of rank p */
+	void* params[NGP_MAX_PEERS];          /* fp16 parameter arena of rank p */
+	uint32_t* flags[NGP_MAX_PEERS];       /* flag block of rank p */
+} ngp_peer_set;
+/* after the backward pass: tell every rank that this rank's gradients of `epoch` (>= 1, increasing) are complete */
+int ngp_peer_publish_gradients(void* stream, const ngp_peer_set* peers, uint32_t epoch);
+/* the fused step on [shard_begin, shard_end) (multiples of 8); state arrays are full-size, only the shard is touched */
+int ngp_optimizer_step_sharded(void* stream, const ngp_optimizer_cfg* cfg, uint64_t shard_begin, uint64_t shard_end, uint64_t n_matrix_params, uint32_t step,
+                               float learning_rate, float* d_w32, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16,
+                               const ngp_peer_set* peers, uint32_t epoch, uint32_t* d_ticket /* one zeroed uint32 of scratch */);
+/* before anything reads the parameters again: wait until every rank has stored its shard of `epoch` into this rank's arena */
+int ngp_peer_wait_weights(void* stream, const ngp_peer_set* peers, uint32_t epoch);
+
 /* from_rgba32<__half> (internal/utils/common_device.h:160-175) */
 int ngp_from_rgba32(void* stream, uint64_t n_pixels, const uint8_t* d_rgba8, void* d_out_half);
 /* reduce_sum of the per-ray loss (testbed.cu:288).  d_out: 1 result float followed by >= 599 floats of scratch; the word

@@ -35,6 +35,13 @@ class RenderCfg(C.Structure):
                 ("transmittance_threshold", f32), ("min_optical_thickness", f32), ("loss_scale", f32), ("background_color", f32 * 3)]
 
 
+NGP_MAX_PEERS = 8
+
+
+class PeerSet(C.Structure):
+    _fields_ = [("world", u32), ("rank", u32), ("grads", vp * NGP_MAX_PEERS), ("params", vp * NGP_MAX_PEERS), ("flags", vp * NGP_MAX_PEERS)]
+
+
 class OptimizerCfg(C.Structure):
     _fields_ = [("learning_rate", f32), ("beta1", f32), ("beta2", f32), ("epsilon", f32), ("l2_reg", f32), ("loss_scale", f32), ("ema_decay", f32)]
 
@@ -76,6 +83,9 @@ SIGNATURES = {
     "ngp_tonemap": (i32, [vp, u32, f32, C.POINTER(f32), vp, i32, i32, i32, vp]),
     "ngp_init_params": (i32, [vp, C.POINTER(u64), u64, u64, vp, vp]),
     "ngp_optimizer_step": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u32, f32, vp, vp, vp, vp, vp, vp, vp]),
+    "ngp_peer_publish_gradients": (i32, [vp, C.POINTER(PeerSet), u32]),
+    "ngp_optimizer_step_sharded": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u64, u32, f32, vp, vp, vp, vp, vp, C.POINTER(PeerSet), u32, vp]),
+    "ngp_peer_wait_weights": (i32, [vp, C.POINTER(PeerSet), u32]),
     "ngp_from_rgba32": (i32, [vp, u64, vp, vp]),
     "ngp_reduce_sum": (i32, [vp, vp, u64, vp]),
     "ngp_render_procedural_views": (i32, [vp, u32, u32, i32, i32, f32, f32, vp, vp]),

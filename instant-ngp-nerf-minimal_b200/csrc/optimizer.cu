@@ -64,6 +64,12 @@ __device__ __forceinline__ void adam_one(const AdamHyper& h, bool matrix, float 
 	w16 = __float2half_rn(w);
 }
 
+// system-scope flag accesses and peer loads of the data-parallel step (peers' memory is mapped through CUDA IPC)
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) { uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory"); }
+// peer loads must come from the owner's L2, never from a stale local line
+__device__ __forceinline__ uint4 ld_peer16(const void* p) { uint4 v; asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory"); return v; }
+
 __device__ __forceinline__ void unpack8(const uint4& p, float* f) {
 	const uint32_t w[4] = {p.x, p.y, p.z, p.w};
 	#pragma unroll
@@ -78,11 +84,15 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 
 // 8 parameters per thread: three 16-byte loads (gradient, fp16 weight, EMA) are issued together; the 64 bytes of fp32
 // state are only touched when one of the 8 gradients is non-zero (or the group belongs to the MLP matrices).
-__global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t n, uint64_t n_matrix, AdamHyper h, float* __restrict__ w32, __half* __restrict__ w16,
+// PEER: the range [begin, n) is this rank's shard; new fp16 weights are stored into every rank's arena (all-gather half of the
+// sharded step) and the last CTA to finish raises the "weights of this epoch have landed" flag at every rank.
+template <bool PEER>
+__global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t begin, uint64_t n, uint64_t n_matrix, AdamHyper h, float* __restrict__ w32, __half* __restrict__ w16,
                                                         const __half* __restrict__ g16, float* __restrict__ m1, float* __restrict__ m2,
-                                                        uint32_t* __restrict__ steps, __half* __restrict__ ema16) {
+                                                        uint32_t* __restrict__ steps, __half* __restrict__ ema16, ngp_peer_set ps, uint32_t epoch,
+                                                        uint32_t* __restrict__ ticket) {
 	const uint64_t n8 = n / 8;
-	for (uint64_t q = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < n8; q += (uint64_t)gridDim.x * blockDim.x) {
+	for (uint64_t q = begin / 8 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < n8; q += (uint64_t)gridDim.x * blockDim.x) {
 		const uint64_t i = q * 8;
 		const uint4 gp = __ldg(reinterpret_cast<const uint4*>(g16) + q);
 		const uint4 wp = reinterpret_cast<const uint4*>(w16)[q];
@@ -112,13 +122,32 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t n, uint64_t n_ma
 				reinterpret_cast<float4*>(w32)[q * 2 + v] = w[v]; reinterpret_cast<float4*>(m1)[q * 2 + v] = a[v];
 				reinterpret_cast<float4*>(m2)[q * 2 + v] = b[v]; reinterpret_cast<uint4*>(steps)[q * 2 + v] = st[v];
 			}
-			reinterpret_cast<uint4*>(w16)[q] = pack8(wh);
+			const uint4 nw = pack8(wh);
+			if (PEER) {
+				#pragma unroll 1
+				for (uint32_t p = 0; p < ps.world; ++p) reinterpret_cast<uint4*>(ps.params[p])[q] = nw;
+			} else {
+				reinterpret_cast<uint4*>(w16)[q] = nw;
+			}
 		}
 		float eh[8], e[8];
 		unpack8(ep, eh);
 		#pragma unroll
 		for (int k = 0; k < 8; ++k) e[k] = (eh[k] * h.ema_decay * h.deb_old + wh[k] * (1 - h.ema_decay)) * h.deb_new;
 		reinterpret_cast<uint4*>(ema16)[q] = pack8(e);
+	}
+	if (PEER) {
+		__threadfence_system();
+		__syncthreads();
+		__shared__ bool last;
+		if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+		__syncthreads();
+		if (last) {
+			if (threadIdx.x == 0) *ticket = 0;
+			__threadfence_system();
+			if (threadIdx.x < ps.world) st_release_sys(ps.flags[threadIdx.x] + NGP_MAX_PEERS + ps.rank, epoch);
+		}
+		return;
 	}
 	// scalar tail
 	if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
@@ -130,9 +159,48 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t n, uint64_t n_ma
 	}
 }
 
+// ---- sharded step over peer memory ---------------------------------------------------------------------------------
+__global__ void peer_publish_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t epoch) {
+	// stream order has completed this rank's backward pass; make it visible system-wide, then raise the flag at every rank
+	__threadfence_system();
+	if (threadIdx.x < ps.world) st_release_sys(ps.flags[threadIdx.x] + slot_base + ps.rank, epoch);
+}
+
+__global__ void peer_wait_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t epoch) {
+	if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + slot_base + threadIdx.x) < epoch) __nanosleep(64); }
+}
+
+// Reduce-scatter half of the sharded step: waits for every rank's "gradients complete" flag, then sums this rank's shard out of
+// all arenas (P2P loads over NVLink, fixed rank order, fp32) and leaves the fp16 sum in the local arena.  Few registers and
+// 16-byte loads from every peer in flight per thread: the kernel exists to keep enough bytes in flight to cover NVLink latency.
+template <int WORLD>
+__global__ void __launch_bounds__(512) peer_reduce_kernel(uint64_t begin, uint64_t end, ngp_peer_set ps, uint32_t epoch) {
+	if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + threadIdx.x) < epoch) __nanosleep(32); }
+	__syncthreads();
+	uint4* mine = reinterpret_cast<uint4*>(const_cast<void*>(ps.grads[ps.rank]));
+	for (uint64_t q = begin / 8 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < end / 8; q += (uint64_t)gridDim.x * blockDim.x) {
+		uint4 g[WORLD];
+		#pragma unroll
+		for (int p = 0; p < WORLD; ++p) if (p < (int)ps.world) g[p] = ld_peer16(reinterpret_cast<const uint4*>(ps.grads[p]) + q);
+		float sum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+		#pragma unroll
+		for (int p = 0; p < WORLD; ++p) {
+			if (p < (int)ps.world) {
+				float t[8];
+				unpack8(g[p], t);
+				#pragma unroll
+				for (int k = 0; k < 8; ++k) sum[k] += t[k];
+			}
+		}
+		mine[q] = pack8(sum);
+	}
+}
+
 } // namespace ngp
 
 using namespace ngp;
+
+static void fill_hyper(AdamHyper& h, const ngp_optimizer_cfg* cfg, uint32_t step, float learning_rate);
 
 extern "C" int ngp_init_params(void* stream, uint64_t* rng_state, uint64_t rng_inc, uint64_t n_grid_params, float* d_params_fp32, void* d_params_fp16) {
 	NGP_REQUIRE(rng_state && d_params_fp32 && d_params_fp16, "null pointer");
@@ -164,8 +232,55 @@ extern "C" int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, ui
 	NGP_REQUIRE(cfg && d_w32 && d_w16 && d_g16 && d_m1 && d_m2 && d_param_steps && d_ema16, "null pointer");
 	NGP_REQUIRE(n_matrix_params % 8 == 0, "n_matrix_params must be a multiple of 8");
 	if (n_params == 0) return 0;
-	const uint32_t new_step = step + 1;
 	AdamHyper h;
+	fill_hyper(h, cfg, step, learning_rate);
+	NGP_LAUNCH("adam_ema_kernel", (cudaStream_t)stream, adam_ema_kernel<false><<<grid_for(n_params / 8 + 1, 256, 6), 256, 0, (cudaStream_t)stream>>>(0, n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
+		d_m1, d_m2, d_param_steps, (__half*)d_ema16, ngp_peer_set{}, 0, nullptr));
+	return check_launch("optimizer_step");
+}
+
+static int check_peers(const ngp_peer_set* ps) {
+	if (!ps || ps->world < 1 || ps->world > NGP_MAX_PEERS || ps->rank >= ps->world) { set_error("peer set: world must be in [1,%d] and rank < world", NGP_MAX_PEERS); return -1; }
+	for (uint32_t p = 0; p < ps->world; ++p) if (!ps->grads[p] || !ps->params[p] || !ps->flags[p]) { set_error("peer set: null pointer for rank %u", p); return -1; }
+	return 0;
+}
+
+extern "C" int ngp_peer_publish_gradients(void* stream, const ngp_peer_set* peers, uint32_t epoch) {
+	if (check_peers(peers)) return -1;
+	NGP_LAUNCH("peer_publish_kernel", (cudaStream_t)stream, peer_publish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*peers, 0, epoch));
+	return check_launch("peer_publish_gradients");
+}
+
+extern "C" int ngp_peer_wait_weights(void* stream, const ngp_peer_set* peers, uint32_t epoch) {
+	if (check_peers(peers)) return -1;
+	NGP_LAUNCH("peer_wait_kernel", (cudaStream_t)stream, peer_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*peers, NGP_MAX_PEERS, epoch));
+	return check_launch("peer_wait_weights");
+}
+
+extern "C" int ngp_optimizer_step_sharded(void* stream, const ngp_optimizer_cfg* cfg, uint64_t shard_begin, uint64_t shard_end, uint64_t n_matrix_params, uint32_t step,
+                                          float learning_rate, float* d_w32, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16,
+                                          const ngp_peer_set* peers, uint32_t epoch, uint32_t* d_ticket) {
+	NGP_REQUIRE(cfg && d_w32 && d_m1 && d_m2 && d_param_steps && d_ema16 && d_ticket, "null pointer");
+	if (check_peers(peers)) return -1;
+	NGP_REQUIRE(shard_begin % 8 == 0 && shard_end % 8 == 0 && shard_begin <= shard_end && n_matrix_params % 8 == 0, "shard bounds and n_matrix_params must be multiples of 8");
+	NGP_REQUIRE(epoch >= 1, "epoch starts at 1");
+	AdamHyper h;
+	fill_hyper(h, cfg, step, learning_rate);
+	const uint64_t groups = (shard_end - shard_begin) / 8;
+	cudaStream_t st = (cudaStream_t)stream;
+	const uint32_t rgrid = grid_for(groups ? groups : 1, 512, 4);
+	if (peers->world <= 2) NGP_LAUNCH("peer_reduce_kernel", st, peer_reduce_kernel<2><<<rgrid, 512, 0, st>>>(shard_begin, shard_end, *peers, epoch));
+	else if (peers->world <= 4) NGP_LAUNCH("peer_reduce_kernel", st, peer_reduce_kernel<4><<<rgrid, 512, 0, st>>>(shard_begin, shard_end, *peers, epoch));
+	else NGP_LAUNCH("peer_reduce_kernel", st, peer_reduce_kernel<8><<<rgrid, 512, 0, st>>>(shard_begin, shard_end, *peers, epoch));
+	__half* w16 = (__half*)peers->params[peers->rank];
+	const __half* g16 = (const __half*)peers->grads[peers->rank];
+	NGP_LAUNCH("adam_ema_kernel", st, adam_ema_kernel<true><<<grid_for(groups ? groups : 1, 256, 6), 256, 0, st>>>(shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+		d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
+	return check_launch("optimizer_step_sharded");
+}
+
+static void fill_hyper(AdamHyper& h, const ngp_optimizer_cfg* cfg, uint32_t step, float learning_rate) {
+	const uint32_t new_step = step + 1;
 	h.lr = learning_rate; h.beta1 = cfg->beta1; h.beta2 = cfg->beta2; h.eps = cfg->epsilon; h.l2_reg = cfg->l2_reg; h.loss_scale = cfg->loss_scale;
 	h.ema_decay = cfg->ema_decay;
 	{
@@ -182,7 +297,4 @@ extern "C" int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, ui
 	}
 	h.deb_old = 1 - (float)std::pow(cfg->ema_decay, new_step - 1);
 	h.deb_new = 1.0f / (1 - (float)std::pow(cfg->ema_decay, new_step));
-	NGP_LAUNCH("adam_ema_kernel", (cudaStream_t)stream, adam_ema_kernel<<<grid_for(n_params / 8 + 1, 256, 6), 256, 0, (cudaStream_t)stream>>>(n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
-		d_m1, d_m2, d_param_steps, (__half*)d_ema16));
-	return check_launch("optimizer_step");
 }

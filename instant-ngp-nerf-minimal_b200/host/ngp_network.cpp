@@ -88,8 +88,11 @@ OptimizerConfig OptimizerConfig::from_json(const Json& config) {
 
 Trainer::Trainer(std::shared_ptr<NGPNetwork> network, const OptimizerConfig& opt, uint32_t seed, cudaStream_t stream)
 	: m_network(network), m_opt(opt), m_seed(seed), m_n(network->n_params()) {
-	// one extra vector of padding so the 16-byte accesses of the fused optimizer never leave the allocation
-	const size_t n_alloc = m_n + 8;
+	// padding: the 16-byte accesses of the fused optimizer never leave the allocation, and world x shard_size (<= n + 8 * world)
+	// fits for the in-place all-gathers of the data-parallel mode
+	const size_t n_alloc = m_n + 8 + 8 * NGP_MAX_PEERS;
+	m_ticket.resize(1); m_ticket.memset(0, stream);
+	m_shard_size = (m_n + 7) / 8 * 8;
 	m_params_fp32.resize(n_alloc); m_m1.resize(n_alloc); m_m2.resize(n_alloc);
 	m_params.resize(n_alloc); m_grads.resize(n_alloc); m_ema.resize(n_alloc); m_param_steps.resize(n_alloc);
 	m_network->set_params(m_params.data(), params_inference(), m_grads.data());
@@ -118,6 +121,20 @@ void Trainer::optimizer_step(cudaStream_t stream, float loss_scale) {
 	ngp_optimizer_cfg c{m_opt.learning_rate, m_opt.beta1, m_opt.beta2, m_opt.epsilon, m_opt.l2_reg, loss_scale, m_opt.has_ema ? m_opt.ema_decay : 0.0f};
 	api_check(ngp_optimizer_step(stream, &c, m_n, m_network->n_matrix_params(), m_step, m_opt.learning_rate * m_lr_factor, m_params_fp32.data(), m_params.data(),
 	                             m_grads.data(), m_m1.data(), m_m2.data(), m_param_steps.data(), m_ema.data()));
+	++m_step;
+}
+
+void Trainer::set_shard(uint32_t rank, uint32_t world) {
+	if (world < 1 || world > NGP_MAX_PEERS || rank >= world) throw std::runtime_error("Trainer::set_shard: bad rank / world");
+	m_shard_rank = rank;
+	m_shard_size = ((padded_n() + world - 1) / world + 7) / 8 * 8;
+}
+
+void Trainer::optimizer_step_sharded(cudaStream_t stream, float loss_scale, const ngp_peer_set& peers, uint32_t epoch) {
+	if (m_opt.has_decay && m_step >= m_opt.decay_start && (m_step - m_opt.decay_start) % m_opt.decay_interval == 0) m_lr_factor *= m_opt.decay_base;
+	ngp_optimizer_cfg c{m_opt.learning_rate, m_opt.beta1, m_opt.beta2, m_opt.epsilon, m_opt.l2_reg, loss_scale, m_opt.has_ema ? m_opt.ema_decay : 0.0f};
+	api_check(ngp_optimizer_step_sharded(stream, &c, shard_begin(), shard_end(), m_network->n_matrix_params(), m_step, m_opt.learning_rate * m_lr_factor,
+	                                     m_params_fp32.data(), m_m1.data(), m_m2.data(), m_param_steps.data(), m_ema.data(), &peers, epoch, m_ticket.data()));
 	++m_step;
 }
 

@@ -60,6 +60,17 @@ public:
 	void initialize_params(cudaStream_t stream);
 	// Trainer::optimizer_step (trainer.h:198): ExponentialDecay -> Adam -> EMA in one fused launch
 	void optimizer_step(cudaStream_t stream, float loss_scale);
+	// data parallel over peer memory: this rank updates only [shard_begin(), shard_end()) and stores the new weights into every rank's arena
+	void set_shard(uint32_t rank, uint32_t world);
+	size_t shard_size() const { return m_shard_size; }
+	size_t shard_begin() const { return std::min(m_shard_rank * m_shard_size, padded_n()); }
+	size_t shard_end() const { return std::min((m_shard_rank + 1) * m_shard_size, padded_n()); }
+	size_t padded_n() const { return (m_n + 7) / 8 * 8; }
+	void optimizer_step_sharded(cudaStream_t stream, float loss_scale, const ngp_peer_set& peers, uint32_t epoch);
+	precision_t* ema() const { return m_ema.data(); }
+	float* m1() const { return m_m1.data(); }
+	float* m2() const { return m_m2.data(); }
+	uint32_t* param_steps() const { return m_param_steps.data(); }
 
 	precision_t* params() const { return m_params.data(); }
 	precision_t* params_inference() const { return m_opt.has_ema ? m_ema.data() : m_params.data(); }
@@ -79,6 +90,8 @@ private:
 	DeviceBuffer<float> m_params_fp32, m_m1, m_m2;
 	DeviceBuffer<precision_t> m_params, m_grads, m_ema;
 	DeviceBuffer<uint32_t> m_param_steps;
+	DeviceBuffer<uint32_t> m_ticket;
+	size_t m_shard_size = 0, m_shard_rank = 0;
 	uint32_t m_step = 0;
 	float m_lr_factor = 1.0f;
 };

@@ -103,8 +103,11 @@ PYBIND11_MODULE(pyngp, m) {
 		})
 		.def_property_readonly("n_training_images", [](const Testbed& t) { return t.m_training_buffer.dataset.n_images; })
 		// ---- additions for data-parallel training (not in the reference) ----
-		.def("set_data_parallel", [](Testbed& t, int rank, int world, uintptr_t comm) { t.set_data_parallel(rank, world, (void*)comm); },
-		     py::arg("rank"), py::arg("world_size"), py::arg("nccl_comm"))
+		.def("set_data_parallel", [](Testbed& t, int rank, int world, uintptr_t comm, bool peer_memory) { t.set_data_parallel(rank, world, (void*)comm, peer_memory); },
+		     py::arg("rank"), py::arg("world_size"), py::arg("nccl_comm"), py::arg("peer_memory") = false,
+		     "Data-parallel training, one process per GPU (collective).  peer_memory: fused reduce-scatter + Adam + all-gather over NVLink peer memory.")
+		.def_property_readonly("peer_memory_enabled", &Testbed::peer_memory_enabled)
+		.def("gather_optimizer_state", &Testbed::gather_optimizer_state, "all-gather sharded optimizer state (collective); call before save_snapshot(..., True) in peer-memory mode")
 		.def_property_readonly("gradients_ptr", [](const Testbed& t) { return (uintptr_t)t.gradients(); })
 		.def_property_readonly("n_params", &Testbed::n_params)
 		.def_property_readonly("stream_ptr", [](const Testbed& t) { return (uintptr_t)t.m_stream; })

@@ -46,6 +46,7 @@ Testbed::Testbed() {
 }
 
 Testbed::~Testbed() {
+	for (void* p : m_peer_opened) cudaIpcCloseMemHandle(p);
 	for (auto& e : m_ev) if (e) cudaEventDestroy(e);
 	for (cudaEvent_t e : {m_ev_march_go, m_ev_march_ready[0], m_ev_march_ready[1], m_ev_slot_free[0], m_ev_slot_free[1]}) if (e) cudaEventDestroy(e);
 	if (m_march_stream) cudaStreamDestroy(m_march_stream);
@@ -140,10 +141,67 @@ void Testbed::load_snapshot(const std::string& snapshot_path) {
 	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 }
 
-void Testbed::set_data_parallel(int rank, int world_size, void* nccl_comm) {
+void Testbed::set_data_parallel(int rank, int world_size, void* nccl_comm, bool peer_memory) {
 	if (world_size < 1 || rank < 0 || rank >= world_size) throw std::runtime_error("set_data_parallel: bad rank / world size");
 	if (world_size > 1 && !nccl_comm) throw std::runtime_error("set_data_parallel: a communicator is required for world_size > 1");
+	if (!m_trainer) throw std::runtime_error("set_data_parallel: load_model_config first");
 	m_dp_rank = rank; m_dp_world = world_size; m_nccl_comm = nccl_comm;
+	m_peer_enabled = false;
+	if (!peer_memory || world_size == 1) return;
+	if (world_size > NGP_MAX_PEERS) throw std::runtime_error("set_data_parallel: peer memory supports at most 8 ranks");
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	m_peer_flags.resize(2 * NGP_MAX_PEERS);
+	m_peer_flags.memset(0);
+	// exchange CUDA IPC handles of (gradient arena, parameter arena, flag block) through the communicator
+	struct Handles { cudaIpcMemHandle_t grads, params, flags; };
+	Handles mine;
+	NGP_CUDA_CHECK(cudaIpcGetMemHandle(&mine.grads, m_trainer->gradients()));
+	NGP_CUDA_CHECK(cudaIpcGetMemHandle(&mine.params, m_trainer->params()));
+	NGP_CUDA_CHECK(cudaIpcGetMemHandle(&mine.flags, m_peer_flags.data()));
+	DeviceBuffer<uint8_t> d_all((size_t)world_size * sizeof(Handles));
+	NGP_CUDA_CHECK(cudaMemcpy(d_all.data() + (size_t)rank * sizeof(Handles), &mine, sizeof(Handles), cudaMemcpyHostToDevice));
+	ncclResult_t r = ncclAllGather(d_all.data() + (size_t)rank * sizeof(Handles), d_all.data(), sizeof(Handles), ncclUint8, (ncclComm_t)nccl_comm, m_stream);
+	if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather failed: ") + ncclGetErrorString(r));
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	std::vector<Handles> all(world_size);
+	d_all.copy_to_host((uint8_t*)all.data(), d_all.get_bytes());
+	m_peers = ngp_peer_set{};
+	m_peers.world = (uint32_t)world_size; m_peers.rank = (uint32_t)rank;
+	for (int p = 0; p < world_size; ++p) {
+		if (p == rank) { m_peers.grads[p] = m_trainer->gradients(); m_peers.params[p] = m_trainer->params(); m_peers.flags[p] = m_peer_flags.data(); continue; }
+		void *g = nullptr, *w = nullptr, *f = nullptr;
+		NGP_CUDA_CHECK(cudaIpcOpenMemHandle(&g, all[p].grads, cudaIpcMemLazyEnablePeerAccess));
+		NGP_CUDA_CHECK(cudaIpcOpenMemHandle(&w, all[p].params, cudaIpcMemLazyEnablePeerAccess));
+		NGP_CUDA_CHECK(cudaIpcOpenMemHandle(&f, all[p].flags, cudaIpcMemLazyEnablePeerAccess));
+		m_peers.grads[p] = g; m_peers.params[p] = w; m_peers.flags[p] = (uint32_t*)f;
+		m_peer_opened.push_back(g); m_peer_opened.push_back(w); m_peer_opened.push_back(f);
+	}
+	m_trainer->set_shard((uint32_t)rank, (uint32_t)world_size);
+	m_peer_epoch = 0;
+	m_peer_enabled = true;
+	// nobody may publish into a flag block that its owner has not zeroed yet
+	DeviceBuffer<float> token(1);
+	token.memset(0);
+	r = ncclAllReduce(token.data(), token.data(), 1, ncclFloat, ncclSum, (ncclComm_t)nccl_comm, m_stream);
+	if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce failed: ") + ncclGetErrorString(r));
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+}
+
+// in-place all-gather of one state array whose shard [rank * S, (rank + 1) * S) is current on this rank
+template <typename T>
+static void all_gather_shards(T* base, size_t shard_elems, int rank, ncclDataType_t type, size_t type_scale, void* comm, cudaStream_t stream) {
+	const ncclResult_t r = ncclAllGather(base + (size_t)rank * shard_elems, base, shard_elems * type_scale, type, (ncclComm_t)comm, stream);
+	if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather failed: ") + ncclGetErrorString(r));
+}
+
+void Testbed::gather_optimizer_state() {
+	if (!m_peer_enabled) return;
+	const size_t S = m_trainer->shard_size();
+	all_gather_shards(m_trainer->params_full_precision(), S, m_dp_rank, ncclFloat, 1, m_nccl_comm, m_stream);
+	all_gather_shards(m_trainer->m1(), S, m_dp_rank, ncclFloat, 1, m_nccl_comm, m_stream);
+	all_gather_shards(m_trainer->m2(), S, m_dp_rank, ncclFloat, 1, m_nccl_comm, m_stream);
+	all_gather_shards(m_trainer->param_steps(), S, m_dp_rank, ncclUint32, 1, m_nccl_comm, m_stream);
+	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 }
 
 } // namespace ngp

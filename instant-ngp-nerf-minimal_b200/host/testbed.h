@@ -55,7 +55,12 @@ public:
 
 	// ---- data-parallel training (new: the reference is single-GPU).  Gradients are summed over ranks with NCCL
 	//      before the optimizer step; each rank draws its own rays.  comm is an ncclComm_t created by the caller. ----
-	void set_data_parallel(int rank, int world_size, void* nccl_comm);
+	// peer_memory: fused reduce-scatter + Adam + all-gather over NVLink peer memory (CUDA IPC between the ranks' processes)
+	// instead of NCCL all-reduce + replicated optimizer.  Collective: every rank must call it.
+	void set_data_parallel(int rank, int world_size, void* nccl_comm, bool peer_memory = false);
+	bool peer_memory_enabled() const { return m_peer_enabled; }
+	// all-gather of sharded optimizer state (collective; needed before a snapshot with serialize_optimizer in peer mode)
+	void gather_optimizer_state();
 	precision_t* gradients() const { return m_trainer->gradients(); }
 	size_t n_params() const { return m_trainer->n_params(); }
 
@@ -142,6 +147,11 @@ private:
 	uint32_t* m_host_counter = nullptr;    // pinned
 	int m_dp_rank = 0, m_dp_world = 1;
 	void* m_nccl_comm = nullptr;
+	bool m_peer_enabled = false;
+	ngp_peer_set m_peers{};
+	DeviceBuffer<uint32_t> m_peer_flags;
+	uint32_t m_peer_epoch = 0;
+	std::vector<void*> m_peer_opened;
 	int m_render_row_begin = 0, m_render_row_end = -1;
 };
 

@@ -85,6 +85,13 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 	m_rng = rng_step;
 	tb.n_rays_total += n_rays * n_training_steps;
 
+	if (m_peer_enabled && m_trainer->ema() != m_trainer->params()) {
+		// the EMA (inference) weights are sharded like the rest of the optimizer state: collect them once per call, so render() and
+		// plain snapshots stay local operations
+		const size_t S = m_trainer->shard_size();
+		const ncclResult_t r = ncclAllGather(m_trainer->ema() + (size_t)m_dp_rank * S, m_trainer->ema(), S, ncclHalf, (ncclComm_t)m_nccl_comm, stream);
+		if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather failed: ") + ncclGetErrorString(r));
+	}
 	api_check(ngp_reduce_sum(stream, tb.loss.data(), (uint64_t)n_rays * n_training_steps, tb.loss_sum.data()));
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev[2], stream));
 
@@ -162,7 +169,16 @@ void Testbed::learn_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_r
 	m_network->forward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data());
 	m_network->backward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data(), tb.dloss_drgbsigma.data(),
 	                    tb.compacted_src_index.data(), max_inference);
-	// data parallel: sum the fp16 gradient arena over ranks (NVLink / NVSwitch)
+	if (m_peer_enabled) {
+		// data parallel over peer memory: publish "my gradients are complete", then ONE kernel reduces this rank's shard out of all
+		// ranks' arenas, updates it and stores the new weights into all arenas; the next reader of the weights waits for every shard
+		++m_peer_epoch;
+		api_check(ngp_peer_publish_gradients(stream, &m_peers, m_peer_epoch));
+		m_trainer->optimizer_step_sharded(stream, LOSS_SCALE, m_peers, m_peer_epoch);
+		api_check(ngp_peer_wait_weights(stream, &m_peers, m_peer_epoch));
+		return;
+	}
+	// data parallel through NCCL: sum the fp16 gradient arena over ranks (NVLink / NVSwitch), every rank runs the whole optimizer
 	if (m_dp_world > 1) {
 		const ncclResult_t r = ncclAllReduce(m_trainer->gradients(), m_trainer->gradients(), m_trainer->n_params(), ncclHalf, ncclSum, (ncclComm_t)m_nccl_comm, stream);
 		if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce failed: ") + ncclGetErrorString(r));
