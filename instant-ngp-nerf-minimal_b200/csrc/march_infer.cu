@@ -37,10 +37,29 @@ __host__ __device__ inline float ld_random_val(uint32_t index, uint32_t seed, ui
 
 struct CamMat { float m[12]; };
 
-__global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
+// one 8-point window of a ray's stepping lattice for an octet of lanes (see generate_coords_from_rays_kernel below)
+__device__ __forceinline__ float octet_lattice(float t_base, uint32_t sub, uint32_t shift, uint32_t gmask, const ngp_sampler_cfg& c, bool const_dt, float& t_next_base) {
+	if (const_dt) {
+		const float dt0 = calc_dt(t_base, c);
+		const float dtq = (t_base + dt0) - t_base;
+		const float cand = __fmaf_rn((float)sub, dtq, t_base), next = __fmaf_rn((float)(sub + 1), dtq, t_base);
+		if ((__ballot_sync(gmask, cand + dt0 == next) & gmask) == gmask) { t_next_base = __shfl_sync(gmask, next, shift + 7); return cand; }
+	}
+	float t = t_base, my_t = t_base;
+	#pragma unroll
+	for (int s = 0; s < 8; ++s) { if (s == (int)sub) my_t = t; t += calc_dt(t, c); }
+	t_next_base = t;
+	return my_t;
+}
+
+// 8 lanes per pixel: ray set-up (every lane of the octet computes the same ray), then the skip to the first occupied cell
+// (advance_pos_nerf) on 8-point lattice windows.
+__global__ void __launch_bounds__(256) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
                                                         uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads) {
 	const uint32_t n = (uint32_t)cam.width * (uint32_t)cam.height;
-	const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31, sub = lane & 7, shift = lane & 24;
+	const uint32_t gmask = 0xffu << shift;
+	const uint32_t idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
 	if (idx >= n) return;
 	const uint32_t x = idx % cam.width, y = idx / cam.width;
 	V3 o, d;
@@ -50,47 +69,110 @@ __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_c
 	p.ox = o.x; p.oy = o.y; p.oz = o.z; p.dx = d.x; p.dy = d.y; p.dz = d.z; p.idx = idx; p.n_steps = 0; p.t = t; p.alive = 1;
 	if (!aabb_contains(c, ray_at(o, d, t))) {
 		p.alive = 0; p.dx = p.dy = p.dz = 0.f; p.t = 0.f; p.idx = 0;
-		payloads[idx] = p;
+		if (sub == 0) payloads[idx] = p;
 		return;
 	}
 	const V3 idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
-	float dt = calc_dt(t, c);
-	t = __fmaf_rn(ld_random_val(spp, idx * 786433u, 0), dt, t);
-	V3 pos;
-	while (true) {
-		if (!aabb_contains(c, pos = ray_at(o, d, t))) { p.alive = 0; break; }
-		dt = calc_dt(t, c);
-		const uint32_t mip = mip_from_dt(dt, pos, c);
-		if (grid_occupied(pos, bits, mip, c.grid_size)) break;
-		t = advance_to_next_voxel(t, c, pos, d, idir, c.grid_size >> mip);
+	float t_base = __fmaf_rn(ld_random_val(spp, idx * 786433u, 0), calc_dt(t, c), t);
+	float skip_target = -INFINITY;
+	const bool const_dt = c.cone_angle == 0.f;
+	for (uint32_t window = 0; window < (1u << 18); ++window) {
+		float t_next_base;
+		const float my_t = octet_lattice(t_base, sub, shift, gmask, c, const_dt, t_next_base);
+		const V3 pos = ray_at(o, d, my_t);
+		const bool inside = aabb_contains(c, pos);
+		bool occ = false;
+		float t_target = 0.f;
+		if (inside) {
+			const uint32_t mip = mip_from_dt(calc_dt(my_t, c), pos, c);
+			occ = grid_occupied(pos, bits, mip, c.grid_size);
+			if (!occ) t_target = my_t + distance_to_next_voxel(pos, d, idir, c.grid_size >> mip);
+		}
+		const uint32_t stop_mask = (__ballot_sync(gmask, !inside || occ) >> shift) & 0xffu;     // visiting such a point ends the walk
+		uint32_t q0 = 0;
+		while (q0 < 8) {
+			const uint32_t cand = (__ballot_sync(gmask, sub >= q0 && !(my_t < skip_target)) >> shift) & 0xffu;
+			if (!cand) break;
+			const uint32_t q = (uint32_t)__ffs(cand) - 1u;
+			if ((stop_mask >> q) & 1u) {
+				const float t_stop = __shfl_sync(gmask, my_t, shift + q);
+				const uint32_t still_inside = __shfl_sync(gmask, (uint32_t)inside, shift + q);
+				if (sub == 0) { p.t = t_stop; p.alive = still_inside ? 1 : 0; payloads[idx] = p; }
+				return;
+			}
+			skip_target = __shfl_sync(gmask, t_target, shift + q);
+			q0 = q + 1;
+		}
+		t_base = t_next_base;
 	}
-	p.t = t;
-	payloads[idx] = p;
+	if (sub == 0) { p.t = t_base; p.alive = 0; payloads[idx] = p; }
 }
 
-__global__ void __launch_bounds__(128) generate_coords_from_rays_kernel(ngp_sampler_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr, uint32_t n_steps,
+// 8 lanes per ray ("octet"): the ray's stepping lattice (see march_train.cu) is taken 8 points at a time, every lane evaluates
+// one point (position, cascade, occupancy bit, exit distance of its voxel), and an octet-local ballot replays the reference's
+// sequential control flow: occupied visited points become samples, an empty visited point skips to the first lattice point
+// behind its voxel.  Sample positions, step counts and the stored ray parameter are bit-identical to the thread-per-ray loop,
+// but the 8 Coordinates of a ray leave as one contiguous 224-byte store, four rays share a warp instead of 32 (the reference's
+// loop lengths differ wildly from ray to ray), and empty space is crossed 8 lattice points per round.
+__global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_sampler_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr, uint32_t n_steps,
                                                                          const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads, Coordinate* __restrict__ coords) {
 	const uint32_t n_rays = n_rays_ptr ? min(*n_rays_ptr, n_rays_max) : n_rays_max;
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_rays) return;
+	const uint32_t lane = threadIdx.x & 31, sub = lane & 7, shift = lane & 24;
+	const uint32_t gmask = 0xffu << shift;
+	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+	if (i >= n_rays) return;                                   // the whole octet leaves together
 	RayPayload& p = payloads[i];
 	if (!p.alive) return;
 	const V3 o = {p.ox, p.oy, p.oz}, d = {p.dx, p.dy, p.dz}, idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
-	float t = p.t;
-	for (uint32_t j = 0; j < n_steps; ++j) {
-		V3 pos; float dt = 0.f;
-		while (true) {
-			if (!aabb_contains(c, pos = ray_at(o, d, t))) { p.n_steps = j; return; }
-			dt = calc_dt(t, c);
+	float t_base = p.t, skip_target = -INFINITY;
+	uint32_t j = 0;
+	if (n_steps == 0) { if (sub == 0) p.n_steps = 0; return; }
+	const bool const_dt = c.cone_angle == 0.f;
+	for (uint32_t window = 0; window < (1u << 18); ++window) {
+		float t_next_base;
+		const float my_t = octet_lattice(t_base, sub, shift, gmask, c, const_dt, t_next_base);
+		const V3 pos = ray_at(o, d, my_t);
+		const bool inside = aabb_contains(c, pos);
+		const float dt = calc_dt(my_t, c);
+		bool occ = false;
+		float t_target = 0.f;
+		if (inside) {
 			const uint32_t mip = mip_from_dt(dt, pos, c);
-			if (grid_occupied(pos, bits, mip, c.grid_size)) break;
-			t = advance_to_next_voxel(t, c, pos, d, idir, c.grid_size >> mip);
+			occ = grid_occupied(pos, bits, mip, c.grid_size);
+			if (!occ) t_target = my_t + distance_to_next_voxel(pos, d, idir, c.grid_size >> mip);
 		}
-		coords[(size_t)i * n_steps + j] = make_coord(pos, d, dt, c);
-		t += dt;
+		const uint32_t inside_mask = (__ballot_sync(gmask, inside) >> shift) & 0xffu;
+		const uint32_t run_mask = (__ballot_sync(gmask, inside && occ) >> shift) & 0xffu;
+		uint32_t q0 = 0;
+		while (q0 < 8) {
+			const uint32_t cand = (__ballot_sync(gmask, sub >= q0 && !(my_t < skip_target)) >> shift) & 0xffu;
+			if (!cand) break;                                      // the rest of the window is stepped over; the target carries on
+			const uint32_t q = (uint32_t)__ffs(cand) - 1u;
+			if (!((inside_mask >> q) & 1u)) {                      // the ray left the box: n_steps = samples so far, t stays (:581-584)
+				if (sub == 0) p.n_steps = j;
+				return;
+			}
+			if ((run_mask >> q) & 1u) {
+				const uint32_t rest = (~run_mask & 0xffu) >> q;    // bit 0 is clear
+				const uint32_t run = rest ? (uint32_t)__ffs(rest) - 1u : 8u - q;
+				const uint32_t take = min(run, n_steps - j);
+				if (sub >= q && sub < q + take) coords[(size_t)i * n_steps + j + (sub - q)] = make_coord(pos, d, dt, c);
+				j += take;
+				if (j >= n_steps) {                                // t after the last sample is the next lattice point
+					const float t_after = __shfl_sync(gmask, my_t, shift + ((q + take) & 7u));
+					if (sub == 0) { p.t = q + take < 8 ? t_after : t_next_base; p.n_steps = n_steps; }
+					return;
+				}
+				q0 = q + run;
+				skip_target = -INFINITY;
+			} else {
+				skip_target = __shfl_sync(gmask, t_target, shift + q);
+				q0 = q + 1;
+			}
+		}
+		t_base = t_next_base;
 	}
-	p.t = t;
-	p.n_steps = n_steps;
+	if (sub == 0) { p.t = t_base; p.n_steps = j; }                 // unreachable for sane cameras (2 M lattice points)
 }
 
 } // namespace ngp
@@ -109,7 +191,7 @@ extern "C" int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp
 	const float offx = fractf_host(0.5f - ax + bx), offy = fractf_host(0.5f - ay + by);
 	const uint32_t n = (uint32_t)cam->width * (uint32_t)cam->height;
 	CamMat cm; memcpy(cm.m, camera_matrix_host, sizeof(cm.m));
-	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads));
+	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up((uint64_t)n * 8, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads));
 	return check_launch("init_rays");
 }
 
@@ -117,6 +199,6 @@ extern "C" int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg
                                              const uint8_t* d_bitfield, void* d_payloads, float* d_coords) {
 	NGP_REQUIRE(cfg && d_bitfield && d_payloads && d_coords, "null pointer");
 	if (n_rays == 0) return 0;
-	NGP_LAUNCH("generate_coords_from_rays_kernel", (cudaStream_t)stream, generate_coords_from_rays_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, d_bitfield, (RayPayload*)d_payloads, (Coordinate*)d_coords));
+	NGP_LAUNCH("generate_coords_from_rays_kernel", (cudaStream_t)stream, generate_coords_from_rays_kernel<<<div_up((uint64_t)n_rays * 8, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, d_bitfield, (RayPayload*)d_payloads, (Coordinate*)d_coords));
 	return check_launch("generate_coords_from_rays");
 }
