@@ -126,8 +126,8 @@ void Trainer::optimizer_step(cudaStream_t stream, float loss_scale) {
 
 void Trainer::set_shard(uint32_t rank, uint32_t world) {
 	if (world < 1 || world > NGP_MAX_PEERS || rank >= world) throw std::runtime_error("Trainer::set_shard: bad rank / world");
-	m_shard_rank = rank;
-	m_shard_size = ((padded_n() + world - 1) / world + 7) / 8 * 8;
+	m_shard_rank = rank; m_shard_world = world;
+	m_shard_size = shard_range(m_n, rank, world).size;
 }
 
 void Trainer::optimizer_step_sharded(cudaStream_t stream, float loss_scale, const ngp_peer_set& peers, uint32_t epoch) {

@@ -54,6 +54,15 @@ struct OptimizerConfig {
 	static OptimizerConfig from_json(const Json& config);
 };
 
+// parameter range [begin, end) rank `rank` of `world` owns in the sharded data-parallel optimizer: equal shards of a multiple of 8
+// parameters (16-byte fp16 vectors, in-place all-gather friendly); the last shard absorbs the remainder
+struct ShardRange { size_t begin, end, size; };
+inline ShardRange shard_range(size_t n_params, uint32_t rank, uint32_t world) {
+	const size_t padded = (n_params + 7) / 8 * 8;
+	const size_t size = ((padded + world - 1) / world + 7) / 8 * 8;
+	return {std::min((size_t)rank * size, padded), std::min((size_t)(rank + 1) * size, padded), size};
+}
+
 class Trainer {
 public:
 	Trainer(std::shared_ptr<NGPNetwork> network, const OptimizerConfig& opt, uint32_t seed, cudaStream_t stream);
@@ -63,8 +72,8 @@ public:
 	// data parallel over peer memory: this rank updates only [shard_begin(), shard_end()) and stores the new weights into every rank's arena
 	void set_shard(uint32_t rank, uint32_t world);
 	size_t shard_size() const { return m_shard_size; }
-	size_t shard_begin() const { return std::min(m_shard_rank * m_shard_size, padded_n()); }
-	size_t shard_end() const { return std::min((m_shard_rank + 1) * m_shard_size, padded_n()); }
+	size_t shard_begin() const { return shard_range(m_n, (uint32_t)m_shard_rank, (uint32_t)m_shard_world).begin; }
+	size_t shard_end() const { return shard_range(m_n, (uint32_t)m_shard_rank, (uint32_t)m_shard_world).end; }
 	size_t padded_n() const { return (m_n + 7) / 8 * 8; }
 	void optimizer_step_sharded(cudaStream_t stream, float loss_scale, const ngp_peer_set& peers, uint32_t epoch);
 	precision_t* ema() const { return m_ema.data(); }
@@ -91,7 +100,7 @@ private:
 	DeviceBuffer<precision_t> m_params, m_grads, m_ema;
 	DeviceBuffer<uint32_t> m_param_steps;
 	DeviceBuffer<uint32_t> m_ticket;
-	size_t m_shard_size = 0, m_shard_rank = 0;
+	size_t m_shard_size = 0, m_shard_rank = 0, m_shard_world = 1;
 	uint32_t m_step = 0;
 	float m_lr_factor = 1.0f;
 };

@@ -25,6 +25,11 @@ static void to_vec(const py::object& o, float* dst, size_t n, const char* what) 
 }
 
 PYBIND11_MODULE(pyngp, m) {
+	m.def("shard_range", [](size_t n_params, uint32_t rank, uint32_t world) {
+		if (world < 1 || world > NGP_MAX_PEERS || rank >= world) throw std::runtime_error("shard_range: bad rank / world");
+		const ShardRange r = shard_range(n_params, rank, world);
+		return py::make_tuple(r.begin, r.end, r.size);
+	}, "(begin, end, shard size) of the parameter range a rank owns in the sharded data-parallel optimizer");
 	m.doc() = "Instant neural graphics primitives (NeRF) minimal version -- B200-native build";
 
 	py::enum_<EActivation>(m, "Activation")

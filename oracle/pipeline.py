@@ -92,12 +92,16 @@ class CpuTrainer:
         self.mean = grid_mean(self.cfg, self.grid)
         self.bits = grid_to_bitfield(self.cfg, self.grid, self.mean)
 
-    def step(self, n_rays):
-        """one training step on n_rays rays; returns (samples marched, samples trained on)"""
+    def compute_gradients(self, n_rays, rank=0, world=1):
+        """march -> network -> composite -> rollover -> forward/backward of one step; returns (fp16 gradient arena, marched, compacted, loss).
+        Data parallel (testbed_train.cpp march_step / learn_step): rank r draws its rays 2^18 * 8 generator draws further along and
+        carries 1/world of the loss scale, so the sum of the ranks' gradients is the gradient of the mean loss."""
         w16 = self.opt.w16
+        ray_rng = Pcg32(state=self.rng.state, inc=self.rng.inc)
+        if rank:
+            ray_rng.advance(rank * (1 << 18) * 8)
         s = generate_training_samples(self.cfg, n_rays, self.n_rays_total, self.batch * 16, self.xforms, self.images, self.W, self.H, self.fx, self.fx,
-                                      self.bits, self.rng)
-        self.n_rays_total += n_rays
+                                      self.bits, ray_rng)
         kept, total = int(s["counters"][0]), int(min(s["counters"][1], self.batch * 16))
         if kept == 0:
             raise RuntimeError("Training generated 0 samples. Aborting training.")
@@ -106,7 +110,7 @@ class CpuTrainer:
         enc = hash_encode_fwd(coords, 7, total, table, self.levels)
         rgbsigma = network_fwd(w16[:10240], enc, coords, total)
         n_target = min(self.batch, max(total, 1))
-        c = composite_train(n_rays, kept, n_target, s["rgba"], s["numsteps"], coords, rgbsigma, self.cfg, self.mean, self.rng)
+        c = composite_train(n_rays, kept, n_target, s["rgba"], s["numsteps"], coords, rgbsigma, self.cfg, self.mean, self.rng, loss_scale=128.0 / world)
         n_comp = min(c["counter"], n_target)
         cc, dl = c["coords_compacted"], c["dloss"]
         if n_comp < n_target:
@@ -114,10 +118,18 @@ class CpuTrainer:
         enc2 = hash_encode_fwd(cc, 7, n_target, table, self.levels)
         wgrad, denc, _ = network_fwd_bwd(w16[:10240], enc2, cc, dl, n_target)
         ggrid = hash_encode_bwd(cc, 7, n_target, denc, self.levels)
-        grads = np.concatenate([wgrad, ggrid]).astype(np.float16)
+        return np.concatenate([wgrad, ggrid]).astype(np.float16), total, n_comp, float(c["loss"].sum())
+
+    def apply_gradients(self, grads, n_rays):
+        self.n_rays_total += n_rays
         self.rng.advance()
         self.opt.step(grads)
-        return total, n_comp, float(c["loss"].sum())
+
+    def step(self, n_rays):
+        """one training step on n_rays rays; returns (samples marched, samples trained on)"""
+        grads, total, n_comp, loss = self.compute_gradients(n_rays)
+        self.apply_gradients(grads, n_rays)
+        return total, n_comp, loss
 
 
 def time_cpu_steps(n_steps, n_rays, warmup=1, **kw):
