@@ -376,7 +376,11 @@ def run_ours(args):
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(name)
+            # measured DRAM bytes per unit (ncu --set full, profiles/traffic.json) x the units of this run's average launch
+            t = json.load(open(tp)).get(name)
+            units = {"hash_encode_fwd_kernel": m + g, "hash_encode_bwd_kernel": b, "adam_ema_kernel": tb.n_params}.get(name)
+            if t and units:
+                traffic = t["dram_bytes_per_unit"] * units / launches_per_step
         roofline.update({"bound": bound, "achieved": achieved, "peak": peak, "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "algorithmic_per_launch": per_launch})
     roofline["kernels_ms_per_step"] = {k: v[0] / prof_steps for k, v in sorted(kt.items(), key=lambda kv: -kv[1][0])}
