@@ -118,6 +118,12 @@ int ngp_mark_untrained_grid(void* stream, const ngp_sampler_cfg* cfg, const ngp_
 /* sample_positions_from_grid -> generate_grid_samples_nerf_nonuniform (:63-105) */
 int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
                               const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices);
+/* The same n samples -- the identical multiset of (position, index) pairs -- written in the Morton order of each sample's first
+ * candidate cell instead of in sample order, so the density pass that follows reads spatially coherent positions.  Everything
+ * downstream (density per position, max-splat by index) is order-free.  Needs grid_size^3 to be a power of two >= 256, else the
+ * plain order is written. */
+int ngp_generate_grid_samples_sorted(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
+                                     const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices);
 /* update_grid (:705-735): memset current, splat max, decay max */
 int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,
                     int density_activation, float decay, float* d_grid_current, float* d_grid);

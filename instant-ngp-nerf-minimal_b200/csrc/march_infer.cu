@@ -52,14 +52,13 @@ __device__ __forceinline__ float octet_lattice(float t_base, uint32_t sub, uint3
 	return my_t;
 }
 
-// 8 lanes per pixel: ray set-up (every lane of the octet computes the same ray), then the skip to the first occupied cell
-// (advance_pos_nerf) on 8-point lattice windows.
-__global__ void __launch_bounds__(256) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
+// One thread per pixel: ray set-up, then the skip to the first occupied cell (advance_pos_nerf).  An 8-lanes-per-pixel variant of
+// this kernel was measured 6x slower (1.2 -> 7.1 ms at 1080p): the skip crosses about one voxel per 8-point window, so the
+// rounds do not shrink while the thread count grows 8x.
+__global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
                                                         uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads) {
 	const uint32_t n = (uint32_t)cam.width * (uint32_t)cam.height;
-	const uint32_t lane = threadIdx.x & 31, sub = lane & 7, shift = lane & 24;
-	const uint32_t gmask = 0xffu << shift;
-	const uint32_t idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+	const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= n) return;
 	const uint32_t x = idx % cam.width, y = idx / cam.width;
 	V3 o, d;
@@ -69,43 +68,22 @@ __global__ void __launch_bounds__(256) init_rays_kernel(ngp_sampler_cfg c, ngp_c
 	p.ox = o.x; p.oy = o.y; p.oz = o.z; p.dx = d.x; p.dy = d.y; p.dz = d.z; p.idx = idx; p.n_steps = 0; p.t = t; p.alive = 1;
 	if (!aabb_contains(c, ray_at(o, d, t))) {
 		p.alive = 0; p.dx = p.dy = p.dz = 0.f; p.t = 0.f; p.idx = 0;
-		if (sub == 0) payloads[idx] = p;
+		payloads[idx] = p;
 		return;
 	}
 	const V3 idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
-	float t_base = __fmaf_rn(ld_random_val(spp, idx * 786433u, 0), calc_dt(t, c), t);
-	float skip_target = -INFINITY;
-	const bool const_dt = c.cone_angle == 0.f;
-	for (uint32_t window = 0; window < (1u << 18); ++window) {
-		float t_next_base;
-		const float my_t = octet_lattice(t_base, sub, shift, gmask, c, const_dt, t_next_base);
-		const V3 pos = ray_at(o, d, my_t);
-		const bool inside = aabb_contains(c, pos);
-		bool occ = false;
-		float t_target = 0.f;
-		if (inside) {
-			const uint32_t mip = mip_from_dt(calc_dt(my_t, c), pos, c);
-			occ = grid_occupied(pos, bits, mip, c.grid_size);
-			if (!occ) t_target = my_t + distance_to_next_voxel(pos, d, idir, c.grid_size >> mip);
-		}
-		const uint32_t stop_mask = (__ballot_sync(gmask, !inside || occ) >> shift) & 0xffu;     // visiting such a point ends the walk
-		uint32_t q0 = 0;
-		while (q0 < 8) {
-			const uint32_t cand = (__ballot_sync(gmask, sub >= q0 && !(my_t < skip_target)) >> shift) & 0xffu;
-			if (!cand) break;
-			const uint32_t q = (uint32_t)__ffs(cand) - 1u;
-			if ((stop_mask >> q) & 1u) {
-				const float t_stop = __shfl_sync(gmask, my_t, shift + q);
-				const uint32_t still_inside = __shfl_sync(gmask, (uint32_t)inside, shift + q);
-				if (sub == 0) { p.t = t_stop; p.alive = still_inside ? 1 : 0; payloads[idx] = p; }
-				return;
-			}
-			skip_target = __shfl_sync(gmask, t_target, shift + q);
-			q0 = q + 1;
-		}
-		t_base = t_next_base;
+	float dt = calc_dt(t, c);
+	t = __fmaf_rn(ld_random_val(spp, idx * 786433u, 0), dt, t);
+	V3 pos;
+	while (true) {
+		if (!aabb_contains(c, pos = ray_at(o, d, t))) { p.alive = 0; break; }
+		dt = calc_dt(t, c);
+		const uint32_t mip = mip_from_dt(dt, pos, c);
+		if (grid_occupied(pos, bits, mip, c.grid_size)) break;
+		t = advance_to_next_voxel(t, c, pos, d, idir, c.grid_size >> mip);
 	}
-	if (sub == 0) { p.t = t_base; p.alive = 0; payloads[idx] = p; }
+	p.t = t;
+	payloads[idx] = p;
 }
 
 // 8 lanes per ray ("octet"): the ray's stepping lattice (see march_train.cu) is taken 8 points at a time, every lane evaluates
@@ -191,7 +169,7 @@ extern "C" int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp
 	const float offx = fractf_host(0.5f - ax + bx), offy = fractf_host(0.5f - ay + by);
 	const uint32_t n = (uint32_t)cam->width * (uint32_t)cam->height;
 	CamMat cm; memcpy(cm.m, camera_matrix_host, sizeof(cm.m));
-	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up((uint64_t)n * 8, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads));
+	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads));
 	return check_launch("init_rays");
 }
 

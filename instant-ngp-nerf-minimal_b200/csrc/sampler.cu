@@ -6,6 +6,8 @@
 
 namespace ngp {
 
+constexpr uint32_t kCellMul = 56924617u, kCellAdd = 96925573u;     // the cell hash of occupancy_sampler.cu:81
+
 __global__ void mark_untrained_grid_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, uint32_t n_images, const float* __restrict__ xforms, float* __restrict__ grid_out) {
 	const uint32_t G = c.grid_size, cells = G * G * G, total = cells * c.n_cascades;
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -31,31 +33,83 @@ __global__ void mark_untrained_grid_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam
 	}
 }
 
+// sample i of generate_grid_samples_nerf_nonuniform (occupancy_sampler.cu:63-105): cascade from the first random number, up to 10
+// pseudo-random cells until one is above the threshold, a uniform position inside the cell that was kept
+__device__ __forceinline__ void grid_sample_one(const ngp_sampler_cfg& c, uint32_t i, uint32_t n, const Pcg32& rng0, uint32_t step, const float* __restrict__ grid_in,
+                                                float thresh, float* __restrict__ pos_out, uint32_t* __restrict__ idx_out) {
+	const uint32_t G = c.grid_size, cells = G * G * G;
+	Pcg32 rng = rng0;
+	rng.advance((uint64_t)i * 4);
+	const uint32_t level = (uint32_t)(rng.next_float() * (float)c.n_cascades) % c.n_cascades;
+	uint32_t idx = 0;
+	for (uint32_t j = 0; j < 10; ++j) {
+		idx = ((i + step * n) * kCellMul + j * 19349663u + kCellAdd) % cells;
+		idx += level * cells;
+		if (grid_in[idx] > thresh) break;
+	}
+	const uint32_t pos_idx = idx % cells;
+	const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
+	const float rx = rng.next_float(), ry = rng.next_float(), rz = rng.next_float();
+	const float s = scalbnf(1.0f, (int)level), g = (float)G, diag = c.aabb_max - c.aabb_min;
+	const float px = (((float)x + rx) / g - 0.5f) * s + 0.5f;
+	const float py = (((float)y + ry) / g - 0.5f) * s + 0.5f;
+	const float pz = (((float)z + rz) / g - 0.5f) * s + 0.5f;
+	pos_out[0] = (px - c.aabb_min) / diag;
+	pos_out[1] = (py - c.aabb_min) / diag;
+	pos_out[2] = (pz - c.aabb_min) / diag;
+	*idx_out = idx;
+}
+
 __global__ void generate_grid_samples_kernel(ngp_sampler_cfg c, uint32_t n, Pcg32 rng0, uint32_t step, const float* __restrict__ grid_in, float thresh,
                                              float* __restrict__ out_pos, uint32_t* __restrict__ out_idx) {
-	const uint32_t G = c.grid_size, cells = G * G * G;
-	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-		Pcg32 rng = rng0;
-		rng.advance((uint64_t)i * 4);
-		const uint32_t level = (uint32_t)(rng.next_float() * (float)c.n_cascades) % c.n_cascades;
-		uint32_t idx = 0;
-		for (uint32_t j = 0; j < 10; ++j) {
-			idx = ((i + step * n) * 56924617u + j * 19349663u + 96925573u) % cells;
-			idx += level * cells;
-			if (grid_in[idx] > thresh) break;
-		}
-		const uint32_t pos_idx = idx % cells;
-		const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
-		const float rx = rng.next_float(), ry = rng.next_float(), rz = rng.next_float();
-		const float s = scalbnf(1.0f, (int)level), g = (float)G, diag = c.aabb_max - c.aabb_min;
-		const float px = (((float)x + rx) / g - 0.5f) * s + 0.5f;
-		const float py = (((float)y + ry) / g - 0.5f) * s + 0.5f;
-		const float pz = (((float)z + rz) / g - 0.5f) * s + 0.5f;
-		out_pos[(size_t)i * 3 + 0] = (px - c.aabb_min) / diag;
-		out_pos[(size_t)i * 3 + 1] = (py - c.aabb_min) / diag;
-		out_pos[(size_t)i * 3 + 2] = (pz - c.aabb_min) / diag;
-		out_idx[i] = idx;
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+		grid_sample_one(c, i, n, rng0, step, grid_in, thresh, out_pos + (size_t)i * 3, out_idx + i);
+}
+
+// sum_{i<n} floor((a i + b) / m), all unsigned, in O(log m) (the Euclid-like descent)
+__host__ __device__ inline uint64_t floor_sum(uint64_t n, uint64_t m, uint64_t a, uint64_t b) {
+	uint64_t ans = 0;
+	while (true) {
+		if (a >= m) { ans += n * (n - 1) / 2 * (a / m); a %= m; }
+		if (b >= m) { ans += n * (b / m); b %= m; }
+		const uint64_t y_max = a * n + b;
+		if (y_max < m) break;
+		n = y_max / m; b = y_max % m;
+		const uint64_t t = m; m = a; a = t;
 	}
+	return ans;
+}
+// how many of x_k = (alpha k + beta) mod C, k < M, are below R   (0 <= beta < C, 0 < R < C)
+__host__ __device__ inline uint64_t count_below(uint64_t M, uint64_t C, uint64_t alpha, uint64_t beta, uint64_t R) {
+	return M + floor_sum(M, C, alpha, beta) - floor_sum(M, C, alpha, beta + C - R);
+}
+
+// The same samples, emitted in the order of their FIRST candidate cell.  The cell hash (i + step n) * kCellMul + kCellAdd is a
+// bijection modulo the power-of-two cell count, so thread m inverts it: the samples whose first candidate is Morton cell m are
+// i = i0(m) + r * cells < n with i0(m) = (alpha m + beta) mod cells.  Output slots are the running count of those samples over
+// the cells before m -- closed form through floor_sum, so there is no counting pass and the order is deterministic.  A warp then
+// encodes 32 Morton-adjacent cells instead of 32 cells spread over the whole volume: the hash-grid gathers of the coarse
+// levels hit L1 instead of L2.  The multiset of (position, index) pairs equals generate_grid_samples_kernel's.
+__global__ void __launch_bounds__(256) generate_grid_samples_sorted_kernel(ngp_sampler_cfg c, uint32_t n, Pcg32 rng0, uint32_t step, uint32_t alpha, uint32_t beta,
+                                                                            const float* __restrict__ grid_in, float thresh, float* __restrict__ out_pos, uint32_t* __restrict__ out_idx) {
+	const uint32_t cells = c.grid_size * c.grid_size * c.grid_size, mask = cells - 1;
+	const uint32_t K = n / cells, R = n % cells;
+	const uint32_t m = blockIdx.x * 256 + threadIdx.x;                         // grid covers exactly `cells` threads
+	const uint32_t i0 = (alpha * m + beta) & mask;
+	const uint32_t cnt = K + (i0 < R ? 1u : 0u);
+	__shared__ uint32_t warp_tot[8];
+	__shared__ uint64_t block_base;
+	if (threadIdx.x == 0) block_base = (uint64_t)(blockIdx.x * 256) * K + (R ? count_below(blockIdx.x * 256, cells, alpha, beta, R) : 0);
+	uint32_t incl = cnt;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if ((threadIdx.x & 31) >= o) incl += v; }
+	if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
+	__syncthreads();
+	uint32_t before = 0;
+	for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) before += warp_tot[w];
+	const uint64_t slot0 = block_base + before + incl - cnt;
+	for (uint32_t r = 0; r < cnt; ++r)
+		grid_sample_one(c, i0 + r * cells, n, rng0, step, grid_in, thresh, out_pos + (slot0 + r) * 3, out_idx + slot0 + r);
 }
 
 __device__ __forceinline__ float density_act(float v, int act) {
@@ -143,6 +197,22 @@ extern "C" int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cf
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
 	NGP_LAUNCH("generate_grid_samples_kernel", (cudaStream_t)stream, generate_grid_samples_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, d_grid, thresh, d_positions, d_indices));
 	return check_launch("generate_grid_samples");
+}
+
+extern "C" int ngp_generate_grid_samples_sorted(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
+                                                const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices) {
+	NGP_REQUIRE(cfg && d_grid && d_positions && d_indices, "null pointer");
+	if (n == 0) return 0;
+	const uint32_t cells = cfg->grid_size * cfg->grid_size * cfg->grid_size;
+	if ((cells & (cells - 1)) != 0 || cells < 256)          // the inversion needs a power-of-two cell count: plain order otherwise
+		return ngp_generate_grid_samples(stream, cfg, n, rng_state, rng_inc, step, d_grid, thresh, d_positions, d_indices);
+	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
+	uint32_t inv = kCellMul;                                 // Newton: the inverse of an odd number modulo 2^32
+	for (int k = 0; k < 5; ++k) inv *= 2u - kCellMul * inv;
+	const uint32_t mask = cells - 1;
+	const uint32_t alpha = inv & mask, beta = (0u - inv * kCellAdd - step * n) & mask;
+	NGP_LAUNCH("generate_grid_samples_sorted_kernel", (cudaStream_t)stream, generate_grid_samples_sorted_kernel<<<cells / 256, 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, alpha, beta, d_grid, thresh, d_positions, d_indices));
+	return check_launch("generate_grid_samples_sorted");
 }
 
 extern "C" int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,

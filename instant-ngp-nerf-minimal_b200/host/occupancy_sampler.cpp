@@ -54,11 +54,12 @@ void OccupancySampler::sample_positions_from_grid(uint32_t n_uniform_positions, 
 	grid_positions.enlarge(n_total);
 	grid_indices.enlarge(n_total);
 	const ngp_sampler_cfg c = cfg();
-	api_check(ngp_generate_grid_samples(stream, &c, n_uniform_positions, rng.state, rng.inc, i_step, density_grid.data(), -0.01f,
-	                                    (float*)grid_positions.data(), grid_indices.data()));
+	// Morton-ordered emission: the same samples as the reference's kernel, in an order the hash-grid gathers like (see ngp_b200.h)
+	api_check(ngp_generate_grid_samples_sorted(stream, &c, n_uniform_positions, rng.state, rng.inc, i_step, density_grid.data(), -0.01f,
+	                                           (float*)grid_positions.data(), grid_indices.data()));
 	rng.advance();
-	api_check(ngp_generate_grid_samples(stream, &c, n_nonuniform_positions, rng.state, rng.inc, i_step, density_grid.data(), min_optical_thickness,
-	                                    (float*)(grid_positions.data() + n_uniform_positions), grid_indices.data() + n_uniform_positions));
+	api_check(ngp_generate_grid_samples_sorted(stream, &c, n_nonuniform_positions, rng.state, rng.inc, i_step, density_grid.data(), min_optical_thickness,
+	                                           (float*)(grid_positions.data() + n_uniform_positions), grid_indices.data() + n_uniform_positions));
 	rng.advance();
 }
 

@@ -54,6 +54,46 @@ def test_generate_grid_samples_matches_oracle(capi, orc, thresh, step):
     assert np.array_equal(G.host(pos).reshape(n, 3), rpos)
 
 
+@pytest.mark.parametrize("n_mult,thresh,step", [(0.02, -0.01, 0), (0.5, 0.01, 3), (1.0, -0.01, 17), (2.0, -0.01, 5), (1.5 + 17 / (1 << 21), 0.01, 40), (0.25, 0.01, 257)])
+def test_generate_grid_samples_sorted_is_a_permutation_in_cell_order(capi, orc, n_mult, thresh, step):
+    """ngp_generate_grid_samples_sorted: the identical multiset of (position, index) pairs, in Morton order of the first candidate
+    cell.  Checked against the plain-order kernel (itself checked against the oracle above) and, for the smallest case, the oracle."""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg, ocfg = capi.make_sampler_cfg(1), orc.SamplerCfg(1)
+    cells = 128 ** 3
+    grid = make_density_grid()
+    if thresh < 0:
+        grid = np.abs(grid)                       # every first candidate is accepted: the output must be sorted by cell
+    rng = orc.Pcg32(91)
+    n = int(round(n_mult * cells))
+    d_grid = G.dev(grid)
+    pos, idx = G.zeros(n * 3, torch.float32), G.zeros(n, torch.int32)
+    spos, sidx = G.zeros(n * 3 + 3, torch.float32), G.zeros(n + 1, torch.int32)
+    capi.check(lib.ngp_generate_grid_samples(G.stream(), C.byref(cfg), n, rng.state, rng.inc, step, G.p(d_grid), thresh, G.p(pos), G.p(idx)))
+    capi.check(lib.ngp_generate_grid_samples_sorted(G.stream(), C.byref(cfg), n, rng.state, rng.inc, step, G.p(d_grid), thresh, G.p(spos), G.p(sidx)))
+    G.sync()
+    a_idx, a_pos = G.host(idx, np.uint32), G.host(pos).reshape(n, 3).view(np.uint32)
+    b_idx, b_pos = G.host(sidx, np.uint32), G.host(spos).view(np.uint32)
+    assert b_idx[n] == 0 and not b_pos[3 * n:].any(), "wrote past the n-th slot"
+    b_idx, b_pos = b_idx[:n], b_pos[:3 * n].reshape(n, 3)
+
+    def canon(i, p):
+        o = np.lexsort((p[:, 2], p[:, 1], p[:, 0], i))
+        return i[o], p[o]
+    ai, ap = canon(a_idx, a_pos)
+    bi, bp = canon(b_idx, b_pos)
+    assert np.array_equal(ai, bi) and np.array_equal(ap, bp)
+    if thresh < 0:
+        assert (np.diff((b_idx % cells).astype(np.int64)) >= 0).all(), "not in cell order"
+        assert not np.array_equal(a_idx, b_idx)
+    if n <= 50000:
+        rpos, ridx = orc.generate_grid_samples(ocfg, n, rng, step, grid, thresh)
+        ri, rp = canon(ridx, rpos.view(np.uint32))
+        assert np.array_equal(ri, bi) and np.array_equal(rp, bp)
+
+
 def test_update_grid_and_bitfield_match_oracle(capi, orc):
     import gpuutil as G
     import torch
