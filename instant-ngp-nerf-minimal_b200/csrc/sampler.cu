@@ -90,26 +90,35 @@ __host__ __device__ inline uint64_t count_below(uint64_t M, uint64_t C, uint64_t
 // the cells before m -- closed form through floor_sum, so there is no counting pass and the order is deterministic.  A warp then
 // encodes 32 Morton-adjacent cells instead of 32 cells spread over the whole volume: the hash-grid gathers of the coarse
 // levels hit L1 instead of L2.  The multiset of (position, index) pairs equals generate_grid_samples_kernel's.
-__global__ void __launch_bounds__(256) generate_grid_samples_sorted_kernel(ngp_sampler_cfg c, uint32_t n, Pcg32 rng0, uint32_t step, uint32_t alpha, uint32_t beta,
+__global__ void __launch_bounds__(256) generate_grid_samples_sorted_kernel(ngp_sampler_cfg c, uint32_t n, Pcg32 rng0, uint32_t step, uint32_t alpha, uint32_t beta, uint32_t chunk,
                                                                             const float* __restrict__ grid_in, float thresh, float* __restrict__ out_pos, uint32_t* __restrict__ out_idx) {
 	const uint32_t cells = c.grid_size * c.grid_size * c.grid_size, mask = cells - 1;
 	const uint32_t K = n / cells, R = n % cells;
-	const uint32_t m = blockIdx.x * 256 + threadIdx.x;                         // grid covers exactly `cells` threads
-	const uint32_t i0 = (alpha * m + beta) & mask;
-	const uint32_t cnt = K + (i0 < R ? 1u : 0u);
+	const uint32_t m_begin = blockIdx.x * chunk, m_end = min(m_begin + chunk, cells);      // chunk and cells are multiples of 256
+	if (m_begin >= cells) return;
 	__shared__ uint32_t warp_tot[8];
-	__shared__ uint64_t block_base;
-	if (threadIdx.x == 0) block_base = (uint64_t)(blockIdx.x * 256) * K + (R ? count_below(blockIdx.x * 256, cells, alpha, beta, R) : 0);
-	uint32_t incl = cnt;
-	#pragma unroll
-	for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if ((threadIdx.x & 31) >= o) incl += v; }
-	if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
+	__shared__ uint64_t fs[2];
+	// one closed-form prefix per CTA (the 64-bit divisions of floor_sum are slow: two lanes of different warps take one sum each)
+	if (R && (threadIdx.x == 0 || threadIdx.x == 32)) fs[threadIdx.x >> 5] = floor_sum(m_begin, cells, alpha, threadIdx.x ? (uint64_t)beta + cells - R : (uint64_t)beta);
 	__syncthreads();
-	uint32_t before = 0;
-	for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) before += warp_tot[w];
-	const uint64_t slot0 = block_base + before + incl - cnt;
-	for (uint32_t r = 0; r < cnt; ++r)
-		grid_sample_one(c, i0 + r * cells, n, rng0, step, grid_in, thresh, out_pos + (slot0 + r) * 3, out_idx + slot0 + r);
+	uint64_t base = (uint64_t)m_begin * K + (R ? m_begin + fs[0] - fs[1] : 0);
+	for (uint32_t m0 = m_begin; m0 < m_end; m0 += 256) {
+		const uint32_t i0 = (alpha * (m0 + threadIdx.x) + beta) & mask;
+		const uint32_t cnt = K + (i0 < R ? 1u : 0u);
+		uint32_t incl = cnt;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if ((threadIdx.x & 31) >= o) incl += v; }
+		__syncthreads();                                                                     // the previous round's warp_tot has been read
+		if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
+		__syncthreads();
+		uint32_t before = 0, total = 0;
+		#pragma unroll
+		for (uint32_t w = 0; w < 8; ++w) { const uint32_t v = warp_tot[w]; total += v; if (w < (threadIdx.x >> 5)) before += v; }
+		const uint64_t slot0 = base + before + incl - cnt;
+		for (uint32_t r = 0; r < cnt; ++r)
+			grid_sample_one(c, i0 + r * cells, n, rng0, step, grid_in, thresh, out_pos + (slot0 + r) * 3, out_idx + slot0 + r);
+		base += total;
+	}
 }
 
 __device__ __forceinline__ float density_act(float v, int act) {
@@ -211,7 +220,8 @@ extern "C" int ngp_generate_grid_samples_sorted(void* stream, const ngp_sampler_
 	for (int k = 0; k < 5; ++k) inv *= 2u - kCellMul * inv;
 	const uint32_t mask = cells - 1;
 	const uint32_t alpha = inv & mask, beta = (0u - inv * kCellAdd - step * n) & mask;
-	NGP_LAUNCH("generate_grid_samples_sorted_kernel", (cudaStream_t)stream, generate_grid_samples_sorted_kernel<<<cells / 256, 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, alpha, beta, d_grid, thresh, d_positions, d_indices));
+	const uint32_t chunk = div_up(div_up(cells, 256), kNumSMs * 4) * 256;        // one resident wave of CTAs, each walks a contiguous run of cells
+	NGP_LAUNCH("generate_grid_samples_sorted_kernel", (cudaStream_t)stream, generate_grid_samples_sorted_kernel<<<div_up(cells, chunk), 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, alpha, beta, chunk, d_grid, thresh, d_positions, d_indices));
 	return check_launch("generate_grid_samples_sorted");
 }
 
