@@ -1,6 +1,7 @@
 // Error plumbing of the C ABI plus the two small utility kernels (dataset conversion, loss reduction).
 #include "common.cuh"
 #include <stdarg.h>
+#include <stdlib.h>
 #include <vector>
 #include <string>
 #include <map>
@@ -27,6 +28,11 @@ static bool g_timing = false;
 struct TimedLaunch { const char* name; cudaEvent_t a, b; bool used; };
 static std::vector<TimedLaunch> g_pool;
 static size_t g_pool_used = 0;
+
+bool chained_launch_enabled() {
+	static const bool on = !(getenv("NGP_PDL") && getenv("NGP_PDL")[0] == '0');
+	return on && !g_timing;          // per-kernel timing wants each kernel alone between its two events
+}
 
 KernelTimer::KernelTimer(const char* name, cudaStream_t s) : slot(-1), stream(s) {
 	++g_launches;

@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(256) composite_count_kernel(
 	ngp_render_cfg c, uint32_t n_rays, const uint32_t* __restrict__ ray_counter, const uint32_t* __restrict__ numsteps_in,
 	const Coordinate* __restrict__ coords_in, const __half* __restrict__ net_out, RayTmp* __restrict__ tmp, uint32_t* __restrict__ n_used_out)
 {
+	chain_enter();
 	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const uint32_t n_kept = min(*ray_counter, n_rays);
 	if (i >= n_kept) return;
@@ -74,6 +75,7 @@ __global__ void __launch_bounds__(256) composite_count_kernel(
 // Replaces one global atomicAdd per ray and makes the compacted batch bit-reproducible.
 __global__ void __launch_bounds__(1024) composite_scan_kernel(uint32_t n_rays, const uint32_t* __restrict__ ray_counter, const uint32_t* __restrict__ n_used,
                                                               uint32_t* __restrict__ cbase, uint32_t* __restrict__ compacted_counter) {
+	chain_enter();
 	__shared__ uint32_t warp_tot[32];
 	const uint32_t n_kept = min(*ray_counter, n_rays);
 	const uint32_t per = (n_kept + 1023) / 1024, lo = min(threadIdx.x * per, n_kept), hi = min(lo + per, n_kept);
@@ -107,6 +109,7 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 	float* __restrict__ loss_out, const RayTmp* __restrict__ tmp, const uint32_t* __restrict__ n_used_in, const uint32_t* __restrict__ cbase_in,
 	uint32_t* __restrict__ src_index)
 {
+	chain_enter();
 	const uint32_t lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const uint32_t n_kept = min(*ray_counter, n_rays);
 	if (i >= n_kept) return;
@@ -201,6 +204,7 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 // fill_rollover_and_rescale (grads) + fill_rollover (coords) in one launch
 __global__ void rollover_kernel(uint32_t batch, const uint32_t* __restrict__ n_in_ptr, __half* __restrict__ grads, uint32_t stride, Coordinate* __restrict__ coords,
                                 uint32_t* __restrict__ src_index) {
+	chain_enter();
 	const uint32_t n_in = *n_in_ptr;
 	if (n_in == 0 || n_in >= batch) return;
 	for (uint32_t i = n_in + blockIdx.x * blockDim.x + threadIdx.x; i < batch; i += gridDim.x * blockDim.x) {
@@ -232,10 +236,10 @@ extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint
 	uint32_t* n_used = (uint32_t*)(tmp + n_rays);
 	uint32_t* cbase = n_used + n_rays;
 	const uint32_t grid = div_up(n_rays, 8);
-	NGP_LAUNCH("composite_count_kernel", s, composite_count_kernel<<<grid, 256, 0, s>>>(*cfg, n_rays, d_ray_counter, d_numsteps, (const Coordinate*)d_coords,
+	NGP_LAUNCH("composite_count_kernel", s, launch_chained(composite_count_kernel, grid, 256, 0, s, *cfg, n_rays, d_ray_counter, d_numsteps, (const Coordinate*)d_coords,
 		(const __half*)d_rgbsigma, tmp, n_used));
-	NGP_LAUNCH("composite_scan_kernel", s, composite_scan_kernel<<<1, 1024, 0, s>>>(n_rays, d_ray_counter, n_used, cbase, d_compacted_counter));
-	NGP_LAUNCH("composite_grad_kernel", s, composite_grad_kernel<<<grid, 256, 0, s>>>(*cfg, n_rays, max_compacted, d_ray_counter, (const float4*)d_rays_rgba, d_numsteps,
+	NGP_LAUNCH("composite_scan_kernel", s, launch_chained(composite_scan_kernel, 1, 1024, 0, s, n_rays, d_ray_counter, n_used, cbase, d_compacted_counter));
+	NGP_LAUNCH("composite_grad_kernel", s, launch_chained(composite_grad_kernel, grid, 256, 0, s, *cfg, n_rays, max_compacted, d_ray_counter, (const float4*)d_rays_rgba, d_numsteps,
 		(const Coordinate*)d_coords, (Coordinate*)d_coords_compacted, (const __half*)d_rgbsigma, (__half*)d_dloss, padded_width, d_mean_density, rng, d_loss,
 		tmp, n_used, cbase, d_src_index));
 	return check_launch("composite_train");
@@ -243,6 +247,6 @@ extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint
 
 extern "C" int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted, uint32_t* d_src_index) {
 	NGP_REQUIRE(d_compacted_counter && d_dloss && d_coords_compacted, "null pointer");
-	NGP_LAUNCH("rollover_kernel", (cudaStream_t)stream, rollover_kernel<<<grid_for(batch, 256), 256, 0, (cudaStream_t)stream>>>(batch, d_compacted_counter, (__half*)d_dloss, padded_width, (Coordinate*)d_coords_compacted, d_src_index));
+	NGP_LAUNCH("rollover_kernel", (cudaStream_t)stream, launch_chained(rollover_kernel, grid_for(batch, 256), 256, 0, (cudaStream_t)stream, batch, d_compacted_counter, (__half*)d_dloss, padded_width, (Coordinate*)d_coords_compacted, d_src_index));
 	return check_launch("rollover");
 }

@@ -46,6 +46,7 @@ __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 	const __half2* __restrict__ table, const __grid_constant__ ngp_grid_desc desc,
 	__half* __restrict__ out, uint32_t out_stride, uint32_t* __restrict__ indices)
 {
+	chain_enter();
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (n_valid && blockIdx.x * blockDim.x >= *n_valid) return;
 	if (i >= n) return;
@@ -136,6 +137,7 @@ __global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
 	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad)
 {
+	chain_enter();
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t lane = threadIdx.x & 31;
 	const bool valid = i < n;
@@ -220,8 +222,8 @@ extern "C" int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t st
 	NGP_REQUIRE(out_stride >= 2 * desc->n_levels && out_stride % 2 == 0, "out_stride too small or odd");
 	if (n == 0) return 0;
 	const uint32_t grid = div_up(n, 256);
-	if (d_indices) NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, hash_encode_fwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, d_indices));
-	else NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, hash_encode_fwd_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	if (d_indices) NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<true>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, d_indices));
+	else NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<false>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
 	return check_launch("hash_encode_fwd");
 }
 
@@ -230,8 +232,8 @@ int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t st
                             const void* d_table, const ngp_grid_desc* desc, void* d_out, uint32_t out_stride) {
 	if (n == 0) return 0;
 	static const bool pairs = !(getenv("NGP_HASH_PAIRS") && getenv("NGP_HASH_PAIRS")[0] == '0');
-	if (pairs) NGP_LAUNCH("hash_encode_fwd_kernel", stream, hash_encode_fwd_kernel<false><<<div_up(n, 256), 256, 0, stream>>>(d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
-	else NGP_LAUNCH("hash_encode_fwd_kernel", stream, hash_encode_fwd_kernel<false, false><<<div_up(n, 256), 256, 0, stream>>>(d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	if (pairs) NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	else NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, false>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
 	return check_launch("hash_encode_fwd");
 }
 }
@@ -244,6 +246,6 @@ extern "C" int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t st
 		if (cudaMemsetAsync(d_grad, 0, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half), (cudaStream_t)stream) != cudaSuccess) { set_error("ngp_hash_encode_bwd: memset failed"); return -2; }
 	}
 	if (n == 0) return 0;
-	NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, hash_encode_bwd_kernel<<<div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad));
+	NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad));
 	return check_launch("hash_encode_bwd");
 }

@@ -126,6 +126,10 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 	uint32_t* ctrl = reinterpret_cast<uint32_t*>(smem + kEnd);   // [0..1] mbarrier, [2] tmem base
 	const uint32_t row = threadIdx.x;
 
+	// barrier and TMEM set-up touch no global memory: they run while the previous kernel of the chain is still draining
+	if (threadIdx.x == 0) { mbar_init(sbase + kEnd, 1); fence_mbar_init(); }
+	if (threadIdx.x < 32) tmem_alloc(sbase + kEnd + 8, kTmemCols);
+	chain_enter();
 	stage_weights(weights + kW0, smem, Smem::W0, 64, 32);
 	stage_weights(weights + kW1, smem, Smem::W1, 16, 64);
 	if (MODE != MODE_DENSITY) {
@@ -133,8 +137,6 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 		stage_weights(weights + kV1, smem, Smem::V1, 64, 64);
 		stage_weights(weights + kV2, smem, Smem::V2, 16, 64);
 	}
-	if (threadIdx.x == 0) { mbar_init(sbase + kEnd, 1); fence_mbar_init(); }
-	if (threadIdx.x < 32) tmem_alloc(sbase + kEnd + 8, kTmemCols);
 	fence_before_sync();
 	__syncthreads();
 	fence_after_sync();
@@ -351,6 +353,7 @@ int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t st
 
 // sums the per-CTA weight-gradient slots in CTA order (deterministic) and rounds to the fp16 gradient arena
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partials, uint32_t n_slots, __half* __restrict__ w16, uint32_t n) {
+	chain_enter();
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
 	float s = 0.f;
@@ -373,7 +376,7 @@ static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords,
 	}
 	const uint32_t n_tiles = div_up(n, 128);
 	const uint32_t grid = n_tiles < kNumSMs * ctas_per_sm ? n_tiles : kNumSMs * ctas_per_sm;
-	NGP_LAUNCH("mlp_kernel", stream, mlp_kernel<MODE><<<grid, 128, smem, stream>>>((const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
+	NGP_LAUNCH("mlp_kernel", stream, launch_chained(mlp_kernel<MODE>, grid, 128, smem, stream, (const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
 		(const __half*)dloss, (__half*)out, (__half*)denc, wgrad, wgrad_partials, enc_rows, n_enc_rows));
 	if (grid_out) *grid_out = grid;
 	return check_launch("mlp_kernel");
@@ -444,7 +447,7 @@ static int network_train_impl(void* stream, const float* d_coords, uint32_t n, c
 	uint32_t n_slots = 0;
 	rc = launch_mlp<MODE_TRAIN>(s, d_encoded ? d_encoded : enc, d_coords, 7, n, nullptr, params, d_dloss, d_rgbsigma, denc, nullptr, wgrad_slots, &n_slots, d_src_index, n_encoded);
 	if (rc) return rc;
-	NGP_LAUNCH("wgrad_reduce_kernel", s, wgrad_reduce_kernel<<<div_up(NGP_MLP_PARAMS, 128), 128, 0, s>>>(wgrad_slots, n_slots, (__half*)d_grads, NGP_MLP_PARAMS));
+	NGP_LAUNCH("wgrad_reduce_kernel", s, launch_chained(wgrad_reduce_kernel, div_up(NGP_MLP_PARAMS, 128), 128, 0, s, wgrad_slots, n_slots, (__half*)d_grads, NGP_MLP_PARAMS));
 	return ngp_hash_encode_bwd(stream, d_coords, 7, n, denc, 32, desc, (__half*)d_grads + NGP_MLP_PARAMS, 1);
 }
 

@@ -91,6 +91,7 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t begin, uint64_t 
                                                         const __half* __restrict__ g16, float* __restrict__ m1, float* __restrict__ m2,
                                                         uint32_t* __restrict__ steps, __half* __restrict__ ema16, ngp_peer_set ps, uint32_t epoch,
                                                         uint32_t* __restrict__ ticket) {
+	chain_enter();
 	const uint64_t n8 = n / 8;
 	for (uint64_t q = begin / 8 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < n8; q += (uint64_t)gridDim.x * blockDim.x) {
 		const uint64_t i = q * 8;
@@ -161,12 +162,14 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t begin, uint64_t 
 
 // ---- sharded step over peer memory ---------------------------------------------------------------------------------
 __global__ void peer_publish_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t epoch) {
+	chain_enter();
 	// stream order has completed this rank's backward pass; make it visible system-wide, then raise the flag at every rank
 	__threadfence_system();
 	if (threadIdx.x < ps.world) st_release_sys(ps.flags[threadIdx.x] + slot_base + ps.rank, epoch);
 }
 
 __global__ void peer_wait_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t epoch) {
+	chain_enter();
 	if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + slot_base + threadIdx.x) < epoch) __nanosleep(64); }
 }
 
@@ -175,6 +178,7 @@ __global__ void peer_wait_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t e
 // 16-byte loads from every peer in flight per thread: the kernel exists to keep enough bytes in flight to cover NVLink latency.
 template <int WORLD>
 __global__ void __launch_bounds__(512) peer_reduce_kernel(uint64_t begin, uint64_t end, ngp_peer_set ps, uint32_t epoch) {
+	chain_enter();
 	if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + threadIdx.x) < epoch) __nanosleep(32); }
 	__syncthreads();
 	uint4* mine = reinterpret_cast<uint4*>(const_cast<void*>(ps.grads[ps.rank]));
@@ -234,7 +238,7 @@ extern "C" int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, ui
 	if (n_params == 0) return 0;
 	AdamHyper h;
 	fill_hyper(h, cfg, step, learning_rate);
-	NGP_LAUNCH("adam_ema_kernel", (cudaStream_t)stream, adam_ema_kernel<false><<<grid_for(n_params / 8 + 1, 256, 6), 256, 0, (cudaStream_t)stream>>>(0, n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
+	NGP_LAUNCH("adam_ema_kernel", (cudaStream_t)stream, launch_chained(adam_ema_kernel<false>, grid_for(n_params / 8 + 1, 256, 6), 256, 0, (cudaStream_t)stream, 0, n_params, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
 		d_m1, d_m2, d_param_steps, (__half*)d_ema16, ngp_peer_set{}, 0, nullptr));
 	return check_launch("optimizer_step");
 }
@@ -247,13 +251,13 @@ static int check_peers(const ngp_peer_set* ps) {
 
 extern "C" int ngp_peer_publish_gradients(void* stream, const ngp_peer_set* peers, uint32_t epoch) {
 	if (check_peers(peers)) return -1;
-	NGP_LAUNCH("peer_publish_kernel", (cudaStream_t)stream, peer_publish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*peers, 0, epoch));
+	NGP_LAUNCH("peer_publish_kernel", (cudaStream_t)stream, launch_chained(peer_publish_kernel, 1, 32, 0, (cudaStream_t)stream, *peers, 0, epoch));
 	return check_launch("peer_publish_gradients");
 }
 
 extern "C" int ngp_peer_wait_weights(void* stream, const ngp_peer_set* peers, uint32_t epoch) {
 	if (check_peers(peers)) return -1;
-	NGP_LAUNCH("peer_wait_kernel", (cudaStream_t)stream, peer_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*peers, NGP_MAX_PEERS, epoch));
+	NGP_LAUNCH("peer_wait_kernel", (cudaStream_t)stream, launch_chained(peer_wait_kernel, 1, 32, 0, (cudaStream_t)stream, *peers, NGP_MAX_PEERS, epoch));
 	return check_launch("peer_wait_weights");
 }
 
@@ -269,12 +273,12 @@ extern "C" int ngp_optimizer_step_sharded(void* stream, const ngp_optimizer_cfg*
 	const uint64_t groups = (shard_end - shard_begin) / 8;
 	cudaStream_t st = (cudaStream_t)stream;
 	const uint32_t rgrid = grid_for(groups ? groups : 1, 512, 4);
-	if (peers->world <= 2) NGP_LAUNCH("peer_reduce_kernel", st, peer_reduce_kernel<2><<<rgrid, 512, 0, st>>>(shard_begin, shard_end, *peers, epoch));
-	else if (peers->world <= 4) NGP_LAUNCH("peer_reduce_kernel", st, peer_reduce_kernel<4><<<rgrid, 512, 0, st>>>(shard_begin, shard_end, *peers, epoch));
-	else NGP_LAUNCH("peer_reduce_kernel", st, peer_reduce_kernel<8><<<rgrid, 512, 0, st>>>(shard_begin, shard_end, *peers, epoch));
+	if (peers->world <= 2) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<2>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
+	else if (peers->world <= 4) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<4>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
+	else NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<8>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
 	__half* w16 = (__half*)peers->params[peers->rank];
 	const __half* g16 = (const __half*)peers->grads[peers->rank];
-	NGP_LAUNCH("adam_ema_kernel", st, adam_ema_kernel<true><<<grid_for(groups ? groups : 1, 256, 6), 256, 0, st>>>(shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+	NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true>, grid_for(groups ? groups : 1, 256, 6), 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
 		d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
 	return check_launch("optimizer_step_sharded");
 }
