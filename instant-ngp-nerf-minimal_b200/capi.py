@@ -57,11 +57,13 @@ SIGNATURES = {
     "ngp_auto_per_level_scale": (f32, [f32, u32, u32]),
     "ngp_hash_encode_fwd": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, u32, vp]),
     "ngp_hash_encode_bwd": (i32, [vp, vp, u32, u32, vp, u32, C.POINTER(GridDesc), vp, i32]),
+    "ngp_hash_encode_bwd_levels": (i32, [vp, vp, u32, u32, vp, u32, C.POINTER(GridDesc), vp, u32, u32]),
     "ngp_network_workspace_bytes": (sz, [u32]),
     "ngp_network_inference": (i32, [vp, vp, u32, vp, vp, C.POINTER(GridDesc), vp, vp, sz]),
     "ngp_network_density": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, vp, sz]),
     "ngp_network_train": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, sz]),
     "ngp_network_train_reuse": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, u32, vp, vp, sz]),
+    "ngp_network_train_reuse_phased": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, u32, vp, vp, sz, u32, vp, i32]),
     "ngp_mlp_inference": (i32, [vp, vp, vp, u32, vp, vp]),
     "ngp_mlp_train": (i32, [vp, vp, vp, u32, vp, vp, vp, vp, vp]),
     "ngp_mark_untrained_grid": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), u32, vp, vp]),
@@ -84,6 +86,7 @@ SIGNATURES = {
     "ngp_tonemap": (i32, [vp, u32, f32, C.POINTER(f32), vp, i32, i32, i32, vp]),
     "ngp_init_params": (i32, [vp, C.POINTER(u64), u64, u64, vp, vp]),
     "ngp_optimizer_step": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u32, f32, vp, vp, vp, vp, vp, vp, vp]),
+    "ngp_optimizer_step_range": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u64, u32, f32, vp, vp, vp, vp, vp, vp, vp, i32]),
     "ngp_peer_publish_gradients": (i32, [vp, C.POINTER(PeerSet), u32]),
     "ngp_optimizer_step_sharded": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u64, u32, f32, vp, vp, vp, vp, vp, C.POINTER(PeerSet), u32, vp]),
     "ngp_peer_wait_weights": (i32, [vp, C.POINTER(PeerSet), u32]),

@@ -135,7 +135,8 @@ __device__ __forceinline__ void red_half2x2(__half2* p, float x0, float y0, floa
 // contended coarse levels issue one reduction per run instead of one per sample.
 __global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
-	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad)
+	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad,
+	uint32_t level_begin, uint32_t level_end)
 {
 	chain_enter();
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
 	const float x = xyz[(size_t)ii * stride_floats + 0], y = xyz[(size_t)ii * stride_floats + 1], z = xyz[(size_t)ii * stride_floats + 2];
 	const __half* drow = dy + (size_t)ii * dy_stride;
 
-	for (uint32_t l = 0; l < desc.n_levels; ++l) {
+	for (uint32_t l = level_begin; l < level_end; ++l) {
 		const uint32_t off = desc.offsets[l], size = desc.offsets[l + 1] - off, res = desc.resolutions[l];
 		const float scale = desc.scales[l];
 		const bool hashed = level_is_hashed(size, res);
@@ -238,14 +239,21 @@ int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t st
 }
 }
 
+extern "C" int ngp_hash_encode_bwd_levels(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
+                                          const ngp_grid_desc* desc, void* d_grad, uint32_t level_begin, uint32_t level_end) {
+	NGP_REQUIRE(d_xyz && d_dy && desc && d_grad, "null pointer");
+	NGP_REQUIRE(((uintptr_t)d_grad & 7u) == 0, "d_grad must be 8-byte aligned");
+	NGP_REQUIRE(level_begin <= level_end && level_end <= desc->n_levels, "bad level range");
+	if (n == 0 || level_begin == level_end) return 0;
+	NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
+	return check_launch("hash_encode_bwd");
+}
+
 extern "C" int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
                                    const ngp_grid_desc* desc, void* d_grad, int zero_first) {
 	NGP_REQUIRE(d_xyz && d_dy && desc && d_grad, "null pointer");
-	NGP_REQUIRE(((uintptr_t)d_grad & 7u) == 0, "d_grad must be 8-byte aligned");
 	if (zero_first) {
 		if (cudaMemsetAsync(d_grad, 0, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half), (cudaStream_t)stream) != cudaSuccess) { set_error("ngp_hash_encode_bwd: memset failed"); return -2; }
 	}
-	if (n == 0) return 0;
-	NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad));
-	return check_launch("hash_encode_bwd");
+	return ngp_hash_encode_bwd_levels(stream, d_xyz, stride_floats, n, d_dy, dy_stride, desc, d_grad, 0, desc->n_levels);
 }

@@ -94,6 +94,7 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readonly("training_buffer", &Testbed::m_training_buffer)
 		.def_readonly("rendering_buffer", &Testbed::m_rendering_buffer)
 		.def_readwrite("pipeline_march", &Testbed::m_pipeline_march, "march step i+1 on a second stream underneath step i (default on)")
+		.def_readwrite("fine_level_begin", &Testbed::m_fine_level_begin, "single GPU: grid levels >= this are stepped by the optimizer on a side stream while the coarser levels' gradients are still being scattered (0 = off)")
 		.def_property("fov", &Testbed::fov, &Testbed::set_fov)
 		.def_property("fov_xy",
 			[](const Testbed& t) { return std::vector<float>{focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[0]), focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[1])}; },
