@@ -141,7 +141,9 @@ def test_hash_encode_bwd_levels_partition_the_full_scatter(capi, orc, split):
     a, b, c = (G.host(t, np.float16).astype(np.float32) for t in (full, parts, only))
     cut = int(L.offsets[split]) * 2
     assert not c[:cut].any(), "a level range wrote below its first level"
-    assert np.array_equal(c[cut:] != 0, a[cut:] != 0)
+    differ = (c[cut:] != 0) != (a[cut:] != 0)      # an order-dependent fp16 sum may cancel to exactly 0 in one run only
+    assert np.all(np.maximum(np.abs(c[cut:][differ]), np.abs(a[cut:][differ])) <= 2e-5), "a level range missed entries of its levels"
+    assert differ.sum() <= 1e-4 * max(1, int((a[cut:] != 0).sum()))
     fine = int(L.offsets[10]) * 2
     assert np.allclose(a[fine:], b[fine:], rtol=2e-3, atol=1e-6)
     assert np.allclose(a, b, rtol=1e-2, atol=2e-5)
