@@ -37,6 +37,7 @@ def parse():
     p.add_argument("--views", type=int, default=100)
     p.add_argument("--res", type=int, default=800)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--timeline", default=None, help="write a per-launch timeline (json per rank) of two further train() calls with the march pipelined")
     p.add_argument("--dp-mode", default="peer", choices=["peer", "nccl"],
                    help="N > 1: fused reduce-scatter + Adam + all-gather over NVLink peer memory (default), or NCCL all-reduce + replicated optimizer")
     p.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference's own CUDA build (oracle/_ref/ref_harness) beside ours")
@@ -65,26 +66,40 @@ class ClockSampler:
             import pynvml
             pynvml.nvmlInit()
             self.nvml, self.handle = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx.append(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))     # static
+            self._query()                          # first use of each query initialises driver state: keep that out of the timed region
+            self.sm, self.reasons = [], set()
         except Exception:
             self.nvml = None
 
-    def _poll(self):
+    def _query(self):
         n = self.nvml
-        names = {n.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", n.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
-                 n.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", n.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        self.sm.append(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+        r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+        for bit, name in ((n.nvmlClocksThrottleReasonHwSlowdown, "hw_slowdown"), (n.nvmlClocksThrottleReasonHwThermalSlowdown, "hw_thermal_slowdown"),
+                          (n.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_thermal_slowdown"), (n.nvmlClocksThrottleReasonSwPowerCap, "sw_power_cap")):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _poll(self):
+        # first sample 30 ms into the region, then every 200 ms (the recipe's nvidia-smi -lms 200): every query takes a driver lock
+        # that can hold up the launches of all processes on the box for milliseconds, and a 0.6 ms step notices
+        period = float(os.environ.get("NGP_CLOCK_PERIOD_S", "0.2"))
+        t_next = time.perf_counter() + 0.03
         while not self.stop_flag:
-            try:
-                self.sm.append(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
-                self.mx.append(n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM))
-                r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
-                for bit, name in names.items():
-                    if r & bit:
-                        self.reasons.add(name)
-            except Exception:
-                pass
-            time.sleep(0.02)
+            if time.perf_counter() >= t_next:
+                try:
+                    self._query()
+                except Exception:
+                    pass
+                t_next += period
+            time.sleep(0.005)
 
     def start(self):
+        if os.environ.get("NGP_NO_CLOCKS") or (int(os.environ.get("RANK", "0")) != 0 and not os.environ.get("NGP_CLOCKS_ALL_RANKS")):
+            # rank 0 samples its GPU; a query takes a driver lock that holds up launches of every process on the box, and in a
+            # lock-stepped data-parallel run each hold-up is paid by all ranks (measured at 2 GPUs: 0.805 -> 0.737 ms/step)           #             self.nvml, self.thread, self.proc = None, None, None
+            return
         if self.nvml is not None:
             self.thread = threading.Thread(target=self._poll, daemon=True)
             self.thread.start()
@@ -303,6 +318,8 @@ def run_ours(args):
 
     tb = pyngp.Testbed()
     tb.load_model_config(os.path.join(ROOT, PKG, "configs", "base.json"))
+    if os.environ.get("NGP_SERIAL_MARCH"):        # experiment switch: no look-ahead march
+        tb.pipeline_march = False
     comm = 0
     if world > 1:
         box = [pyngp.nccl_unique_id() if rank == 0 else None]
@@ -342,10 +359,16 @@ def run_ours(args):
     capi.check(lib.ngp_kernel_timing_enable(1, 64 * prof_steps + 4096))
     tb.pipeline_march = False             # kernels one after another on one stream, so each duration is the kernel's own
     p_samples, p_marched, p_rays, _ = train_steps(tb, prof_steps, args.batch)
-    tb.pipeline_march = True
+    tb.pipeline_march = not os.environ.get("NGP_SERIAL_MARCH")
     kt = capi.kernel_timing_collect()
     capi.check(lib.ngp_kernel_timing_enable(0, 0))
 
+    if args.timeline:
+        capi.check(lib.ngp_kernel_timing_enable(1, 8192))
+        train_steps(tb, 2 * CALL_STEPS, args.batch)
+        tl = capi.kernel_timing_timeline()
+        capi.check(lib.ngp_kernel_timing_enable(0, 0))
+        json.dump(tl, open(f"{args.timeline}.rank{rank}.json", "w"))
     if world > 1:
         t = torch.tensor([dev_ms, wall * 1e3, t_upload * 1e3], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

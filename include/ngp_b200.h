@@ -70,6 +70,8 @@ int ngp_abi_version(void);
 unsigned long long ngp_launch_count(void);
 int ngp_kernel_timing_enable(int on, uint32_t max_launches);
 int ngp_kernel_timing_collect(uint32_t max_kernels, char* names /* [max_kernels][64] */, float* total_ms, uint32_t* counts);
+/* per-launch start / end (ms since the first recorded launch), in launch order; synchronises and resets like _collect */
+int ngp_kernel_timing_timeline(uint32_t max_launches, char* names /* [max_launches][64] */, float* start_ms, float* end_ms);
 
 /* ---- hash grid -------------------------------------------------------------------------------- */
 /* replaces GridEncodingTemplated ctor (grid.h:475-537); returns the number of table entries */

@@ -53,6 +53,7 @@ SIGNATURES = {
     "ngp_launch_count": (u64, []),
     "ngp_kernel_timing_enable": (i32, [i32, u32]),
     "ngp_kernel_timing_collect": (i32, [u32, vp, vp, vp]),
+    "ngp_kernel_timing_timeline": (i32, [u32, vp, vp, vp]),
     "ngp_grid_desc_init": (u32, [C.POINTER(GridDesc), u32, u32, u32, f32]),
     "ngp_auto_per_level_scale": (f32, [f32, u32, u32]),
     "ngp_hash_encode_fwd": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, u32, vp]),
@@ -153,6 +154,19 @@ def make_sampler_cfg(aabb_scale=1, grid_size=128, max_steps=1024, cone_angle=0.0
     c.max_step = float(sqrt3 * np.float32(1 << (n_cascades - 1)) / np.float32(grid_size))
     c.near_distance = near_distance
     return c
+
+
+def kernel_timing_timeline(max_launches=8192):
+    """[(kernel name, start ms, end ms)] per recorded launch, relative to the first one; synchronises the device"""
+    import numpy as np
+    lib = load()
+    names = C.create_string_buffer(max_launches * 64)
+    a = np.zeros(max_launches, np.float32)
+    b = np.zeros(max_launches, np.float32)
+    k = lib.ngp_kernel_timing_timeline(max_launches, names, a.ctypes.data_as(vp), b.ctypes.data_as(vp))
+    if k < 0:
+        raise NgpError(lib.ngp_last_error().decode())
+    return [(names.raw[i * 64:(i + 1) * 64].split(b"\0")[0].decode(), float(a[i]), float(b[i])) for i in range(k)]
 
 
 def kernel_timing_collect(max_kernels=64):

@@ -129,6 +129,22 @@ extern "C" int ngp_kernel_timing_collect(uint32_t max_kernels, char* names, floa
 	return (int)k;
 }
 
+// Per-launch timeline of the recorded region: start / end of launch i in ms relative to the first recorded launch, in launch
+// order (events on different streams of one device share a clock).  Synchronises the device and resets the recorder.
+extern "C" int ngp_kernel_timing_timeline(uint32_t max_launches, char* names, float* start_ms, float* end_ms) {
+	if (cudaDeviceSynchronize() != cudaSuccess) { set_error("ngp_kernel_timing_timeline: device synchronise failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
+	uint32_t k = 0;
+	for (size_t i = 0; i < g_pool_used && k < max_launches; ++i) {
+		float a = 0.f, b = 0.f;
+		if (cudaEventElapsedTime(&a, g_pool[0].a, g_pool[i].a) != cudaSuccess || cudaEventElapsedTime(&b, g_pool[0].a, g_pool[i].b) != cudaSuccess) { cudaGetLastError(); continue; }
+		snprintf(names + (size_t)k * 64, 64, "%s", g_pool[i].name);
+		start_ms[k] = a; end_ms[k] = b;
+		++k;
+	}
+	g_pool_used = 0;
+	return (int)k;
+}
+
 extern "C" int ngp_from_rgba32(void* stream, uint64_t n_pixels, const uint8_t* d_rgba8, void* d_out_half) {
 	NGP_REQUIRE(d_rgba8 && d_out_half, "null pointer");
 	if (n_pixels == 0) return 0;

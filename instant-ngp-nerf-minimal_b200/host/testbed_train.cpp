@@ -79,6 +79,8 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 		learn_step(slot, target_batch_size, n_rays, rng_step, tb.n_coords_counter.data() + 2 * i, tb.n_compacted_coords_counter.data() + i,
 		           tb.loss.data() + (size_t)n_rays * i, stream);
 		NGP_CUDA_CHECK(cudaEventRecord(m_ev_slot_free[slot], stream));
+		static const bool sync_each_step = getenv("NGP_SYNC_EACH_STEP") != nullptr;     // experiment switch
+		if (sync_each_step) NGP_CUDA_CHECK(cudaStreamSynchronize(stream));
 		rng_step.advance();
 		++tb.i_step;
 	}
