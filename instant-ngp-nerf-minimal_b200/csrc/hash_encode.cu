@@ -189,6 +189,114 @@ __global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
 	}
 }
 
+
+// all 8 corner entries of one cell; same values as grid_index() corner by corner.  Hashed: the y and z products are formed once
+// and stepped by their primes.  Dense: one base index stepped by the strides, wrapped by a compare (the index of a point inside
+// the unit cube is below 2 * size), with the general modulo kept for anything else.
+__device__ __forceinline__ void cell_entries(uint32_t size, uint32_t res, bool hashed, uint32_t gx, uint32_t gy, uint32_t gz, uint32_t (&e)[8]) {
+	if (hashed) {
+		const uint32_t hy0 = gy * 19349663u, hy1 = hy0 + 19349663u, hz0 = gz * 83492791u, hz1 = hz0 + 83492791u;
+		const uint32_t h[4] = {hy0 ^ hz0, hy1 ^ hz0, hy0 ^ hz1, hy1 ^ hz1};
+		const bool pow2 = (size & (size - 1)) == 0;
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			const uint32_t idx = (gx + (c & 1)) ^ h[c >> 1];
+			e[c] = pow2 ? (idx & (size - 1)) : (idx % size);
+		}
+	} else {
+		const uint32_t sy = res, sz = res * res;
+		const uint32_t base = gx + gy * sy + gz * sz;
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			uint32_t idx = base + (c & 1) + ((c & 2) ? sy : 0u) + ((c & 4) ? sz : 0u);
+			if (idx >= size) { idx -= size; if (idx >= size) idx %= size; }
+			e[c] = idx;
+		}
+	}
+}
+
+__device__ __forceinline__ void red_h2(__half2* p, __half2 v) {
+	asm volatile("red.global.add.noftz.f16x2 [%0], %1;" :: "l"(p), "r"(*reinterpret_cast<const uint32_t*>(&v)) : "memory");
+}
+__device__ __forceinline__ void red_h2x2(__half2* p, __half2 a, __half2 b) {
+	asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" :: "l"(p), "r"(*reinterpret_cast<const uint32_t*>(&a)), "r"(*reinterpret_cast<const uint32_t*>(&b)) : "memory");
+}
+
+// Backward, second generation.  Same mapping (thread = sample, warp = 32 consecutive samples of mostly one ray) and the same
+// arithmetic per term (weight product order, fp16 rounding of every term as in grid.h:303-306), but the merge of equal targets
+// is keyed by the CELL: neighbouring lanes inside one cell share all 8 corners, so the run structure is found once per level
+// (3 shuffles + 1 ballot) instead of once per corner, the 16 partial sums of a run are reduced in fp32 with only as many
+// shuffle rounds as the longest run of the warp needs, and warps without any run (the fine levels) skip the merge altogether.
+// x-adjacent corner pairs whose entries are adjacent in memory leave as one 8-byte reduction.  The first-generation kernel
+// spent ~800 instructions per warp and level, most of them in eight corner-keyed run sums; it was issue-bound (72 %).
+__global__ void __launch_bounds__(256) hash_encode_bwd_cell_kernel(
+	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
+	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad,
+	uint32_t level_begin, uint32_t level_end)
+{
+	chain_enter();
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31;
+	const bool valid = i < n;
+	const uint32_t ii = valid ? i : n - 1;
+	const float x = xyz[(size_t)ii * stride_floats + 0], y = xyz[(size_t)ii * stride_floats + 1], z = xyz[(size_t)ii * stride_floats + 2];
+	const __half* drow = dy + (size_t)ii * dy_stride;
+
+	for (uint32_t l = level_begin; l < level_end; ++l) {
+		const uint32_t off = desc.offsets[l], size = desc.offsets[l + 1] - off, res = desc.resolutions[l];
+		const float scale = desc.scales[l];
+		const bool hashed = level_is_hashed(size, res);
+		__half2* grid = grad + off;
+		uint32_t gx, gy, gz; float wx, wy, wz;
+		pos_fract(x, scale, gx, wx); pos_fract(y, scale, gy, wy); pos_fract(z, scale, gz, wz);
+		const float2 g = __half22float2(*reinterpret_cast<const __half2*>(drow + 2 * l));
+
+		// runs of neighbouring lanes inside one cell (invalid lanes sit at the tail of the last warp and are runs of their own)
+		const uint32_t pgx = __shfl_up_sync(0xffffffffu, gx, 1), pgy = __shfl_up_sync(0xffffffffu, gy, 1), pgz = __shfl_up_sync(0xffffffffu, gz, 1);
+		const bool joins = valid && lane != 0 && pgx == gx && pgy == gy && pgz == gz;
+		const uint32_t heads = ~__ballot_sync(0xffffffffu, joins);
+
+		uint32_t e[8];
+		cell_entries(size, res, hashed, gx, gy, gz, e);
+		__half2 t[8];
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			// same product order as the forward pass: (wx' * wy') * wz'
+			const float w = (((c & 1) ? wx : 1 - wx) * ((c & 2) ? wy : 1 - wy)) * ((c & 4) ? wz : 1 - wz);
+			t[c] = __floats2half2_rn(g.x * w, g.y * w);
+		}
+		bool head = true;
+		if (heads != 0xffffffffu) {
+			const uint32_t above = heads & ~((2u << lane) - 1u);              // heads strictly above this lane
+			const uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;     // last lane of this lane's run
+			const uint32_t reach = __reduce_max_sync(0xffffffffu, end - lane);  // longest run of the warp, minus one
+			float v[16];
+			#pragma unroll
+			for (int c = 0; c < 8; ++c) { const float2 f = __half22float2(t[c]); v[2 * c] = f.x; v[2 * c + 1] = f.y; }
+			for (uint32_t o = 1; o <= reach; o <<= 1) {
+				const bool take = lane + o <= end;
+				#pragma unroll
+				for (int k = 0; k < 16; ++k) { const float a = __shfl_down_sync(0xffffffffu, v[k], o); if (take) v[k] += a; }
+			}
+			#pragma unroll
+			for (int c = 0; c < 8; ++c) t[c] = __floats2half2_rn(v[2 * c], v[2 * c + 1]);
+			head = (heads >> lane) & 1u;
+		}
+		if (valid && head) {
+			#pragma unroll
+			for (int c = 0; c < 8; c += 2) {
+				if (e[c + 1] == (e[c] ^ 1u)) {
+					if (e[c] & 1u) red_h2x2(grid + e[c + 1], t[c + 1], t[c]);
+					else red_h2x2(grid + e[c], t[c], t[c + 1]);
+				} else {
+					red_h2(grid + e[c], t[c]);
+					red_h2(grid + e[c + 1], t[c + 1]);
+				}
+			}
+		}
+	}
+}
+
 } // namespace ngp
 
 using namespace ngp;
@@ -247,7 +355,9 @@ extern "C" int ngp_hash_encode_bwd_levels(void* stream, const float* d_xyz, uint
 	NGP_REQUIRE(((uintptr_t)d_grad & 7u) == 0, "d_grad must be 8-byte aligned");
 	NGP_REQUIRE(level_begin <= level_end && level_end <= desc->n_levels, "bad level range");
 	if (n == 0 || level_begin == level_end) return 0;
-	NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
+	static const bool corner_keyed = getenv("NGP_HASH_BWD") && getenv("NGP_HASH_BWD")[0] == '1';       // first-generation kernel, for A/B runs
+	if (corner_keyed) NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
+	else NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_cell_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
 	return check_launch("hash_encode_bwd");
 }
 
