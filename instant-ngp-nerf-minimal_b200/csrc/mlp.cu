@@ -82,6 +82,10 @@ struct Pipe {
 	// thread 0 after issuing: commit; everyone: wait for completion
 	__device__ __forceinline__ void commit_and_wait() {
 		if (threadIdx.x == 0) mma_commit(bar);
+		wait();
+	}
+	// the issuing thread has already committed (possibly with more MMAs queued behind the commit)
+	__device__ __forceinline__ void wait() {
 		__syncwarp();
 		mbar_wait(bar, parity);
 		parity ^= 1;
@@ -89,12 +93,23 @@ struct Pipe {
 	}
 };
 
+// the global-memory inputs of one tile row, fetched one tile ahead so that their latency (two dependent loads for a reused
+// encoding row) hides under the current tile's layers instead of heading its serial chain
+struct TileIn { uint4 e[4]; float dx, dy, dz; uint2 dl; };
+
 // read this thread's row: n16 groups of 16 fp32 columns starting at column col
 template <int N16>
 __device__ __forceinline__ void read_row(uint32_t tmem, uint32_t col, float* v) {
 	const uint32_t lane_base = (threadIdx.x & ~31u) << 16;
+	// all groups are requested before the one wait: one TMEM round trip per epilogue instead of N16
+	uint32_t r[N16 * 16];
 	#pragma unroll
-	for (int g = 0; g < N16; ++g) tmem_ld16(tmem + lane_base + col + g * 16, v + g * 16);
+	for (int g = 0; g < N16; ++g) tmem_ld16_nowait(tmem + lane_base + col + g * 16, r + g * 16);
+	tmem_ld_wait();
+	#pragma unroll
+	for (int g = 0; g < N16; ++g) tmem_ld_pin(r + g * 16);
+	#pragma unroll
+	for (int i = 0; i < N16 * 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
 // zero the gradient where the forward activation (fp16, this thread's row in buf) was not positive
@@ -113,7 +128,7 @@ __device__ __forceinline__ void relu_mask64(const uint8_t* smem, uint32_t buf, u
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(128) mlp_kernel(
+__global__ void __launch_bounds__(128, MODE == MODE_TRAIN ? 2 : 3) mlp_kernel(
 	const __half* __restrict__ enc, const float* __restrict__ coords, uint32_t coord_stride, uint32_t n, const uint32_t* __restrict__ n_valid,
 	const __half* __restrict__ weights, const __half* __restrict__ dloss, __half* __restrict__ out, __half* __restrict__ denc, float* __restrict__ wgrad,
 	float* __restrict__ wgrad_partials, const uint32_t* __restrict__ enc_rows, uint32_t n_enc_rows)
@@ -123,11 +138,11 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 	constexpr uint32_t kH2 = MODE == MODE_TRAIN ? Smem::H2 : Smem::H;
 	constexpr uint32_t kTmemCols = MODE == MODE_TRAIN ? 256 : 64;
 	const uint32_t sbase = smem_u32(smem);
-	uint32_t* ctrl = reinterpret_cast<uint32_t*>(smem + kEnd);   // [0..1] mbarrier, [2] tmem base
+	uint32_t* ctrl = reinterpret_cast<uint32_t*>(smem + kEnd);   // [0..1] mbarrier, [2] tmem base, [4..5] second mbarrier (weight-gradient MMAs)
 	const uint32_t row = threadIdx.x;
 
 	// barrier and TMEM set-up touch no global memory: they run while the previous kernel of the chain is still draining
-	if (threadIdx.x == 0) { mbar_init(sbase + kEnd, 1); fence_mbar_init(); }
+	if (threadIdx.x == 0) { mbar_init(sbase + kEnd, 1); mbar_init(sbase + kEnd + 16, 1); fence_mbar_init(); }
 	if (threadIdx.x < 32) tmem_alloc(sbase + kEnd + 8, kTmemCols);
 	chain_enter();
 	stage_weights(weights + kW0, smem, Smem::W0, 64, 32);
@@ -150,25 +165,39 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 	const uint32_t n_limit = n_valid ? min(*n_valid, n) : n;
 	const uint32_t n_tiles = (n_limit + 127) / 128;
 	uint32_t wg_acc = 0;   // 0 for the CTA's first tile, 1 afterwards
+	uint32_t wg_parity = 0;
+
+	auto load_tile = [&](uint32_t tile, TileIn& t) {
+		const uint32_t s = tile * 128 + row;
+		const bool valid = s < n_limit;
+		const uint32_t enc_row = (MODE == MODE_TRAIN && enc_rows && valid) ? min(__ldg(enc_rows + s), n_enc_rows - 1u) : s;   // reuse of the inference pass's encodings
+		const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)enc_row * 32);
+		#pragma unroll
+		for (int c = 0; c < 4; ++c) t.e[c] = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+		t.dx = t.dy = t.dz = 0.f;
+		if (MODE != MODE_DENSITY && valid) {
+			const float* cp = coords + (size_t)s * coord_stride + 4;
+			t.dx = cp[0]; t.dy = cp[1]; t.dz = cp[2];
+		}
+		t.dl = make_uint2(0u, 0u);
+		if (MODE == MODE_TRAIN && valid) t.dl = __ldg(reinterpret_cast<const uint2*>(dloss + (size_t)s * 4));
+	};
+	TileIn nxt;
+	if (blockIdx.x < n_tiles) load_tile(blockIdx.x, nxt);
 
 	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
 		const uint32_t s = tile * 128 + row;
 		const bool valid = s < n_limit;
+		const TileIn cur = nxt;
 
 		// ---- stage the encoded positions (64 B / sample) and the SH of the direction --------------
 		{
-			const uint32_t enc_row = (MODE == MODE_TRAIN && enc_rows && valid) ? min(__ldg(enc_rows + s), n_enc_rows - 1u) : s;   // reuse of the inference pass's encodings
-			const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)enc_row * 32);
 			#pragma unroll
-			for (int c = 0; c < 4; ++c) {
-				const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
-				*reinterpret_cast<uint4*>(smem + Smem::E + tile_off(row, c, 32)) = v;
-			}
+			for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(smem + Smem::E + tile_off(row, c, 32)) = cur.e[c];
 			if (MODE != MODE_DENSITY) {
 				float sh[16];
 				if (valid) {
-					const float* cp = coords + (size_t)s * coord_stride + 4;
-					sh4(cp[0], cp[1], cp[2], sh);
+					sh4(cur.dx, cur.dy, cur.dz, sh);
 				} else {
 					#pragma unroll
 					for (int i = 0; i < 16; ++i) sh[i] = 0.f;
@@ -178,6 +207,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 			}
 		}
 		pipe.publish();
+		if (tile + gridDim.x < n_tiles) load_tile(tile + gridDim.x, nxt);
 
 		float v[64];
 		// ---- density net layer 0: h = relu(W0 e) ---------------------------------------------------
@@ -236,7 +266,7 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 			#pragma unroll
 			for (int i = 0; i < 16; ++i) dc[i] = 0.f;
 			if (valid) {
-				const uint2 d = __ldg(reinterpret_cast<const uint2*>(dloss + (size_t)s * 4));
+				const uint2 d = cur.dl;
 				const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&d.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&d.y));
 				dc[0] = a.x; dc[1] = a.y; dc[2] = b.x; dsigma = b.y;
 			}
@@ -247,10 +277,11 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 		// dV2^T[64][16] += H2^T dc ; dh2 = dc V2
 		if (threadIdx.x == 0) {
 			fence_after_sync();
-			gemm(tm + kTmemV2, I_w16, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
 			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::G16, 16), mn_major(sbase + Smem::V2, 64), 1, 0);
+			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
+			gemm(tm + kTmemV2, I_w16, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
 		}
-		pipe.commit_and_wait();
+		pipe.wait();
 		read_row<4>(tm, kTmemWork, v);
 		relu_mask64(smem, kH2, row, v);
 		#pragma unroll
@@ -259,10 +290,11 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 		// dV1[64][64] += dh2^T H1 ; dh1 = dh2 V1
 		if (threadIdx.x == 0) {
 			fence_after_sync();
-			gemm(tm + kTmemV1, I_w64, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::H1, 64), 8, wg_acc);
 			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::V1, 64), 4, 0);
+			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
+			gemm(tm + kTmemV1, I_w64, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::H1, 64), 8, wg_acc);
 		}
-		pipe.commit_and_wait();
+		pipe.wait();
 		read_row<4>(tm, kTmemWork, v);
 		relu_mask64(smem, Smem::H1, row, v);
 		#pragma unroll
@@ -271,10 +303,11 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 		// dV0[64][32] += dh1^T x ; dx = dh1 V0
 		if (threadIdx.x == 0) {
 			fence_after_sync();
-			gemm(tm + kTmemV0, I_w32, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::X, 32), 8, wg_acc);
 			gemm(tm + kTmemWork, I_d32, k_major(sbase + kH2, 64), mn_major(sbase + Smem::V0, 32), 4, 0);
+			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
+			gemm(tm + kTmemV0, I_w32, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::X, 32), 8, wg_acc);
 		}
-		pipe.commit_and_wait();
+		pipe.wait();
 		read_row<1>(tm, kTmemWork, v);      // only dL/d(density_out[0..16)) is needed; the SH half has no parameters
 		v[0] = __half2float(__float2half_rn(v[0])) + dsigma;   // ngp_network.h:119-126
 		store_chunk(smem, Smem::G16, 16, row, 0, v, false);
@@ -283,10 +316,11 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 		// dW1^T[64][16] += H^T do ; dh = do W1
 		if (threadIdx.x == 0) {
 			fence_after_sync();
-			gemm(tm + kTmemW1, I_w16, mn_major(sbase + Smem::H, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
 			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::G16, 16), mn_major(sbase + Smem::W1, 64), 1, 0);
+			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
+			gemm(tm + kTmemW1, I_w16, mn_major(sbase + Smem::H, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
 		}
-		pipe.commit_and_wait();
+		pipe.wait();
 		read_row<4>(tm, kTmemWork, v);
 		relu_mask64(smem, Smem::H, row, v);
 		#pragma unroll
@@ -295,10 +329,12 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 		// dW0[64][32] += dh^T e ; de = dh W0
 		if (threadIdx.x == 0) {
 			fence_after_sync();
-			gemm(tm + kTmemW0, I_w32, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::E, 32), 8, wg_acc);
 			gemm(tm + kTmemWork, I_d32, k_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::W0, 32), 4, 0);
+			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
+			gemm(tm + kTmemW0, I_w32, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::E, 32), 8, wg_acc);
+			mma_commit(sbase + kEnd + 16);   // second barrier: every weight-gradient MMA of this tile has read its operands
 		}
-		pipe.commit_and_wait();
+		pipe.wait();
 		read_row<2>(tm, kTmemWork, v);
 		if (valid && denc) {
 			uint4* dst = reinterpret_cast<uint4*>(denc + (size_t)s * 32);
@@ -309,6 +345,10 @@ __global__ void __launch_bounds__(128) mlp_kernel(
 			}
 		}
 		wg_acc = 1;
+		// the next tile's staging overwrites E / X / H..., which the trailing weight-gradient MMAs may still be reading
+		__syncwarp();
+		mbar_wait(sbase + kEnd + 16, wg_parity);
+		wg_parity ^= 1;
 		fence_before_sync();
 		__syncthreads();
 	}
