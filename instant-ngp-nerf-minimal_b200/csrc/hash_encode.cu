@@ -40,7 +40,11 @@ __device__ __forceinline__ void pos_fract(float x, float scale, uint32_t& g, flo
 	w = p - f;
 }
 
-template <bool WRITE_INDICES, bool PAIRS = true>
+// WIDTH: 0 = one 4-byte gather per corner; 1 = x-adjacent corners share an aligned 8-byte load when the lower index is even;
+// 2 = they share an aligned 16-byte load whenever both fall into one group of four entries (3 cases out of 4).  The kernel is
+// bound by the tag stage of L1TEX -- one look-up per lane and instruction once every lane hits its own line -- so what counts
+// is the number of gather instructions per level (8 -> 6 -> 5), not the bytes they return.
+template <bool WRITE_INDICES, int WIDTH = 2>
 __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n, const uint32_t* __restrict__ n_valid,
 	const __half2* __restrict__ table, const __grid_constant__ ngp_grid_desc desc,
@@ -69,9 +73,24 @@ __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 		// gx ^ h and (gx+1) ^ h differ in bit 0 only when gx is even; dense: e and e+1).  One aligned 8-byte load then brings
 		// both, and only the other half of the lanes issue a second gather: a quarter fewer L1 wavefronts per level.
 		__half2 v[8];
-		if (!PAIRS) {
+		if (WIDTH == 0) {
 			#pragma unroll
 			for (int c = 0; c < 8; ++c) v[c] = __ldg(grid + e[c]);
+		} else if (WIDTH == 2) {
+			uint4 q[4];
+			#pragma unroll
+			for (int c = 0; c < 8; c += 2) q[c >> 1] = __ldg(reinterpret_cast<const uint4*>(grid) + (e[c] >> 2));
+			#pragma unroll
+			for (int c = 0; c < 8; c += 2) {
+				const uint4 t = q[c >> 1];
+				const uint32_t k0 = e[c] & 3u, k1 = e[c + 1] & 3u;
+				const uint32_t a = (k0 & 2u) ? ((k0 & 1u) ? t.w : t.z) : ((k0 & 1u) ? t.y : t.x);
+				v[c] = *reinterpret_cast<const __half2*>(&a);
+				if ((e[c + 1] >> 2) == (e[c] >> 2)) {
+					const uint32_t b = (k1 & 2u) ? ((k1 & 1u) ? t.w : t.z) : ((k1 & 1u) ? t.y : t.x);
+					v[c + 1] = *reinterpret_cast<const __half2*>(&b);
+				} else v[c + 1] = __ldg(grid + e[c + 1]);
+			}
 		} else {
 		uint2 pr[4];
 		#pragma unroll
@@ -222,6 +241,11 @@ __device__ __forceinline__ void red_h2x2(__half2* p, __half2 a, __half2 b) {
 	asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" :: "l"(p), "r"(*reinterpret_cast<const uint32_t*>(&a)), "r"(*reinterpret_cast<const uint32_t*>(&b)) : "memory");
 }
 
+// one 16-byte reduction onto four adjacent half2 entries (p 16-byte aligned); unused slots carry -0, the identity of the sum
+__device__ __forceinline__ void red_h2x4(__half2* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+	asm volatile("red.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
 // Backward, second generation.  Same mapping (thread = sample, warp = 32 consecutive samples of mostly one ray) and the same
 // arithmetic per term (weight product order, fp16 rounding of every term as in grid.h:303-306), but the merge of equal targets
 // is keyed by the CELL: neighbouring lanes inside one cell share all 8 corners, so the run structure is found once per level
@@ -229,6 +253,7 @@ __device__ __forceinline__ void red_h2x2(__half2* p, __half2 a, __half2 b) {
 // shuffle rounds as the longest run of the warp needs, and warps without any run (the fine levels) skip the merge altogether.
 // x-adjacent corner pairs whose entries are adjacent in memory leave as one 8-byte reduction.  The first-generation kernel
 // spent ~800 instructions per warp and level, most of them in eight corner-keyed run sums; it was issue-bound (72 %).
+template <bool QUADS>
 __global__ void __launch_bounds__(256) hash_encode_bwd_cell_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
 	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad,
@@ -285,7 +310,12 @@ __global__ void __launch_bounds__(256) hash_encode_bwd_cell_kernel(
 		if (valid && head) {
 			#pragma unroll
 			for (int c = 0; c < 8; c += 2) {
-				if (e[c + 1] == (e[c] ^ 1u)) {
+				if (QUADS && (e[c + 1] >> 2) == (e[c] >> 2) && e[c + 1] != e[c]) {
+					// both entries inside one aligned group of four: one 16-byte reduction (3 cases out of 4 instead of 2 out of 4)
+					const uint32_t k0 = e[c] & 3u, k1 = e[c + 1] & 3u, a = *reinterpret_cast<const uint32_t*>(&t[c]), b = *reinterpret_cast<const uint32_t*>(&t[c + 1]);
+					const uint32_t nz = 0x80008000u;
+					red_h2x4(grid + (e[c] & ~3u), k0 == 0 ? a : (k1 == 0 ? b : nz), k0 == 1 ? a : (k1 == 1 ? b : nz), k0 == 2 ? a : (k1 == 2 ? b : nz), k0 == 3 ? a : (k1 == 3 ? b : nz));
+				} else if (e[c + 1] == (e[c] ^ 1u)) {
 					if (e[c] & 1u) red_h2x2(grid + e[c + 1], t[c + 1], t[c]);
 					else red_h2x2(grid + e[c], t[c], t[c + 1]);
 				} else {
@@ -327,12 +357,12 @@ extern "C" uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, u
 extern "C" int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_table,
                                    const ngp_grid_desc* desc, void* d_out, uint32_t out_stride, uint32_t* d_indices) {
 	NGP_REQUIRE(d_xyz && d_table && desc && d_out, "null pointer");
-	NGP_REQUIRE(((uintptr_t)d_table & 7u) == 0, "d_table must be 8-byte aligned");
+	NGP_REQUIRE(((uintptr_t)d_table & 15u) == 0, "d_table must be 16-byte aligned");
 	NGP_REQUIRE(out_stride >= 2 * desc->n_levels && out_stride % 2 == 0, "out_stride too small or odd");
 	if (n == 0) return 0;
 	const uint32_t grid = div_up(n, 256);
-	if (d_indices) NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<true>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, d_indices));
-	else NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<false>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	if (d_indices) NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<true, 2>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, d_indices));
+	else NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<false, 2>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
 	return check_launch("hash_encode_fwd");
 }
 
@@ -340,11 +370,13 @@ namespace ngp {
 int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const uint32_t* d_n_valid,
                             const void* d_table, const ngp_grid_desc* desc, void* d_out, uint32_t out_stride) {
 	if (n == 0) return 0;
-	static const bool pairs = !(getenv("NGP_HASH_PAIRS") && getenv("NGP_HASH_PAIRS")[0] == '0');
+	static const int width = getenv("NGP_HASH_WIDTH") ? atoi(getenv("NGP_HASH_WIDTH")) : 2;
 	// (an explicit L2 prefetch of the 24 MB table before this launch was measured: no change, the kernel is L1TEX-bound, not
 	// bound by its first-touch DRAM misses)
-	if (pairs) NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
-	else NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, false>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	if (((uintptr_t)d_table & 15u) != 0) { set_error("hash_encode_fwd: d_table must be 16-byte aligned"); return -1; }
+	if (width == 2) NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, 2>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	else if (width == 1) NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, 1>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	else NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, 0>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
 	return check_launch("hash_encode_fwd");
 }
 }
@@ -357,7 +389,13 @@ extern "C" int ngp_hash_encode_bwd_levels(void* stream, const float* d_xyz, uint
 	if (n == 0 || level_begin == level_end) return 0;
 	static const bool corner_keyed = getenv("NGP_HASH_BWD") && getenv("NGP_HASH_BWD")[0] == '1';       // first-generation kernel, for A/B runs
 	if (corner_keyed) NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
-	else NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_cell_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
+	// 16-byte reductions (REDG.E.ADD.F16x8): 89 -> 78 us per step; NGP_HASH_BWD_QUADS=0 falls back to 8-byte pairs, also used when
+	// the caller's arena is only 8-byte aligned
+	static const bool quads_on = !(getenv("NGP_HASH_BWD_QUADS") && getenv("NGP_HASH_BWD_QUADS")[0] == '0');
+	const bool quads = quads_on && ((uintptr_t)d_grad & 15u) == 0;
+	if (corner_keyed) {}
+	else if (quads) NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_cell_kernel<true>, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
+	else NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_cell_kernel<false>, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
 	return check_launch("hash_encode_bwd");
 }
 

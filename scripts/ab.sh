@@ -2,7 +2,7 @@
 A="--steps 128 --warmup 96 --no-cpu-baseline --no-ref-cuda"
 for rep in 1 2; do
 python bench.py $A 2>/dev/null | grep '^{"metric' > gpurun_out/ab_new_$rep.json
-env $1=1 python bench.py $A 2>/dev/null | grep '^{"metric' > gpurun_out/ab_old_$rep.json
+env $1 python bench.py $A 2>/dev/null | grep '^{"metric' > gpurun_out/ab_old_$rep.json
 done
 for f in gpurun_out/ab_*.json; do python -c "
 import json,sys
