@@ -5,6 +5,7 @@
 // unchanged weight exactly like the reference).  HBM-bound: 42 B / parameter when touched, 6 B when skipped.
 #include "common.cuh"
 #include <vector>
+#include <stdlib.h>
 #include <cmath>
 
 namespace ngp {
@@ -86,20 +87,50 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 // state are only touched when one of the 8 gradients is non-zero (or the group belongs to the MLP matrices).
 // PEER: the range [begin, n) is this rank's shard; new fp16 weights are stored into every rank's arena (all-gather half of the
 // sharded step) and the last CTA to finish raises the "weights of this epoch have landed" flag at every rank.
-template <bool PEER, bool ZERO_GRADS = false>
-__global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t begin, uint64_t n, uint64_t n_matrix, AdamHyper h, float* __restrict__ w32, __half* __restrict__ w16,
+// PEER with WORLD > 0: the reduce-scatter is fused in -- the kernel first waits for every rank's "gradients complete" flag, then
+// each group of 8 gradients is summed straight out of all ranks' arenas (16-byte P2P loads over NVLink, fixed rank order, fp32,
+// rounded to fp16 exactly like the stand-alone peer_reduce_kernel it replaces) while the fp32 state streams from local HBM.
+template <bool PEER, bool ZERO_GRADS = false, int WORLD = 0>
+__global__ void __launch_bounds__(256, 3) adam_ema_kernel(uint64_t begin, uint64_t n, uint64_t n_matrix, AdamHyper h, float* __restrict__ w32, __half* __restrict__ w16,
                                                         const __half* g16, float* __restrict__ m1, float* __restrict__ m2,
                                                         uint32_t* __restrict__ steps, __half* __restrict__ ema16, ngp_peer_set ps, uint32_t epoch,
                                                         uint32_t* __restrict__ ticket) {
 	chain_enter();
+	if (PEER && WORLD > 0) {
+		if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + threadIdx.x) < epoch) __nanosleep(32); }
+		__syncthreads();
+	}
 	const uint64_t n8 = n / 8;
 	for (uint64_t q = begin / 8 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < n8; q += (uint64_t)gridDim.x * blockDim.x) {
 		const uint64_t i = q * 8;
 		// (streaming .cs loads/stores for the once-per-step state were measured: the kernel slows from 86 to 104 us and the next
 		// step's gathers gain 1 us -- plain policy kept)
-		const uint4 gp = ZERO_GRADS ? reinterpret_cast<const uint4*>(g16)[q] : __ldg(reinterpret_cast<const uint4*>(g16) + q);
-		// the consumer leaves the arena clean for the next backward pass (saves a 24 MB memset and a launch boundary per step)
-		if (ZERO_GRADS && ((gp.x | gp.y | gp.z | gp.w) != 0u)) reinterpret_cast<uint4*>(const_cast<__half*>(g16))[q] = make_uint4(0u, 0u, 0u, 0u);
+		uint4 gp;
+		if (PEER && WORLD > 0) {
+			// (requesting the NEXT group's peer gradients one iteration ahead was measured: 104-121 registers, one CTA fewer per SM,
+			// 88 -> 111 us; the three resident CTAs per SM already cover the NVLink round trip)
+			// at most four 16-byte peer loads in flight per thread (8 ranks: two rounds), summed in rank order
+			constexpr int kRound = WORLD > 4 ? 4 : (WORLD > 0 ? WORLD : 1);
+			float sum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+			#pragma unroll
+			for (int p0 = 0; p0 < WORLD; p0 += kRound) {
+				uint4 pg[kRound];
+				#pragma unroll
+				for (int p = 0; p < kRound; ++p) if (p0 + p < (int)ps.world) pg[p] = ld_peer16(reinterpret_cast<const uint4*>(ps.grads[p0 + p]) + q);
+				#pragma unroll
+				for (int p = 0; p < kRound; ++p) {
+					if (p0 + p < (int)ps.world) {
+						float t[8];
+						unpack8(pg[p], t);
+						#pragma unroll
+						for (int k = 0; k < 8; ++k) sum[k] += t[k];
+					}
+				}
+			}
+			gp = pack8(sum);
+		} else {
+			gp = ZERO_GRADS ? reinterpret_cast<const uint4*>(g16)[q] : __ldg(reinterpret_cast<const uint4*>(g16) + q);
+		}
 		const uint4 wp = reinterpret_cast<const uint4*>(w16)[q];
 		const uint4 ep = reinterpret_cast<const uint4*>(ema16)[q];
 		const bool any = i < n_matrix || ((gp.x | gp.y | gp.z | gp.w) & 0x7fff7fffu) != 0u;      // any gradient that is not +-0
@@ -168,8 +199,8 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(uint64_t begin, uint64_t 
 // ---- sharded step over peer memory ---------------------------------------------------------------------------------
 __global__ void peer_publish_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t epoch) {
 	chain_enter();
-	// stream order has completed this rank's backward pass; make it visible system-wide, then raise the flag at every rank
-	__threadfence_system();
+	// stream order has completed this rank's backward pass before this grid started; the release store (a system-scope fence
+	// followed by the store) publishes it cumulatively and raises the flag at every rank
 	if (threadIdx.x < ps.world) st_release_sys(ps.flags[threadIdx.x] + slot_base + ps.rank, epoch);
 }
 
@@ -293,14 +324,27 @@ extern "C" int ngp_optimizer_step_sharded(void* stream, const ngp_optimizer_cfg*
 	fill_hyper(h, cfg, step, learning_rate);
 	const uint64_t groups = (shard_end - shard_begin) / 8;
 	cudaStream_t st = (cudaStream_t)stream;
-	const uint32_t rgrid = grid_for(groups ? groups : 1, 512, 4);
-	if (peers->world <= 2) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<2>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
-	else if (peers->world <= 4) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<4>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
-	else NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<8>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
 	__half* w16 = (__half*)peers->params[peers->rank];
 	const __half* g16 = (const __half*)peers->grads[peers->rank];
-	NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true>, grid_for(groups ? groups : 1, 256, 6), 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
-		d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
+	static const bool fused = !(getenv("NGP_PEER_FUSED") && getenv("NGP_PEER_FUSED")[0] == '0');     // 0: separate reduce kernel, for A/B runs
+	const uint32_t agrid = grid_for(groups ? groups : 1, 256, 6);
+	if (!fused) {
+		const uint32_t rgrid = grid_for(groups ? groups : 1, 512, 4);
+		if (peers->world <= 2) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<2>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
+		else if (peers->world <= 4) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<4>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
+		else NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<8>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
+		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
+	} else if (peers->world <= 2) {
+		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, false, 2>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
+	} else if (peers->world <= 4) {
+		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, false, 4>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
+	} else {
+		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, false, 8>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
+	}
 	return check_launch("optimizer_step_sharded");
 }
 
