@@ -401,12 +401,16 @@ def run_ours(args):
 
     hbm_peak, tf_peak, peak_src = measured_peaks()
     total_kernel_ms = sum(v[0] for v in kt.values())
-    name, (k_ms, k_n) = max(kt.items(), key=lambda kv: kv[1][0])
+    # dominant kernel of the STEP: the march kernels run one step ahead on the look-ahead stream, underneath the others, so they
+    # are listed in kernels_ms_per_step (this profiling region runs them serially) but cannot be the kernel that bounds the step
+    on_path = {k: v for k, v in kt.items() if not k.startswith("march_")} or kt
+    name, (k_ms, k_n) = max(on_path.items(), key=lambda kv: kv[1][0])
     m, b, r = p_marched / prof_steps, p_samples / prof_steps, p_rays / prof_steps
     first = args.warmup + args.steps                                     # index of the first profiled step
     g = sum((1 << 22) if (first + k) < 256 else (1 << 21) for k in range(0, prof_steps, CALL_STEPS)) / prof_steps
     work = kernel_work(name, m, b, r, tb.n_params, g)
     launches_per_step = k_n / prof_steps
+    total_kernel_ms = sum(v[0] for v in on_path.values())
     roofline = {"kernel": name, "share_of_kernel_time": k_ms / total_kernel_ms, "avg_launch_us": k_ms / k_n * 1e3, "launches_per_step": launches_per_step}
     if work:
         bound, per_step = work

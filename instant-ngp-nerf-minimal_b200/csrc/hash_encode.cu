@@ -327,6 +327,25 @@ __global__ void __launch_bounds__(256) hash_encode_bwd_cell_kernel(
 	}
 }
 
+// zeroes the gradient table as a link of the step's launch chain (a cudaMemsetAsync in the middle of the chain costs two full
+// launch boundaries); also leaves the table in L2 for the reductions that follow
+__global__ void __launch_bounds__(256) zero_fill_kernel(uint4* __restrict__ p, uint64_t n16, uint8_t* __restrict__ tail, uint32_t n_tail) {
+	chain_enter();
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x) p[i] = make_uint4(0u, 0u, 0u, 0u);
+	if (blockIdx.x == 0 && threadIdx.x < n_tail) tail[threadIdx.x] = 0;
+}
+
+int zero_fill(cudaStream_t stream, void* d_ptr, size_t bytes) {
+	if (bytes == 0) return 0;
+	if (((uintptr_t)d_ptr & 15u) != 0) {
+		if (cudaMemsetAsync(d_ptr, 0, bytes, stream) != cudaSuccess) { set_error("zero_fill: memset failed"); return -2; }
+		return 0;
+	}
+	const uint64_t n16 = bytes / 16;
+	NGP_LAUNCH("zero_fill_kernel", stream, launch_chained(zero_fill_kernel, grid_for(n16 ? n16 : 1, 256, 8), 256, 0, stream, (uint4*)d_ptr, n16, (uint8_t*)d_ptr + n16 * 16, (uint32_t)(bytes & 15u)));
+	return check_launch("zero_fill");
+}
+
 } // namespace ngp
 
 using namespace ngp;
@@ -403,7 +422,8 @@ extern "C" int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t st
                                    const ngp_grid_desc* desc, void* d_grad, int zero_first) {
 	NGP_REQUIRE(d_xyz && d_dy && desc && d_grad, "null pointer");
 	if (zero_first) {
-		if (cudaMemsetAsync(d_grad, 0, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half), (cudaStream_t)stream) != cudaSuccess) { set_error("ngp_hash_encode_bwd: memset failed"); return -2; }
+		const int rc = zero_fill((cudaStream_t)stream, d_grad, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half));
+		if (rc) return rc;
 	}
 	return ngp_hash_encode_bwd_levels(stream, d_xyz, stride_floats, n, d_dy, dy_stride, desc, d_grad, 0, desc->n_levels);
 }
