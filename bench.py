@@ -371,6 +371,10 @@ def run_ours(args):
         if not disturbed or attempts >= 3:
             break
     clk["attempts"] = attempts
+    st_timed = None
+    if world > 1 and args.dp_mode == "peer":
+        st_timed = np.zeros((2, 4096), np.uint64)          # read now: the profiling region below leaves stamps of its own
+        capi.check(lib.ngp_peer_stamps_read(st_timed.ctypes.data_as(C.c_void_p)))
 
     # ---- per-kernel durations, live, with CUDA events on the launching stream (same workload, a further timed region) ----
     prof_steps = min(args.steps, 64)
@@ -381,6 +385,25 @@ def run_ours(args):
     kt = capi.kernel_timing_collect()
     capi.check(lib.ngp_kernel_timing_enable(0, 0))
 
+    peer_trace = None
+    if world > 1 and args.dp_mode == "peer":
+        # free-running trace of the timed region: per step, own work (previous "all shards landed" -> "my gradients published")
+        # and exchange (published -> all shards landed), from the two globaltimer stamps the peer kernels leave
+        st = st_timed
+        e_hi = int(np.argmax(st[1]))                       # newest epoch slot
+        idx = [(e_hi - k) % 4096 for k in range(min(args.steps, 2048))][::-1]
+        pub, land = st[0][idx].astype(np.int64), st[1][idx].astype(np.int64)
+        if os.environ.get("NGP_PEER_TRACE_DUMP"):
+            np.save(f"{os.environ['NGP_PEER_TRACE_DUMP']}.rank{rank}.npy", np.stack([pub, land]))
+        own = (pub[1:] - land[:-1]) * 1e-3
+        exch = (land - pub) * 1e-3
+        inner = np.array([k for k in range(len(own)) if own[k] < 5 * np.median(own)])     # drops the call boundaries (refresh + host)
+        peer_trace = {"own_us_median": float(np.median(own[inner])), "exchange_us_median": float(np.median(exch)), "exchange_us_p90": float(np.percentile(exch, 90)),
+                      "call_boundary_us_mean": float(np.mean(own[own >= 5 * np.median(own)])) if (own >= 5 * np.median(own)).any() else 0.0}
+        tt = torch.tensor([peer_trace["own_us_median"], peer_trace["exchange_us_median"], peer_trace["exchange_us_p90"], peer_trace["call_boundary_us_mean"]], dtype=torch.float64, device="cuda")
+        gathered = [torch.zeros_like(tt) for _ in range(world)]
+        dist.all_gather(gathered, tt)
+        peer_trace = {"per_rank_[own_us_median, exchange_us_median, exchange_us_p90, call_boundary_us_mean]": [[round(float(x), 1) for x in g] for g in gathered]}
     if args.timeline:
         capi.check(lib.ngp_kernel_timing_enable(1, 8192))
         train_steps(tb, 2 * CALL_STEPS, args.batch)
@@ -438,6 +461,8 @@ def run_ours(args):
                    "host_enqueue_ms_per_step": enqueue_ms / args.steps},
            "roofline": roofline,
            "samples_marched_per_step": marched / args.steps / max(world, 1), "rays_per_step": rays / args.steps / max(world, 1), "loss": tb.training_buffer.loss}
+    if peer_trace:
+        out["peer_trace"] = peer_trace
     if args.gpus == 1 and not args.no_ref_cuda:
         # the reference's own CUDA build on the same GPU, same scene, right after ours (reported, not part of any timed region)
         r = time_reference_cuda(args, capi, lib, xf_np, fx, rgba8, args.steps, args.warmup)

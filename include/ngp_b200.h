@@ -223,6 +223,9 @@ int ngp_optimizer_step_sharded(void* stream, const ngp_optimizer_cfg* cfg, uint6
                                const ngp_peer_set* peers, uint32_t epoch, uint32_t* d_ticket /* one zeroed uint32 of scratch */);
 /* before anything reads the parameters again: wait until every rank has stored its shard of `epoch` into this rank's arena */
 int ngp_peer_wait_weights(void* stream, const ngp_peer_set* peers, uint32_t epoch);
+/* free-running trace of the data-parallel step: host_out[0][e % 4096] = globaltimer ns at which this rank published the gradients
+   of epoch e, host_out[1][e % 4096] = when all weight shards of epoch e had landed.  Synchronises the device. */
+int ngp_peer_stamps_read(uint64_t* host_out /* [2][4096] */);
 
 /* from_rgba32<__half> (internal/utils/common_device.h:160-175) */
 int ngp_from_rgba32(void* stream, uint64_t n_pixels, const uint8_t* d_rgba8, void* d_out_half);

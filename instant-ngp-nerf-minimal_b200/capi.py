@@ -54,6 +54,7 @@ SIGNATURES = {
     "ngp_kernel_timing_enable": (i32, [i32, u32]),
     "ngp_kernel_timing_collect": (i32, [u32, vp, vp, vp]),
     "ngp_kernel_timing_timeline": (i32, [u32, vp, vp, vp]),
+    "ngp_peer_stamps_read": (i32, [vp]),
     "ngp_grid_desc_init": (u32, [C.POINTER(GridDesc), u32, u32, u32, f32]),
     "ngp_auto_per_level_scale": (f32, [f32, u32, u32]),
     "ngp_hash_encode_fwd": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, u32, vp]),

@@ -198,17 +198,25 @@ __global__ void __launch_bounds__(256, 3) adam_ema_kernel(uint64_t begin, uint64
 	}
 }
 
+// Free-running trace of the data-parallel step: the publish kernel stamps "my backward pass is complete", the wait kernel
+// stamps "all shards have landed" (globaltimer, ns, slot = epoch mod 4096).  Two stores per step; read with ngp_peer_stamps_read.
+__device__ unsigned long long g_peer_stamps[2][4096];
+__device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+
 // ---- sharded step over peer memory ---------------------------------------------------------------------------------
 __global__ void peer_publish_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t epoch) {
 	chain_enter();
 	// stream order has completed this rank's backward pass before this grid started; the release store (a system-scope fence
 	// followed by the store) publishes it cumulatively and raises the flag at every rank
+	if (threadIdx.x == 0) g_peer_stamps[0][epoch & 4095u] = global_ns();
 	if (threadIdx.x < ps.world) st_release_sys(ps.flags[threadIdx.x] + slot_base + ps.rank, epoch);
 }
 
 __global__ void peer_wait_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t epoch) {
 	chain_enter();
 	if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + slot_base + threadIdx.x) < epoch) __nanosleep(64); }
+	__syncwarp();
+	if (threadIdx.x == 0) g_peer_stamps[1][epoch & 4095u] = global_ns();
 }
 
 // Reduce-scatter half of the sharded step: waits for every rank's "gradients complete" flag, then sums this rank's shard out of
@@ -295,6 +303,14 @@ extern "C" int ngp_optimizer_step_range(void* stream, const ngp_optimizer_cfg* c
 	else NGP_LAUNCH("adam_ema_kernel", s, launch_chained(adam_ema_kernel<false, false>, grid, 256, 0, s, begin, end, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
 		d_m1, d_m2, d_param_steps, (__half*)d_ema16, ngp_peer_set{}, 0, nullptr));
 	return check_launch("optimizer_step_range");
+}
+
+extern "C" int ngp_peer_stamps_read(uint64_t* host_out /* [2][4096] */) {
+	NGP_REQUIRE(host_out, "null pointer");
+	if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpyFromSymbol(host_out, g_peer_stamps, sizeof(unsigned long long) * 2 * 4096) != cudaSuccess) {
+		set_error("ngp_peer_stamps_read: %s", cudaGetErrorString(cudaGetLastError())); return -2;
+	}
+	return 0;
 }
 
 static int check_peers(const ngp_peer_set* ps) {
