@@ -290,6 +290,9 @@ def train_steps(tb, n_steps, batch):
         marched += sum(b.n_coords_counter_cpu)
         rays += r * k
         dev_ms += b.training_ms + b.training_prep_ms
+        if os.environ.get("NGP_PRINT_CALLS"):           # per-call trace: marched samples, rays and device ms per step
+            print(f"call i_step={b.i_step} marched/step={sum(b.n_coords_counter_cpu) / k:.0f} rays={r} ms/step={(b.training_ms + b.training_prep_ms) / k:.4f} prep_ms={b.training_prep_ms:.3f}",
+                  file=sys.stderr, flush=True)
         ENQUEUE_MS += b.enqueue_ms
         done += k
     return samples, marched, rays, dev_ms
