@@ -155,6 +155,11 @@ int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg* cfg, cons
 /* generate_rays_from_camera_matrix (:813-855): init_rays_with_payload_kernel_nerf + advance_pos_nerf; payload = 40 B records */
 int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
                   int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads);
+/* the same for the rows [row_begin, row_end) of the image only (inference sharded over image tiles, one band per GPU, no
+ * collective): payload slot i holds pixel row_begin * width + i, and everything derived from the pixel uses that global index,
+ * so a band is bit-identical to the same rows of the full frame */
+int ngp_init_rays_rows(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                       int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end);
 /* generate_coords_from_rays (:857-877) */
 int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps,
                                   const uint8_t* d_bitfield, void* d_payloads, float* d_coords);

@@ -77,6 +77,7 @@ SIGNATURES = {
     "ngp_generate_training_samples": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), u32, u32, u32, u32, vp, vp, vp, i32, u64, u64,
                                             vp, vp, vp, vp, vp, vp, vp]),
     "ngp_init_rays": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), C.POINTER(f32), u32, i32, vp, vp]),
+    "ngp_init_rays_rows": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), C.POINTER(f32), u32, i32, vp, vp, u32, u32]),
     "ngp_generate_coords_from_rays": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, u32, vp, vp, vp]),
     "ngp_composite_workspace_bytes": (sz, [u32]),
     "ngp_composite_train": (i32, [vp, C.POINTER(RenderCfg), u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, u64, u64, vp, vp, vp]),

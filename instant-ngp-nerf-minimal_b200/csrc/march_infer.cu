@@ -56,10 +56,14 @@ __device__ __forceinline__ float octet_lattice(float t_base, uint32_t sub, uint3
 // this kernel was measured 6x slower (1.2 -> 7.1 ms at 1080p): the skip crosses about one voxel per 8-point window, so the
 // rounds do not shrink while the thread count grows 8x.
 __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
-                                                        uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads) {
-	const uint32_t n = (uint32_t)cam.width * (uint32_t)cam.height;
-	const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= n) return;
+                                                        uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads,
+                                                        uint32_t first_pixel, uint32_t n) {
+	// tile-sharded rendering: the launch covers the n pixels from first_pixel on (whole rows); every quantity that depends on the
+	// pixel -- the ray, the jitter seed, the scatter target -- uses the GLOBAL pixel index, so a band is bit-identical to the same
+	// rows of the full frame; only the slot in the payload array is band-relative
+	const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+	if (slot >= n) return;
+	const uint32_t idx = first_pixel + slot;
 	const uint32_t x = idx % cam.width, y = idx / cam.width;
 	V3 o, d;
 	make_ray(cam_matrix.m, ((float)x + offx) / (float)cam.width, ((float)y + offy) / (float)cam.height, cam, o, d);
@@ -68,7 +72,7 @@ __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_c
 	p.ox = o.x; p.oy = o.y; p.oz = o.z; p.dx = d.x; p.dy = d.y; p.dz = d.z; p.idx = idx; p.n_steps = 0; p.t = t; p.alive = 1;
 	if (!aabb_contains(c, ray_at(o, d, t))) {
 		p.alive = 0; p.dx = p.dy = p.dz = 0.f; p.t = 0.f; p.idx = 0;
-		payloads[idx] = p;
+		payloads[slot] = p;
 		return;
 	}
 	const V3 idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
@@ -83,7 +87,7 @@ __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_c
 		t = advance_to_next_voxel(t, c, pos, d, idir, c.grid_size >> mip);
 	}
 	p.t = t;
-	payloads[idx] = p;
+	payloads[slot] = p;
 }
 
 // 8 lanes per ray ("octet"): the ray's stepping lattice (see march_train.cu) is taken 8 points at a time, every lane evaluates
@@ -159,18 +163,26 @@ using namespace ngp;
 
 static float fractf_host(float x) { return x - floorf(x); }
 
-extern "C" int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
-                             int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads) {
+extern "C" int ngp_init_rays_rows(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                                  int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end) {
 	NGP_REQUIRE(cfg && cam && camera_matrix_host && d_bitfield && d_payloads, "null pointer");
+	NGP_REQUIRE(row_begin <= row_end && row_end <= (uint32_t)cam->height, "row range outside the image");
+	if (row_begin == row_end) return 0;
 	// ld_random_pixel_offset (random_val.cuh:273-278): identical for every pixel, so it is evaluated once on the host
 	const uint32_t s1 = snap_to_pixel_centers ? 0u : spp;
 	const float ax = ld_random_val(0, 0xdeadbeefu, 0), ay = ld_random_val(0, 0xdeadbeefu, 1);
 	const float bx = ld_random_val(s1, 0xdeadbeefu, 0), by = ld_random_val(s1, 0xdeadbeefu, 1);
 	const float offx = fractf_host(0.5f - ax + bx), offy = fractf_host(0.5f - ay + by);
-	const uint32_t n = (uint32_t)cam->width * (uint32_t)cam->height;
+	const uint32_t n = (uint32_t)cam->width * (row_end - row_begin), first = (uint32_t)cam->width * row_begin;
 	CamMat cm; memcpy(cm.m, camera_matrix_host, sizeof(cm.m));
-	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads));
+	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads, first, n));
 	return check_launch("init_rays");
+}
+
+extern "C" int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                             int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads) {
+	NGP_REQUIRE(cam, "null pointer");
+	return ngp_init_rays_rows(stream, cfg, cam, camera_matrix_host, spp, snap_to_pixel_centers, d_bitfield, d_payloads, 0, (uint32_t)cam->height);
 }
 
 extern "C" int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps,

@@ -93,10 +93,13 @@ void OccupancySampler::sample_coords_from_dataset(uint32_t n_rays, uint32_t n_ra
 }
 
 void OccupancySampler::generate_rays_from_camera_matrix(const int resolution[2], const float focal_length[2], const float principal_point[2],
-                                                        const Mat34& camera_matrix, uint32_t spp, DeviceBuffer<RayPayload>& payload, cudaStream_t stream) {
+                                                        const Mat34& camera_matrix, uint32_t spp, DeviceBuffer<RayPayload>& payload, cudaStream_t stream,
+                                                        int row_begin, int row_end) {
 	const ngp_sampler_cfg c = cfg();
 	ngp_camera_cfg cam{resolution[0], resolution[1], focal_length[0], focal_length[1], principal_point[0], principal_point[1]};
-	api_check(ngp_init_rays(stream, &c, &cam, camera_matrix.m, spp, snap_to_pixel_centers_in_rendering ? 1 : 0, density_grid_bitfield.data(), payload.data()));
+	if (row_end < 0) { row_begin = 0; row_end = resolution[1]; }
+	api_check(ngp_init_rays_rows(stream, &c, &cam, camera_matrix.m, spp, snap_to_pixel_centers_in_rendering ? 1 : 0, density_grid_bitfield.data(), payload.data(),
+	                             (uint32_t)row_begin, (uint32_t)row_end));
 }
 
 void OccupancySampler::generate_coords_from_rays(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, DeviceBuffer<RayPayload>& payloads,

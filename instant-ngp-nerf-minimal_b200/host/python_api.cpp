@@ -84,6 +84,9 @@ PYBIND11_MODULE(pyngp, m) {
 			{ py::gil_scoped_release rel; t.render_to_host(width, height, spp, to_srgb, ptr); }
 			return image;
 		}, "Renders an image at the requested resolution.", py::arg("width") = 1920, py::arg("height") = 1080, py::arg("spp") = 1, py::arg("to_srgb") = true)
+		.def("set_render_rows", &Testbed::set_render_rows,
+		     "Tile-sharded inference: render() marches only the rays of rows [row_begin, row_end) (the other rows of the returned image hold the background); "
+		     "row_end = -1 restores the whole image.  Bands are bit-identical to the same rows of the full frame.", py::arg("row_begin"), py::arg("row_end"))
 		.def_readwrite("loss_type", &Testbed::m_loss_type)
 		.def_readwrite("density_activation", &Testbed::m_density_activation)
 		.def_readwrite("rgb_activation", &Testbed::m_rgb_activation)

@@ -9,27 +9,34 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 	RenderingBuffer& rb = m_rendering_buffer;
 	const int* resolution = render_buffer.resolution();
 	const float focal_length[2] = {(float)resolution[rb.fov_axis] * rb.relative_focal_length[0], (float)resolution[rb.fov_axis] * rb.relative_focal_length[1]};
-	const uint32_t n_pixels = (uint32_t)(resolution[0] * resolution[1]);
+	// tile-sharded inference (BASELINE configs[3]): this rank marches the rays of rows [row_begin, row_end) only; the frame buffer
+	// keeps the full size and the band's pixels land at their own positions, so the caller assembles bands without any exchange
+	const int row_begin = m_render_row_end < 0 ? 0 : std::max(0, std::min(m_render_row_begin, resolution[1]));
+	const int row_end = m_render_row_end < 0 ? resolution[1] : std::max(row_begin, std::min(m_render_row_end, resolution[1]));
+	const uint32_t n_pixels = (uint32_t)(resolution[0] * (row_end - row_begin));
+	const uint32_t n_frame_pixels = (uint32_t)(resolution[0] * resolution[1]);
 	const ERenderMode render_mode = rb.render_mode;
 	if (render_mode == ERenderMode::Normals) throw std::runtime_error("RenderMode::Normals (network input gradients) is not implemented in this build");
 	const uint32_t padded_output_width = m_network->padded_output_width();
 
 	{
-		const uint32_t n_elements = next_multiple(n_pixels, BATCH_SIZE_MULTIPLE);
+		const uint32_t n_elements = next_multiple(std::max(n_pixels, 1u), BATCH_SIZE_MULTIPLE);
 		rb.rays[0].enlarge(n_elements); rb.rays[1].enlarge(n_elements); rb.rays_hit.enlarge(n_elements);
 		rb.coords.enlarge((size_t)n_elements * rb.MAX_STEPS_INBETWEEN_COMPACTION);
 		rb.rgbsigma.enlarge((size_t)n_elements * rb.MAX_STEPS_INBETWEEN_COMPACTION * padded_output_width);
 	}
 
 	render_buffer.clear_frame_buffer(m_stream);
-	m_sampler->generate_rays_from_camera_matrix(resolution, focal_length, rb.principal_point, camera_matrix, render_buffer.spp(), rb.rays[0].payload, m_stream);
-	NGP_CUDA_CHECK(cudaMemsetAsync(rb.rays[0].rgba.data(), 0, (size_t)n_pixels * 4 * sizeof(float), m_stream));
+	(void)n_frame_pixels;
+	m_sampler->generate_rays_from_camera_matrix(resolution, focal_length, rb.principal_point, camera_matrix, render_buffer.spp(), rb.rays[0].payload, m_stream,
+	                                            row_begin, row_end);
+	NGP_CUDA_CHECK(cudaMemsetAsync(rb.rays[0].rgba.data(), 0, (size_t)std::max(n_pixels, 1u) * 4 * sizeof(float), m_stream));
 	NGP_CUDA_CHECK(cudaMemsetAsync(rb.n_hit_counter.data(), 0, sizeof(uint32_t), m_stream));
 
 	uint32_t i_steps_offset = 1;
 	uint32_t double_buffer_index = 0;
 	uint32_t n_alive = n_pixels;
-	while (i_steps_offset < MARCH_ITER) {
+	while (n_alive > 0 && i_steps_offset < MARCH_ITER) {
 		RaysSoA& rays_previous = rb.rays[double_buffer_index % 2];
 		RaysSoA& rays_current = rb.rays[(double_buffer_index + 1) % 2];
 		++double_buffer_index;
