@@ -464,6 +464,29 @@ def run_ours(args):
                    "host_enqueue_ms_per_step": enqueue_ms / args.steps},
            "roofline": roofline,
            "samples_marched_per_step": marched / args.steps / max(world, 1), "rays_per_step": rays / args.steps / max(world, 1), "loss": tb.training_buffer.loss}
+    # ---- the encoder kernels against MEASURED ceilings of the L1TEX / L2 path (the table is L2-resident: SURVEY.md 8d) ----
+    try:
+        scratch = torch.zeros(32 << 20, dtype=torch.uint8, device="cuda")
+        sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        probe = {}
+        for kind, key in ((0, "l2_stream_read_GBs"), (1, "scattered_gather_4B_G_per_s"), (2, "scattered_gather_16B_G_per_s"),
+                          (3, "scattered_red_f16x2_G_per_s"), (4, "scattered_red_v4_f16x2_G_per_s")):
+            val = C.c_double(0.0)
+            capi.check(lib.ngp_l2_probe(sp, kind, C.c_void_p(scratch.data_ptr()), scratch.numel(), 5, C.byref(val)))
+            probe[key] = val.value
+        del scratch
+        k = roofline["kernels_ms_per_step"]
+        # accesses the kernels issue per point and level: 4 x-pairs, 3 of 4 served by one 16-byte access, the 4th by two 4-byte ones
+        per_point = 16 * 5
+        fwd = (m + g) * per_point / (k["hash_encode_fwd_kernel"] * 1e-3) / 1e9 if k.get("hash_encode_fwd_kernel") else None
+        bwd = b * per_point / (k["hash_encode_bwd_kernel"] * 1e-3) / 1e9 if k.get("hash_encode_bwd_kernel") else None
+        out["l2_roofline"] = {"probes": probe, "table": "32 MB scratch, L2-resident; every lane of a warp hits its own line (worst case of the fine levels)",
+                              "accesses_per_point": per_point,
+                              "hash_encode_fwd": {"achieved_G_accesses_per_s": fwd, "frac_of_scattered_gather_16B": fwd / probe["scattered_gather_16B_G_per_s"] if fwd else None},
+                              "hash_encode_bwd": {"achieved_G_accesses_per_s": bwd, "frac_of_scattered_red_v4": bwd / probe["scattered_red_v4_f16x2_G_per_s"] if bwd else None,
+                                                  "note": "before the in-warp merge of lanes that share a cell; the coarse levels issue fewer reductions than counted"}}
+    except Exception as e:                      # evidence, not part of the contract line
+        out["l2_roofline"] = {"unavailable": str(e)}
     if peer_trace:
         out["peer_trace"] = peer_trace
     if args.gpus == 1 and not args.no_ref_cuda:

@@ -73,6 +73,12 @@ int ngp_kernel_timing_collect(uint32_t max_kernels, char* names /* [max_kernels]
 /* per-launch start / end (ms since the first recorded launch), in launch order; synchronises and resets like _collect */
 int ngp_kernel_timing_timeline(uint32_t max_launches, char* names /* [max_launches][64] */, float* start_ms, float* end_ms);
 
+/* Measured ceilings of the L1TEX / L2 path for the hash-grid kernels' access patterns ("L2 peak ... must be measured
+ * on the box"): kind 0 = coalesced 16-byte reads of an L2-resident buffer (result in GB/s); 1 / 2 = scattered 4- / 16-byte gathers,
+ * 3 / 4 = scattered 4- / 16-byte fp16 reductions, every lane its own line (result in 1e9 accesses / s).  d_table: table_bytes of
+ * scratch (power of two; 32 MB stays L2-resident), zero-filled by the call.  Times `repeats` launches with CUDA events; synchronises. */
+int ngp_l2_probe(void* stream, int kind, void* d_table, uint64_t table_bytes, uint32_t repeats, double* result);
+
 /* ---- hash grid -------------------------------------------------------------------------------- */
 /* replaces GridEncodingTemplated ctor (grid.h:475-537); returns the number of table entries */
 uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, uint32_t log2_hashmap_size, uint32_t base_resolution, float per_level_scale);

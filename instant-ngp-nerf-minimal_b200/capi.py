@@ -55,6 +55,7 @@ SIGNATURES = {
     "ngp_kernel_timing_collect": (i32, [u32, vp, vp, vp]),
     "ngp_kernel_timing_timeline": (i32, [u32, vp, vp, vp]),
     "ngp_peer_stamps_read": (i32, [vp]),
+    "ngp_l2_probe": (i32, [vp, i32, vp, u64, u32, vp]),
     "ngp_grid_desc_init": (u32, [C.POINTER(GridDesc), u32, u32, u32, f32]),
     "ngp_auto_per_level_scale": (f32, [f32, u32, u32]),
     "ngp_hash_encode_fwd": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, u32, vp]),
