@@ -13,19 +13,24 @@ from util import rng_uniform, half_ulp_diff
 pytestmark = pytest.mark.gpu
 
 
-def _inputs(orc, n, stride, seed, table_amp):
-    L = orc.GridLevels(16, 19, 16)
+def _inputs(orc, n, stride, seed, table_amp, log2_T=19):
+    L = orc.GridLevels(16, log2_T, 16)
     xyz = rng_uniform((n, stride), seed)
     table = rng_uniform(L.n_params, seed + 1, -table_amp, table_amp).astype(np.float16)
     return L, xyz, table
 
 
-@pytest.mark.parametrize("n,stride,amp", [(1 << 16, 3, 1.0), (1 << 16, 7, 1e-4), (1000, 3, 1.0), (1, 7, 1.0), (257, 3, 1.0)])
-def test_hash_encode_fwd_matches_oracle(capi, orc, n, stride, amp):
+# (1 << 18, 3, ..., 19) is BASELINE configs[0] at full size (2^18 points, L=16 F=2 T=2^19); log2_T = 22 is the table of configs[4]
+# (levels 0-7 dense, 8-15 hashed, 39 474 024 entries = 150.6 MB fp16: spills L2)
+@pytest.mark.parametrize("n,stride,amp,log2_T", [(1 << 16, 3, 1.0, 19), (1 << 16, 7, 1e-4, 19), (1000, 3, 1.0, 19), (1, 7, 1.0, 19), (257, 3, 1.0, 19),
+                                                 (1 << 18, 3, 1.0, 19), (1 << 18, 3, 1e-4, 19), (1 << 16, 3, 1.0, 22), (1 << 15, 7, 1.0, 14)])
+def test_hash_encode_fwd_matches_oracle(capi, orc, n, stride, amp, log2_T):
     import gpuutil as G
     lib = capi.load()
-    L, xyz, table = _inputs(orc, n, stride, 1337, amp)
-    d, n_entries = capi.make_grid_desc()
+    L, xyz, table = _inputs(orc, n, stride, 1337, amp, log2_T)
+    d, n_entries = capi.make_grid_desc(log2_hashmap_size=log2_T)
+    if log2_T == 22:
+        assert n_entries == 39474024
     assert n_entries == L.n_entries
     ref, ref_idx = orc.hash_encode_fwd(xyz, stride, n, table.view(np.uint16), L, want_indices=True)
     dx, dt = G.dev(xyz), G.dev(table.view(np.uint16))
@@ -71,15 +76,16 @@ def test_hash_encode_empty_is_a_noop(capi):
     capi.check(lib.ngp_hash_encode_fwd(G.stream(), G.p(x), 3, 0, G.p(x), C.byref(d), G.p(x), 32, None))
 
 
-@pytest.mark.parametrize("n,stride", [(1 << 16, 3), (4099, 7)])
-def test_hash_encode_bwd_matches_oracle(capi, orc, n, stride):
+# (1 << 18, 3, 19): configs[0] at full size; (1 << 16, 3, 22): the L2-spilling table of configs[4]
+@pytest.mark.parametrize("n,stride,log2_T", [(1 << 16, 3, 19), (4099, 7, 19), (1 << 18, 3, 19), (1 << 16, 3, 22)])
+def test_hash_encode_bwd_matches_oracle(capi, orc, n, stride, log2_T):
     import gpuutil as G
     import torch
     lib = capi.load()
-    L, xyz, _ = _inputs(orc, n, stride, 99, 1.0)
+    L, xyz, _ = _inputs(orc, n, stride, 99, 1.0, log2_T)
     dy = (rng_uniform((n, 32), 7, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
     ref = orc.hash_encode_bwd(xyz, stride, n, dy, L)                      # fp32 sums of fp16-rounded terms
-    d, _ = capi.make_grid_desc()
+    d, _ = capi.make_grid_desc(log2_hashmap_size=log2_T)
     grad = torch.full((L.n_params,), 0x3C00, dtype=torch.int16, device="cuda")   # garbage: zero_first must clear it
     capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(G.dev(xyz)), stride, n, G.p(G.dev(dy.view(np.uint16))), 32, C.byref(d), G.p(grad), 1))
     G.sync()
@@ -98,6 +104,41 @@ def test_hash_encode_bwd_matches_oracle(capi, orc, n, stride):
     for l in range(16):
         s = got[L.offsets[l] * 2: L.offsets[l + 1] * 2].reshape(-1, 2).sum(0)
         assert np.allclose(s, per_slot[l], rtol=5e-2, atol=5e-2), (l, s, per_slot[l])
+
+
+@pytest.mark.parametrize("n,step", [(5003, 1.6915e-3), (4096, 2e-2), (777, 1e-5)])
+def test_hash_encode_bwd_on_ray_ordered_samples(capi, orc, n, step):
+    """Consecutive samples of a ray share grid cells on the coarse levels: this is the input the in-warp merge of the backward kernel
+    is built for (runs of every length, runs that cross warp boundaries, a ragged last warp).  The merged sums are fp32, so the
+    result must sit at least as close to the oracle's fp32 sums as independent fp16 atomics would."""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    L = orc.GridLevels(16, 19, 16)
+    g = np.random.Generator(np.random.PCG64(31))
+    per_ray = 37
+    n_rays = (n + per_ray - 1) // per_ray
+    o = g.random((n_rays, 3), dtype=np.float32) * 0.5 + 0.2
+    dvec = g.normal(size=(n_rays, 3)).astype(np.float32)
+    dvec /= np.linalg.norm(dvec, axis=1, keepdims=True)
+    k = np.arange(per_ray, dtype=np.float32)[None, :, None]
+    xyz = np.clip((o[:, None, :] + dvec[:, None, :] * k * np.float32(step)).reshape(-1, 3)[:n], 0, 1).astype(np.float32)
+    dy = (rng_uniform((n, 32), 7, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
+    ref = orc.hash_encode_bwd(xyz, 3, n, dy, L)
+    d, _ = capi.make_grid_desc()
+    grad = G.zeros(L.n_params, torch.int16)
+    capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(G.dev(xyz)), 3, n, G.p(G.dev(dy.view(np.uint16))), 32, C.byref(d), G.p(grad), 1))
+    G.sync()
+    got = G.host(grad, np.float16).astype(np.float32)
+    assert np.count_nonzero((got == 0) != (ref == 0)) <= 1e-4 * np.count_nonzero(ref)
+    scale = np.abs(ref).max()
+    assert np.abs(got - ref).max() <= 2e-2 * scale, np.abs(got - ref).max() / scale
+    nz = ref != 0
+    assert np.median(np.abs(got[nz] - ref[nz]) / np.abs(ref[nz])) < 1e-3
+    per_slot = dy.astype(np.float32).reshape(n, 16, 2).sum(0)
+    for l in range(16):
+        ssum = got[L.offsets[l] * 2: L.offsets[l + 1] * 2].reshape(-1, 2).sum(0)
+        assert np.allclose(ssum, per_slot[l], rtol=2e-2, atol=2e-2), (l, ssum, per_slot[l])
 
 
 def test_hash_encode_bwd_accumulates_when_not_zeroed(capi, orc):
