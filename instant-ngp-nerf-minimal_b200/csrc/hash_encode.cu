@@ -27,8 +27,11 @@ __device__ __forceinline__ uint32_t grid_index(uint32_t size, uint32_t res, bool
 }
 
 __device__ __forceinline__ bool level_is_hashed(uint32_t size, uint32_t res) {
-	// after the dense loop stride == res^3 unless it stopped early; "size < stride" decides (grid.h:95)
-	uint64_t s = 1;
+	// grid.h:88-95: the stride is a uint32_t and is multiplied once more after the last dimension; "size < stride" then decides.
+	// The wrap-around is part of the contract: with T = 2^22 the finest level has res^2 == size, the third product is 2^33 = 0
+	// (mod 2^32), and the reference indexes that level DENSELY as (gx + gy * res + gz * res^2) mod size -- found by the T = 2^22
+	// parity test, a 64-bit stride here called the level hashed.
+	uint32_t s = 1;
 	for (int d = 0; d < 3 && s <= size; ++d) s *= res;
 	return size < s;
 }
@@ -228,7 +231,7 @@ __device__ __forceinline__ void cell_entries(uint32_t size, uint32_t res, bool h
 		#pragma unroll
 		for (int c = 0; c < 8; ++c) {
 			uint32_t idx = base + (c & 1) + ((c & 2) ? sy : 0u) + ((c & 4) ? sz : 0u);
-			if (idx >= size) { idx -= size; if (idx >= size) idx %= size; }
+			if (idx >= size) { idx -= size; if (idx >= size) idx = (size & (size - 1)) == 0 ? (idx & (size - 1)) : (idx % size); }
 			e[c] = idx;
 		}
 	}

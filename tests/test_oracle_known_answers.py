@@ -52,6 +52,11 @@ def test_hash_index_known_answers(orc):
     # dense level: x + y*res + z*res^2, wrapped by the padded size
     assert lib.orc_grid_index(4096, 16, 3, 2, 1) == 3 + 2 * 16 + 1 * 256
     assert lib.orc_grid_index(4096, 16, 16, 15, 15) == (16 + 15 * 16 + 15 * 256) % 4096
+    # grid.h:88-95 with a uint32_t stride: at T = 2^22 the finest level has res^2 == size, the next product is 2^33 == 0 (mod 2^32),
+    # "size < stride" is false and the level is indexed densely -- the z term vanishes modulo the size
+    T22 = 1 << 22
+    assert lib.orc_grid_index(T22, 2048, 7, 9, 1234) == (7 + 9 * 2048) % T22
+    assert lib.orc_grid_index(T22, 1483, 7, 9, 12) == (7 ^ (9 * 19349663) % (1 << 32) ^ (12 * 83492791) % (1 << 32)) % T22
 
 
 def test_hash_encode_constant_table_is_partition_of_unity(orc):
