@@ -482,8 +482,13 @@ def run_ours(args):
         bwd = b * per_point / (k["hash_encode_bwd_kernel"] * 1e-3) / 1e9 if k.get("hash_encode_bwd_kernel") else None
         out["l2_roofline"] = {"probes": probe, "table": "32 MB scratch, L2-resident; every lane of a warp hits its own line (worst case of the fine levels)",
                               "accesses_per_point": per_point,
-                              "hash_encode_fwd": {"achieved_G_accesses_per_s": fwd, "frac_of_scattered_gather_16B": fwd / probe["scattered_gather_16B_G_per_s"] if fwd else None},
+                              "reading": "a frac above 1 means the kernel beats the all-lanes-scattered ceiling because neighbouring samples of a ray share lines on the coarse levels; "
+                                         "sector_GBs = accesses x one 32-byte L2 sector each, against the coalesced L2 read rate",
+                              "sector_bytes": 32,
+                              "hash_encode_fwd": {"achieved_G_accesses_per_s": fwd, "frac_of_scattered_gather_16B": fwd / probe["scattered_gather_16B_G_per_s"] if fwd else None,
+                                                  "sector_GBs": fwd * 32 if fwd else None, "frac_of_l2_stream_read": fwd * 32 / probe["l2_stream_read_GBs"] if fwd else None},
                               "hash_encode_bwd": {"achieved_G_accesses_per_s": bwd, "frac_of_scattered_red_v4": bwd / probe["scattered_red_v4_f16x2_G_per_s"] if bwd else None,
+                                                  "sector_GBs": bwd * 32 if bwd else None, "frac_of_l2_stream_read": bwd * 32 / probe["l2_stream_read_GBs"] if bwd else None,
                                                   "note": "before the in-warp merge of lanes that share a cell; the coarse levels issue fewer reductions than counted"}}
     except Exception as e:                      # evidence, not part of the contract line
         out["l2_roofline"] = {"unavailable": str(e)}
