@@ -84,6 +84,13 @@ PYBIND11_MODULE(pyngp, m) {
 			{ py::gil_scoped_release rel; t.render_to_host(width, height, spp, to_srgb, ptr); }
 			return image;
 		}, "Renders an image at the requested resolution.", py::arg("width") = 1920, py::arg("height") = 1080, py::arg("spp") = 1, py::arg("to_srgb") = true)
+		.def("render_band", [](Testbed& t, int width, int height, int spp, bool to_srgb) {
+			const int r0 = t.render_row_begin(height), r1 = t.render_row_end(height);
+			py::array_t<float> image({r1 - r0, width, 4});
+			float* ptr = (float*)image.request().ptr;
+			{ py::gil_scoped_release rel; t.render_band_to_host(width, height, spp, to_srgb, ptr); }
+			return image;
+		}, "Renders the rows set by set_render_rows and returns them alone, [rows][width][4].", py::arg("width") = 1920, py::arg("height") = 1080, py::arg("spp") = 1, py::arg("to_srgb") = true)
 		.def("set_render_rows", &Testbed::set_render_rows,
 		     "Tile-sharded inference: render() marches only the rays of rows [row_begin, row_end) (the other rows of the returned image hold the background); "
 		     "row_end = -1 restores the whole image.  Bands are bit-identical to the same rows of the full frame.", py::arg("row_begin"), py::arg("row_end"))

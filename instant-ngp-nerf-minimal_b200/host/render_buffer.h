@@ -13,28 +13,38 @@ public:
 		m_res[0] = w; m_res[1] = h;
 		const size_t n = (size_t)w * h * 4;
 		m_frame.resize(n); m_accumulate.resize(n); m_surface.resize(n);
+		m_row0 = 0; m_row1 = h;
 		reset_accumulation();
 	}
 	const int* resolution() const { return m_res; }
 	void reset_accumulation() { m_spp = 0; }
 	uint32_t spp() const { return m_spp; }
-	void clear_frame_buffer(cudaStream_t s) { m_frame.memset(0, s); }
+	// tile-sharded rendering: clear / accumulate / tonemap touch the rows [r0, r1) only (r1 < 0: the whole frame)
+	void set_rows(int r0, int r1) { m_row0 = r1 < 0 ? 0 : r0; m_row1 = r1 < 0 ? m_res[1] : r1; }
+	size_t first_pixel() const { return (size_t)m_row0 * m_res[0]; }
+	uint32_t n_band_pixels() const { return (uint32_t)((m_row1 - m_row0) * m_res[0]); }
+	void clear_frame_buffer(cudaStream_t s) {
+		if (n_band_pixels()) NGP_CUDA_CHECK(cudaMemsetAsync(m_frame.data() + first_pixel() * 4, 0, (size_t)n_band_pixels() * 4 * sizeof(float), s));
+	}
 	float* frame_buffer() const { return m_frame.data(); }
 	float* surface() const { return m_surface.data(); }
 	void set_color_space(EColorSpace c) { m_color_space = c; }
 	void set_tonemap_curve(ETonemapCurve c) { m_curve = c; }
 	void accumulate(cudaStream_t s) {
-		const uint32_t n = (uint32_t)(m_res[0] * m_res[1]);
-		if (m_spp == 0) m_accumulate.memset(0, s);
-		api_check(ngp_accumulate(s, n, m_frame.data(), m_accumulate.data(), (float)m_spp, (int)m_color_space));
+		const uint32_t n = n_band_pixels();
+		const size_t o = first_pixel() * 4;
+		if (n && m_spp == 0) NGP_CUDA_CHECK(cudaMemsetAsync(m_accumulate.data() + o, 0, (size_t)n * 4 * sizeof(float), s));
+		if (n) api_check(ngp_accumulate(s, n, m_frame.data() + o, m_accumulate.data() + o, (float)m_spp, (int)m_color_space));
 		++m_spp;
 	}
 	void tonemap(float exposure, const float background_color[4], EColorSpace output_color_space, cudaStream_t s) {
-		const uint32_t n = (uint32_t)(m_res[0] * m_res[1]);
-		api_check(ngp_tonemap(s, n, exposure, background_color, m_accumulate.data(), (int)m_color_space, (int)output_color_space, (int)m_curve, m_surface.data()));
+		const uint32_t n = n_band_pixels();
+		const size_t o = first_pixel() * 4;
+		if (n) api_check(ngp_tonemap(s, n, exposure, background_color, m_accumulate.data() + o, (int)m_color_space, (int)output_color_space, (int)m_curve, m_surface.data() + o));
 	}
 private:
 	int m_res[2] = {0, 0};
+	int m_row0 = 0, m_row1 = 0;
 	uint32_t m_spp = 0;
 	EColorSpace m_color_space = EColorSpace::Linear;
 	ETonemapCurve m_curve = ETonemapCurve::Identity;

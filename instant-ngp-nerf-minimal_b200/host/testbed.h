@@ -2,6 +2,7 @@
 // save/load_snapshot, train(n_steps, batch), render_frame / render, fov helpers, training_buffer / rendering_buffer views),
 // driving the sampler / network / render modules whose kernels live behind the C ABI.
 #pragma once
+#include <algorithm>
 #include <chrono>
 #include <memory>
 #include "common.h"
@@ -45,6 +46,9 @@ public:
 	void render_to_host(int width, int height, int spp, bool to_srgb, float* out);
 	// tile-sharded inference: this rank renders rows [row_begin, row_end) only (no collective)
 	void set_render_rows(int row_begin, int row_end) { m_render_row_begin = row_begin; m_render_row_end = row_end; }
+	int render_row_begin(int height) const { return m_render_row_end < 0 ? 0 : std::max(0, std::min(m_render_row_begin, height)); }
+	int render_row_end(int height) const { return m_render_row_end < 0 ? height : std::max(render_row_begin(height), std::min(m_render_row_end, height)); }
+	void render_band_to_host(int width, int height, int spp, bool to_srgb, float* out_band);
 
 	float fov() const { return focal_length_to_fov(1, m_rendering_buffer.relative_focal_length[m_rendering_buffer.fov_axis]); }
 	void set_fov(float val) { m_rendering_buffer.relative_focal_length[0] = m_rendering_buffer.relative_focal_length[1] = fov_to_focal_length(1, val); }

@@ -26,6 +26,7 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 		rb.rgbsigma.enlarge((size_t)n_elements * rb.MAX_STEPS_INBETWEEN_COMPACTION * padded_output_width);
 	}
 
+	render_buffer.set_rows(row_begin, row_end);
 	render_buffer.clear_frame_buffer(m_stream);
 	(void)n_frame_pixels;
 	m_sampler->generate_rays_from_camera_matrix(resolution, focal_length, rb.principal_point, camera_matrix, render_buffer.spp(), rb.rays[0].payload, m_stream,
@@ -77,7 +78,25 @@ void Testbed::render_to_host(int width, int height, int spp, bool to_srgb, float
 	rb.render_buffer.resize(width, height);
 	rb.render_buffer.reset_accumulation();
 	for (int i = 0; i < spp; ++i) render_frame(rb.camera_matrix, rb.render_buffer, to_srgb);
-	NGP_CUDA_CHECK(cudaMemcpy(out, rb.render_buffer.surface(), (size_t)width * height * 4 * sizeof(float), cudaMemcpyDeviceToHost));
+	if (m_render_row_end < 0) {
+		NGP_CUDA_CHECK(cudaMemcpy(out, rb.render_buffer.surface(), (size_t)width * height * 4 * sizeof(float), cudaMemcpyDeviceToHost));
+		return;
+	}
+	// a band: only its rows were rendered and only they are copied; the rest of the caller's image reads zero
+	const size_t first = rb.render_buffer.first_pixel() * 4, n = (size_t)rb.render_buffer.n_band_pixels() * 4, total = (size_t)width * height * 4;
+	std::fill(out, out + first, 0.f);
+	std::fill(out + first + n, out + total, 0.f);
+	if (n) NGP_CUDA_CHECK(cudaMemcpy(out + first, rb.render_buffer.surface() + first, n * sizeof(float), cudaMemcpyDeviceToHost));
+}
+
+// the band alone, [row_end - row_begin][width][4]: what a rank of a tile-sharded render hands on (no full-frame traffic at all)
+void Testbed::render_band_to_host(int width, int height, int spp, bool to_srgb, float* out_band) {
+	RenderingBuffer& rb = m_rendering_buffer;
+	rb.render_buffer.resize(width, height);
+	rb.render_buffer.reset_accumulation();
+	for (int i = 0; i < spp; ++i) render_frame(rb.camera_matrix, rb.render_buffer, to_srgb);
+	const size_t first = rb.render_buffer.first_pixel() * 4, n = (size_t)rb.render_buffer.n_band_pixels() * 4;
+	if (n) NGP_CUDA_CHECK(cudaMemcpy(out_band, rb.render_buffer.surface() + first, n * sizeof(float), cudaMemcpyDeviceToHost));
 }
 
 void Testbed::set_camera_to_training_view(uint32_t i) {

@@ -104,6 +104,9 @@ def test_render_row_bands_are_bit_identical_to_the_full_frame(pyngp):
             tb.set_render_rows(r0, r1)
             band = np.array(tb.render(w, h, 1, True))
             stitched[r0:r1] = band[r0:r1]
+            assert not band[:r0].any() and not band[r1:].any(), "rows outside the band read zero"
+            alone = np.array(tb.render_band(w, h, 1, True))
+            assert alone.shape == (r1 - r0, w, 4) and np.array_equal(alone.view(np.uint32), band[r0:r1].view(np.uint32))
         tb.set_render_rows(0, -1)
         assert np.array_equal(stitched.view(np.uint32), full.view(np.uint32)), f"{n_bands} bands differ from the full frame"
     tb.set_render_rows(7, 7)                             # empty band: nothing marched, nothing crashes
