@@ -70,6 +70,11 @@ __device__ __forceinline__ float unwarp_dt(float dt, float min_step, uint32_t n_
 	return dt * (max_stepsize - min_step) + min_step;
 }
 
+__device__ __forceinline__ void unpack_rgbsigma(const uint2 v, float* raw) {
+	const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+	raw[0] = a.x; raw[1] = a.y; raw[2] = b.x; raw[3] = b.y;
+}
+
 __device__ __forceinline__ void load_rgbsigma(const __half* p, float* raw) {
 	const uint2 v = *reinterpret_cast<const uint2*>(p);
 	const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&v.y));

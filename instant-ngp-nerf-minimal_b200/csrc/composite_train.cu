@@ -43,13 +43,19 @@ __global__ void __launch_bounds__(256) composite_count_kernel(
 	const __half* no = net_out + (size_t)base * 4;
 	float T = 1.f, acc[3] = {0.f, 0.f, 0.f};
 	uint32_t n_used = numst;
+	// The kernel lasts as long as its longest ray (every warp is resident at once), i.e. chunks x the latency of one chunk: the
+	// loads of chunk c + 1 are requested before chunk c is scanned, so a chunk costs its shuffles, not a trip to L2 / HBM.
+	uint2 nx_raw = make_uint2(0u, 0u); float nx_dt = 0.f;
+	if (lane < numst) { nx_raw = *reinterpret_cast<const uint2*>(no + (size_t)lane * 4); nx_dt = cs[lane].dt; }
 	for (uint32_t c0 = 0; c0 < numst; c0 += 32) {
 		const uint32_t k = c0 + lane;
 		const bool valid = k < numst;
+		const uint2 cur_raw = nx_raw; const float cur_dt = nx_dt;
+		if (k + 32 < numst) { nx_raw = *reinterpret_cast<const uint2*>(no + (size_t)(k + 32) * 4); nx_dt = cs[k + 32].dt; }
 		float raw[4] = {0.f, 0.f, 0.f, 0.f}, alpha = 0.f;
 		if (valid) {
-			load_rgbsigma(no + (size_t)k * 4, raw);
-			const float dt = unwarp_dt(cs[k].dt, c.min_step, c.n_cascades);
+			unpack_rgbsigma(cur_raw, raw);
+			const float dt = unwarp_dt(cur_dt, c.min_step, c.n_cascades);
 			alpha = 1.f - __expf(-net_to_density(raw[3], c.density_activation) * dt);
 		}
 		const float incl = warp_scan_mul(1.f - alpha, lane);
@@ -159,13 +165,17 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 	const Coordinate* cs = coords_in + base;
 	const __half* no = net_out + (size_t)base * 4;
 	float T = 1.f, pre[3] = {0.f, 0.f, 0.f};          // carried: transmittance and colour in front of the chunk
+	uint2 nx_raw = make_uint2(0u, 0u); float nx_dt = 0.f;        // next chunk's loads, requested one chunk ahead (see composite_count_kernel)
+	if (lane < n) { nx_raw = *reinterpret_cast<const uint2*>(no + (size_t)lane * 4); nx_dt = cs[lane].dt; }
 	for (uint32_t c0 = 0; c0 < n; c0 += 32) {
 		const uint32_t k = c0 + lane;
 		const bool valid = k < n;
+		const uint2 cur_raw = nx_raw; const float cur_dt = nx_dt;
+		if (k + 32 < n) { nx_raw = *reinterpret_cast<const uint2*>(no + (size_t)(k + 32) * 4); nx_dt = cs[k + 32].dt; }
 		float raw[4] = {0.f, 0.f, 0.f, 0.f}, alpha = 0.f, dt = 0.f;
 		if (valid) {
-			load_rgbsigma(no + (size_t)k * 4, raw);
-			dt = unwarp_dt(cs[k].dt, c.min_step, c.n_cascades);
+			unpack_rgbsigma(cur_raw, raw);
+			dt = unwarp_dt(cur_dt, c.min_step, c.n_cascades);
 			alpha = 1.f - __expf(-net_to_density(raw[3], c.density_activation) * dt);
 		}
 		const float incl = warp_scan_mul(1.f - alpha, lane);
