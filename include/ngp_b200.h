@@ -108,6 +108,11 @@ int ngp_network_inference(void* stream, const float* d_coords, uint32_t n, const
 /* replaces NGPNetwork::density (ngp_network.h:286-307): positions (stride floats) -> [n][16] fp16 */
 int ngp_network_density(void* stream, const float* d_positions, uint32_t stride_floats, uint32_t n, const void* d_params,
                         const ngp_grid_desc* desc, void* d_out, void* d_workspace, size_t workspace_bytes);
+/* NGPNetwork::input_gradient(stream, 3, coords, coords) (tiny-cuda-nn/object.h:126-150; testbed.cu:558-560, RenderMode::Normals):
+ * d sigma_raw / d input written OVER the 7-float Coordinates: position <- gradient, warped dt <- dt / 128 (the reference rescales
+ * the row its backward pass never wrote), direction <- 0.  d_workspace as for ngp_network_train. */
+int ngp_network_input_gradient(void* stream, float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_params,
+                               const ngp_grid_desc* desc, void* d_workspace, size_t workspace_bytes);
 /* replaces NGPNetwork::forward + ::backward (ngp_network.h:325-494) on the compacted batch: writes rgbsigma [n][4]
  * (optional) and the fp16 gradient arena d_grads [NGP_MLP_PARAMS | grid] (overwritten, not accumulated). */
 int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,

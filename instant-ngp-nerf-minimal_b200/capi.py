@@ -64,6 +64,7 @@ SIGNATURES = {
     "ngp_network_workspace_bytes": (sz, [u32]),
     "ngp_network_inference": (i32, [vp, vp, u32, vp, vp, C.POINTER(GridDesc), vp, vp, sz]),
     "ngp_network_density": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, vp, sz]),
+    "ngp_network_input_gradient": (i32, [vp, vp, u32, vp, vp, C.POINTER(GridDesc), vp, sz]),
     "ngp_network_train": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, sz]),
     "ngp_network_train_reuse": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, u32, vp, vp, sz]),
     "ngp_network_train_reuse_phased": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, u32, vp, vp, sz, u32, vp, i32]),

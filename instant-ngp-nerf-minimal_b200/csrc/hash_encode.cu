@@ -330,6 +330,64 @@ __global__ void __launch_bounds__(256) hash_encode_bwd_cell_kernel(
 	}
 }
 
+// dL/dx of the encoding (grid.h:217-255 dy_dx + kernel_grid_backward_input :400-422, fused: dy_dx is never stored).  Per level and
+// input dimension the derivative of the trilinear blend is scale * sum over the 4 corner pairs along that dimension of
+// (product of the other two weights) * (right - left); dL/dx_j = sum_k dL/dy_k * dy_k/dx_j in feature order k = 2 * level + f.
+// The result overwrites the sample's Coordinate: position <- gradient * inv_scale, dt <- dt * inv_scale, direction <- 0.
+__global__ void __launch_bounds__(256) hash_input_grad_kernel(float* __restrict__ coords, uint32_t n, const uint32_t* __restrict__ n_valid,
+                                                              const __half2* __restrict__ table, const __grid_constant__ ngp_grid_desc desc,
+                                                              const __half* __restrict__ denc, float inv_scale) {
+	chain_enter();
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= (n_valid ? min(*n_valid, n) : n)) return;
+	float* co = coords + (size_t)i * 7;
+	const float pos[3] = {co[0], co[1], co[2]};
+	const __half2* drow = reinterpret_cast<const __half2*>(denc + (size_t)i * 32);
+	float g[3] = {0.f, 0.f, 0.f};
+	for (uint32_t l = 0; l < desc.n_levels; ++l) {
+		const uint32_t off = desc.offsets[l], size = desc.offsets[l + 1] - off, res = desc.resolutions[l];
+		const float scale = desc.scales[l];
+		const bool hashed = level_is_hashed(size, res);
+		uint32_t gi[3]; float w[3];
+		pos_fract(pos[0], scale, gi[0], w[0]); pos_fract(pos[1], scale, gi[1], w[1]); pos_fract(pos[2], scale, gi[2], w[2]);
+		uint32_t e[8];
+		cell_entries(size, res, hashed, gi[0], gi[1], gi[2], e);
+		float2 v[8];
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) v[c] = __half22float2(__ldg(table + off + e[c]));
+		const float2 d = __half22float2(drow[l]);
+		#pragma unroll
+		for (int gd = 0; gd < 3; ++gd) {
+			float gx = 0.f, gy = 0.f;
+			#pragma unroll
+			for (int idx = 0; idx < 4; ++idx) {
+				float weight = scale;
+				int corner = 0;
+				#pragma unroll
+				for (int ngd = 0; ngd < 2; ++ngd) {
+					const int dim = ngd >= gd ? ngd + 1 : ngd;
+					if ((idx & (1 << ngd)) == 0) weight *= 1 - w[dim];
+					else { weight *= w[dim]; corner |= 1 << dim; }
+				}
+				const float2 left = v[corner], right = v[corner | (1 << gd)];
+				gx += weight * (right.x - left.x);
+				gy += weight * (right.y - left.y);
+			}
+			g[gd] += d.x * gx;
+			g[gd] += d.y * gy;
+		}
+	}
+	co[0] = g[0] * inv_scale; co[1] = g[1] * inv_scale; co[2] = g[2] * inv_scale;
+	co[3] = co[3] * inv_scale;
+	co[4] = 0.f; co[5] = 0.f; co[6] = 0.f;
+}
+
+int hash_input_gradient(cudaStream_t stream, float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_table, const ngp_grid_desc* desc, const void* d_denc, float inv_scale) {
+	if (n == 0) return 0;
+	NGP_LAUNCH("hash_input_grad_kernel", stream, launch_chained(hash_input_grad_kernel, div_up(n, 256), 256, 0, stream, d_coords, n, d_n_valid, (const __half2*)d_table, *desc, (const __half*)d_denc, inv_scale));
+	return check_launch("hash_input_gradient");
+}
+
 // zeroes the gradient table as a link of the step's launch chain (a cudaMemsetAsync in the middle of the chain costs two full
 // launch boundaries); also leaves the table in L2 for the reductions that follow
 __global__ void __launch_bounds__(256) zero_fill_kernel(uint4* __restrict__ p, uint64_t n16, uint8_t* __restrict__ tail, uint32_t n_tail) {

@@ -180,7 +180,9 @@ __global__ void __launch_bounds__(128, MODE == MODE_TRAIN ? 2 : 3) mlp_kernel(
 			t.dx = cp[0]; t.dy = cp[1]; t.dz = cp[2];
 		}
 		t.dl = make_uint2(0u, 0u);
-		if (MODE == MODE_TRAIN && valid) t.dl = __ldg(reinterpret_cast<const uint2*>(dloss + (size_t)s * 4));
+		// dloss == nullptr: "input gradient" mode (tiny-cuda-nn/object.h:126-150) -- the loss gradient is one-hot on sigma_raw with the
+		// reference's backprop scale 128 (fp16 0x5800), zero on r, g, b
+		if (MODE == MODE_TRAIN && valid) t.dl = dloss ? __ldg(reinterpret_cast<const uint2*>(dloss + (size_t)s * 4)) : make_uint2(0u, 0x58000000u);
 	};
 	TileIn nxt;
 	if (blockIdx.x < n_tiles) load_tile(blockIdx.x, nxt);
@@ -433,6 +435,33 @@ static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords,
 	return check_launch("mlp_kernel");
 }
 } // namespace ngp
+
+namespace ngp {
+int hash_input_gradient(cudaStream_t stream, float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_table, const ngp_grid_desc* desc, const void* d_denc, float inv_scale);
+}
+
+// NGPNetwork::input_gradient(stream, 3, coords, coords) (tiny-cuda-nn/object.h:126-150 through ngp_network.h:325-494): d sigma_raw /
+// d input, written OVER the coordinates like the reference does (testbed.cu:558-560 passes the same matrix as input and output):
+// position <- gradient, warped dt <- dt / 128 (the reference rescales the whole matrix, including the row its backward pass never
+// wrote), direction <- 0.  Uses the weights it is given (the reference uses the inference / EMA weights).
+extern "C" int ngp_network_input_gradient(void* stream, float* d_coords, uint32_t n, const uint32_t* d_n_valid, const void* d_params,
+                                          const ngp_grid_desc* desc, void* d_workspace, size_t workspace_bytes) {
+	NGP_REQUIRE(d_coords && d_params && desc && d_workspace, "null pointer");
+	NGP_REQUIRE(desc->n_levels == 16, "the fused network expects 16 levels x 2 features = 32 encoded dims");
+	NGP_REQUIRE(workspace_bytes >= ngp_network_workspace_bytes(n), "workspace too small");
+	if (n == 0) return 0;
+	cudaStream_t s = (cudaStream_t)stream;
+	const __half* params = (const __half*)d_params;
+	const size_t n_pad = ((size_t)n + 127) / 128 * 128;
+	__half* enc = (__half*)d_workspace;
+	__half* denc = enc + n_pad * 32;
+	float* wgrad_slots = (float*)(denc + n_pad * 32);       // the weight gradients of this pass are not wanted; the slots absorb them
+	int rc = hash_encode_fwd_counted(s, d_coords, 7, n, d_n_valid, params + NGP_MLP_PARAMS, desc, enc, 32);
+	if (rc) return rc;
+	rc = launch_mlp<MODE_TRAIN>(s, enc, d_coords, 7, n, d_n_valid, params, nullptr, nullptr, denc, nullptr, wgrad_slots);
+	if (rc) return rc;
+	return hash_input_gradient(s, d_coords, n, d_n_valid, params + NGP_MLP_PARAMS, desc, denc, 1.0f / 128.0f);
+}
 
 extern "C" int ngp_mlp_inference(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, void* d_rgbsigma) {
 	NGP_REQUIRE(d_enc && d_coords && d_mlp_params && d_rgbsigma, "null pointer");

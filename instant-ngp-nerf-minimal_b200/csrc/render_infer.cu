@@ -36,6 +36,14 @@ __global__ void __launch_bounds__(128) composite_infer_kernel(
 			else if (render_mode == 4) { const float dx = px - p.ox, dy = py - p.oy, dz = pz - p.oz; const float z = sqrtf(dx * dx + dy * dy + dz * dz) * depth_scale; r = g = b = z; }
 			else if (render_mode == 5) { r = g = b = co.dt; }
 			else if (render_mode == 0) { r = g = b = alpha; }
+			else if (render_mode == 2) {
+				// ray_marcher.cu:260-266: the Coordinate holds d sigma_raw / d position (ngp_network_input_gradient ran on it); chain rule
+				// through the density activation, the normal points towards decreasing density
+				const float k = -net_to_density_d(raw[3], c.density_activation);
+				const float nx = k * co.px, ny = k * co.py, nz = k * co.pz;
+				const float inv = 1.0f / sqrtf(nx * nx + ny * ny + nz * nz);
+				r = nx * inv; g = ny * inv; b = nz * inv;
+			}
 		}
 		l.x += r * w; l.y += g * w; l.z += b * w; l.w += w;
 		if (l.w > (1.0f - c.transmittance_threshold)) break;
@@ -80,6 +88,10 @@ __global__ void shade_kernel(uint32_t n_hit_max, const uint32_t* __restrict__ n_
 	if (i >= n_hit) return;
 	float4 t = rgba[i];
 	const RayPayload p = payloads[i];
+	if (render_mode == 2) {          // testbed.cu:463-465: accumulated normal -> unit length -> [0, 1], premultiplied
+		const float inv = 1.0f / sqrtf(t.x * t.x + t.y * t.y + t.z * t.z);
+		t.x = (0.5f * (t.x * inv) + 0.5f) * t.w; t.y = (0.5f * (t.y * inv) + 0.5f) * t.w; t.z = (0.5f * (t.z * inv) + 0.5f) * t.w;
+	}
 	if (render_mode == 6) { const float col = (float)p.n_steps / 128; t = make_float4(col, col, col, 1.0f); }
 	if (!train_in_linear && render_mode == 1) { t.x = srgb_to_linear(t.x); t.y = srgb_to_linear(t.y); t.z = srgb_to_linear(t.z); }
 	const float4 f = frame[p.idx];

@@ -16,7 +16,6 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 	const uint32_t n_pixels = (uint32_t)(resolution[0] * (row_end - row_begin));
 	const uint32_t n_frame_pixels = (uint32_t)(resolution[0] * resolution[1]);
 	const ERenderMode render_mode = rb.render_mode;
-	if (render_mode == ERenderMode::Normals) throw std::runtime_error("RenderMode::Normals (network input gradients) is not implemented in this build");
 	const uint32_t padded_output_width = m_network->padded_output_width();
 
 	{
@@ -54,6 +53,7 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 		m_sampler->generate_coords_from_rays(n_alive, nullptr, n_steps, rays_current.payload, rb.coords, m_stream);
 		// rendering uses the EMA weights (use_inference_matrices = true, testbed.cu:556)
 		m_network->inference_mixed_precision(m_stream, rb.coords.data(), n_alive * n_steps, nullptr, rb.rgbsigma.data(), true);
+		if (render_mode == ERenderMode::Normals) m_network->input_gradient(m_stream, 3, rb.coords.data(), n_alive * n_steps);   // testbed.cu:558-560
 		m_render->volume_rendering(n_alive, nullptr, n_steps, i_steps_offset, rays_current, rb.coords, rb.rgbsigma, padded_output_width, m_density_activation,
 		                           m_rgb_activation, render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix,
 		                           1.f / m_scene_scale, m_stream);

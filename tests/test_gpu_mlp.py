@@ -177,3 +177,61 @@ def test_network_train_reuse_equals_network_train(capi, orc):
     assert np.allclose(a[10240:], b[10240:], rtol=2e-2, atol=2e-3 * np.abs(a[10240:]).max())
     # aliasing the two workspaces is refused
     assert lib.ngp_network_train_reuse(G.stream(), G.p(dsub), n, G.p(dp), C.byref(d), G.p(ddl), G.p(ob), G.p(gb), G.p(ws_b), m, G.p(didx), G.p(ws_b), ws_bytes) != 0
+
+
+def test_network_input_gradient_matches_analytic_float64(capi, orc):
+    """ngp_network_input_gradient (RenderMode::Normals): d sigma_raw / d position against a float64 restatement of
+    grid.h:217-255 (dy/dx of the trilinear blend) chained through the density MLP; dt <- dt / 128 and direction <- 0 like the
+    reference, which rescales the whole Coordinate matrix (object.h:149)."""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    n = 3000
+    L = orc.GridLevels(16, 19, 16)
+    g = np.random.Generator(np.random.PCG64(11))
+    w = ((g.random(capi.NGP_MLP_PARAMS, dtype=np.float32) - 0.5) * 0.6).astype(np.float16)
+    table = ((g.random(L.n_params, dtype=np.float32) - 0.5) * 2).astype(np.float16)
+    coords = g.random((n, 7), dtype=np.float32)
+    params = np.concatenate([w, table])
+    desc, _ = capi.make_grid_desc()
+    d_coords, d_params = G.dev(coords.copy()), G.dev(params.view(np.uint16))
+    ws_bytes = lib.ngp_network_workspace_bytes(n)
+    ws = torch.zeros(ws_bytes, dtype=torch.uint8, device="cuda")
+    capi.check(lib.ngp_network_input_gradient(G.stream(), G.p(d_coords), n, None, G.p(d_params), C.byref(desc), G.p(ws), ws_bytes))
+    G.sync()
+    got = G.host(d_coords).reshape(n, 7)
+    assert np.array_equal(got[:, 3], coords[:, 3] * np.float32(1 / 128)), "dt is rescaled with the rest of the matrix"
+    assert not got[:, 4:].any(), "the direction rows receive a zero gradient"
+
+    # ---- float64 restatement ----
+    _, idx = orc.hash_encode_fwd(coords, 7, n, table.view(np.uint16), L, want_indices=True)       # [n][16][8], corner bit 0 = x
+    tab = table.astype(np.float64).reshape(-1, 2)
+    enc = np.zeros((n, 32)); denc_dpos = np.zeros((n, 32, 3))
+    for l in range(16):
+        scale = np.float32(L.scales[l])
+        p = (coords[:, :3] * scale + np.float32(0.5)).astype(np.float32)
+        wgt = (p - np.floor(p)).astype(np.float64)                                                # [n][3]
+        v = tab[int(L.offsets[l]) + idx[:, l, :].astype(np.int64)]                                # [n][8][2]
+        for c in range(8):
+            wc = np.ones(n)
+            for d in range(3):
+                wc = wc * (wgt[:, d] if (c >> d) & 1 else 1 - wgt[:, d])
+            enc[:, 2 * l:2 * l + 2] += wc[:, None] * v[:, c]
+        for gd in range(3):
+            others = [d for d in range(3) if d != gd]
+            for c in range(8):
+                if (c >> gd) & 1:
+                    continue
+                wc = np.full(n, float(scale))
+                for d in others:
+                    wc = wc * (wgt[:, d] if (c >> d) & 1 else 1 - wgt[:, d])
+                denc_dpos[:, 2 * l:2 * l + 2, gd] += wc[:, None] * (v[:, c | (1 << gd)] - v[:, c])
+    W0 = w[:2048].astype(np.float64).reshape(64, 32); W1 = w[2048:3072].astype(np.float64).reshape(16, 64)
+    pre = enc @ W0.T
+    dsig_denc = ((pre > 0) * W1[0][None, :]) @ W0                                                 # [n][32]
+    ref = np.einsum("nk,nkd->nd", dsig_denc, denc_dpos)
+    err = np.abs(got[:, :3] - ref)
+    tol = 5e-2 * np.abs(ref) + 2e-2 * np.abs(ref).mean()
+    assert (err <= tol).mean() > 0.98, (err <= tol).mean()
+    cos = (got[:, :3] * ref).sum(1) / (np.linalg.norm(got[:, :3], axis=1) * np.linalg.norm(ref, axis=1) + 1e-30)
+    assert np.median(cos) > 0.999

@@ -138,10 +138,17 @@ def test_render_modes_and_tonemap_curves(pyngp):
     rb.render_mode = pyngp.RenderMode.Depth
     depth = np.array(tb.render(w, h, 1, False))
     assert np.isfinite(depth).all() and depth[..., 0].max() > 0
-    rb.render_mode = pyngp.RenderMode.Normals
-    with pytest.raises(RuntimeError):
-        tb.render(w, h, 1, False)
+    rb.render_mode = pyngp.RenderMode.Normals              # network input gradients (testbed.cu:558-560, ray_marcher.cu:260-266)
+    tb.background_color = [0, 0, 0, 0]                     # transparent: alpha is the object's own coverage
+    nrm = np.array(tb.render(w, h, 1, False))
+    tb.background_color = [0, 0, 0, 1]
     rb.render_mode = pyngp.RenderMode.Shade
+    assert np.isfinite(nrm).all()
+    hit = nrm[..., 3] > 0.9
+    assert hit.sum() > 200, "the object must be visible"
+    n = nrm[hit][:, :3] / nrm[hit][:, 3:4] * 2 - 1           # shade: (0.5 n + 0.5) * alpha
+    assert np.all(np.abs(np.linalg.norm(n, axis=1) - 1) < 2e-3), "shaded normals are unit vectors"
+    assert not np.array_equal(nrm[..., :3], shade[..., :3])
 
 
 def _load_and_render(pyngp, path):
