@@ -36,6 +36,7 @@ typedef struct ngp_sampler_cfg {
 	float    cone_angle;             /* cone_angle_constant */
 	float    min_step, max_step;     /* sqrt3/max_steps, sqrt3*2^(C-1)/grid_size */
 	float    near_distance;          /* 0.2 */
+	uint32_t keep_empty_rays;        /* train_envmap (occupancy_sampler.cu:408): training rays without a single sample stay in the ray list */
 } ngp_sampler_cfg;
 
 /* Pinhole camera set (internal/dataset/nerf_synthetic.h; xforms 3x4 column-major, 12 floats each). */
@@ -56,6 +57,13 @@ typedef struct ngp_render_cfg {
 	float    min_optical_thickness;
 	float    loss_scale;                           /* 128 */
 	float    background_color[3];
+	/* trainable environment map (internal/utils/envmap.h, ray_marcher.cu:96-102,190-212); all zero / NULL = none.
+	 * envmap: fp16 [res_y][res_x][4]; the reference fills the resolution as {height, width} and indexes x + y * res_x */
+	const void* envmap;              /* read behind the volume: background = envmap.rgb + background * (1 - envmap.a) */
+	void*       envmap_gradient;     /* fp16, same shape: dL/d(envmap.rgb) deposited bilinearly for fully traversed rays */
+	const float* rays;               /* device, 6 floats per kept ray {o, d}: the directions the envmap is looked up with */
+	int32_t  envmap_res_x, envmap_res_y;
+	int32_t  envmap_loss_type;       /* ELossType of the envmap's own loss (base.json: RelativeL2) */
 } ngp_render_cfg;
 
 /* Optimizer chain Ema(ExponentialDecay(Adam)) (tiny-cuda-nn/optimizers/{adam,ema,exponential_decay}.h). */
@@ -171,6 +179,10 @@ int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg
  * so a band is bit-identical to the same rows of the full frame */
 int ngp_init_rays_rows(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
                        int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end);
+/* with a trained environment map (occupancy_sampler.cu:459-502): additionally frame_buffer[pixel] <- read_envmap(ray direction) */
+int ngp_init_rays_rows_envmap(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                              int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end,
+                              const void* d_envmap, int32_t env_res_x, int32_t env_res_y, float* d_frame_buffer);
 /* generate_coords_from_rays (:857-877) */
 int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps,
                                   const uint8_t* d_bitfield, void* d_payloads, float* d_coords);

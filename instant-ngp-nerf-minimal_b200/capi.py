@@ -22,7 +22,7 @@ class GridDesc(C.Structure):
 
 class SamplerCfg(C.Structure):
     _fields_ = [("aabb_min", f32), ("aabb_max", f32), ("grid_size", u32), ("n_cascades", u32), ("max_steps", u32),
-                ("cone_angle", f32), ("min_step", f32), ("max_step", f32), ("near_distance", f32)]
+                ("cone_angle", f32), ("min_step", f32), ("max_step", f32), ("near_distance", f32), ("keep_empty_rays", u32)]
 
 
 class CameraCfg(C.Structure):
@@ -32,7 +32,8 @@ class CameraCfg(C.Structure):
 class RenderCfg(C.Structure):
     _fields_ = [("n_cascades", u32), ("min_step", f32), ("rgb_activation", i32), ("density_activation", i32), ("loss_type", i32),
                 ("color_space", i32), ("train_with_random_bg_color", i32), ("train_in_linear_color", i32),
-                ("transmittance_threshold", f32), ("min_optical_thickness", f32), ("loss_scale", f32), ("background_color", f32 * 3)]
+                ("transmittance_threshold", f32), ("min_optical_thickness", f32), ("loss_scale", f32), ("background_color", f32 * 3),
+                ("envmap", vp), ("envmap_gradient", vp), ("rays", vp), ("envmap_res_x", i32), ("envmap_res_y", i32), ("envmap_loss_type", i32)]
 
 
 NGP_MAX_PEERS = 8
@@ -80,6 +81,7 @@ SIGNATURES = {
                                             vp, vp, vp, vp, vp, vp, vp]),
     "ngp_init_rays": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), C.POINTER(f32), u32, i32, vp, vp]),
     "ngp_init_rays_rows": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), C.POINTER(f32), u32, i32, vp, vp, u32, u32]),
+    "ngp_init_rays_rows_envmap": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), C.POINTER(f32), u32, i32, vp, vp, u32, u32, vp, i32, i32, vp]),
     "ngp_generate_coords_from_rays": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, u32, vp, vp, vp]),
     "ngp_composite_workspace_bytes": (sz, [u32]),
     "ngp_composite_train": (i32, [vp, C.POINTER(RenderCfg), u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, u64, u64, vp, vp, vp]),

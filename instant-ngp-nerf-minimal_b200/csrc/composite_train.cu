@@ -129,6 +129,15 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 	if (c.train_with_random_bg_color) { bg[0] = rng.next_float(); bg[1] = rng.next_float(); bg[2] = rng.next_float(); }
 	#pragma unroll
 	for (int k = 0; k < 3; ++k) bg[k] = srgb_to_linear(bg[k]);
+	// the environment map sits between the volume and the flat background (ray_marcher.cu:96-102)
+	float dir[3] = {0.f, 0.f, 0.f};
+	if (c.envmap) {
+		dir[0] = c.rays[(size_t)i * 6 + 3]; dir[1] = c.rays[(size_t)i * 6 + 4]; dir[2] = c.rays[(size_t)i * 6 + 5];
+		float ev[4];
+		read_envmap(reinterpret_cast<const __half*>(c.envmap), c.envmap_res_x, c.envmap_res_y, dir[0], dir[1], dir[2], ev);
+		#pragma unroll
+		for (int k = 0; k < 3; ++k) bg[k] = ev[k] + bg[k] * (1.0f - ev[3]);
+	}
 	const float4 gt4 = rays_rgba[i];
 	const float gt[4] = {gt4.x, gt4.y, gt4.z, gt4.w};
 	float tgt[3];
@@ -203,6 +212,21 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 		#pragma unroll
 		for (int j = 0; j < 3; ++j) pre[j] = __shfl_sync(0xffffffffu, rgb2[j], 31);
 	}
+	// gradient of the loss w.r.t. the environment map, only for rays that were traversed to their end (ray_marcher.cu:190-212):
+	// the background entered the ray colour with the final transmittance; alpha receives no gradient (:208-209)
+	if (c.envmap_gradient && n == numst && lane == 0) {
+		float ge[3] = {g[0], g[1], g[2]};
+		if (c.envmap_loss_type != c.loss_type) { float l2[3]; loss_and_grad(c.envmap_loss_type, tgt, rgb_ray, l2, ge); }
+		float v[4];
+		#pragma unroll
+		for (int k = 0; k < 3; ++k) {
+			float d = t0.T * ge[k];
+			if (!c.train_in_linear_color) d /= srgb_to_linear_derivative(bg[k]);
+			v[k] = ls * d;
+		}
+		v[3] = 0.f;
+		deposit_envmap_gradient(v, reinterpret_cast<__half*>(c.envmap_gradient), c.envmap_res_x, c.envmap_res_y, dir[0], dir[1], dir[2]);
+	}
 	// compaction: the ray's n Coordinates are one contiguous run of 7n floats on both sides
 	const float* src = reinterpret_cast<const float*>(cs);
 	float* dst = reinterpret_cast<float*>(coords_compacted + cbase);
@@ -240,6 +264,7 @@ extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint
 	NGP_REQUIRE(cfg && d_ray_counter && d_rays_rgba && d_numsteps && d_coords && d_coords_compacted && d_compacted_counter && d_rgbsigma && d_dloss && d_mean_density && d_scan_ws, "null pointer");
 	NGP_REQUIRE(padded_width >= 4 && padded_width % 4 == 0, "padded_width must be a multiple of 4");
 	NGP_REQUIRE(n_rays > 0, "n_rays must be positive");
+	NGP_REQUIRE(!(cfg->envmap || cfg->envmap_gradient) || (cfg->rays && cfg->envmap && cfg->envmap_res_x > 0 && cfg->envmap_res_y > 0), "an environment map needs its data, its resolution and the ray directions");
 	cudaStream_t s = (cudaStream_t)stream;
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
 	RayTmp* tmp = (RayTmp*)d_scan_ws;

@@ -3,6 +3,7 @@
 // into one kernel -- and generate_coords_from_rays_regularly_kernel (:552).  Live-ray counts are read from device
 // memory so the render loop needs no host round trip per iteration (the reference syncs every iteration, testbed.cu:540).
 #include "march.cuh"
+#include "composite.cuh"
 
 namespace ngp {
 
@@ -57,7 +58,8 @@ __device__ __forceinline__ float octet_lattice(float t_base, uint32_t sub, uint3
 // rounds do not shrink while the thread count grows 8x.
 __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
                                                         uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads,
-                                                        uint32_t first_pixel, uint32_t n) {
+                                                        uint32_t first_pixel, uint32_t n, const __half* __restrict__ envmap, int env_res_x, int env_res_y,
+                                                        float4* __restrict__ frame) {
 	// tile-sharded rendering: the launch covers the n pixels from first_pixel on (whole rows); every quantity that depends on the
 	// pixel -- the ray, the jitter seed, the scatter target -- uses the GLOBAL pixel index, so a band is bit-identical to the same
 	// rows of the full frame; only the slot in the payload array is band-relative
@@ -67,6 +69,11 @@ __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_c
 	const uint32_t x = idx % cam.width, y = idx / cam.width;
 	V3 o, d;
 	make_ray(cam_matrix.m, ((float)x + offx) / (float)cam.width, ((float)y + offy) / (float)cam.height, cam, o, d);
+	if (envmap) {            // occupancy_sampler.cu:500-502: every pixel starts from the environment map seen along its ray
+		float ev[4];
+		read_envmap(envmap, env_res_x, env_res_y, d.x, d.y, d.z, ev);
+		frame[idx] = make_float4(ev[0], ev[1], ev[2], ev[3]);
+	}
 	float t = fmaxf(ray_intersect_tmin(c, o, d), 0.05f) + 1e-6f;
 	RayPayload p;
 	p.ox = o.x; p.oy = o.y; p.oz = o.z; p.dx = d.x; p.dy = d.y; p.dz = d.z; p.idx = idx; p.n_steps = 0; p.t = t; p.alive = 1;
@@ -163,8 +170,9 @@ using namespace ngp;
 
 static float fractf_host(float x) { return x - floorf(x); }
 
-extern "C" int ngp_init_rays_rows(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
-                                  int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end) {
+static int init_rays_impl(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                          int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end,
+                          const void* d_envmap, int env_res_x, int env_res_y, float* d_frame_buffer) {
 	NGP_REQUIRE(cfg && cam && camera_matrix_host && d_bitfield && d_payloads, "null pointer");
 	NGP_REQUIRE(row_begin <= row_end && row_end <= (uint32_t)cam->height, "row range outside the image");
 	if (row_begin == row_end) return 0;
@@ -175,8 +183,23 @@ extern "C" int ngp_init_rays_rows(void* stream, const ngp_sampler_cfg* cfg, cons
 	const float offx = fractf_host(0.5f - ax + bx), offy = fractf_host(0.5f - ay + by);
 	const uint32_t n = (uint32_t)cam->width * (row_end - row_begin), first = (uint32_t)cam->width * row_begin;
 	CamMat cm; memcpy(cm.m, camera_matrix_host, sizeof(cm.m));
-	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads, first, n));
+	NGP_LAUNCH("init_rays_kernel", (cudaStream_t)stream, init_rays_kernel<<<div_up(n, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, *cam, cm, offx, offy, spp, d_bitfield, (RayPayload*)d_payloads, first, n,
+		(const __half*)d_envmap, env_res_x, env_res_y, (float4*)d_frame_buffer));
 	return check_launch("init_rays");
+}
+
+extern "C" int ngp_init_rays_rows(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                                  int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end) {
+	return init_rays_impl(stream, cfg, cam, camera_matrix_host, spp, snap_to_pixel_centers, d_bitfield, d_payloads, row_begin, row_end, nullptr, 0, 0, nullptr);
+}
+
+// the same with a trained environment map: frame_buffer[pixel] <- read_envmap(ray direction) for every pixel of the rows
+// (occupancy_sampler.cu:459-502); shade_kernel later composites the hits over it
+extern "C" int ngp_init_rays_rows_envmap(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,
+                                         int snap_to_pixel_centers, const uint8_t* d_bitfield, void* d_payloads, uint32_t row_begin, uint32_t row_end,
+                                         const void* d_envmap, int32_t env_res_x, int32_t env_res_y, float* d_frame_buffer) {
+	NGP_REQUIRE(d_envmap && d_frame_buffer && env_res_x > 0 && env_res_y > 0, "envmap, its resolution and the frame buffer are required");
+	return init_rays_impl(stream, cfg, cam, camera_matrix_host, spp, snap_to_pixel_centers, d_bitfield, d_payloads, row_begin, row_end, d_envmap, env_res_x, env_res_y, d_frame_buffer);
 }
 
 extern "C" int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp_camera_cfg* cam, const float* camera_matrix_host, uint32_t spp,

@@ -154,13 +154,14 @@ __global__ void __launch_bounds__(256) march_count_kernel(
 // exclusive scan in ray order of (ray has samples, sample count); one CTA.  counters[0] = rays kept, counters[1] = samples
 // counted including dropped rays (what the reference's atomicAdd would have reached).
 __global__ void __launch_bounds__(1024) march_scan_kernel(uint32_t n_rays, uint32_t n_coords, const uint32_t* __restrict__ n_in, uint32_t* __restrict__ base_out,
-                                                          uint32_t* __restrict__ ridx_out, uint32_t* __restrict__ counters) {
+                                                          uint32_t* __restrict__ ridx_out, uint32_t* __restrict__ counters, uint32_t keep_empty) {
 	__shared__ unsigned long long warp_tot[32];
 	__shared__ uint32_t kept_total;
 	if (threadIdx.x == 0) kept_total = 0;
 	const uint32_t per = (n_rays + 1023) / 1024, lo = min(threadIdx.x * per, n_rays), hi = min(lo + per, n_rays);
 	unsigned long long sum = 0;
-	for (uint32_t j = lo; j < hi; ++j) { const uint32_t n = n_in[j]; sum += ((unsigned long long)(n > 0) << 32) | n; }
+	// keep_empty (train_envmap, occupancy_sampler.cu:408): a ray without samples still takes a slot in the ray list
+	for (uint32_t j = lo; j < hi; ++j) { const uint32_t n = n_in[j]; sum += ((unsigned long long)(n > 0 || keep_empty) << 32) | n; }
 	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	unsigned long long incl = sum;
 	#pragma unroll
@@ -181,8 +182,8 @@ __global__ void __launch_bounds__(1024) march_scan_kernel(uint32_t n_rays, uint3
 	for (uint32_t j = lo; j < hi; ++j) {
 		const uint32_t n = n_in[j], base = (uint32_t)run;
 		base_out[j] = base; ridx_out[j] = (uint32_t)(run >> 32);
-		if (n > 0 && (uint64_t)base + n <= n_coords) ++kept;
-		run += ((unsigned long long)(n > 0) << 32) | n;
+		if ((n > 0 || keep_empty) && (uint64_t)base + n <= n_coords) ++kept;
+		run += ((unsigned long long)(n > 0 || keep_empty) << 32) | n;
 	}
 	if (kept) atomicAdd(&kept_total, kept);
 	__syncthreads();
@@ -195,10 +196,11 @@ __global__ void __launch_bounds__(256) march_emit_kernel(
 	const uint32_t* __restrict__ n_in, const uint32_t* __restrict__ base_in, const uint32_t* __restrict__ ridx_in,
 	const uint32_t* __restrict__ n_windows_in, const uint32_t* __restrict__ masks_in, float* __restrict__ rays_out, float4* __restrict__ rgba_out, uint32_t* __restrict__ numsteps_out, Coordinate* __restrict__ coords_out)
 {
+	const bool keep_empty = c.keep_empty_rays != 0;
 	const uint32_t lane = threadIdx.x & 31, warps = gridDim.x * (blockDim.x >> 5);
 	for (uint32_t i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n_rays; i += warps) {
 	const uint32_t n = n_in[i], base = base_in[i], ray_idx = ridx_in[i];
-	if (n == 0 || (uint64_t)base + n > n_coords) continue;    // no samples, or over budget: dropped like the reference does
+	if ((n == 0 && !keep_empty) || (uint64_t)base + n > n_coords) continue;    // no samples, or over budget: dropped like the reference does
 	const RaySetup r = setup_ray(c, cam, i, n_rays, n_rays_shift, n_images, xforms, snap, rng);
 	if (lane == 0) {
 		float* ro = rays_out + (size_t)ray_idx * 6;
@@ -210,6 +212,7 @@ __global__ void __launch_bounds__(256) march_emit_kernel(
 		numsteps_out[(size_t)ray_idx * 2 + 0] = n;
 		numsteps_out[(size_t)ray_idx * 2 + 1] = base;
 	}
+	if (n == 0) continue;                                   // kept for the environment map only: a ray record, no samples
 	const uint32_t nw = n_windows_in[i];
 	if (nw <= kMaskWindows) {
 		const uint32_t rec_lo = lane < nw ? masks_in[(size_t)i * kMaskWindows + lane] : 0u;
@@ -247,7 +250,7 @@ extern "C" int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg
 	const uint32_t grid = std::min(div_up(n_rays, 8), kNumSMs * ctas_per_sm);
 	NGP_LAUNCH("march_count_kernel", s, march_count_kernel<<<grid, 256, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_images, d_xforms, d_bitfield,
 		snap_to_pixel_centers, rng, n_tmp, d_per_ray_n, nwin_tmp, mask_tmp));
-	NGP_LAUNCH("march_scan_kernel", s, march_scan_kernel<<<1, 1024, 0, s>>>(n_rays, n_coords, n_tmp, base_tmp, ridx_tmp, d_counters));
+	NGP_LAUNCH("march_scan_kernel", s, march_scan_kernel<<<1, 1024, 0, s>>>(n_rays, n_coords, n_tmp, base_tmp, ridx_tmp, d_counters, cfg->keep_empty_rays));
 	NGP_LAUNCH("march_emit_kernel", s, march_emit_kernel<<<grid, 256, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_coords, n_images, d_xforms, (const uint2*)d_images,
 		d_bitfield, snap_to_pixel_centers, rng, n_tmp, base_tmp, ridx_tmp, nwin_tmp, mask_tmp, d_rays, (float4*)d_rays_rgba, d_numsteps, (Coordinate*)d_coords));
 	return check_launch("generate_training_samples");

@@ -32,7 +32,7 @@ OccupancySampler::OccupancySampler(const Json& config) {
 }
 
 ngp_sampler_cfg OccupancySampler::cfg() const {
-	ngp_sampler_cfg c;
+	ngp_sampler_cfg c{};
 	c.aabb_min = aabb.min[0]; c.aabb_max = aabb.max[0];
 	c.grid_size = n_grid_size; c.n_cascades = n_cascades; c.max_steps = n_max_steps;
 	c.cone_angle = cone_angle_constant; c.min_step = min_cone_stepsize; c.max_step = max_cone_stepsize; c.near_distance = near_distance;
@@ -76,14 +76,15 @@ void OccupancySampler::update_grid_bitfield(cudaStream_t stream) {
 	api_check(ngp_update_grid_bitfield(stream, &c, density_grid.data(), min_optical_thickness, density_grid_mean.data(), density_grid_bitfield.data()));
 }
 
-void OccupancySampler::sample_coords_from_dataset(uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_coords, const NeRFSynthetic& dataset, bool,
+void OccupancySampler::sample_coords_from_dataset(uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_coords, const NeRFSynthetic& dataset, bool train_envmap,
                                                   DeviceBuffer<Ray>& rays, DeviceBuffer<float>& rays_rgba, uint32_t* n_rays_counter,
                                                   DeviceBuffer<uint32_t>& ray_coord_indices, DeviceBuffer<Coordinate>& coords, uint32_t* n_coords_counter,
                                                   default_rng_t rng_step, cudaStream_t stream) {
 	// the C ABI keeps the two counters adjacent: [0] rays kept, [1] samples counted
 	if (n_coords_counter != n_rays_counter + 1) throw std::runtime_error("sample_coords_from_dataset: counters must be adjacent (rays, samples)");
 	m_scan_ws.enlarge(ngp_scan_workspace_bytes(n_rays));
-	const ngp_sampler_cfg c = cfg();
+	ngp_sampler_cfg c = cfg();
+	c.keep_empty_rays = train_envmap ? 1u : 0u;          // occupancy_sampler.cu:408
 	ngp_camera_cfg cam{dataset.image_resolution[0], dataset.image_resolution[1], dataset.focal_length[0], dataset.focal_length[1],
 	                   dataset.principal_point[0], dataset.principal_point[1]};
 	api_check(ngp_generate_training_samples(stream, &c, &cam, n_rays, n_rays_shift, n_coords, dataset.n_images, (const float*)dataset.xforms.data(),
@@ -94,10 +95,15 @@ void OccupancySampler::sample_coords_from_dataset(uint32_t n_rays, uint32_t n_ra
 
 void OccupancySampler::generate_rays_from_camera_matrix(const int resolution[2], const float focal_length[2], const float principal_point[2],
                                                         const Mat34& camera_matrix, uint32_t spp, DeviceBuffer<RayPayload>& payload, cudaStream_t stream,
-                                                        int row_begin, int row_end) {
+                                                        int row_begin, int row_end, const void* envmap, const int* envmap_resolution, float* frame_buffer) {
 	const ngp_sampler_cfg c = cfg();
 	ngp_camera_cfg cam{resolution[0], resolution[1], focal_length[0], focal_length[1], principal_point[0], principal_point[1]};
 	if (row_end < 0) { row_begin = 0; row_end = resolution[1]; }
+	if (envmap) {
+		api_check(ngp_init_rays_rows_envmap(stream, &c, &cam, camera_matrix.m, spp, snap_to_pixel_centers_in_rendering ? 1 : 0, density_grid_bitfield.data(), payload.data(),
+		                                    (uint32_t)row_begin, (uint32_t)row_end, envmap, envmap_resolution[0], envmap_resolution[1], frame_buffer));
+		return;
+	}
 	api_check(ngp_init_rays_rows(stream, &c, &cam, camera_matrix.m, spp, snap_to_pixel_centers_in_rendering ? 1 : 0, density_grid_bitfield.data(), payload.data(),
 	                             (uint32_t)row_begin, (uint32_t)row_end));
 }

@@ -33,7 +33,8 @@ public:
 	// :813-855
 	void generate_rays_from_camera_matrix(const int resolution[2], const float focal_length[2], const float principal_point[2], const Mat34& camera_matrix,
 	                                      uint32_t spp, DeviceBuffer<RayPayload>& payload, cudaStream_t stream,
-	                                      int row_begin = 0, int row_end = -1);      // rows [row_begin, row_end) only; -1 = the whole image
+	                                      int row_begin = 0, int row_end = -1,       // rows [row_begin, row_end) only; -1 = the whole image
+	                                      const void* envmap = nullptr, const int* envmap_resolution = nullptr, float* frame_buffer = nullptr);   // :459-502
 	// :857-877.  d_n_rays (optional): live-ray count in device memory, so no host round trip is needed
 	void generate_coords_from_rays(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, DeviceBuffer<RayPayload>& payloads,
 	                               DeviceBuffer<Coordinate>& coords, cudaStream_t stream);

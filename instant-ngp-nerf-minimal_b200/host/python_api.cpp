@@ -91,6 +91,22 @@ PYBIND11_MODULE(pyngp, m) {
 			{ py::gil_scoped_release rel; t.render_band_to_host(width, height, spp, to_srgb, ptr); }
 			return image;
 		}, "Renders the rows set by set_render_rows and returns them alone, [rows][width][4].", py::arg("width") = 1920, py::arg("height") = 1080, py::arg("spp") = 1, py::arg("to_srgb") = true)
+		.def("envmap_image", [](const Testbed& t) {
+			// the trained environment map as render() uses it (EMA weights), [resolution[1]][resolution[0]][4] floats; zeros when not trained
+			const auto& e = t.m_envmap;
+			py::array_t<float> img({e.resolution[1], e.resolution[0], 4});
+			float* out = (float*)img.request().ptr;
+			const size_t n = (size_t)e.resolution[0] * e.resolution[1] * 4;
+			if (!t.m_train_envmap || e.n_params != n) { std::fill(out, out + n, 0.f); return img; }
+			std::vector<uint16_t> h(n);
+			NGP_CUDA_CHECK(cudaMemcpy(h.data(), e.params_inference(), n * 2, cudaMemcpyDeviceToHost));
+			for (size_t k = 0; k < n; ++k) {
+				const uint32_t s = (h[k] >> 15) & 1, ex = (h[k] >> 10) & 0x1f, m = h[k] & 0x3ff;
+				const float v = ex == 0 ? std::ldexp((float)m, -24) : ex == 31 ? (m ? NAN : INFINITY) : std::ldexp((float)(m | 0x400), (int)ex - 25);
+				out[k] = s ? -v : v;
+			}
+			return img;
+		}, "The trained environment map (inference weights) as float32 [y][x][4].")
 		.def("set_render_rows", &Testbed::set_render_rows,
 		     "Tile-sharded inference: render() marches only the rays of rows [row_begin, row_end) (the other rows of the returned image hold the background); "
 		     "row_end = -1 restores the whole image.  Bands are bit-identical to the same rows of the full frame.", py::arg("row_begin"), py::arg("row_end"))

@@ -10,7 +10,7 @@ RayMarcher::RayMarcher(const Json& config) {
 
 void RayMarcher::volume_rendering_with_loss_and_gradient(
 	uint32_t n_rays, uint32_t n_max_compacted_coords,
-	const DeviceBuffer<Ray>&, const DeviceBuffer<float>& rays_rgba, const uint32_t* n_rays_counter, DeviceBuffer<uint32_t>& ray_coord_indices,
+	const DeviceBuffer<Ray>& rays, const DeviceBuffer<float>& rays_rgba, const uint32_t* n_rays_counter, DeviceBuffer<uint32_t>& ray_coord_indices,
 	const DeviceBuffer<Coordinate>& coords, DeviceBuffer<Coordinate>& compacted_coords, uint32_t* n_compacted_coords_counter,
 	const DeviceBuffer<precision_t>& network_output, DeviceBuffer<precision_t>& dloss_doutput, int padded_output_width,
 	EActivation rgb_activation, EActivation density_activation,
@@ -18,13 +18,17 @@ void RayMarcher::volume_rendering_with_loss_and_gradient(
 	const BoundingBox&, uint32_t n_cascades, float min_cone_stepsize, const DeviceBuffer<float>& density_grid_mean, float min_optical_thickness,
 	const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream, uint32_t* compacted_src_index)
 {
-	ngp_render_cfg c;
+	ngp_render_cfg c{};
 	c.n_cascades = n_cascades; c.min_step = min_cone_stepsize;
 	c.rgb_activation = (int)rgb_activation; c.density_activation = (int)density_activation;
 	c.loss_type = (int)loss_type; c.color_space = (int)color_space;
 	c.train_with_random_bg_color = train_with_random_bg_color ? 1 : 0; c.train_in_linear_color = train_in_linear_color ? 1 : 0;
 	c.transmittance_threshold = transmittance_threshold; c.min_optical_thickness = min_optical_thickness; c.loss_scale = loss_scale;
 	for (int k = 0; k < 3; ++k) c.background_color[k] = background_color[k];
+	if (m_envmap) {
+		c.envmap = m_envmap; c.envmap_gradient = m_envmap_gradient; c.rays = (const float*)rays.data();
+		c.envmap_res_x = m_envmap_res[0]; c.envmap_res_y = m_envmap_res[1]; c.envmap_loss_type = (int)m_envmap_loss_type;
+	}
 	m_scan_ws.enlarge(ngp_composite_workspace_bytes(n_rays));
 	api_check(ngp_composite_train(stream, &c, n_rays, n_max_compacted_coords, n_rays_counter, rays_rgba.data(), ray_coord_indices.data(),
 	                              (const float*)coords.data(), (float*)compacted_coords.data(), n_compacted_coords_counter, network_output.data(),

@@ -13,6 +13,7 @@ struct RaysSoA {   // internal/utils/common.h:146-153
 };
 
 class RayMarcher {
+	const void* m_envmap = nullptr; void* m_envmap_gradient = nullptr; int m_envmap_res[2] = {0, 0}; ELossType m_envmap_loss_type = ELossType::L2;
 public:
 	explicit RayMarcher(const Json& config);
 
@@ -26,6 +27,11 @@ public:
 		float* loss_output, ELossType loss_type, float loss_scale,
 		const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const DeviceBuffer<float>& density_grid_mean, float min_optical_thickness,
 		const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream, uint32_t* compacted_src_index = nullptr);
+
+	// environment map arguments of ray_marcher.cu:43-46 (data, gradient, resolution, loss type); nullptr data = none
+	void set_envmap(const void* data, void* gradient, int res_x, int res_y, ELossType loss_type) {
+		m_envmap = data; m_envmap_gradient = gradient; m_envmap_res[0] = res_x; m_envmap_res[1] = res_y; m_envmap_loss_type = loss_type;
+	}
 
 	// ray_marcher.cu:379-416
 	void volume_rendering(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t i_steps_offset, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,

@@ -81,8 +81,35 @@ void Testbed::load_model_config_json(const Json& config) {
 	m_trainer = std::make_shared<Trainer>(m_network, OptimizerConfig::from_json(m_model_config["optimizer"]), m_seed, m_stream);
 	m_grid_grads_clean = false;
 	m_train_envmap = m_model_config.contains("envmap") ? m_model_config["envmap"].value("train", false) : false;
-	if (m_train_envmap) throw std::runtime_error("envmap training is not implemented in this build (base.json keeps it off)");
+	if (m_train_envmap) {
+		// testbed.cu:83-90.  All buffers start at zero (trainable_buffer.h:45-55), so an untrained map changes nothing.
+		const Json& e = m_model_config["envmap"];
+		const int h = e.value("height", 256), w = e.value("width", 256);
+		if (h <= 0 || w <= 0) throw std::runtime_error("envmap: height and width must be positive");
+		if (m_dp_world > 1) throw std::runtime_error("envmap training is single-GPU (its gradients are not exchanged)");
+		m_envmap.resolution[0] = h; m_envmap.resolution[1] = w;
+		m_envmap.loss_type = string_to_loss_type(e.contains("loss") ? e["loss"].str() : std::string("RelativeL2"));
+		m_envmap.opt = OptimizerConfig::from_json(e["optimizer"]);
+		m_envmap.n_params = (size_t)h * w * 4;
+		const size_t n_alloc = m_envmap.n_params + 16;
+		m_envmap.params_fp32.resize(n_alloc); m_envmap.m1.resize(n_alloc); m_envmap.m2.resize(n_alloc); m_envmap.param_steps.resize(n_alloc);
+		m_envmap.params.resize(n_alloc); m_envmap.gradients.resize(n_alloc); m_envmap.ema.resize(n_alloc);
+		m_envmap.params_fp32.memset(0, m_stream); m_envmap.m1.memset(0, m_stream); m_envmap.m2.memset(0, m_stream); m_envmap.param_steps.memset(0, m_stream);
+		m_envmap.params.memset(0, m_stream); m_envmap.gradients.memset(0, m_stream); m_envmap.ema.memset(0, m_stream);
+		m_envmap.step = 0; m_envmap.lr_factor = 1.0f;
+		NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	}
 	m_training_buffer.i_step = 0;
+}
+
+void Testbed::envmap_optimizer_step(cudaStream_t stream, float loss_scale) {
+	Envmap& e = m_envmap;
+	if (e.opt.has_decay && e.step >= e.opt.decay_start && (e.step - e.opt.decay_start) % e.opt.decay_interval == 0) e.lr_factor *= e.opt.decay_base;
+	ngp_optimizer_cfg c{e.opt.learning_rate, e.opt.beta1, e.opt.beta2, e.opt.epsilon, e.opt.l2_reg, loss_scale, e.opt.has_ema ? e.opt.ema_decay : 0.0f};
+	// a TrainableBuffer has no matrix parameters (layer_sizes() is empty): no weight decay, texels without gradient are skipped
+	api_check(ngp_optimizer_step(stream, &c, e.n_params, 0, e.step, e.opt.learning_rate * e.lr_factor, e.params_fp32.data(), e.params.data(), e.gradients.data(),
+	                             e.m1.data(), e.m2.data(), e.param_steps.data(), e.ema.data()));
+	++e.step;
 }
 
 // testbed.cu:95-125
@@ -153,6 +180,7 @@ void Testbed::set_data_parallel(int rank, int world_size, void* nccl_comm, bool 
 	if (world_size < 1 || rank < 0 || rank >= world_size) throw std::runtime_error("set_data_parallel: bad rank / world size");
 	if (world_size > 1 && !nccl_comm) throw std::runtime_error("set_data_parallel: a communicator is required for world_size > 1");
 	if (!m_trainer) throw std::runtime_error("set_data_parallel: load_model_config first");
+	if (m_train_envmap && world_size > 1) throw std::runtime_error("envmap training is single-GPU (its gradients are not exchanged)");
 	m_dp_rank = rank; m_dp_world = world_size; m_nccl_comm = nccl_comm;
 	m_peer_enabled = false;
 	if (!peer_memory || world_size == 1) return;

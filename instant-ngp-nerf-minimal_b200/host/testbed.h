@@ -84,6 +84,20 @@ public:
 	float m_background_color[4] = {0.0f, 0.0f, 0.0f, 1.0f};
 	EColorSpace m_color_space = EColorSpace::Linear;
 	bool m_train_envmap = false;
+	// trainable environment map (testbed.cu:82-90: TrainableBuffer<4, 2> + its own Ema(ExponentialDecay(Adam)) and loss).  The
+	// reference stores the resolution as {height, width} and indexes x + y * resolution.x (utils/envmap.h:19-47): kept.
+	struct Envmap {
+		int resolution[2] = {256, 256};
+		ELossType loss_type = ELossType::RelativeL2;
+		OptimizerConfig opt;
+		size_t n_params = 0;
+		DeviceBuffer<float> params_fp32, m1, m2;
+		DeviceBuffer<precision_t> params, gradients, ema;
+		DeviceBuffer<uint32_t> param_steps;
+		uint32_t step = 0; float lr_factor = 1.0f;
+		precision_t* params_inference() const { return opt.has_ema ? ema.data() : params.data(); }
+	} m_envmap;
+	void envmap_optimizer_step(cudaStream_t stream, float loss_scale);      // Trainer::optimizer_step of the envmap (testbed.cu:296-298)
 
 	float m_scene_scale = 1.f;
 	float m_scene_offset[3] = {0.5f, 0.5f, 0.5f};

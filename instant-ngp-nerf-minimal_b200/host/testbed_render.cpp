@@ -29,7 +29,8 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 	render_buffer.clear_frame_buffer(m_stream);
 	(void)n_frame_pixels;
 	m_sampler->generate_rays_from_camera_matrix(resolution, focal_length, rb.principal_point, camera_matrix, render_buffer.spp(), rb.rays[0].payload, m_stream,
-	                                            row_begin, row_end);
+	                                            row_begin, row_end, m_train_envmap ? m_envmap.params_inference() : nullptr, m_envmap.resolution,
+	                                            m_train_envmap ? render_buffer.frame_buffer() : nullptr);      // testbed.cu:506-512
 	NGP_CUDA_CHECK(cudaMemsetAsync(rb.rays[0].rgba.data(), 0, (size_t)std::max(n_pixels, 1u) * 4 * sizeof(float), m_stream));
 	NGP_CUDA_CHECK(cudaMemsetAsync(rb.n_hit_counter.data(), 0, sizeof(uint32_t), m_stream));
 

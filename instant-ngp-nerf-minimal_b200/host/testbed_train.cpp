@@ -38,6 +38,13 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 	uint32_t& n_rays = m_training_buffer.n_rays_per_batch;
 	TrainingBuffer& tb = m_training_buffer;
 
+	// envmap gradient initialisation (testbed.cu:235-239): the gradients of all steps of this call accumulate, one optimizer step at its end
+	if (m_train_envmap) {
+		m_envmap.gradients.memset(0, stream);
+		m_render->set_envmap(m_envmap.params.data(), m_envmap.gradients.data(), m_envmap.resolution[0], m_envmap.resolution[1], m_envmap.loss_type);
+	} else {
+		m_render->set_envmap(nullptr, nullptr, 0, 0, ELossType::L2);
+	}
 	tb.n_coords_counter.enlarge((size_t)n_training_steps * 2);
 	NGP_CUDA_CHECK(cudaMemsetAsync(tb.n_coords_counter.data(), 0, sizeof(uint32_t) * 2 * n_training_steps, stream));
 	tb.n_compacted_coords_counter.enlarge(n_training_steps);
@@ -95,6 +102,7 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 		const ncclResult_t r = ncclAllGather(m_trainer->ema() + (size_t)m_dp_rank * S, m_trainer->ema(), S, ncclHalf, (ncclComm_t)m_nccl_comm, stream);
 		if (r != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather failed: ") + ncclGetErrorString(r));
 	}
+	if (m_train_envmap) envmap_optimizer_step(stream, LOSS_SCALE * (float)n_training_steps);      // testbed.cu:295-298
 	api_check(ngp_reduce_sum(stream, tb.loss.data(), (uint64_t)n_rays * n_training_steps, tb.loss_sum.data()));
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev[2], stream));
 

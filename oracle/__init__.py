@@ -247,6 +247,29 @@ def composite_train(n_rays, n_kept, max_compacted, rgba_gt, numsteps, coords, ne
     return dict(counter=int(counter), coords_compacted=cc, dloss=dloss.view(np.float16), loss=loss, rgb_ray=rgb_ray)
 
 
+def composite_train_envmap(n_rays, n_kept, max_compacted, rgba_gt, numsteps, coords, net_out, cfg, mean_density, rng, rays, envmap, env_res_x, env_res_y,
+                           env_loss_type=6, min_optical_thickness=0.01, T_thresh=1e-4, loss_scale=128.0, bg=(0, 0, 0), rgb_act=2, density_act=3, loss_type=4,
+                           color_space=0, random_bg=1, train_in_linear=0, padded_width=4):
+    """composite_train with a trainable environment map behind the volume (ray_marcher.cu:96-102,190-212; utils/envmap.h).
+    rays: [n_kept][6] f32 {o, d}; envmap: fp16 [res_y][res_x][4].  Returns the dict of composite_train + envmap_grad (fp32 sums)."""
+    import ctypes as C
+    cc = np.zeros((max_compacted, 7), np.float32)
+    dloss = np.zeros((max_compacted, padded_width), np.uint16)
+    loss = np.zeros(n_rays, np.float32)
+    rgb_ray = np.zeros((max(n_kept, 1), 3), np.float32)
+    egrad = np.zeros(env_res_x * env_res_y * 4, np.float32)
+    cf = np.array([cfg.min_step, mean_density, min_optical_thickness, T_thresh, loss_scale, bg[0], bg[1], bg[2]], np.float32)
+    cu = np.array([cfg.n_cascades, rgb_act, density_act, loss_type, color_space, random_bg, train_in_linear], np.uint32)
+    rays = np.ascontiguousarray(rays, np.float32)
+    env = np.ascontiguousarray(envmap).view(np.uint16)
+    fn = lib().orc_composite_train_envmap
+    fn.restype = C.c_uint32
+    counter = fn(u32(n_rays), u32(n_kept), u32(max_compacted), P(rgba_gt), P(numsteps), P(coords), P(cc), P(net_out.view(np.uint16)),
+                 P(dloss), u32(padded_width), P(cf), P(cu), u64(rng.state), u64(rng.inc), P(loss), P(rgb_ray),
+                 P(rays), P(env), P(egrad), C.c_int32(env_res_x), C.c_int32(env_res_y), C.c_int32(env_loss_type))
+    return dict(counter=int(counter), coords_compacted=cc, dloss=dloss.view(np.float16), loss=loss, rgb_ray=rgb_ray, envmap_grad=egrad)
+
+
 def rollover(B, n_in, grads, coords, stride=4):
     g = np.ascontiguousarray(grads).view(np.uint16)
     lib().orc_rollover(u32(B), u32(n_in), P(g), u32(stride), P(coords))

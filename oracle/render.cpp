@@ -86,11 +86,49 @@ extern "C" {
 // cfg_u: n_cascades, rgb_act, density_act, loss_type, color_space(0 linear,1 srgb), random_bg, train_in_linear
 // numsteps [n_rays_kept][2] in/out.  Compaction in ray order.  Returns the final compacted counter
 // (may exceed max_compacted, as in the reference).
-uint32_t orc_composite_train(uint32_t n_rays, uint32_t n_rays_kept, uint32_t max_compacted, const float* rgba_gt,
+// ---- environment map (internal/utils/envmap.h:19-88; dir_to_spherical_unorm: internal/utils/random_val.cuh:47-52) ----------
+struct EnvTap { int x0, y0; float wx, wy; };
+static EnvTap env_tap(const float* d, int res_x, int res_y) {
+	const float v[3] = {d[2], -d[0], d[1]};                                   // envmap.h:20
+	const float cos_theta = fminf(fmaxf(v[2], -1.0f), 1.0f);
+	const float theta = acosf(cos_theta), phi = atan2f(v[1], v[0]);
+	const float cx = theta / 3.14159265358979323846f, cy = phi / (2.0f * 3.14159265358979323846f) + 0.5f;
+	const float fx = cy * (float)(res_x - 1), fy = cx * (float)(res_y - 1);   // envmap.h:22 (x from the azimuth)
+	EnvTap t; t.x0 = (int)fx; t.y0 = (int)fy; t.wx = fx - (float)t.x0; t.wy = fy - (float)t.y0;
+	return t;
+}
+static size_t env_texel(int x, int y, int res_x, int res_y) {                   // envmap.h:27-33
+	if (x < 0) x += res_x; else if (x >= res_x) x -= res_x;
+	y = std::max(std::min(y, res_y - 1), 0);
+	return ((size_t)x + (size_t)y * res_x) * 4;
+}
+static void env_read(const uint16_t* env, int res_x, int res_y, const float* d, float* out) {
+	const EnvTap t = env_tap(d, res_x, res_y);
+	const float w[4] = {(1 - t.wx) * (1 - t.wy), t.wx * (1 - t.wy), (1 - t.wx) * t.wy, t.wx * t.wy};
+	for (int c = 0; c < 4; ++c) out[c] = 0.f;
+	for (int k = 0; k < 4; ++k) {
+		const uint16_t* p = env + env_texel(t.x0 + (k & 1), t.y0 + (k >> 1), res_x, res_y);
+		for (int c = 0; c < 4; ++c) out[c] += w[k] * h16from(p[c]);
+	}
+}
+// the reference deposits fp16 products with fp16 atomics (order-dependent); the oracle sums the same fp16-rounded products in fp32
+static void env_deposit(const float* value, float* grad, int res_x, int res_y, const float* d) {
+	const EnvTap t = env_tap(d, res_x, res_y);
+	const float w[4] = {(1 - t.wx) * (1 - t.wy), t.wx * (1 - t.wy), (1 - t.wx) * t.wy, t.wx * t.wy};
+	for (int k = 0; k < 4; ++k) {
+		float* p = grad + env_texel(t.x0 + (k & 1), t.y0 + (k >> 1), res_x, res_y);
+		const float wk = h16from(h16bits(w[k]));
+		for (int c = 0; c < 4; ++c) p[c] += h16from(h16bits(h16from(h16bits(value[c])) * wk));
+	}
+}
+static float srgb_to_linear_derivative(float srgb) { return srgb <= 0.04045f ? 1.0f / 12.92f : 2.4f / 1.055f * powf((srgb + 0.055f) / 1.055f, 1.4f); }
+
+static uint32_t composite_train_impl(uint32_t n_rays, uint32_t n_rays_kept, uint32_t max_compacted, const float* rgba_gt,
                              uint32_t* numsteps, const float* coords, float* coords_compacted,
                              const uint16_t* net_out, uint16_t* dloss, uint32_t padded_width,
                              const float* cfg_f, const uint32_t* cfg_u, uint64_t rng_state, uint64_t rng_inc,
-                             float* loss_out, float* rgb_ray_out) {
+                             float* loss_out, float* rgb_ray_out,
+                             const float* rays, const uint16_t* envmap, float* envmap_grad, int env_res_x, int env_res_y, int env_loss_type) {
 	const float min_step = cfg_f[0], mean_density = cfg_f[1], min_thick = cfg_f[2], T_thresh = cfg_f[3], loss_scale0 = cfg_f[4];
 	const uint32_t n_cascades = cfg_u[0]; const int rgb_act = cfg_u[1], den_act = cfg_u[2], loss_type = cfg_u[3];
 	const int color_space = cfg_u[4], random_bg = cfg_u[5], lin = cfg_u[6];
@@ -114,6 +152,11 @@ uint32_t orc_composite_train(uint32_t n_rays, uint32_t n_rays_kept, uint32_t max
 			T *= (1.f - alpha);
 		}
 		float bg[3] = {bg0[0], bg0[1], bg0[2]}, tgt[3];
+		if (envmap) {                                                           // ray_marcher.cu:96-102
+			float ev[4];
+			env_read(envmap, env_res_x, env_res_y, rays + (size_t)i * 6 + 3, ev);
+			for (int k = 0; k < 3; ++k) bg[k] = ev[k] + bg[k] * (1.0f - ev[3]);
+		}
 		const float* gt = rgba_gt + (size_t)i * 4;
 		if (lin || color_space == 0) {
 			for (int k = 0; k < 3; ++k) tgt[k] = gt[k] + (1 - gt[3]) * bg[k];
@@ -153,8 +196,41 @@ uint32_t orc_composite_train(uint32_t n_rays, uint32_t n_rays_kept, uint32_t max
 			float dmlp = net_to_density_d(raw[3], den_act) * (dt * dot);
 			dl[3] = h16bits(ls * dmlp + (raw[3] < 0 ? -l1reg : 0.f));
 		}
+		if (envmap_grad && n == numst) {                                        // ray_marcher.cu:190-212 (T = transmittance behind the ray)
+			float ge[3] = {g[0], g[1], g[2]}, l2[3];
+			if (env_loss_type != loss_type) loss_and_grad(env_loss_type, tgt, rgb_ray, l2, ge);
+			float v[4];
+			for (int k = 0; k < 3; ++k) {
+				float d = T * ge[k];
+				if (!lin) d /= srgb_to_linear_derivative(bg[k]);
+				v[k] = ls * d;
+			}
+			v[3] = 0.f;
+			env_deposit(v, envmap_grad, env_res_x, env_res_y, rays + (size_t)i * 6 + 3);
+		}
 	}
 	return counter;
+}
+
+uint32_t orc_composite_train(uint32_t n_rays, uint32_t n_rays_kept, uint32_t max_compacted, const float* rgba_gt,
+                             uint32_t* numsteps, const float* coords, float* coords_compacted,
+                             const uint16_t* net_out, uint16_t* dloss, uint32_t padded_width,
+                             const float* cfg_f, const uint32_t* cfg_u, uint64_t rng_state, uint64_t rng_inc,
+                             float* loss_out, float* rgb_ray_out) {
+	return composite_train_impl(n_rays, n_rays_kept, max_compacted, rgba_gt, numsteps, coords, coords_compacted, net_out, dloss, padded_width, cfg_f, cfg_u,
+	                            rng_state, rng_inc, loss_out, rgb_ray_out, nullptr, nullptr, nullptr, 0, 0, 0);
+}
+
+// the same with a trainable environment map behind the volume: rays = 6 floats per kept ray {o, d}, envmap fp16 [res_y][res_x][4],
+// envmap_grad fp32 of the same shape (accumulated, caller zeroes)
+uint32_t orc_composite_train_envmap(uint32_t n_rays, uint32_t n_rays_kept, uint32_t max_compacted, const float* rgba_gt,
+                             uint32_t* numsteps, const float* coords, float* coords_compacted,
+                             const uint16_t* net_out, uint16_t* dloss, uint32_t padded_width,
+                             const float* cfg_f, const uint32_t* cfg_u, uint64_t rng_state, uint64_t rng_inc,
+                             float* loss_out, float* rgb_ray_out,
+                             const float* rays, const uint16_t* envmap, float* envmap_grad, int32_t env_res_x, int32_t env_res_y, int32_t env_loss_type) {
+	return composite_train_impl(n_rays, n_rays_kept, max_compacted, rgba_gt, numsteps, coords, coords_compacted, net_out, dloss, padded_width, cfg_f, cfg_u,
+	                            rng_state, rng_inc, loss_out, rgb_ray_out, rays, envmap, envmap_grad, env_res_x, env_res_y, env_loss_type);
 }
 
 // fill_rollover(_and_rescale): grads [B][stride] fp16, coords [B][7] f32

@@ -95,6 +95,63 @@ def test_composite_train_matches_oracle(capi, orc, n_rays, max_compacted, kw):
         assert got_counter > max_compacted
 
 
+@pytest.mark.parametrize("kw", [dict(), dict(color_space=1, random_bg=0), dict(train_in_linear=1, loss_type=0), dict(env_loss_type=4)])
+def test_composite_train_with_environment_map_matches_oracle(capi, orc, kw):
+    """trainable environment map behind the volume (ray_marcher.cu:96-102, 190-212; utils/envmap.h): the background of every ray is
+    envmap(dir).rgb + bg * (1 - envmap(dir).a), and fully traversed rays deposit dL/d(envmap.rgb) bilinearly (fp16 atomics on the
+    GPU, fp32 sums of the same fp16 products in the oracle)."""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    ocfg = orc.SamplerCfg(1)
+    n_rays, max_compacted, rx, ry = 2000, 1 << 20, 64, 48
+    numsteps, coords, net, rgba, total = _rays(n_rays, 7, max_len=60, sigma_hi=1.0)      # thin media: many rays reach the background
+    g = np.random.Generator(np.random.PCG64(3))
+    rays = g.normal(size=(n_rays, 6)).astype(np.float32)
+    rays[:, 3:] /= np.linalg.norm(rays[:, 3:], axis=1, keepdims=True)
+    rays[0, 3:] = (0, 0, 1); rays[1, 3:] = (0, 1, 0); rays[2, 3:] = (-1, 0, 0); rays[3, 3:] = (0, -1, 0)      # poles and the azimuth seam
+    env = g.random((ry, rx, 4), dtype=np.float32).astype(np.float16)
+    rng = orc.Pcg32(99)
+    ref_ns = numsteps.copy()
+    env_loss = kw.get("env_loss_type", 6)
+    ref = orc.composite_train_envmap(n_rays, n_rays, max_compacted, rgba, ref_ns, coords, net, ocfg, 0.05, rng, rays, env, rx, ry, env_loss_type=env_loss,
+                                     bg=(0.2, 0.4, 0.6), loss_type=kw.get("loss_type", 4), color_space=kw.get("color_space", 0),
+                                     random_bg=kw.get("random_bg", 1), train_in_linear=kw.get("train_in_linear", 0))
+    d_rays, d_env = G.dev(rays), G.dev(env.view(np.uint16))
+    d_egrad = G.zeros(rx * ry * 4, torch.int16)
+    c = _render_cfg(capi, ocfg, **kw)
+    c.envmap, c.envmap_gradient, c.rays = d_env.data_ptr(), d_egrad.data_ptr(), d_rays.data_ptr()
+    c.envmap_res_x, c.envmap_res_y, c.envmap_loss_type = rx, ry, env_loss
+    d_ns = G.dev(numsteps)
+    cc, dloss = G.zeros(max_compacted * 7, torch.float32), G.zeros(max_compacted * 4, torch.int16)
+    counter, loss = G.zeros(1, torch.int32), G.zeros(n_rays, torch.float32)
+    ray_counter, d_mean = G.dev(np.array([n_rays], np.uint32)), G.dev(np.array([0.05], np.float32))
+    ws = G.zeros(lib.ngp_composite_workspace_bytes(n_rays) + 64, torch.uint8)
+    capi.check(lib.ngp_composite_train(G.stream(), C.byref(c), n_rays, max_compacted, G.p(ray_counter), G.p(G.dev(rgba)), G.p(d_ns), G.p(G.dev(coords)),
+                                       G.p(cc), G.p(counter), G.p(G.dev(net)), G.p(dloss), 4, G.p(d_mean), rng.state, rng.inc, G.p(loss), G.p(ws), None))
+    G.sync()
+    assert int(G.host(counter, np.uint32)[0]) == ref["counter"]
+    assert np.array_equal(G.host(d_ns, np.uint32).reshape(-1, 2), ref_ns)
+    assert np.allclose(G.host(loss), ref["loss"], rtol=2e-3, atol=1e-8), "the loss sees the environment map through the target and the ray colour"
+    n_comp = ref["counter"]
+    gd, rd = G.host(dloss, np.float16).reshape(-1, 4)[:n_comp].astype(np.float32), ref["dloss"][:n_comp].astype(np.float32)
+    assert (np.abs(gd - rd) <= 5e-2 * np.abs(rd) + 1e-4 * np.abs(rd).max()).mean() > 0.9995
+    ge, re_ = G.host(d_egrad, np.float16).astype(np.float32).reshape(ry, rx, 4), ref["envmap_grad"].reshape(ry, rx, 4)
+    assert np.abs(re_[..., :3]).max() > 0, "some rays must reach the background"
+    assert not ge[..., 3].any() and not re_[..., 3].any(), "alpha receives no gradient (ray_marcher.cu:208-209)"
+    assert np.array_equal(ge[..., :3] != 0, re_[..., :3] != 0) or np.count_nonzero((ge[..., :3] != 0) != (re_[..., :3] != 0)) <= 0.01 * np.count_nonzero(re_)
+    scale = np.abs(re_).max()
+    assert np.abs(ge - re_).max() <= 2e-2 * scale, np.abs(ge - re_).max() / scale
+    # without the gradient buffer nothing is deposited, with neither nothing changes against the plain call
+    c.envmap_gradient = None
+    capi.check(lib.ngp_composite_train(G.stream(), C.byref(c), n_rays, max_compacted, G.p(ray_counter), G.p(G.dev(rgba)), G.p(G.dev(numsteps)), G.p(G.dev(coords)),
+                                       G.p(cc), G.p(counter), G.p(G.dev(net)), G.p(dloss), 4, G.p(d_mean), rng.state, rng.inc, G.p(loss), G.p(ws), None))
+    c.rays = None
+    assert lib.ngp_composite_train(G.stream(), C.byref(c), n_rays, max_compacted, G.p(ray_counter), G.p(G.dev(rgba)), G.p(G.dev(numsteps)), G.p(G.dev(coords)),
+                                   G.p(cc), G.p(counter), G.p(G.dev(net)), G.p(dloss), 4, G.p(d_mean), rng.state, rng.inc, G.p(loss), G.p(ws), None) != 0
+    G.sync()
+
+
 def test_rollover_matches_oracle(capi, orc):
     import gpuutil as G
     lib = capi.load()

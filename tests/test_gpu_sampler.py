@@ -173,6 +173,43 @@ def test_generate_training_samples_matches_oracle(capi, orc, n_rays, n_coords, c
         assert cnt[1] > n_coords and kept < n_rays      # the budget really clipped rays
 
 
+def test_generate_training_samples_keeps_empty_rays_for_the_envmap(capi, orc):
+    """train_envmap (occupancy_sampler.cu:408): rays without a single sample keep a slot in the ray list (count 0), every other
+    ray keeps exactly the samples, the pixel and the order it has without the flag"""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    n_rays, n_coords, W, H, fx = 4096, 1 << 20, 64, 64, 70.0
+    xf, images, bits = _scene(orc)
+    rng = orc.Pcg32(43)
+    cam = _cam(capi, W, H, fx)
+    out = []
+    for keep in (0, 1):
+        cfg = capi.make_sampler_cfg(1)
+        cfg.keep_empty_rays = keep
+        rays, rgba = G.zeros(n_rays * 6, torch.float32), G.zeros(n_rays * 4, torch.float32)
+        numsteps, coords = G.zeros(n_rays * 2, torch.int32), G.zeros(n_coords * 7, torch.float32)
+        counters, per_ray = G.zeros(2, torch.int32), G.zeros(n_rays, torch.int32)
+        ws = G.zeros(lib.ngp_scan_workspace_bytes(n_rays) + 64, torch.uint8)
+        capi.check(lib.ngp_generate_training_samples(G.stream(), C.byref(cfg), C.byref(cam), n_rays, 17, n_coords, 4, G.p(G.dev(xf)), G.p(G.dev(images)),
+                                                     G.p(G.dev(bits)), 1, rng.state, rng.inc, G.p(rays), G.p(rgba), G.p(numsteps), G.p(coords), G.p(counters),
+                                                     G.p(per_ray), G.p(ws)))
+        G.sync()
+        cnt = G.host(counters, np.uint32)
+        kept = int(cnt[0])
+        out.append(dict(kept=kept, total=int(cnt[1]), per_ray=G.host(per_ray, np.uint32).copy(), ns=G.host(numsteps, np.uint32).reshape(-1, 2)[:kept].copy(),
+                        rays=G.host(rays).reshape(-1, 6)[:kept].copy(), rgba=G.host(rgba).reshape(-1, 4)[:kept].copy(), coords=G.host(coords).reshape(-1, 7)[:int(cnt[1])].copy()))
+    a, b = out
+    assert np.array_equal(a["per_ray"], b["per_ray"]) and a["total"] == b["total"]
+    assert (a["per_ray"] == 0).any(), "the test scene must have rays that miss everything"
+    assert b["kept"] == n_rays and a["kept"] == int((a["per_ray"] > 0).sum())
+    assert np.array_equal(b["ns"][:, 0], b["per_ray"]), "with the flag the ray list is the launch order, empty rays included"
+    full = b["ns"][:, 0] > 0
+    assert np.array_equal(b["ns"][full], a["ns"]) and np.array_equal(b["rays"][full], a["rays"]) and np.array_equal(b["rgba"][full], a["rgba"])
+    assert np.array_equal(a["coords"], b["coords"])
+    assert np.all(np.abs(np.linalg.norm(b["rays"][~full][:, 3:], axis=1) - 1) < 1e-5), "empty rays still carry their direction"
+
+
 @pytest.mark.parametrize("spp,n_steps", [(0, 1), (3, 8)])
 def test_inference_rays_and_coords_match_oracle(capi, orc, spp, n_steps):
     import gpuutil as G

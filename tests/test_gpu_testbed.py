@@ -182,6 +182,32 @@ def test_snapshot_round_trip_renders_identically(pyngp, tmp_path):
         pyngp.Testbed().load_snapshot(os.path.join(tmp_path, "missing.msgpack"))
 
 
+def test_trainable_environment_map(pyngp, tmp_path):
+    """envmap.train (testbed.cu:82-90, 235-239, 295-298): the map starts at zero, collects gradients over the steps of a train()
+    call, steps its own optimizer once per call, and render() starts every pixel from it"""
+    cfg = _config(str(tmp_path), **{"envmap.train": True, "envmap.height": 64, "envmap.width": 32, "render.train_with_random_bg_color": False})
+    tb = pyngp.Testbed()
+    tb.load_model_config(cfg)
+    assert not np.array(tb.envmap_image()).any()
+    tb.background_color = [0.3, 0.6, 0.2, 1.0]
+    tb.load_procedural_training_data(12, 160, 160, 2024, 0.33, [0.5, 0.5, 0.5])
+    losses = []
+    for _ in range(8):
+        tb.train(16, 1 << 16)
+        losses.append(tb.training_buffer.loss)
+    assert np.all(np.isfinite(losses)) and np.mean(losses[-3:]) < 0.5 * losses[0], losses
+    env = np.array(tb.envmap_image())
+    assert env.shape == (32, 64, 4) and np.isfinite(env).all()
+    assert np.count_nonzero(env[..., :3]) > 100, "rays that reach the background train the map"
+    assert not env[..., 3].any(), "alpha receives no gradient (ray_marcher.cu:208-209)"
+    tb.set_camera_to_training_view(1)
+    img = np.array(tb.render(96, 96, 1, True))
+    assert np.isfinite(img).all()
+    # the plain configuration is untouched by the feature: its map reads zero and its training is the one of the other tests
+    tb0, l0 = _trained(pyngp, calls=2)
+    assert not np.array(tb0.envmap_image()).any() and np.all(np.isfinite(l0))
+
+
 def test_large_table_cascaded_configuration_trains(pyngp, tmp_path):
     """BASELINE configs[4]: log2_hashmap_size 22 (150 MB fp16 table, spills L2), aabb_scale 16 (5 cascades), 2^20-sample batches"""
     cfg = _config(str(tmp_path), **{"samlper.aabb_scale": 16, "network.encoding.log2_hashmap_size": 22})
