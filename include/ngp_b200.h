@@ -90,6 +90,10 @@ int ngp_l2_probe(void* stream, int kind, void* d_table, uint64_t table_bytes, ui
 /* ---- hash grid -------------------------------------------------------------------------------- */
 /* replaces GridEncodingTemplated ctor (grid.h:475-537); returns the number of table entries */
 uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, uint32_t log2_hashmap_size, uint32_t base_resolution, float per_level_scale);
+/* replaces desc->scales / resolutions by what the reference's kernels evaluate per thread ON THE DEVICE (grid.h:157-158: exp2f ->
+ * MUFU.EX2, one FFMA): an ulp away from the host value on some levels.  Offsets are untouched (the reference sizes the levels on
+ * the host, grid.h:497-510).  Allocates 64 bytes, launches one tiny kernel on the default stream and synchronises: call once. */
+int ngp_grid_desc_device_scales(ngp_grid_desc* desc, uint32_t base_resolution, float per_level_scale);
 /* replaces NGPNetwork::auto_determine_grid_parameters (internal/network/ngp_network.h:597-641) */
 float ngp_auto_per_level_scale(float desired_resolution, uint32_t base_resolution, uint32_t n_levels);
 

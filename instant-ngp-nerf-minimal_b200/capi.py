@@ -59,6 +59,7 @@ SIGNATURES = {
     "ngp_l2_probe": (i32, [vp, i32, vp, u64, u32, vp]),
     "ngp_grid_desc_init": (u32, [C.POINTER(GridDesc), u32, u32, u32, f32]),
     "ngp_auto_per_level_scale": (f32, [f32, u32, u32]),
+    "ngp_grid_desc_device_scales": (i32, [C.POINTER(GridDesc), u32, f32]),
     "ngp_hash_encode_fwd": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, u32, vp]),
     "ngp_hash_encode_bwd": (i32, [vp, vp, u32, u32, vp, u32, C.POINTER(GridDesc), vp, i32]),
     "ngp_hash_encode_bwd_levels": (i32, [vp, vp, u32, u32, vp, u32, C.POINTER(GridDesc), vp, u32, u32]),
@@ -133,7 +134,9 @@ def ptr(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
-def make_grid_desc(n_levels=16, log2_hashmap_size=19, base_resolution=16, per_level_scale=None, desired_resolution=2048.0):
+def make_grid_desc(n_levels=16, log2_hashmap_size=19, base_resolution=16, per_level_scale=None, desired_resolution=2048.0, device_scales=False):
+    """device_scales: per-level scales as the reference's kernels evaluate them on the GPU (needs a device); the default host
+    values are what the CPU oracle uses"""
     lib = load()
     if per_level_scale is None:
         per_level_scale = lib.ngp_auto_per_level_scale(desired_resolution, base_resolution, n_levels)
@@ -141,6 +144,8 @@ def make_grid_desc(n_levels=16, log2_hashmap_size=19, base_resolution=16, per_le
     n_entries = lib.ngp_grid_desc_init(C.byref(d), n_levels, log2_hashmap_size, base_resolution, per_level_scale)
     if n_entries == 0:
         raise NgpError(lib.ngp_last_error().decode())
+    if device_scales:
+        check(lib.ngp_grid_desc_device_scales(C.byref(d), base_resolution, per_level_scale))
     return d, n_entries
 
 

@@ -388,6 +388,16 @@ int hash_input_gradient(cudaStream_t stream, float* d_coords, uint32_t n, const 
 	return check_launch("hash_input_gradient");
 }
 
+// The reference's kernels do not read a scale table: every thread evaluates scale = exp2f(level * log2_per_level_scale) *
+// base_resolution - 1 ON THE DEVICE (grid.h:157, :293), i.e. MUFU.EX2 and one contracted FFMA, and derives the resolution from it.
+// glibc's exp2f gives a float that differs by an ulp on some levels (2, 5, 6, 8, 10 of base.json), which moves 0.3-5 % of the
+// encodings of those levels by one fp16 ulp -- found by running the reference's own GridEncoding beside ours (scripts/c1_bench.py).
+// This kernel evaluates the same expression once per level; ngp_grid_desc_device_scales stores the results in the descriptor.
+__global__ void grid_scales_kernel(uint32_t n_levels, float log2_per_level_scale, uint32_t base_resolution, float* __restrict__ scales) {
+	const uint32_t level = threadIdx.x;
+	if (level < n_levels) scales[level] = __fmaf_rn(exp2f((float)level * log2_per_level_scale), (float)base_resolution, -1.0f);
+}
+
 // zeroes the gradient table as a link of the step's launch chain (a cudaMemsetAsync in the middle of the chain costs two full
 // launch boundaries); also leaves the table in L2 for the reductions that follow
 __global__ void __launch_bounds__(256) zero_fill_kernel(uint4* __restrict__ p, uint64_t n16, uint8_t* __restrict__ tail, uint32_t n_tail) {
@@ -432,6 +442,22 @@ extern "C" uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, u
 	}
 	desc->offsets[n_levels] = offset;
 	return offset;
+}
+
+extern "C" int ngp_grid_desc_device_scales(ngp_grid_desc* desc, uint32_t base_resolution, float per_level_scale) {
+	NGP_REQUIRE(desc && desc->n_levels >= 1 && desc->n_levels <= NGP_MAX_LEVELS, "bad descriptor");
+	float* d = nullptr;
+	if (cudaMalloc(&d, sizeof(float) * NGP_MAX_LEVELS) != cudaSuccess) { set_error("ngp_grid_desc_device_scales: cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
+	grid_scales_kernel<<<1, NGP_MAX_LEVELS>>>(desc->n_levels, std::log2(per_level_scale), base_resolution, d);
+	float h[NGP_MAX_LEVELS];
+	const cudaError_t e = cudaMemcpy(h, d, sizeof(float) * NGP_MAX_LEVELS, cudaMemcpyDeviceToHost);
+	cudaFree(d);
+	if (e != cudaSuccess) { set_error("ngp_grid_desc_device_scales: %s", cudaGetErrorString(e)); return -2; }
+	for (uint32_t l = 0; l < desc->n_levels; ++l) {
+		desc->scales[l] = h[l];
+		desc->resolutions[l] = (uint32_t)ceilf(h[l]) + 1;      // grid.h:158, from the device value; the offsets keep the host value (grid.h:497-510)
+	}
+	return 0;
 }
 
 extern "C" int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_table,

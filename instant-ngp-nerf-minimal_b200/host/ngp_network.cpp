@@ -25,6 +25,8 @@ NGPNetwork::NGPNetwork(Json& config) {
 	if (lower(enc.value("interpolation", "Linear")) != "linear") throw std::runtime_error("NGPNetwork: only linear grid interpolation is implemented");
 	m_n_grid_entries = ngp_grid_desc_init(&m_grid, n_levels, log2_hashmap_size, base_resolution, per_level_scale);
 	if (!m_n_grid_entries) throw std::runtime_error(ngp_last_error());
+	// the per-level scales the reference's kernels evaluate on the device (grid.h:157), not glibc's: an ulp apart on some levels
+	api_check(ngp_grid_desc_device_scales(&m_grid, base_resolution, per_level_scale));
 
 	auto check_mlp = [](const Json& c, int hidden, const char* name) {
 		if (lower(c.value("otype", "FullyFusedMLP")) != "fullyfusedmlp" || c.value("n_neurons", 64) != 64 || c.value("n_hidden_layers", hidden) != hidden ||

@@ -6,8 +6,11 @@
 //   ref_harness dump  <dir> [batch] [n_rays]   reads <dir>/{config.json,meta.txt,xforms.f32,images.f16}, writes <dir>/ref_*.bin
 //   ref_harness bench <dir> <calls> <warmup>   train(16, batch) loop as experiment/run.py:71 drives it; one JSON line
 //   ref_harness trainrender <dir> <calls> <W> <H> <spp> <fov>   train, then render <dir>/test_xforms.f32 -> ref_render_<i>.f32
+//   ref_harness c1 <dir> <iters> [log2_T]      BASELINE configs[0]: the reference's own GridEncoding (tcnn::create_encoding) on <dir>/c1_xyz.f32
+//                                              ([N][3]), c1_table.f16, c1_dy.f16 ([N][32]): times encode / backward, writes ref_c1_enc.f16, ref_c1_grad.f16
 #include "internal/testbed.h"
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <fstream>
@@ -250,9 +253,49 @@ static int run_trainrender(const std::string& dir, uint32_t calls, int W, int H,
 	return 0;
 }
 
+// BASELINE configs[0]: the reference's GridEncoding alone, exactly as NGPNetwork builds it (ngp_network.h:162, 620-632)
+static int run_c1(const std::string& dir, uint32_t iters, uint32_t log2_T) {
+	using T = precision_t;
+	auto xyz = read_file<float>(dir + "/c1_xyz.f32");
+	auto table = read_file<uint16_t>(dir + "/c1_table.f16");
+	auto dy = read_file<uint16_t>(dir + "/c1_dy.f16");
+	const uint32_t n = (uint32_t)(xyz.size() / 3);
+	const uint32_t n_levels = 16, base = 16;
+	nlohmann::json cfg = {{"otype", "HashGrid"}, {"n_levels", n_levels}, {"n_features_per_level", 2}, {"log2_hashmap_size", log2_T}, {"base_resolution", base}};
+	cfg["per_level_scale"] = std::exp(std::log(2048.0f / (float)base) / (n_levels - 1));
+	std::unique_ptr<tcnn::Encoding<T>> enc(tcnn::create_encoding<T>(3, cfg, 16));
+	const size_t P = enc->n_params();
+	if (P != table.size() || dy.size() != (size_t)n * 32) throw std::runtime_error("c1: table / dy size mismatch");
+	tcnn::GPUMemory<float> d_xyz(xyz.size()), d_full(P);
+	tcnn::GPUMemory<T> d_params(P), d_grads(P), d_out((size_t)n * 32), d_dy((size_t)n * 32);
+	tcnn::pcg32 rnd(1337);
+	enc->initialize_params(rnd, d_full.data(), d_params.data(), d_params.data(), d_params.data(), d_grads.data());
+	CUDA_CHECK_THROW(cudaMemcpy(d_params.data(), table.data(), P * sizeof(T), cudaMemcpyHostToDevice));
+	CUDA_CHECK_THROW(cudaMemcpy(d_xyz.data(), xyz.data(), xyz.size() * sizeof(float), cudaMemcpyHostToDevice));
+	CUDA_CHECK_THROW(cudaMemcpy(d_dy.data(), dy.data(), dy.size() * sizeof(T), cudaMemcpyHostToDevice));
+	cudaStream_t stream; CUDA_CHECK_THROW(cudaStreamCreate(&stream));
+	cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+	auto fwd = [&]() { enc->encode(stream, n, {d_xyz.data(), 3}, {d_out.data(), 32}, nullptr, false); };
+	auto bwd = [&]() { enc->backward(stream, n, {d_dy.data(), 32}, nullptr, {}, {d_xyz.data(), 3}, false); };
+	auto timed = [&](auto&& fn) {
+		for (int i = 0; i < 10; ++i) fn();
+		std::vector<float> ms(iters);
+		for (uint32_t i = 0; i < iters; ++i) { cudaEventRecord(a, stream); fn(); cudaEventRecord(b, stream); cudaEventSynchronize(b); cudaEventElapsedTime(&ms[i], a, b); }
+		std::sort(ms.begin(), ms.end());
+		return ms[iters / 2] * 1e3f;
+	};
+	const float fwd_us = timed(fwd), bwd_us = timed(bwd);
+	CUDA_CHECK_THROW(cudaStreamSynchronize(stream));
+	write_device(dir + "/ref_c1_enc.f16", d_out.data(), (size_t)n * 32 * sizeof(T));
+	write_device(dir + "/ref_c1_grad.f16", d_grads.data(), P * sizeof(T));
+	printf("{\"impl\": \"reference-cuda-sm100 GridEncoding\", \"n_points\": %u, \"n_params\": %zu, \"iterations\": %u, \"fwd_us\": %.3f, \"bwd_us\": %.3f}\n", n, P, iters, fwd_us, bwd_us);
+	return 0;
+}
+
 int main(int argc, char** argv) {
 	try {
 		if (argc >= 3 && std::string(argv[1]) == "dump") return run_dump(argv[2], argc > 3 ? (uint32_t)atoi(argv[3]) : (1u << 18), argc > 4 ? (uint32_t)atoi(argv[4]) : 0u);
+		if (argc >= 4 && std::string(argv[1]) == "c1") return run_c1(argv[2], (uint32_t)atoi(argv[3]), argc > 4 ? (uint32_t)atoi(argv[4]) : 19u);
 		if (argc >= 5 && std::string(argv[1]) == "bench") return run_bench(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argc > 5 ? (uint32_t)atoi(argv[5]) : (1u << 18));
 		if (argc >= 8 && std::string(argv[1]) == "trainrender")
 			return run_trainrender(argv[2], (uint32_t)atoi(argv[3]), atoi(argv[4]), atoi(argv[5]), atoi(argv[6]), (float)atof(argv[7]), argc > 8 ? (uint32_t)atoi(argv[8]) : (1u << 18));

@@ -29,7 +29,9 @@ N, ITERS, WARM = 1 << 18, 100, 10
 def main():
     out = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "c1_bench.json")
     L = oracle.GridLevels(16, 19, 16)
-    desc, n_entries = capi.make_grid_desc()
+    desc, n_entries = capi.make_grid_desc(device_scales=True)          # the scales the reference's kernels evaluate (grid.h:157)
+    L.scales[:] = np.frombuffer(bytes(desc.scales), np.float32)[:16]    # the oracle restates the same arithmetic with the same inputs
+    L.resolutions[:] = np.frombuffer(bytes(desc.resolutions), np.uint32)[:16]
     xyz = rng_uniform((N, 3), 1337)
     table = rng_uniform(L.n_params, 43, -1e-4, 1e-4).astype(np.float16)
     dy = (rng_uniform((N, 32), 7, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
@@ -78,6 +80,36 @@ def main():
     t_f = best_of(lambda: oracle.hash_encode_fwd(xyz, 3, N, table.view(np.uint16), L))
     t_b = best_of(lambda: oracle.hash_encode_bwd(xyz, 3, N, dy, L))
     res["cpu_oracle"] = {"cores": os.cpu_count(), "fwd_ms": t_f * 1e3, "bwd_ms": t_b * 1e3, "kind": "port"}
+    # ---- the reference's own GridEncoding on the same three files (oracle/_ref/ref_harness c1), outputs compared, times beside ours ----
+    harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+    if os.path.exists(harness):
+        import subprocess, tempfile
+        with tempfile.TemporaryDirectory() as d:
+            xyz.tofile(os.path.join(d, "c1_xyz.f32")); table.view(np.uint16).tofile(os.path.join(d, "c1_table.f16")); dy.view(np.uint16).tofile(os.path.join(d, "c1_dy.f16"))
+            r = subprocess.run([harness, "c1", d, str(ITERS)], capture_output=True, text=True, timeout=600)
+            line = [l for l in r.stdout.splitlines() if l.startswith("{")]
+            if r.returncode == 0 and line:
+                ref_t = json.loads(line[-1])
+                ref_enc = np.fromfile(os.path.join(d, "ref_c1_enc.f16"), np.float16).reshape(N, 32)
+                ref_grad = np.fromfile(os.path.join(d, "ref_c1_grad.f16"), np.float16).astype(np.float32)
+                bwd()
+                torch.cuda.synchronize()
+                our_grad = d_grad.cpu().numpy().view(np.float16).astype(np.float32)
+                ulp = np.abs(got.view(np.int16).astype(np.int32) - ref_enc.view(np.int16).astype(np.int32))
+                gscale = np.abs(ref_grad).max()
+                gf, rf = got.astype(np.float32), ref_enc.astype(np.float32)
+                bad = np.argwhere(ulp > 0)
+                examples = [dict(point=int(i), feature=int(f), ours=float(gf[i, f]), reference=float(rf[i, f]), oracle=float(np.asarray(ref).view(np.float16).reshape(N, 32)[i, f]))
+                            for i, f in bad[:6]]
+                per_level_mismatch = [float((ulp[:, 2 * l:2 * l + 2] > 0).mean()) for l in range(16)]
+                res["reference_grid_encoding"] = dict(ref_t, fwd_speedup=ref_t["fwd_us"] / res["fwd"]["us_table_in_L2"], bwd_speedup=ref_t["bwd_us"] / res["bwd"]["us_table_in_L2"],
+                                                      encodings_max_fp16_ulp_vs_reference=int(ulp.max()), encodings_bit_identical_fraction=float((ulp == 0).mean()),
+                                                      encodings_max_abs_diff_over_max=float(np.abs(gf - rf).max() / np.abs(rf).max()), mismatch_examples=examples,
+                                                      mismatch_fraction_per_level=per_level_mismatch,
+                                                      grad_max_abs_diff_over_max=float(np.abs(our_grad - ref_grad).max() / gscale),
+                                                      grad_same_nonzero_pattern=bool(np.array_equal(our_grad != 0, ref_grad != 0)))
+            else:
+                res["reference_grid_encoding"] = {"unavailable": (r.stderr or r.stdout)[-300:]}
     scratch = torch.zeros(32 << 20, dtype=torch.uint8, device="cuda")
     probes = {}
     for kind, key in ((0, "l2_stream_read_GBs"), (2, "scattered_gather_16B_G_per_s"), (4, "scattered_red_v4_f16x2_G_per_s")):
