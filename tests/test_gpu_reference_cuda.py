@@ -307,3 +307,44 @@ def test_optimizer_step_matches_reference(capi, ref):
     assert np.allclose(got, want, rtol=1e-5, atol=1e-7), np.abs(got - want).max()
     a, b = G.host(w16, np.float16).astype(np.float32), ref.arr("params1_f16", np.float16).astype(np.float32)
     assert (a == b).mean() > 0.999 and np.abs(a - b).max() <= 1e-3 * np.abs(b).max()
+
+
+@pytest.mark.parametrize("amp,n", [(1e-4, 1 << 18), (1.0, 1 << 16)])
+def test_grid_encoding_against_the_references_own_grid_encoding(capi, orc, amp, n, tmp_path):
+    """BASELINE configs[0]: tcnn::create_encoding + encode / backward (ref_harness c1) on the same points, table and dL/dy.
+    Forward: bit-identical, all values -- this needs the per-level scales the reference's kernels evaluate on the device
+    (grid.h:157; ngp_grid_desc_device_scales), glibc's exp2f is an ulp off on five levels.  Backward: fp16 atomics are
+    order-dependent in both implementations, so the sums agree within the rounding of the atomic adds."""
+    import subprocess
+    import gpuutil as G
+    import torch
+    from util import rng_uniform
+    if not refcuda.available():
+        pytest.skip("oracle/_ref/ref_harness is not built")
+    lib = capi.load()
+    L = orc.GridLevels(16, 19, 16)
+    xyz = rng_uniform((n, 3), 1337)
+    table = rng_uniform(L.n_params, 43, -amp, amp).astype(np.float16)
+    dy = (rng_uniform((n, 32), 7, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
+    d = str(tmp_path)
+    xyz.tofile(d + "/c1_xyz.f32"); table.view(np.uint16).tofile(d + "/c1_table.f16"); dy.view(np.uint16).tofile(d + "/c1_dy.f16")
+    r = subprocess.run([refcuda.HARNESS, "c1", d, "3"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-500:]
+    ref_enc = np.fromfile(d + "/ref_c1_enc.f16", np.uint16).reshape(n, 32)
+    ref_grad = np.fromfile(d + "/ref_c1_grad.f16", np.float16).astype(np.float32)
+    desc, _ = capi.make_grid_desc(device_scales=True)
+    host_desc, _ = capi.make_grid_desc()
+    assert list(desc.offsets) == list(host_desc.offsets) and list(desc.resolutions) == list(host_desc.resolutions)
+    assert any(a != b for a, b in zip(list(desc.scales)[:16], list(host_desc.scales)[:16])), "the device evaluation differs from glibc on some levels"
+    dx, dt, ddy = G.dev(xyz), G.dev(table.view(np.uint16)), G.dev(dy.view(np.uint16))
+    out, grad = G.zeros(n * 32, torch.int16), G.zeros(L.n_params, torch.int16)
+    capi.check(lib.ngp_hash_encode_fwd(G.stream(), G.p(dx), 3, n, G.p(dt), C.byref(desc), G.p(out), 32, None))
+    capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(dx), 3, n, G.p(ddy), 32, C.byref(desc), G.p(grad), 1))
+    G.sync()
+    assert np.array_equal(G.host(out, np.uint16).reshape(n, 32), ref_enc), "forward encodings must be bit-identical to the reference's GridEncoding"
+    got = G.host(grad, np.float16).astype(np.float32)
+    scale = np.abs(ref_grad).max()
+    assert scale > 0 and np.abs(got - ref_grad).max() <= 2e-2 * scale
+    fine = int(L.offsets[8]) * 2                     # hashed levels: few addends per entry, the sums agree to fp16 rounding
+    nz = ref_grad[fine:] != 0
+    assert np.median(np.abs(got[fine:][nz] - ref_grad[fine:][nz]) / np.abs(ref_grad[fine:][nz])) < 2e-3
