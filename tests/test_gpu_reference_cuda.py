@@ -96,7 +96,7 @@ def test_density_network_matches_reference(capi, ref):
     import gpuutil as G
     import torch
     lib = capi.load()
-    d, _ = capi.make_grid_desc()
+    d, _ = capi.make_grid_desc(device_scales=True)
     n = ref.meta["n_total_elements"]
     params = ref.arr("params0_f32", np.float32).astype(np.float16)
     want = ref.arr("grid_density_f16", np.float16, (n, 16)).astype(np.float32)
@@ -191,7 +191,7 @@ def test_network_inference_matches_reference(capi, ref):
     import gpuutil as G
     import torch
     lib = capi.load()
-    d, _ = capi.make_grid_desc()
+    d, _ = capi.make_grid_desc(device_scales=True)
     n = ref.meta["n_marched"]
     params = ref.arr("params0_f32", np.float32).astype(np.float16)
     ws_bytes = lib.ngp_network_workspace_bytes(n)
@@ -258,7 +258,7 @@ def test_network_forward_backward_matches_reference(capi, ref):
     import gpuutil as G
     import torch
     lib = capi.load()
-    d, _ = capi.make_grid_desc()
+    d, _ = capi.make_grid_desc(device_scales=True)
     params = ref.arr("params0_f32", np.float32).astype(np.float16)
     n_params = params.size
     ws_bytes = lib.ngp_network_workspace_bytes(BATCH)
