@@ -391,7 +391,7 @@ int hash_input_gradient(cudaStream_t stream, float* d_coords, uint32_t n, const 
 // The reference's kernels do not read a scale table: every thread evaluates scale = exp2f(level * log2_per_level_scale) *
 // base_resolution - 1 ON THE DEVICE (grid.h:157, :293), i.e. MUFU.EX2 and one contracted FFMA, and derives the resolution from it.
 // glibc's exp2f gives a float that differs by an ulp on some levels (2, 5, 6, 8, 10 of base.json), which moves 0.3-5 % of the
-// encodings of those levels by one fp16 ulp -- found by running the reference's own GridEncoding beside ours (scripts/c1_bench.py).
+// encodings of those levels by one fp16 ulp -- found by running the reference's own GridEncoding beside ours (tests/c1_bench.py).
 // This kernel evaluates the same expression once per level; ngp_grid_desc_device_scales stores the results in the descriptor.
 __global__ void grid_scales_kernel(uint32_t n_levels, float log2_per_level_scale, uint32_t base_resolution, float* __restrict__ scales) {
 	const uint32_t level = threadIdx.x;

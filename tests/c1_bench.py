@@ -3,7 +3,7 @@
 timed with CUDA events on the launching stream, next to the CPU oracle on the host cores and to the measured ceilings of the
 L1TEX / L2 path (ngp_l2_probe).  Random points are the worst case for the encoder: no two lanes of a warp share a cell above
 the coarsest levels, so nothing coalesces and the backward merge finds no runs.
-usage: python scripts/c1_bench.py [out.json]"""
+usage: python tests/c1_bench.py [out.json]"""
 import ctypes as C
 import importlib
 import json

@@ -3,7 +3,7 @@
 reference compiled for sm_100 by oracle/build_ref.sh) for one occupancy refresh + one training step on a tiny procedural
 dataset.  Run on a GPU box:
 
-    gpurun -- 'python scripts/make_golden_from_ref.py gpurun_out/golden'      then copy the .npz into tests/golden/
+    gpurun -- 'python tests/make_golden_from_ref.py gpurun_out/golden'      then copy the .npz into tests/golden/
 
 The CPU (-m "not gpu") tests check the oracle against these vectors, which pins the oracle to the reference itself."""
 import importlib

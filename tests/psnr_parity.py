@@ -3,7 +3,7 @@
 steps with (a) our sm_100a path through pyngp and (b) the reference's own CUDA build (oracle/_ref/ref_harness), render the same
 held-out poses with both, and compare each against the analytic ground truth.  Also reports both render rates.
 
-    python scripts/psnr_parity.py [steps=5008] [views=100] [res=800] [n_test=8] [out.json]"""
+    python tests/psnr_parity.py [steps=5008] [views=100] [res=800] [n_test=8] [out.json]"""
 import ctypes as C
 import importlib
 import json

@@ -1,6 +1,6 @@
 """CPU: the oracle against golden vectors produced by the REFERENCE'S OWN CUDA build.
 
-tests/golden/ref_cuda_step.npz was written by scripts/make_golden_from_ref.py on a B200 from oracle/_ref/ref_harness (the
+tests/golden/ref_cuda_step.npz was written by tests/make_golden_from_ref.py on a B200 from oracle/_ref/ref_harness (the
 unmodified reference compiled for sm_100): one occupancy refresh and one training step on 4 procedural 64x64 views, 256
 rays, parameters from refcuda.start_params.  This pins the oracle -- and with it every GPU parity test that uses the oracle as
 its checker -- to the reference itself.  Bars: integer / index / coordinate outcomes bit-exact; network outputs and loss
