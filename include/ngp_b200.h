@@ -64,6 +64,9 @@ typedef struct ngp_render_cfg {
 	const float* rays;               /* device, 6 floats per kept ray {o, d}: the directions the envmap is looked up with */
 	int32_t  envmap_res_x, envmap_res_y;
 	int32_t  envmap_loss_type;       /* ELossType of the envmap's own loss (base.json: RelativeL2) */
+	/* scale of the density L1 regulariser (ray_marcher.cu:153,182), which the reference adds OUTSIDE the loss scale: data-parallel
+	 * ranks pass 1 / world so that the summed gradient carries it once, like the loss terms.  0 is read as 1. */
+	float    reg_scale;
 } ngp_render_cfg;
 
 /* Optimizer chain Ema(ExponentialDecay(Adam)) (tiny-cuda-nn/optimizers/{adam,ema,exponential_decay}.h). */

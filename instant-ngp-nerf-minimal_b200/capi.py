@@ -33,7 +33,7 @@ class RenderCfg(C.Structure):
     _fields_ = [("n_cascades", u32), ("min_step", f32), ("rgb_activation", i32), ("density_activation", i32), ("loss_type", i32),
                 ("color_space", i32), ("train_with_random_bg_color", i32), ("train_in_linear_color", i32),
                 ("transmittance_threshold", f32), ("min_optical_thickness", f32), ("loss_scale", f32), ("background_color", f32 * 3),
-                ("envmap", vp), ("envmap_gradient", vp), ("rays", vp), ("envmap_res_x", i32), ("envmap_res_y", i32), ("envmap_loss_type", i32)]
+                ("envmap", vp), ("envmap_gradient", vp), ("rays", vp), ("envmap_res_x", i32), ("envmap_res_y", i32), ("envmap_loss_type", i32), ("reg_scale", f32)]
 
 
 NGP_MAX_PEERS = 8

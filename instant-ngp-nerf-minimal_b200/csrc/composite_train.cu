@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(256) composite_grad_kernel(
 	if (loss_out && lane == 0) loss_out[i] = ((loss[0] + loss[1] + loss[2]) / 3.f) / (float)n_rays;
 	const float ls = c.loss_scale / (float)n_rays;
 	const float l2reg = c.rgb_activation == ACT_EXP ? 1e-4f : 0.f;
-	const float l1reg = *mean_density_ptr < c.min_optical_thickness ? 1e-4f : 0.f;
+	const float l1reg = *mean_density_ptr < c.min_optical_thickness ? 1e-4f * (c.reg_scale > 0.f ? c.reg_scale : 1.f) : 0.f;
 
 	const Coordinate* cs = coords_in + base;
 	const __half* no = net_out + (size_t)base * 4;

@@ -1,7 +1,7 @@
 // NeRFSynthetic loaders.  load_from_json follows internal/dataset/nerf_synthetic.cu:31-134 (transforms json, one image
 // per frame, spec_opengl_to_opencv on every pose, fov -> focal length, u8 sRGB -> linear premultiplied fp16 on the GPU).
-// stb_image is replaced by a small PNG reader on top of zlib (8-bit gray / gray+alpha / RGB / RGBA, non-interlaced) and a
-// raw ".rgba8" fallback.
+// stb_image is replaced by a PNG reader on top of zlib (every colour type and bit depth, Adam7, tRNS: decode_png below) and a raw
+// ".rgba8" fallback; JPEG (stb's other decoder the reference would fall back to) is not implemented.
 #include "dataset.h"
 #include "json.h"
 #include <zlib.h>
@@ -26,63 +26,123 @@ static std::string extension(const std::string& p) {
 
 static uint32_t be32(const uint8_t* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
 
-// decode to RGBA8; throws on anything but 8-bit non-interlaced colour types 0/2/4/6
-static std::vector<uint8_t> decode_png(const std::string& data, int& w, int& h) {
+// PNG -> RGBA8 with the conversions stb_image applies for req_comp = 4 (dependencies/stb_image/stb_image.h, stbi__parse_png_file /
+// stbi__create_png_image / stbi__convert_format): all colour types (gray, RGB, palette, gray+alpha, RGBA), bit depths 1-16, Adam7
+// interlacing, tRNS colour keys and palette alphas; 16-bit samples keep their high byte; sub-byte gray is scaled to 0..255;
+// gray -> (g, g, g, a), missing alpha -> 255.  Gamma / colour-profile chunks are ignored, as stb ignores them.
+static void png_unfilter(uint8_t* cur, const uint8_t* prev, int filter, size_t stride, size_t bpp) {
+	for (size_t x = 0; x < stride; ++x) {
+		const int a = x >= bpp ? cur[x - bpp] : 0, b = prev ? prev[x] : 0, c = (prev && x >= bpp) ? prev[x - bpp] : 0;
+		int v = cur[x];
+		switch (filter) {
+			case 0: break;
+			case 1: v += a; break;
+			case 2: v += b; break;
+			case 3: v += (a + b) >> 1; break;
+			case 4: { const int pa = abs(b - c), pb = abs(a - c), pc = abs(a + b - 2 * c); v += (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); break; }
+			default: throw std::runtime_error("PNG: bad filter type");
+		}
+		cur[x] = (uint8_t)v;
+	}
+}
+
+std::vector<uint8_t> decode_png(const std::string& data, int& w, int& h) {
 	static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
 	if (data.size() < 8 || memcmp(data.data(), sig, 8) != 0) throw std::runtime_error("not a PNG file");
 	const uint8_t* p = (const uint8_t*)data.data();
 	size_t pos = 8;
 	int depth = 0, ctype = 0, interlace = 0;
 	std::string idat;
+	uint8_t palette[256][4];
+	for (auto& e : palette) { e[0] = e[1] = e[2] = 0; e[3] = 255; }
+	bool has_key = false; uint16_t key[3] = {0, 0, 0};
+	bool seen_ihdr = false;
 	while (pos + 12 <= data.size()) {
 		const uint32_t len = be32(p + pos);
 		const std::string type(data, pos + 4, 4);
-		if (pos + 12 + len > data.size()) throw std::runtime_error("PNG: truncated chunk");
+		if (pos + 12 + (size_t)len > data.size()) throw std::runtime_error("PNG: truncated chunk");
 		const uint8_t* body = p + pos + 8;
-		if (type == "IHDR") { w = (int)be32(body); h = (int)be32(body + 4); depth = body[8]; ctype = body[9]; interlace = body[12]; }
-		else if (type == "IDAT") idat.append((const char*)body, len);
+		if (type == "IHDR") {
+			if (len < 13) throw std::runtime_error("PNG: bad IHDR");
+			w = (int)be32(body); h = (int)be32(body + 4); depth = body[8]; ctype = body[9]; interlace = body[12]; seen_ihdr = true;
+		} else if (type == "PLTE") {
+			for (uint32_t k = 0; k < len / 3 && k < 256; ++k) { palette[k][0] = body[3 * k]; palette[k][1] = body[3 * k + 1]; palette[k][2] = body[3 * k + 2]; }
+		} else if (type == "tRNS") {
+			if (ctype == 3) { for (uint32_t k = 0; k < len && k < 256; ++k) palette[k][3] = body[k]; }
+			else if (ctype == 0 && len >= 2) { has_key = true; key[0] = (uint16_t)((body[0] << 8) | body[1]); }
+			else if (ctype == 2 && len >= 6) { has_key = true; for (int k = 0; k < 3; ++k) key[k] = (uint16_t)((body[2 * k] << 8) | body[2 * k + 1]); }
+		} else if (type == "IDAT") idat.append((const char*)body, len);
 		else if (type == "IEND") break;
-		pos += 12 + len;
+		pos += 12 + (size_t)len;
 	}
-	if (depth != 8 || interlace != 0 || !(ctype == 0 || ctype == 2 || ctype == 4 || ctype == 6))
-		throw std::runtime_error("PNG: only 8-bit non-interlaced gray/RGB(A) images are supported");
-	const int ch = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 4 ? 2 : 4;
-	const size_t stride = (size_t)w * ch;
-	std::vector<uint8_t> raw((stride + 1) * h);
+	if (!seen_ihdr || w <= 0 || h <= 0) throw std::runtime_error("PNG: missing IHDR");
+	const bool depth_ok = depth == 8 || depth == 16 || ((ctype == 0 || ctype == 3) && (depth == 1 || depth == 2 || depth == 4));
+	if (!depth_ok || (ctype == 3 && depth == 16) || interlace > 1 || !(ctype == 0 || ctype == 2 || ctype == 3 || ctype == 4 || ctype == 6))
+		throw std::runtime_error("PNG: unsupported colour type / bit depth");
+	const int ch = ctype == 0 || ctype == 3 ? 1 : ctype == 2 ? 3 : ctype == 4 ? 2 : 4;
+	const size_t bits_pp = (size_t)ch * depth, bpp = std::max<size_t>(1, bits_pp / 8);
+	auto row_bytes = [&](int pw) { return ((size_t)pw * bits_pp + 7) / 8; };
+
+	// passes: one for a plain image, seven for Adam7
+	struct Pass { int x0, y0, dx, dy; };
+	static const Pass adam7[7] = {{0, 0, 8, 8}, {4, 0, 8, 8}, {0, 4, 4, 8}, {2, 0, 4, 4}, {0, 2, 2, 4}, {1, 0, 2, 2}, {0, 1, 1, 2}};
+	const Pass plain = {0, 0, 1, 1};
+	size_t raw_size = 0;
+	for (int k = 0; k < (interlace ? 7 : 1); ++k) {
+		const Pass& ps = interlace ? adam7[k] : plain;
+		const int pw = (w - ps.x0 + ps.dx - 1) / ps.dx, ph = (h - ps.y0 + ps.dy - 1) / ps.dy;
+		if (pw > 0 && ph > 0) raw_size += (row_bytes(pw) + 1) * ph;
+	}
+	std::vector<uint8_t> raw(raw_size);
 	uLongf out_len = (uLongf)raw.size();
 	if (uncompress(raw.data(), &out_len, (const Bytef*)idat.data(), (uLong)idat.size()) != Z_OK || out_len != raw.size())
 		throw std::runtime_error("PNG: inflate failed");
-	std::vector<uint8_t> img(stride * h);
-	for (int y = 0; y < h; ++y) {
-		const uint8_t* src = raw.data() + (stride + 1) * y;
-		const int filter = src[0]; ++src;
-		uint8_t* dst = img.data() + stride * y;
-		const uint8_t* up = y ? dst - stride : nullptr;
-		for (size_t x = 0; x < stride; ++x) {
-			const int a = x >= (size_t)ch ? dst[x - ch] : 0, b = up ? up[x] : 0, c = (up && x >= (size_t)ch) ? up[x - ch] : 0;
-			int v = src[x];
-			switch (filter) {
-				case 0: break;
-				case 1: v += a; break;
-				case 2: v += b; break;
-				case 3: v += (a + b) >> 1; break;
-				case 4: { const int pa = abs(b - c), pb = abs(a - c), pc = abs(a + b - 2 * c); v += (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); break; }
-				default: throw std::runtime_error("PNG: bad filter type");
-			}
-			dst[x] = (uint8_t)v;
-		}
-	}
+
+	// one sample of the unfiltered row as a 16-bit value (depth < 16: the raw sample)
+	auto sample = [&](const uint8_t* row, size_t px, int c) -> uint16_t {
+		if (depth == 8) return row[px * ch + c];
+		if (depth == 16) return (uint16_t)((row[(px * ch + c) * 2] << 8) | row[(px * ch + c) * 2 + 1]);
+		const size_t bit = px * depth;
+		return (uint16_t)((row[bit >> 3] >> (8 - depth - (bit & 7))) & ((1u << depth) - 1));
+	};
+	static const int depth_scale[9] = {0, 0xff, 0x55, 0, 0x11, 0, 0, 0, 0x01};
 	std::vector<uint8_t> rgba((size_t)w * h * 4);
-	for (size_t i = 0; i < (size_t)w * h; ++i) {
-		const uint8_t* s = img.data() + i * ch;
-		uint8_t* d = rgba.data() + i * 4;
-		if (ch == 1) { d[0] = d[1] = d[2] = s[0]; d[3] = 255; }
-		else if (ch == 2) { d[0] = d[1] = d[2] = s[0]; d[3] = s[1]; }
-		else if (ch == 3) { d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = 255; }
-		else { d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = s[3]; }
+	size_t off = 0;
+	for (int k = 0; k < (interlace ? 7 : 1); ++k) {
+		const Pass& ps = interlace ? adam7[k] : plain;
+		const int pw = (w - ps.x0 + ps.dx - 1) / ps.dx, ph = (h - ps.y0 + ps.dy - 1) / ps.dy;
+		if (pw <= 0 || ph <= 0) continue;
+		const size_t stride = row_bytes(pw);
+		const uint8_t* prev = nullptr;
+		for (int y = 0; y < ph; ++y) {
+			uint8_t* row = raw.data() + off;
+			const int filter = row[0]; ++row;
+			png_unfilter(row, prev, filter, stride, bpp);
+			prev = row;
+			off += stride + 1;
+			for (int x = 0; x < pw; ++x) {
+				uint8_t* d = rgba.data() + ((size_t)(ps.y0 + y * ps.dy) * w + (ps.x0 + x * ps.dx)) * 4;
+				auto to8 = [&](uint16_t v) -> uint8_t { return depth == 16 ? (uint8_t)(v >> 8) : depth == 8 ? (uint8_t)v : (uint8_t)(v * depth_scale[depth]); };
+				if (ctype == 3) { const uint8_t* e = palette[sample(row, x, 0) & 255]; d[0] = e[0]; d[1] = e[1]; d[2] = e[2]; d[3] = e[3]; }
+				else if (ctype == 0) {
+					const uint16_t g = sample(row, x, 0);
+					d[0] = d[1] = d[2] = to8(g);
+					// stb compares the colour key after scaling sub-byte gray to 8 bits, 16-bit samples in full
+					d[3] = has_key && (depth == 16 ? g == key[0] : to8(g) == (uint8_t)((key[0] & 255) * (depth < 8 ? depth_scale[depth] : 1))) ? 0 : 255;
+				} else if (ctype == 4) { d[0] = d[1] = d[2] = to8(sample(row, x, 0)); d[3] = to8(sample(row, x, 1)); }
+				else {
+					const uint16_t r = sample(row, x, 0), g = sample(row, x, 1), b = sample(row, x, 2);
+					d[0] = to8(r); d[1] = to8(g); d[2] = to8(b);
+					if (ctype == 6) d[3] = to8(sample(row, x, 3));
+					else d[3] = has_key && (depth == 16 ? (r == key[0] && g == key[1] && b == key[2]) : (d[0] == (key[0] & 255) && d[1] == (key[1] & 255) && d[2] == (key[2] & 255))) ? 0 : 255;
+				}
+			}
+		}
 	}
 	return rgba;
 }
+
+std::vector<uint8_t> decode_png_file(const std::string& path, int& w, int& h) { return decode_png(read_file(path), w, h); }
 
 void NeRFSynthetic::load_from_memory(uint32_t n, int width, int height, float camera_angle_x, const Mat34* xforms_ogl, const uint8_t* rgba8, float scale_, const float offset_[3]) {
 	n_images = n; image_resolution[0] = width; image_resolution[1] = height;

@@ -25,6 +25,10 @@ struct NeRFSynthetic {
 	DeviceBuffer<precision_t> images;        // [n][H][W][4] fp16
 };
 
+// PNG bytes / file -> RGBA8 [h][w][4], converted as stb_image's stbi_load(..., 4) converts (nerf_synthetic.cu:82)
+std::vector<uint8_t> decode_png(const std::string& data, int& w, int& h);
+std::vector<uint8_t> decode_png_file(const std::string& path, int& w, int& h);
+
 // camera-to-world (OpenGL convention, as transforms_*.json stores it) of a camera on a sphere looking at the origin
 Mat34 look_at_origin_opengl(float radius, float theta, float phi);
 

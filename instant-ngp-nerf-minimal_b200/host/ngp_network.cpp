@@ -166,70 +166,92 @@ void Trainer::optimizer_step_sharded(cudaStream_t stream, float loss_scale, cons
 	++m_step;
 }
 
-// trainer.h:294-317 + optimizer serialisers (adam.h:255-277, ema.h:174-187, exponential_decay.h:118-131)
+// trainer.h:294-317 + the optimizer serialisers, key for key: Ema {nested, weights_ema_binary} (ema.h:174-185), ExponentialDecay
+// {nested, learning_rate, learning_rate_factor} (exponential_decay.h:118-129), Adam {current_step, base_learning_rate,
+// first_moments_binary, second_moments_binary, param_steps_binary} (adam.h:255-277).  A file written here loads in the reference
+// and the reverse.  The reference drops the fp32 master and the fp16 training weights (after a load it resumes from the widened
+// EMA weights); they are added under two keys the reference never looks up, so a snapshot written AND read here resumes exactly.
 Json Trainer::serialize(bool serialize_optimizer) {
 	Json data = Json::object();
 	data["n_params"] = Json((uint64_t)m_n);
 	std::vector<precision_t> h(m_n);
-	(m_opt.has_ema ? m_ema : m_params).copy_to_host(h.data(), m_n);
+	(m_opt.has_ema ? m_ema : m_params).copy_to_host(h.data(), m_n);            // m_params_inference (trainer.h:299)
 	data["params_binary"] = Json::binary(h.data(), m_n * sizeof(precision_t));
 	if (serialize_optimizer) {
-		Json adam = Json::object();
-		adam["otype"] = Json("Adam");
-		adam["current_step"] = Json(m_step);
-		adam["base_learning_rate"] = Json(m_opt.learning_rate);
+		Json node = Json::object();                                             // Adam
+		node["current_step"] = Json(m_step);
+		node["base_learning_rate"] = Json(m_opt.learning_rate);
 		std::vector<float> f(m_n);
-		m_m1.copy_to_host(f.data(), m_n); adam["first_moments_binary"] = Json::binary(f.data(), m_n * 4);
-		m_m2.copy_to_host(f.data(), m_n); adam["second_moments_binary"] = Json::binary(f.data(), m_n * 4);
+		m_m1.copy_to_host(f.data(), m_n); node["first_moments_binary"] = Json::binary(f.data(), m_n * 4);
+		m_m2.copy_to_host(f.data(), m_n); node["second_moments_binary"] = Json::binary(f.data(), m_n * 4);
 		std::vector<uint32_t> u(m_n);
-		m_param_steps.copy_to_host(u.data(), m_n); adam["param_steps_binary"] = Json::binary(u.data(), m_n * 4);
-		m_params_fp32.copy_to_host(f.data(), m_n); adam["params_full_precision_binary"] = Json::binary(f.data(), m_n * 4);
-		m_params.copy_to_host(h.data(), m_n); adam["params_binary"] = Json::binary(h.data(), m_n * 2);
-		Json decay = Json::object();
-		decay["otype"] = Json("ExponentialDecay"); decay["learning_rate_factor"] = Json(m_lr_factor); decay["nested"] = adam;
-		Json ema = Json::object();
-		ema["otype"] = Json("Ema"); ema["ema_step"] = Json(m_step); ema["nested"] = decay;
-		data["optimizer"] = ema;
+		m_param_steps.copy_to_host(u.data(), m_n); node["param_steps_binary"] = Json::binary(u.data(), m_n * 4);
+		m_params_fp32.copy_to_host(f.data(), m_n); node["params_full_precision_binary"] = Json::binary(f.data(), m_n * 4);   // extra (see above)
+		std::vector<precision_t> w(m_n);
+		m_params.copy_to_host(w.data(), m_n); node["params_training_binary"] = Json::binary(w.data(), m_n * 2);               // extra
+		if (m_opt.has_decay) {
+			Json decay = Json::object();
+			decay["nested"] = node;
+			decay["learning_rate"] = Json(m_opt.learning_rate);
+			decay["learning_rate_factor"] = Json(m_lr_factor);
+			node = decay;
+		}
+		if (m_opt.has_ema) {
+			Json ema = Json::object();
+			ema["nested"] = node;
+			ema["weights_ema_binary"] = Json::binary(h.data(), m_n * sizeof(precision_t));
+			node = ema;
+		}
+		data["optimizer"] = node;
 	}
 	return data;
 }
 
+static float half_bits_to_float(uint16_t h) {
+	const uint32_t s = (h >> 15) & 1, e = (h >> 10) & 0x1f, m = h & 0x3ff;
+	const float v = e == 0 ? std::ldexp((float)m, -24) : e == 31 ? (m ? NAN : INFINITY) : std::ldexp((float)(m | 0x400), (int)e - 25);
+	return s ? -v : v;
+}
+
 void Trainer::deserialize(const Json& data, cudaStream_t stream) {
-	if ((size_t)data.at("n_params").number() != m_n) throw std::runtime_error("Can't set params because buffer has the wrong size.");
 	const Json& pb = data.at("params_binary");
-	if (pb.type != Json::Binary || pb.s.size() != m_n * sizeof(precision_t)) throw std::runtime_error("snapshot: params_binary has the wrong size");
+	// Trainer::set_params (trainer.h:267-288): the buffer size is what is checked, "n_params" itself is never read back
+	if (pb.type != Json::Binary || pb.s.size() != m_n * sizeof(precision_t)) throw std::runtime_error("Can't set params because buffer has the wrong size.");
 	NGP_CUDA_CHECK(cudaMemcpyAsync(m_ema.data(), pb.s.data(), pb.s.size(), cudaMemcpyHostToDevice, stream));
 	NGP_CUDA_CHECK(cudaMemcpyAsync(m_params.data(), pb.s.data(), pb.s.size(), cudaMemcpyHostToDevice, stream));
-	// fp32 master = widened fp16 (trainer.h:232-247 set_params path)
+	// fp32 master = widened fp16 (set_params)
 	std::vector<float> f(m_n);
 	const uint16_t* h = (const uint16_t*)pb.s.data();
-	for (size_t i = 0; i < m_n; ++i) {
-		const uint32_t s = (h[i] >> 15) & 1, e = (h[i] >> 10) & 0x1f, m = h[i] & 0x3ff;
-		float v;
-		if (e == 0) v = std::ldexp((float)m, -24);
-		else if (e == 31) v = m ? NAN : INFINITY;
-		else v = std::ldexp((float)(m | 0x400), (int)e - 25);
-		f[i] = s ? -v : v;
-	}
+	for (size_t i = 0; i < m_n; ++i) f[i] = half_bits_to_float(h[i]);
 	NGP_CUDA_CHECK(cudaMemcpyAsync(m_params_fp32.data(), f.data(), m_n * 4, cudaMemcpyHostToDevice, stream));
 	NGP_CUDA_CHECK(cudaStreamSynchronize(stream));
-	if (data.contains("optimizer")) {
-		const Json& ema = data.at("optimizer");
-		const Json& decay = ema.at("nested");
-		const Json& adam = decay.at("nested");
-		m_step = (uint32_t)adam.at("current_step").number();
-		m_lr_factor = (float)decay.at("learning_rate_factor").number();
-		auto load = [&](const char* key, void* dst, size_t bytes) {
-			const Json& b = adam.at(key);
-			if (b.type != Json::Binary || b.s.size() != bytes) throw std::runtime_error(std::string("snapshot: ") + key + " has the wrong size");
-			NGP_CUDA_CHECK(cudaMemcpy(dst, b.s.data(), bytes, cudaMemcpyHostToDevice));
-		};
-		load("first_moments_binary", m_m1.data(), m_n * 4);
-		load("second_moments_binary", m_m2.data(), m_n * 4);
-		load("param_steps_binary", m_param_steps.data(), m_n * 4);
-		load("params_full_precision_binary", m_params_fp32.data(), m_n * 4);
-		load("params_binary", m_params.data(), m_n * 2);
+	if (!data.contains("optimizer")) return;
+	auto load = [&](const Json& node, const char* key, void* dst, size_t bytes) {
+		const Json& b = node.at(key);
+		if (b.type != Json::Binary || b.s.size() != bytes) throw std::runtime_error(std::string("snapshot: ") + key + " has the wrong size");
+		NGP_CUDA_CHECK(cudaMemcpy(dst, b.s.data(), bytes, cudaMemcpyHostToDevice));
+	};
+	const Json* node = &data.at("optimizer");
+	if (m_opt.has_ema) {
+		load(*node, "weights_ema_binary", m_ema.data(), m_n * 2);                 // ema.h:180 requires it
+		node = &node->at("nested");
 	}
+	if (m_opt.has_decay) {
+		(void)node->at("learning_rate");                                          // exponential_decay.h:125 requires it; the value is the configured base rate
+		m_lr_factor = node->contains("learning_rate_factor") ? (float)node->at("learning_rate_factor").number() : 1.0f;
+		node = &node->at("nested");
+	}
+	m_step = (uint32_t)node->at("current_step").number();
+	(void)node->at("base_learning_rate");
+	load(*node, "first_moments_binary", m_m1.data(), m_n * 4);
+	load(*node, "second_moments_binary", m_m2.data(), m_n * 4);
+	if (node->contains("param_steps_binary")) load(*node, "param_steps_binary", m_param_steps.data(), m_n * 4);
+	else m_param_steps.memset(0, stream);                                         // adam.h:268-271
+	// our own extras: exact resume.  A reference-written file has neither; training then continues from the widened EMA weights,
+	// which is what the reference itself does after load_snapshot.
+	if (node->contains("params_full_precision_binary")) load(*node, "params_full_precision_binary", m_params_fp32.data(), m_n * 4);
+	if (node->contains("params_training_binary")) load(*node, "params_training_binary", m_params.data(), m_n * 2);
+	NGP_CUDA_CHECK(cudaStreamSynchronize(stream));
 }
 
 } // namespace ngp

@@ -30,6 +30,13 @@ PYBIND11_MODULE(pyngp, m) {
 		const ShardRange r = shard_range(n_params, rank, world);
 		return py::make_tuple(r.begin, r.end, r.size);
 	}, "(begin, end, shard size) of the parameter range a rank owns in the sharded data-parallel optimizer");
+	m.def("decode_png", [](const std::string& path) {
+		int w = 0, h = 0;
+		const std::vector<uint8_t> px = decode_png_file(path, w, h);
+		py::array_t<uint8_t> img({h, w, 4});
+		std::memcpy(img.request().ptr, px.data(), px.size());
+		return img;
+	}, "The dataset loader's PNG decoder (host code): RGBA8 [h][w][4], converted as stb_image's stbi_load(path, ..., 4) converts.");
 	m.doc() = "Instant neural graphics primitives (NeRF) minimal version -- B200-native build";
 
 	py::enum_<EActivation>(m, "Activation")
@@ -120,7 +127,6 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readonly("training_buffer", &Testbed::m_training_buffer)
 		.def_readonly("rendering_buffer", &Testbed::m_rendering_buffer)
 		.def_readwrite("pipeline_march", &Testbed::m_pipeline_march, "march step i+1 on a second stream underneath step i (default on)")
-		.def_readwrite("fine_level_begin", &Testbed::m_fine_level_begin, "single GPU: grid levels >= this are stepped by the optimizer on a side stream while the coarser levels' gradients are still being scattered (0 = off)")
 		.def_property("fov", &Testbed::fov, &Testbed::set_fov)
 		.def_property("fov_xy",
 			[](const Testbed& t) { return std::vector<float>{focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[0]), focal_length_to_fov(1, t.m_rendering_buffer.relative_focal_length[1])}; },
@@ -133,6 +139,15 @@ PYBIND11_MODULE(pyngp, m) {
 			t.training_image_to_host(i, (float*)image.request().ptr);
 			return image;
 		})
+		.def_property_readonly("training_xforms", [](const Testbed& t) {
+			// camera-to-world matrices after spec_opengl_to_opencv, [n][12] column-major (what nerf_synthetic.cu:98 uploads)
+			const NeRFSynthetic& d = t.m_training_buffer.dataset;
+			py::array_t<float> out({(py::ssize_t)d.n_images, (py::ssize_t)12});
+			if (d.n_images) NGP_CUDA_CHECK(cudaMemcpy(out.request().ptr, d.xforms.data(), (size_t)d.n_images * sizeof(Mat34), cudaMemcpyDeviceToHost));
+			return out;
+		})
+		.def_property_readonly("training_focal_length", [](const Testbed& t) { const NeRFSynthetic& d = t.m_training_buffer.dataset; return std::vector<float>{d.focal_length[0], d.focal_length[1]}; })
+		.def_property_readonly("training_filenames", [](const Testbed& t) { return t.m_training_buffer.dataset.filenames; })
 		.def_property_readonly("n_training_images", [](const Testbed& t) { return t.m_training_buffer.dataset.n_images; })
 		// ---- additions for data-parallel training (not in the reference) ----
 		.def("set_data_parallel", [](Testbed& t, int rank, int world, uintptr_t comm, bool peer_memory) { t.set_data_parallel(rank, world, (void*)comm, peer_memory); },

@@ -24,6 +24,7 @@ void RayMarcher::volume_rendering_with_loss_and_gradient(
 	c.loss_type = (int)loss_type; c.color_space = (int)color_space;
 	c.train_with_random_bg_color = train_with_random_bg_color ? 1 : 0; c.train_in_linear_color = train_in_linear_color ? 1 : 0;
 	c.transmittance_threshold = transmittance_threshold; c.min_optical_thickness = min_optical_thickness; c.loss_scale = loss_scale;
+	c.reg_scale = m_reg_scale;
 	for (int k = 0; k < 3; ++k) c.background_color[k] = background_color[k];
 	if (m_envmap) {
 		c.envmap = m_envmap; c.envmap_gradient = m_envmap_gradient; c.rays = (const float*)rays.data();

@@ -28,6 +28,9 @@ public:
 		const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const DeviceBuffer<float>& density_grid_mean, float min_optical_thickness,
 		const float background_color[3], EColorSpace color_space, default_rng_t rng, cudaStream_t stream, uint32_t* compacted_src_index = nullptr);
 
+	// data parallel: 1 / world, so the density L1 regulariser (added outside the loss scale) is summed once over the ranks
+	void set_regulariser_scale(float s) { m_reg_scale = s; }
+	float m_reg_scale = 1.f;
 	// environment map arguments of ray_marcher.cu:43-46 (data, gradient, resolution, loss type); nullptr data = none
 	void set_envmap(const void* data, void* gradient, int res_x, int res_y, ELossType loss_type) {
 		m_envmap = data; m_envmap_gradient = gradient; m_envmap_res[0] = res_x; m_envmap_res[1] = res_y; m_envmap_loss_type = loss_type;

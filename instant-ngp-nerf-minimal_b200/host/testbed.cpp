@@ -50,8 +50,15 @@ Testbed::Testbed() {
 	m_rendering_buffer.n_alive_counter.memset(0);
 }
 
-Testbed::~Testbed() {
+void Testbed::close_peer_handles() {
 	for (void* p : m_peer_opened) cudaIpcCloseMemHandle(p);
+	m_peer_opened.clear();
+	m_peers = ngp_peer_set{};
+	m_peer_enabled = false;
+}
+
+Testbed::~Testbed() {
+	close_peer_handles();
 	for (auto& e : m_ev) if (e) cudaEventDestroy(e);
 	for (cudaEvent_t e : {m_ev_march_go, m_ev_march_ready[0], m_ev_march_ready[1], m_ev_slot_free[0], m_ev_slot_free[1]}) if (e) cudaEventDestroy(e);
 	if (m_march_stream) cudaStreamDestroy(m_march_stream);
@@ -73,6 +80,13 @@ void Testbed::load_model_config(const std::string& config_path) {
 }
 
 void Testbed::load_model_config_json(const Json& config) {
+	if (m_dp_world > 1) {
+		// The Trainer below owns new gradient / parameter arenas: this rank's peer set would point at freed memory and the handles the
+		// other ranks opened are stale.  Data-parallel training has to be set up again (collectively) before the next train().
+		if (m_stream) cudaStreamSynchronize(m_stream);
+		close_peer_handles();
+		m_dp_stale = true;
+	}
 	m_model_config = config;
 	m_sampler = std::make_shared<OccupancySampler>(m_model_config["samlper"]);   // (sic) the key the reference reads, testbed.cu:67
 	m_network = std::make_shared<NGPNetwork>(m_model_config["network"]);
@@ -145,6 +159,8 @@ void Testbed::load_procedural_training_data(uint32_t n_images, int width, int he
 
 // testbed.cu:127-141
 void Testbed::save_snapshot(const std::string& snapshot_path, bool serialize_optimizer) {
+	if (serialize_optimizer && m_peer_enabled && m_sharded_state_dirty)
+		throw std::runtime_error("save_snapshot: the optimizer state is sharded over the ranks; call gather_optimizer_state() on every rank first");
 	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 	m_model_config["snapshot"] = m_trainer->serialize(serialize_optimizer);
 	std::vector<float> grid(m_sampler->n_total_elements);
@@ -182,7 +198,10 @@ void Testbed::set_data_parallel(int rank, int world_size, void* nccl_comm, bool 
 	if (!m_trainer) throw std::runtime_error("set_data_parallel: load_model_config first");
 	if (m_train_envmap && world_size > 1) throw std::runtime_error("envmap training is single-GPU (its gradients are not exchanged)");
 	m_dp_rank = rank; m_dp_world = world_size; m_nccl_comm = nccl_comm;
-	m_peer_enabled = false;
+	close_peer_handles();
+	m_dp_stale = false;
+	m_sharded_state_dirty = false;
+	m_render->set_regulariser_scale(1.f / (float)world_size);
 	if (!peer_memory || world_size == 1) return;
 	if (world_size > NGP_MAX_PEERS) throw std::runtime_error("set_data_parallel: peer memory supports at most 8 ranks");
 	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
@@ -238,6 +257,7 @@ void Testbed::gather_optimizer_state() {
 	all_gather_shards(m_trainer->m2(), S, m_dp_rank, ncclFloat, 1, m_nccl_comm, m_stream);
 	all_gather_shards(m_trainer->param_steps(), S, m_dp_rank, ncclUint32, 1, m_nccl_comm, m_stream);
 	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+	m_sharded_state_dirty = false;
 }
 
 } // namespace ngp

@@ -180,6 +180,9 @@ private:
 	DeviceBuffer<uint32_t> m_peer_flags;
 	uint32_t m_peer_epoch = 0;
 	std::vector<void*> m_peer_opened;
+	bool m_dp_stale = false;                 // the modules were rebuilt after set_data_parallel: the peer set points at freed arenas
+	bool m_sharded_state_dirty = false;      // peer mode: other ranks' shards of the optimizer state are older than the last step
+	void close_peer_handles();
 	int m_render_row_begin = 0, m_render_row_end = -1;
 };
 

@@ -10,6 +10,7 @@ namespace ngp {
 // are timed with CUDA events on the stream and the host waits once, at the end, for the counters Python reads.
 void Testbed::train(uint32_t n_training_steps, uint32_t target_batch_size) {
 	if (!m_trainer || m_training_buffer.dataset.n_images == 0) throw std::runtime_error("train: load_model_config and load_training_data first");
+	if (m_dp_stale) throw std::runtime_error("train: load_model_config / load_snapshot rebuilt the model after set_data_parallel; call set_data_parallel again on every rank");
 	if (n_training_steps == 0) return;
 	m_enqueue_start = std::chrono::steady_clock::now();
 	NGP_CUDA_CHECK(cudaEventRecord(m_ev[0], m_stream));
@@ -213,6 +214,7 @@ void Testbed::learn_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_r
 		// data parallel over peer memory: publish "my gradients are complete", then ONE kernel reduces this rank's shard out of all
 		// ranks' arenas, updates it and stores the new weights into all arenas; the next reader of the weights waits for every shard
 		++m_peer_epoch;
+		m_sharded_state_dirty = true;
 		api_check(ngp_peer_publish_gradients(stream, &m_peers, m_peer_epoch));
 		m_trainer->optimizer_step_sharded(stream, LOSS_SCALE, m_peers, m_peer_epoch);
 		api_check(ngp_peer_wait_weights(stream, &m_peers, m_peer_epoch));

@@ -23,13 +23,36 @@ PKG = "instant-ngp-nerf-minimal_b200"
 BATCH = 1 << 21            # large enough that the first step's 1.7 M samples are not clipped (clipping order is atomic-order dependent)
 
 
-@pytest.fixture(scope="module")
-def ref(capi):
+ENV_W, ENV_H = 64, 32          # envmap.width / envmap.height of the "envmap" variant (the reference's resolution vector is {height, width})
+
+
+@pytest.fixture(scope="module", params=["base", "cascades", "envmap"])
+def ref(capi, request):
+    """one dump of the reference's CUDA build per variant: base.json as shipped; aabb_scale 4 (3 cascades: the cameras sit in the
+    outer cascades, so the cascaded DDA of occupancy_sampler.cu:216-300 and mip selection are exercised); envmap.train true
+    (ray_marcher.cu:96-102,190-212, testbed.cu:236-239,295-298, occupancy_sampler.cu:408) started from random texels"""
     if not refcuda.available():
         pytest.skip("oracle/_ref/ref_harness is not built (oracle/build_ref.sh needs /root/reference at build time)")
     scene = importlib.import_module(PKG + ".scene")
     _, n_entries = capi.make_grid_desc()
-    return refcuda.make(capi, scene, params=refcuda.start_params(10240 + 2 * n_entries), batch=BATCH)
+    kind = request.param
+    config, envmap, n_rays = None, None, 0
+    if kind == "cascades":
+        config, n_rays = {"samlper.aabb_scale": 4}, 2048
+    if kind == "envmap":
+        config = {"envmap.train": True, "envmap.height": ENV_H, "envmap.width": ENV_W}
+        g = np.random.Generator(np.random.PCG64(11))
+        envmap = (g.random((ENV_W * ENV_H, 4), dtype=np.float32) * np.float32([0.6, 0.6, 0.6, 0.8])).astype(np.float16)
+    r = refcuda.make(capi, scene, params=refcuda.start_params(10240 + 2 * n_entries), batch=BATCH, n_rays=n_rays, config=config, envmap=envmap)
+    r.kind, r.aabb_scale, r.envmap = kind, 4 if kind == "cascades" else 1, envmap
+    return r
+
+
+def _sampler_cfg(capi, ref):
+    c = capi.make_sampler_cfg(ref.aabb_scale)
+    c.keep_empty_rays = 1 if ref.kind == "envmap" else 0
+    assert c.n_cascades == ref.meta["n_cascades"]
+    return c
 
 
 def _cam(capi, ds):
@@ -64,7 +87,7 @@ def test_untrained_grid_and_first_bitfield_bit_exact(capi, ref):
     import torch
     lib = capi.load()
     ds = ref.dataset
-    cfg, cam = capi.make_sampler_cfg(1), _cam(capi, ds)
+    cfg, cam = _sampler_cfg(capi, ref), _cam(capi, ds)
     want = ref.arr("grid0_f32", np.float32)
     grid = G.zeros(want.size, torch.float32)
     capi.check(lib.ngp_mark_untrained_grid(G.stream(), C.byref(cfg), C.byref(cam), ds["n_views"], G.p(G.dev(ds["xforms"])), G.p(grid)))
@@ -81,7 +104,7 @@ def test_grid_sample_positions_bit_exact(capi, ref):
     import gpuutil as G
     import torch
     lib = capi.load()
-    cfg = capi.make_sampler_cfg(1)
+    cfg = _sampler_cfg(capi, ref)
     n = ref.meta["n_total_elements"]
     pos, idx = G.zeros(n * 3, torch.float32), G.zeros(n, torch.int32)
     capi.check(lib.ngp_generate_grid_samples(G.stream(), C.byref(cfg), n, ref.meta["sampler_rng_state"], ref.meta["sampler_rng_inc"], 0,
@@ -115,7 +138,7 @@ def test_grid_update_and_bitfield_from_reference_densities(capi, ref):
     import gpuutil as G
     import torch
     lib = capi.load()
-    cfg = capi.make_sampler_cfg(1)
+    cfg = _sampler_cfg(capi, ref)
     n = ref.meta["n_total_elements"]
     grid, cur = G.dev(ref.arr("grid0_f32", np.float32)), G.zeros(n, torch.float32)
     capi.check(lib.ngp_update_grid(G.stream(), C.byref(cfg), n, G.p(G.dev(ref.arr("grid_indices_u32", np.uint32))),
@@ -140,7 +163,8 @@ def _ray_order(rays, numsteps, coords):
     """a canonical order of rays, keyed by the bit patterns of (origin, direction); two rays through the same pixel differ in
     their random start offset, so the first sample's position breaks the tie"""
     k = np.ascontiguousarray(rays, np.float32).view(np.uint32).reshape(-1, 6)
-    first = np.ascontiguousarray(coords[numsteps[:, 1], :3]).view(np.uint32)
+    first = np.ascontiguousarray(coords[np.minimum(numsteps[:, 1], len(coords) - 1), :3]).view(np.uint32).copy()
+    first[numsteps[:, 0] == 0] = 0                        # rays without samples (kept when the environment map trains) have no first sample
     return np.lexsort(tuple(first[:, c] for c in range(3)) + tuple(k[:, c] for c in range(6)))
 
 
@@ -160,7 +184,7 @@ def test_training_march_bit_exact_per_ray(capi, ref):
     import torch
     lib = capi.load()
     ds, m = ref.dataset, ref.meta
-    cfg, cam = capi.make_sampler_cfg(1), _cam(capi, ds)
+    cfg, cam = _sampler_cfg(capi, ref), _cam(capi, ds)
     n_rays, n_coords = m["n_rays"], 16 * BATCH
     rays, rgba = G.zeros(n_rays * 6, torch.float32), G.zeros(n_rays * 4, torch.float32)
     numsteps, coords = G.zeros(n_rays * 2, torch.int32), G.zeros(n_coords * 7, torch.float32)
@@ -181,10 +205,18 @@ def test_training_march_bit_exact_per_ray(capi, ref):
     assert np.array_equal(g_rays[go], r_rays[ro]), "ray origins / directions differ"
     assert np.array_equal(G.host(rgba).reshape(-1, 4)[:k][go], ref.arr("rays_rgba_f32", np.float32, (k, 4))[ro])
     assert np.array_equal(g_ns[go, 0], r_ns[ro, 0]), "per-ray sample counts must be bit-exact"
-    assert g_ns[:, 0].min() >= 1 and g_ns[:, 0].max() > 50 and len(np.unique(g_ns[:, 0])) > 30      # the bitfield really skips
+    assert g_ns[:, 0].max() > 50 and len(np.unique(g_ns[:, 0])) > 30      # the bitfield really skips
+    if ref.kind == "envmap":
+        assert (g_ns[:, 0] == 0).any(), "rays that miss everything stay in the list when the environment map trains"
+    else:
+        assert g_ns[:, 0].min() >= 1
     g_c = g_all[_runs(g_ns[:, 1], g_ns[:, 0], go)]
     r_c = r_all[_runs(r_ns[:, 1], r_ns[:, 0], ro)]
     assert np.array_equal(g_c.view(np.uint32), r_c.view(np.uint32)), "sample coordinates differ"
+    if ref.kind == "cascades":
+        # positions are relative to the scale-4 box: the unit cube is [0.375, 0.625]^3 of it, everything else lies in cascades >= 1
+        outside = (np.abs(g_c[:, :3] - 0.5) > 0.125).any(axis=1)
+        assert outside.mean() > 0.2, "the march must spend samples in the outer cascades"
 
 
 def test_network_inference_matches_reference(capi, ref):
@@ -213,7 +245,13 @@ def test_composite_loss_gradients_and_compaction_match_reference(capi, orc, ref)
     lib = capi.load()
     m = ref.meta
     k, n_rays, n_m = m["n_kept"], m["n_rays"], m["n_marched"]
-    c = _render_cfg(capi, orc.SamplerCfg(1), bg=(0.0, 0.0, 0.0))
+    c = _render_cfg(capi, orc.SamplerCfg(ref.aabb_scale), bg=(0.0, 0.0, 0.0))
+    d_egrad = None
+    if ref.kind == "envmap":
+        # the reference's resolution vector is {height, width} and it indexes x + y * resolution.x (testbed.cu:86, envmap.h:19-47)
+        d_env, d_egrad, d_rays = G.dev(ref.arr("envmap_params0_f16", np.uint16)), G.zeros(ENV_W * ENV_H * 4, torch.int16), G.dev(ref.arr("rays_f32", np.float32))
+        c.envmap, c.envmap_gradient, c.rays = d_env.data_ptr(), d_egrad.data_ptr(), d_rays.data_ptr()
+        c.envmap_res_x, c.envmap_res_y, c.envmap_loss_type = ENV_H, ENV_W, 6
     r_ns = ref.arr("numsteps_u32", np.uint32, (k, 2))
     d_ns = G.dev(r_ns)
     cc, dloss = G.zeros(BATCH * 7, torch.float32), G.zeros(BATCH * 4, torch.int16)
@@ -237,6 +275,14 @@ def test_composite_loss_gradients_and_compaction_match_reference(capi, orc, ref)
     scale = np.abs(rd).max()
     err = np.abs(gd - rd)
     assert scale > 0 and (err <= 5e-2 * np.abs(rd) + 1e-4 * scale).mean() > 0.9995 and err.max() <= 2e-2 * scale, (err.max(), scale)
+    if ref.kind == "envmap":
+        # dL/d(envmap) deposited bilinearly by the fully traversed rays with fp16 atomics on both sides (ray_marcher.cu:190-212)
+        ge = G.host(d_egrad, np.float16).astype(np.float32).reshape(-1, 4)
+        re_ = ref.arr("envmap_grad_f16", np.float16).astype(np.float32).reshape(-1, 4)
+        es = np.abs(re_).max()
+        assert es > 0 and np.count_nonzero(re_[:, :3]) > 100, "rays must reach the background"
+        assert not ge[:, 3].any() and not re_[:, 3].any()
+        assert np.abs(ge - re_).max() <= 2e-2 * es and np.linalg.norm(ge - re_) <= 1e-2 * np.linalg.norm(re_), (np.abs(ge - re_).max() / es)
 
 
 def test_rollover_matches_reference(capi, ref):
@@ -307,6 +353,35 @@ def test_optimizer_step_matches_reference(capi, ref):
     assert np.allclose(got, want, rtol=1e-5, atol=1e-7), np.abs(got - want).max()
     a, b = G.host(w16, np.float16).astype(np.float32), ref.arr("params1_f16", np.float16).astype(np.float32)
     assert (a == b).mean() > 0.999 and np.abs(a - b).max() <= 1e-3 * np.abs(b).max()
+
+
+def test_envmap_optimizer_step_matches_reference(capi, ref):
+    """the environment map's own Ema(ExponentialDecay(Adam)) stepped once per train() call with loss scale 128 * n_steps
+    (testbed.cu:295-298) on the reference's own deposited gradients: no matrix parameters, texels without gradient are skipped"""
+    import gpuutil as G
+    import torch
+    if ref.kind != "envmap":
+        pytest.skip("only the envmap variant trains the environment map")
+    lib = capi.load()
+    p0 = ref.arr("envmap_params0_f16", np.float16)
+    n = p0.size
+    pad = 16
+    w32 = G.dev(np.concatenate([p0.astype(np.float32), np.zeros(pad, np.float32)]))
+    w16, ema = G.dev(np.concatenate([p0, np.zeros(pad, np.float16)]).view(np.uint16)), G.dev(np.concatenate([p0, np.zeros(pad, np.float16)]).view(np.uint16))
+    g16 = G.dev(np.concatenate([ref.arr("envmap_grad_f16", np.uint16), np.zeros(pad, np.uint16)]))
+    m1, m2, ps = G.zeros(n + pad, torch.float32), G.zeros(n + pad, torch.float32), G.zeros(n + pad, torch.int32)
+    cfg = capi.OptimizerCfg(1e-2, 0.9, 0.99, 1e-10, 1e-10, 128.0, 0.99)            # base.json "envmap.optimizer"
+    capi.check(lib.ngp_optimizer_step(G.stream(), C.byref(cfg), n, 0, 0, 1e-2, G.p(w32), G.p(w16), G.p(g16), G.p(m1), G.p(m2), G.p(ps), G.p(ema)))
+    G.sync()
+    want32, want16 = ref.arr("envmap_params1_f32", np.float32), ref.arr("envmap_params1_f16", np.float16).astype(np.float32)
+    got32 = G.host(w32)[:n]
+    assert (want32 != p0.astype(np.float32)).mean() > 0.05
+    assert np.array_equal(got32 != p0.astype(np.float32), want32 != p0.astype(np.float32)), "the same texels are touched"
+    assert np.allclose(got32, want32, rtol=1e-5, atol=1e-7), np.abs(got32 - want32).max()
+    a = G.host(w16, np.float16)[:n].astype(np.float32)
+    assert (a == want16).mean() > 0.999
+    e, we = G.host(ema, np.float16)[:n].astype(np.float32), ref.arr("envmap_inference1_f16", np.float16).astype(np.float32)
+    assert np.abs(e - we).max() <= 2e-3 * max(np.abs(we).max(), 1e-6), "EMA (inference) texels"
 
 
 @pytest.mark.parametrize("amp,n", [(1e-4, 1 << 18), (1.0, 1 << 16)])
