@@ -392,7 +392,11 @@ static int run_loadrender(const std::string& dir, const std::string& file, int W
 	tb.load_snapshot(file);
 	CUDA_CHECK_THROW(cudaDeviceSynchronize());
 	double rays = 0;
-	const double sec = render_specs(tb, dir, "ref_loadrender", W, H, fov_value, parse_specs(specs), &rays);
+	// specs "none": no rendering.  Needed for files WITH optimizer state: Ema::deserialize (ema.h:180) move-assigns a freshly
+	// allocated buffer to m_weights_ema, the old one is freed, and Trainer::m_params_inference / the network's inference pointer
+	// (set once in Trainer::initialize_params, trainer.h:91-105) keep pointing at it -- the reference cannot render after loading
+	// such a file (use after free); training (use_inference_matrices = false) is unaffected.
+	const double sec = specs == "none" ? 0.0 : render_specs(tb, dir, "ref_loadrender", W, H, fov_value, parse_specs(specs), &rays);
 	double loss = -1, first_loss = -1;
 	if (train_calls) {
 		for (uint32_t i = 0; i < train_calls; ++i) { tb.train(16, batch); if (i == 0) first_loss = tb.m_training_buffer.loss_scalar; }

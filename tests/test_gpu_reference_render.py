@@ -163,7 +163,8 @@ def test_reference_loads_our_snapshot_and_renders_the_same_picture(pyngp, snap, 
             err = np.abs(got - want) / span
             assert (err <= 2 / 255).mean() >= 0.995 and (err <= 6 / 255).mean() >= 0.999, (spec, p, float((err <= 2 / 255).mean()), float(err.max()))
     # with optimizer state: the reference resumes from it (Ema / ExponentialDecay / Adam deserialize .at() every key they wrote)
-    info = refcuda.run("loadrender", snap.dir, path_opt, W, H, snap.scene.CAMERA_ANGLE_X, "1:0:1:1", 2)
+    # No rendering on that side: after Ema::deserialize the reference's inference-weight pointer dangles (see ref_harness.cu run_loadrender).
+    info = refcuda.run("loadrender", snap.dir, path_opt, W, H, snap.scene.CAMERA_ANGLE_X, "none", 2)
     assert info["trained_calls"] == 2 and np.isfinite(info["loss"])
     assert info["first_call_loss"] < 2.0 * ours_loss + 1e-4, (info, ours_loss)     # continues at the trained loss level, not from scratch
     # and we resume from the reference's optimizer snapshot
@@ -213,7 +214,10 @@ def rdump(snap, request):
 def _camera(capi, snap):
     """what render_frame derives from fov and resolution (testbed.cu:481-483): focal = resolution[fov_axis = 1] * relative_focal_length"""
     c = capi.CameraCfg()
-    rel = np.float32(0.5) / np.float32(np.tan(np.float32(0.5) * np.float32(snap.scene.CAMERA_ANGLE_X)))      # fov_to_focal_length(1, fov) with the value as radians
+    # relative_focal_length = fov_to_focal_length(1, fov) evaluated by the host library's tanf (numpy's float32 tan is an ulp off): taken from pyngp
+    tb = importlib.import_module(PKG).load_pyngp().Testbed()
+    tb.fov = snap.scene.CAMERA_ANGLE_X
+    rel = np.float32(tb.rendering_buffer.relative_focal_length[0])
     c.width, c.height, c.fx, c.fy, c.ppx, c.ppy = W, H, float(np.float32(H) * rel), float(np.float32(H) * rel), 0.5, 0.5
     return c
 
