@@ -84,7 +84,12 @@ def test_reference_written_snapshot_renders_like_the_reference(pyngp, snap):
         mode = _parse(spec)[0]
         for p in range(N_POSES):
             want, got = snap.ref_image(i, p), _render(pyngp, tb, snap, spec, p)
-            assert np.isfinite(got).all()
+            # Normals: the reference's fp16 input-gradient pass overflows on some samples (inf - inf inside its backward kernels), so
+            # its own picture carries non-finite pixels; ours must be finite wherever the reference's is
+            ok = np.isfinite(want).all(axis=-1)
+            assert ok.mean() > (0.9 if mode == 2 else 0.9999), (spec, p, float(ok.mean()))
+            assert np.isfinite(got[ok]).all(), (spec, p, int((~np.isfinite(got[ok])).sum()))
+            want, got = np.where(ok[..., None], want, 0.0), np.where(ok[..., None], got, 0.0)
             if p == 0 and mode == 1:
                 assert want[..., 3].max() > 0.9 and (want[..., :3].max() > 0.2), "the trained scene must be visible in the reference's picture"
             span = max(float(np.abs(want[..., :3]).max()), 1.0)
@@ -147,8 +152,10 @@ def test_reference_loads_our_snapshot_and_renders_the_same_picture(pyngp, snap, 
     tb.load_model_config(os.path.join(snap.dir, "config.json"))
     ds = snap.ds
     tb.load_training_data_from_memory(ds["rgba8"], ds["ogl"], snap.scene.CAMERA_ANGLE_X, 0.33, [0.5, 0.5, 0.5])
+    first_call_loss = None
     for _ in range(CALLS):
         tb.train(16, 1 << 18)
+        first_call_loss = tb.training_buffer.loss if first_call_loss is None else first_call_loss
     ours_loss = tb.training_buffer.loss
     path = os.path.join(tmp_path, "ours.msgpack")
     path_opt = os.path.join(tmp_path, "ours_opt.msgpack")
@@ -173,7 +180,10 @@ def test_reference_loads_our_snapshot_and_renders_the_same_picture(pyngp, snap, 
     tb2.load_training_data_from_memory(ds["rgba8"], ds["ogl"], snap.scene.CAMERA_ANGLE_X, 0.33, [0.5, 0.5, 0.5])
     tb2.load_snapshot(os.path.join(snap.dir, "ref_snapshot_opt.msgpack"))
     tb2.train(16, 1 << 18)
-    assert np.isfinite(tb2.training_buffer.loss) and tb2.training_buffer.loss < 2.0 * snap.info["loss"] + 1e-4, (tb2.training_buffer.loss, snap.info)
+    # resumed, not restarted: far below the loss of a first call from scratch, and in the range of the loss the file was saved at
+    # (the file carries the EMA weights only, which lag the training weights while the model still improves quickly)
+    resumed = tb2.training_buffer.loss
+    assert np.isfinite(resumed) and resumed < 0.35 * first_call_loss and resumed < 5.0 * snap.info["loss"] + 1e-4, (resumed, first_call_loss, snap.info)
 
 
 # ---------------------------------------------------------------------------------------------------------------------------
@@ -322,8 +332,10 @@ def test_network_and_compositing_on_reference_rounds(capi, orc, snap, rdump):
         assert flips.mean() < 1e-3, f"round {k}: {flips.sum()} rays end differently"
         assert np.array_equal(gp["n_steps"][~flips], wp["n_steps"][~flips])
         gr, wr = G.host(d_rgba).reshape(n, 4), rdump.get(f"r{k}_rgba_out", np.float32, (n, 4))
-        scale = max(float(np.abs(wr).max()), 1.0)
-        assert np.abs(gr - wr)[~flips].max() <= 2e-4 * scale, (k, float(np.abs(gr - wr)[~flips].max()), scale)
+        sane = ~flips & np.isfinite(wr).all(axis=1)            # Normals: the reference's own gradients are non-finite on some samples
+        assert sane.mean() > 0.9 and np.isfinite(gr[sane]).all()
+        scale = max(float(np.abs(wr[sane]).max()), 1.0)
+        assert np.abs(gr - wr)[sane].max() <= 2e-4 * scale, (k, float(np.abs(gr - wr)[sane].max()), scale)
 
 
 def test_input_gradients_match_reference(capi, snap, rdump):
