@@ -98,6 +98,9 @@ PYBIND11_MODULE(pyngp, m) {
 			{ py::gil_scoped_release rel; t.render_band_to_host(width, height, spp, to_srgb, ptr); }
 			return image;
 		}, "Renders the rows set by set_render_rows and returns them alone, [rows][width][4].", py::arg("width") = 1920, py::arg("height") = 1080, py::arg("spp") = 1, py::arg("to_srgb") = true)
+		.def("render_frames_ms", [](Testbed& t, int width, int height, int spp, bool to_srgb) { py::gil_scoped_release rel; return t.render_frames_ms(width, height, spp, to_srgb); },
+		     "Measurement hook: renders spp frames into the device-side surface (no host copy) and returns the wall-clock milliseconds.",
+		     py::arg("width") = 1920, py::arg("height") = 1080, py::arg("spp") = 1, py::arg("to_srgb") = true)
 		.def("envmap_image", [](const Testbed& t) {
 			// the trained environment map as render() uses it (EMA weights), [resolution[1]][resolution[0]][4] floats; zeros when not trained
 			const auto& e = t.m_envmap;

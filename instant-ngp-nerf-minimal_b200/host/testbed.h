@@ -49,6 +49,9 @@ public:
 	int render_row_begin(int height) const { return m_render_row_end < 0 ? 0 : std::max(0, std::min(m_render_row_begin, height)); }
 	int render_row_end(int height) const { return m_render_row_end < 0 ? height : std::max(render_row_begin(height), std::min(m_render_row_end, height)); }
 	void render_band_to_host(int width, int height, int spp, bool to_srgb, float* out_band);
+	// measurement hook: spp frames rendered into the device-side surface (ray generation -> tonemap, what the metric's Mrays/s counts,
+	// SURVEY.md 8d), no device -> host copy; returns the wall-clock milliseconds between two device synchronisations
+	float render_frames_ms(int width, int height, int spp, bool to_srgb);
 
 	float fov() const { return focal_length_to_fov(1, m_rendering_buffer.relative_focal_length[m_rendering_buffer.fov_axis]); }
 	void set_fov(float val) { m_rendering_buffer.relative_focal_length[0] = m_rendering_buffer.relative_focal_length[1] = fov_to_focal_length(1, val); }

@@ -100,6 +100,17 @@ void Testbed::render_band_to_host(int width, int height, int spp, bool to_srgb, 
 	if (n) NGP_CUDA_CHECK(cudaMemcpy(out_band, rb.render_buffer.surface() + first, n * sizeof(float), cudaMemcpyDeviceToHost));
 }
 
+float Testbed::render_frames_ms(int width, int height, int spp, bool to_srgb) {
+	RenderingBuffer& rb = m_rendering_buffer;
+	rb.render_buffer.resize(width, height);
+	rb.render_buffer.reset_accumulation();
+	NGP_CUDA_CHECK(cudaDeviceSynchronize());
+	const auto t0 = std::chrono::steady_clock::now();
+	for (int i = 0; i < spp; ++i) render_frame(rb.camera_matrix, rb.render_buffer, to_srgb);
+	NGP_CUDA_CHECK(cudaDeviceSynchronize());
+	return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
 void Testbed::set_camera_to_training_view(uint32_t i) {
 	const NeRFSynthetic& d = m_training_buffer.dataset;
 	if (i >= d.n_images) throw std::runtime_error("set_camera_to_training_view: no such view");

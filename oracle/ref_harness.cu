@@ -6,7 +6,8 @@
 //   ref_harness dump  <dir> [batch] [n_rays]   reads <dir>/{config.json,meta.txt,xforms.f32,images.f16}, writes <dir>/ref_*.bin
 //   ref_harness bench <dir> <calls> <warmup>   train(16, batch) loop as experiment/run.py:71 drives it; one JSON line
 //   ref_harness trainrender <dir> <calls> <W> <H> <spp> <fov>   train, then render <dir>/test_xforms.f32 -> ref_render_<i>.f32
-//   ref_harness benchsteps <dir> <steps> <warmup_steps> [batch]   the same loop for ANY step counts: calls of 16 plus one remainder call
+//   ref_harness benchsteps <dir> <steps> <warmup_steps> [batch] [psnr_res] [W] [H] [fov]   the same loop for ANY step counts (calls of 16 plus one remainder
+//                                              call); with <dir>/test_xforms.f32 the poses are then rendered at psnr_res^2 (written out) and timed at W x H
 //   ref_harness snapshot <dir> <calls> <W> <H> <fov> <specs> [batch]   train, Testbed::save_snapshot (with and without optimizer state), render test_xforms.f32
 //   ref_harness loadrender <dir> <file.msgpack> <W> <H> <fov> <specs> [train_calls] [batch]   Testbed::load_snapshot of ANY file (e.g. one written by
 //                                              pyngp), render the poses (timed), optionally keep training from the loaded state
@@ -286,8 +287,13 @@ static int run_trainrender(const std::string& dir, uint32_t calls, int W, int H,
 }
 
 
-// the training loop for arbitrary step counts: calls of 16 steps plus one remainder call (Testbed::train takes any n)
-static int run_benchsteps(const std::string& dir, uint32_t steps, uint32_t warmup, uint32_t batch) {
+struct RenderSpec { int mode = 1, curve = 0, spp = 1, srgb = 1; float exposure = 0.f; };
+static std::vector<RenderSpec> parse_specs(const std::string& text);
+static double render_specs(Testbed& tb, const std::string& dir, const std::string& prefix, int W, int H, float fov_value, const std::vector<RenderSpec>& specs, double* n_timed_rays);
+
+// the training loop for arbitrary step counts: calls of 16 steps plus one remainder call (Testbed::train takes any n); then, when
+// <dir>/test_xforms.f32 exists, the held-out poses rendered linear at psnr_res^2 (-> ref_bench_render_0_<p>.f32, for PSNR) and timed at W x H
+static int run_benchsteps(const std::string& dir, uint32_t steps, uint32_t warmup, uint32_t batch, int psnr_res, int W, int H, float fov_value) {
 	Testbed tb;
 	tb.load_model_config(dir + "/config.json");
 	load_dataset(tb, dir);
@@ -306,13 +312,29 @@ static int run_benchsteps(const std::string& dir, uint32_t steps, uint32_t warmu
 	}
 	CUDA_CHECK_THROW(cudaDeviceSynchronize());
 	const double wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+	double render_mrays = 0, render_ms = 0;
+	int n_frames = 0;
+	{
+		std::ifstream probe(dir + "/test_xforms.f32", std::ios::binary);
+		if (probe.good() && psnr_res > 0) {
+			double nrays = 0;
+			render_specs(tb, dir, "ref_bench_render", psnr_res, psnr_res, fov_value, parse_specs("1:0:1:0"), &nrays);
+			if (W > 0 && H > 0) {
+				// the same poses twice at the benchmark resolution; the very first frame (allocation) is not timed
+				const double sec = render_specs(tb, dir, "ref_bench_frame", W, H, fov_value, parse_specs("1:0:1:1,1:0:1:1"), &nrays);
+				n_frames = (int)(nrays / ((double)W * H));
+				if (sec > 0 && n_frames > 0) { render_mrays = nrays / sec / 1e6; render_ms = sec * 1e3 / n_frames; }
+			}
+		}
+	}
 	printf("{\"impl\": \"reference-cuda-sm100\", \"samples_per_s\": %.1f, \"ms_per_step\": %.5f, \"wall_ms_per_step\": %.5f, \"steps\": %u, \"warmup_steps\": %u, "
-	       "\"samples_per_step\": %.1f, \"marched_per_step\": %.1f, \"rays_per_step\": %.1f, \"loss\": %.6g}\n",
-	       samples / (ms * 1e-3), ms / steps, wall_ms / steps, steps, warmup, samples / steps, marched / steps, rays / steps, (double)b.loss_scalar);
+	       "\"samples_per_step\": %.1f, \"marched_per_step\": %.1f, \"rays_per_step\": %.1f, \"loss\": %.6g, \"i_step\": %u, "
+	       "\"render_mrays_per_s\": %.3f, \"render_ms_per_frame\": %.3f, \"render_frames_timed\": %d, \"render_width\": %d, \"render_height\": %d}\n",
+	       samples / (ms * 1e-3), ms / steps, wall_ms / steps, steps, warmup, samples / steps, marched / steps, rays / steps, (double)b.loss_scalar, b.i_step,
+	       render_mrays, render_ms, n_frames, W, H);
 	return 0;
 }
 
-struct RenderSpec { int mode = 1, curve = 0, spp = 1, srgb = 1; float exposure = 0.f; };
 static std::vector<RenderSpec> parse_specs(const std::string& text) {
 	std::vector<RenderSpec> out;
 	size_t pos = 0;
@@ -586,7 +608,9 @@ int main(int argc, char** argv) {
 		if (argc >= 4 && std::string(argv[1]) == "c1") return run_c1(argv[2], (uint32_t)atoi(argv[3]), argc > 4 ? (uint32_t)atoi(argv[4]) : 19u);
 		if (argc >= 5 && std::string(argv[1]) == "bench") return run_bench(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argc > 5 ? (uint32_t)atoi(argv[5]) : (1u << 18));
 		const std::string cmd = argc > 1 ? argv[1] : "";
-		if (argc >= 5 && cmd == "benchsteps") return run_benchsteps(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argc > 5 ? (uint32_t)atoi(argv[5]) : (1u << 18));
+		if (argc >= 5 && cmd == "benchsteps")
+			return run_benchsteps(argv[2], (uint32_t)atoi(argv[3]), (uint32_t)atoi(argv[4]), argc > 5 ? (uint32_t)atoi(argv[5]) : (1u << 18), argc > 6 ? atoi(argv[6]) : 0,
+			                      argc > 7 ? atoi(argv[7]) : 0, argc > 8 ? atoi(argv[8]) : 0, argc > 9 ? (float)atof(argv[9]) : 0.6911112f);
 		if (argc >= 8 && cmd == "snapshot") return run_snapshot(argv[2], (uint32_t)atoi(argv[3]), atoi(argv[4]), atoi(argv[5]), (float)atof(argv[6]), argv[7], argc > 8 ? (uint32_t)atoi(argv[8]) : (1u << 18));
 		if (argc >= 8 && cmd == "loadrender")
 			return run_loadrender(argv[2], argv[3], atoi(argv[4]), atoi(argv[5]), (float)atof(argv[6]), argv[7], argc > 8 ? (uint32_t)atoi(argv[8]) : 0u, argc > 9 ? (uint32_t)atoi(argv[9]) : (1u << 18));
