@@ -6,7 +6,14 @@
   python bench.py --impl reference --steps K --warmup W    the reference's algorithm on the host cores (CPU oracle, rank 0)
 
 A "step" is one training step (march -> network -> composite -> forward/backward -> optimizer); occupancy-grid refreshes
-happen every 16 steps as in the reference's run.py loop and are inside the timed region.  One JSON line on stdout."""
+happen every 16 steps as in the reference's run.py loop and are inside the timed region.  One JSON line on stdout.
+
+BASELINE.json's metric is "train samples/s & render Mrays/s ... PSNR parity" over five configs; the contract keys carry configs[1]
+(training), and the same line carries the rest as objects, measured in the same run by both arms:
+  render   configs[3]: 1920x1080 novel views, spp 1, Mrays/s (N > 1: row bands, one per rank, no collective)
+  psnr_db  4 held-out 800x800 poses after exactly warmup + steps training steps (run.py's protocol: linear render, clipped sRGB)
+  c1       configs[0]: hash-grid encode fwd / bwd on 2^18 random points, microseconds
+  c5       configs[4]: T = 2^22, 2^20-sample batches, aabb_scale 16 (5 cascades): ms/step and samples/s on a bounded number of calls"""
 import argparse
 import importlib
 import json
@@ -37,6 +44,8 @@ def parse():
     p.add_argument("--views", type=int, default=100)
     p.add_argument("--res", type=int, default=800)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-extras", action="store_true", help="skip the render / psnr_db / c1 / c5 objects")
+    p.add_argument("--c5-steps", type=int, default=32, help="timed steps of the configs[4] leg (after 32 warm-up steps)")
     p.add_argument("--timeline", default=None, help="write a per-launch timeline (json per rank) of two further train() calls with the march pipelined")
     p.add_argument("--dp-mode", default="peer", choices=["peer", "nccl"],
                    help="N > 1: fused reduce-scatter + Adam + all-gather over NVLink peer memory (default), or NCCL all-reduce + replicated optimizer")
@@ -87,6 +96,19 @@ class ClockSampler:
             if r & bit:
                 self.reasons.add(name)
 
+    def sample_now(self):
+        """one sample taken by the caller's thread: immediately before and immediately after the timed region, so a region shorter than
+        the polling period still carries its own clocks"""
+        if self.nvml is not None and not os.environ.get("NGP_NO_CLOCKS"):
+            try:
+                self._query()
+            except Exception:
+                pass
+
+    def _summary(self):
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": float(max(self.mx)) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml", "max_query_ms": round(self.max_query_ms, 3)}
+
     def _poll(self):
         # first sample 30 ms into the region, then every 200 ms (the recipe's nvidia-smi -lms 200): every query takes a driver lock
         # that can hold up the launches of all processes on the box for milliseconds, and a 0.6 ms step notices
@@ -121,8 +143,9 @@ class ClockSampler:
         if self.thread is not None:
             self.stop_flag = True
             self.thread.join(timeout=1.0)
-            return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": float(max(self.mx)) if self.mx else None,
-                    "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml", "max_query_ms": round(self.max_query_ms, 3)}
+            return self._summary()
+        if self.nvml is not None and self.sm:
+            return self._summary()
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -151,14 +174,19 @@ def measured_peaks():
 # ALGORITHMIC bytes (or flops) per STEP of each hot kernel, from the units it processes (per-unit figures
 # from SURVEY.md 8d): m = samples marched per step, b = samples in the compacted batch, r = rays, p = params,
 # g = occupancy-refresh positions per step (one refresh of 2^22 / 2^21 positions every 16 steps)
-def kernel_work(name, m, b, r, p, g=0.0):
+def kernel_work(name, m, b, r, p, g=0.0, world=1, peer=False):
+    if name == "adam_ema_kernel" and world > 1 and peer:
+        # the fused exchange kernel: this rank steps p / world parameters (36 B of local fp32 state + 6 B of EMA each), reads their
+        # gradients out of `world` arenas and stores the new fp16 weights into `world` arenas over NVLink (2 B each way per arena)
+        return ("hbm", (p / world) * (42 + 4 * (world - 1)))
     table = {
         "composite_count_kernel": ("hbm", m * (8 + 4) + r * 40),
         "composite_grad_kernel": ("hbm", b * (8 + 28 + 8 + 28 + 4) + r * 40),
         "march_count_kernel": ("hbm", r * (64 + 256)),
         "march_emit_kernel": ("hbm", m * 28 + r * (64 + 256)),
-        "hash_encode_fwd_kernel": ("hbm", (m + g) * 588),                 # the marched samples + the refresh positions; the batch reuses pass 1
-        "hash_encode_bwd_kernel": ("hbm", b * 588 + 2 * (p - 10240)),
+        # the table (24.4 MB at T = 2^19) is L2-resident by design: 512 of the 588 B per point are L2 gathers / reductions
+        "hash_encode_fwd_kernel": ("l2", (m + g) * 588),                  # the marched samples + the refresh positions; the batch reuses pass 1
+        "hash_encode_bwd_kernel": ("l2", b * 588 + 2 * (p - 10240)),
         "adam_ema_kernel": ("hbm", p * 42),
         "mlp_kernel": ("tensor", m * 18816 + b * 54400 + g * 6144),       # inference launch + training launch + density-only refresh
     }
@@ -360,6 +388,8 @@ def run_ours(args):
         clocks = ClockSampler(local_rank)
         barrier()
         launches0 = lib.ngp_launch_count()
+        if rank == 0:
+            clocks.sample_now()
         clocks.start()
         t0 = time.perf_counter()
         enq0 = ENQUEUE_MS
@@ -367,6 +397,8 @@ def run_ours(args):
         enqueue_ms = ENQUEUE_MS - enq0
         barrier()
         wall = time.perf_counter() - t0
+        if rank == 0:
+            clocks.sample_now()                 # the GPU has just finished the last step: still the clocks of the region
         clk = clocks.stop()
         launches = lib.ngp_launch_count() - launches0
         disturbed = (clk.get("max_query_ms") or 0.0) > 5.0 or enqueue_ms > 0.8 * dev_ms
