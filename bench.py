@@ -211,59 +211,265 @@ def make_scene_on_device(args, capi, scene, lib):
     return ogl, xf_np, fx, rgba8
 
 
-def time_reference_cuda(args, capi, lib, xf_np, fx, rgba8, steps, warmup):
-    """The UNMODIFIED reference (Testbed::train compiled for sm_100 by oracle/build_ref.sh) on the same scene, same base.json,
-    same train(16, batch) loop, timed by its own training_ms + training_prep_ms.  Returns its JSON dict, or a reason string."""
+HELD_OUT, RENDER_W, RENDER_H = 4, 1920, 1080
+C5_EDITS = {"samlper.aabb_scale": 16, "network.encoding.log2_hashmap_size": 22}
+C5_BATCH, C5_WARMUP = 1 << 20, 32
+C1_WORKLOAD = "configs[0]: hash-grid encode fwd / bwd (incl. the gradient-table clear), 2^18 uniformly random points, L=16 F=2 T=2^19, table L2-resident, median of 100"
+C5_WORKLOAD = "configs[4]: T=2^22 per level (150.6 MB fp16 table, spills L2), 2^20-sample batches, aabb_scale 16 (5 cascades), same 100 views"
+
+
+def held_out_poses(scene):
+    """4 cameras of the same rig that are not training views (another jitter seed)"""
+    return scene.sphere_cameras(HELD_OUT, 99)
+
+
+def write_config(path, **edits):
+    """base.json with some values replaced (the file carries // comments, which the reference's json reader accepts)"""
+    import re
+    text = re.sub(r"^\s*//.*$", "", open(os.path.join(ROOT, PKG, "configs", "base.json")).read(), flags=re.M)
+    cfg = json.loads(text)
+    for key, value in edits.items():
+        node = cfg
+        keys = key.split(".")
+        for k in keys[:-1]:
+            node = node[k]
+        node[keys[-1]] = value
+    json.dump(cfg, open(path, "w"))
+    return path
+
+
+def ground_truth_linear(args, capi, scene, lib, ogl):
+    """the held-out views as run.py's read_image would return their PNGs: float RGBA, sRGB -> linear, alpha premultiplied"""
+    import ctypes as C
+    import torch
+    run = importlib.import_module(PKG + ".run")
+    xf = torch.from_numpy(np.ascontiguousarray(scene.opengl_to_ngp(ogl), np.float32)).cuda()
+    fx = 0.5 * args.res / np.tan(0.5 * scene.CAMERA_ANGLE_X)
+    rgba8 = torch.empty((len(ogl), args.res, args.res, 4), dtype=torch.uint8, device="cuda")
+    capi.check(lib.ngp_render_procedural_views(C.c_void_p(torch.cuda.current_stream().cuda_stream), 2024, len(ogl), args.res, args.res, fx, fx,
+                                               C.c_void_p(xf.data_ptr()), C.c_void_p(rgba8.data_ptr())))
+    torch.cuda.synchronize()
+    img = rgba8.cpu().numpy().astype(np.float32) / 255.0
+    img[..., :3] = run.srgb_to_linear(img[..., :3]) * img[..., 3:4]
+    return img
+
+
+def psnr_db(images, gt):
+    """run.py:139-143: mean over the views of PSNR between clipped-sRGB render and clipped-sRGB ground truth (black background)"""
+    run = importlib.import_module(PKG + ".run")
+    vals = []
+    for a, r in zip(images, gt):
+        A, R = np.clip(run.linear_to_srgb(a[..., :3]), 0.0, 1.0), np.clip(run.linear_to_srgb(r[..., :3]), 0.0, 1.0)
+        vals.append(float(run.mse2psnr(run.compute_error("MSE", A, R))))
+    return float(np.mean(vals)), vals
+
+
+def stage_reference_dataset(args, capi, lib, xf_np, fx, rgba8, scene):
+    """the raw files ref_harness reads (same images, same cameras, base.json) + the held-out poses"""
     import ctypes as C
     import shutil
     import tempfile
     import torch
+    d = tempfile.mkdtemp(prefix="ngp_refbench_")
+    half = torch.empty(rgba8.shape, dtype=torch.int16, device="cuda")
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    capi.check(lib.ngp_from_rgba32(s, rgba8.numel() // 4, C.c_void_p(rgba8.data_ptr()), C.c_void_p(half.data_ptr())))
+    torch.cuda.synchronize()
+    half.cpu().numpy().tofile(os.path.join(d, "images.f16"))
+    del half
+    np.ascontiguousarray(xf_np, np.float32).tofile(os.path.join(d, "xforms.f32"))
+    with open(os.path.join(d, "meta.txt"), "w") as f:
+        f.write(f"{args.views} {args.res} {args.res} {float(np.float32(fx))!r} {float(np.float32(fx))!r} 0.33\n")
+    shutil.copy(os.path.join(ROOT, PKG, "configs", "base.json"), os.path.join(d, "config.json"))
+    np.ascontiguousarray(scene.opengl_to_ngp(held_out_poses(scene)), np.float32).tofile(os.path.join(d, "test_xforms.f32"))
+    return d
+
+
+def harness(*argv, timeout=900):
+    r = subprocess.run([REF_HARNESS] + [str(a) for a in argv], capture_output=True, text=True, timeout=timeout)
+    if r.returncode != 0:
+        return f"ref_harness {argv[0]} failed ({r.returncode}): {r.stderr[-300:]}"
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    return json.loads(lines[-1]) if lines else "ref_harness printed no result line"
+
+
+def time_reference_cuda(args, d, steps, warmup, extras=True):
+    """The UNMODIFIED reference (Testbed::train compiled for sm_100 by oracle/build_ref.sh) on the same scene, same base.json, the
+    same train(16, batch) loop for EXACTLY warmup + steps steps (calls of 16 and one remainder call), timed by its own
+    training_ms + training_prep_ms; then its render_frame on the held-out poses.  Returns its JSON dict, or a reason string."""
     if not (os.path.exists(REF_HARNESS) and os.access(REF_HARNESS, os.X_OK)):
         return "oracle/_ref/ref_harness not built"
-    d = tempfile.mkdtemp(prefix="ngp_refbench_")
+    scene = importlib.import_module(PKG + ".scene")
+    if extras:
+        return harness("benchsteps", d, steps, warmup, args.batch, args.res, RENDER_W, RENDER_H, scene.CAMERA_ANGLE_X)
+    return harness("benchsteps", d, steps, warmup, args.batch)
+
+
+def c1_inputs():
+    g = lambda shape, seed, lo, hi: (np.random.Generator(np.random.PCG64(seed)).random(shape, dtype=np.float32) * np.float32(hi - lo) + np.float32(lo))
+    n = 1 << 18
+    return n, g((n, 3), 1337, 0, 1), g(12196240, 43, -1e-4, 1e-4).astype(np.float16), (g((n, 32), 7, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
+
+
+def write_c1_inputs(d):
+    n, xyz, table, dy = c1_inputs()
+    xyz.tofile(os.path.join(d, "c1_xyz.f32")); table.view(np.uint16).tofile(os.path.join(d, "c1_table.f16")); dy.view(np.uint16).tofile(os.path.join(d, "c1_dy.f16"))
+
+
+def reference_extras(args, d, r, capi, lib, scene):
+    """render / psnr_db / c1 / c5 objects of the reference arm"""
+    out = {}
+    out["render"] = {"workload": f"configs[3]: {RENDER_W}x{RENDER_H} novel views, spp 1, {HELD_OUT} held-out poses", "mrays_per_s": r.get("render_mrays_per_s"),
+                     "ms_per_frame": r.get("render_ms_per_frame"), "frames_timed": r.get("render_frames_timed"),
+                     "timing": "wall clock around Testbed::render_frame, device synchronised on both sides"}
     try:
-        half = torch.empty(rgba8.shape, dtype=torch.int16, device="cuda")
-        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        capi.check(lib.ngp_from_rgba32(s, rgba8.numel() // 4, C.c_void_p(rgba8.data_ptr()), C.c_void_p(half.data_ptr())))
-        torch.cuda.synchronize()
-        half.cpu().numpy().tofile(os.path.join(d, "images.f16"))
-        del half
-        np.ascontiguousarray(xf_np, np.float32).tofile(os.path.join(d, "xforms.f32"))
-        with open(os.path.join(d, "meta.txt"), "w") as f:
-            f.write(f"{args.views} {args.res} {args.res} {float(np.float32(fx))!r} {float(np.float32(fx))!r} 0.33\n")
-        shutil.copy(os.path.join(ROOT, PKG, "configs", "base.json"), os.path.join(d, "config.json"))
-        calls, wcalls = max(1, -(-steps // CALL_STEPS)), max(1, -(-warmup // CALL_STEPS))
-        r = subprocess.run([REF_HARNESS, "bench", d, str(calls), str(wcalls), str(args.batch)], capture_output=True, text=True, timeout=900)
-        if r.returncode != 0:
-            return f"ref_harness failed ({r.returncode}): {r.stderr[-300:]}"
-        line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
-        return json.loads(line)
-    finally:
-        shutil.rmtree(d, ignore_errors=True)
+        gt = ground_truth_linear(args, capi, scene, lib, held_out_poses(scene))
+        imgs = [np.fromfile(os.path.join(d, f"ref_bench_render_0_{p}.f32"), np.float32).reshape(args.res, args.res, 4) for p in range(HELD_OUT)]
+        mean, per = psnr_db(imgs, gt)
+        out["psnr_db"] = {"value": mean, "per_view": per, "at_step": int(r.get("i_step", 0)), "views": f"{HELD_OUT} held-out {args.res}x{args.res} poses, spp 1"}
+    except Exception as e:
+        out["psnr_db"] = {"unavailable": f"{type(e).__name__}: {e}"}
+    try:                                        # configs[0]
+        c1d = os.path.join(d, "c1")
+        os.makedirs(c1d, exist_ok=True)
+        write_c1_inputs(c1d)
+        c1 = harness("c1", c1d, 100)
+        out["c1"] = {"workload": C1_WORKLOAD, "fwd_us": c1["fwd_us"], "bwd_us": c1["bwd_us"]} if isinstance(c1, dict) else {"unavailable": c1}
+    except Exception as e:
+        out["c1"] = {"unavailable": f"{type(e).__name__}: {e}"}
+    try:                                        # configs[4]: same images, the large-table cascaded model
+        c5d = os.path.join(d, "c5")
+        os.makedirs(c5d, exist_ok=True)
+        for f in ("images.f16", "xforms.f32", "meta.txt"):
+            os.symlink(os.path.join(d, f), os.path.join(c5d, f))
+        write_config(os.path.join(c5d, "config.json"), **C5_EDITS)
+        c5 = harness("benchsteps", c5d, args.c5_steps, C5_WARMUP, C5_BATCH)
+        out["c5"] = ({"workload": C5_WORKLOAD, "ms_per_step": c5["ms_per_step"], "samples_per_s": c5["samples_per_s"], "steps": args.c5_steps, "warmup": C5_WARMUP,
+                      "samples_marched_per_step": c5["marched_per_step"], "loss": c5["loss"]} if isinstance(c5, dict) else {"unavailable": c5})
+    except Exception as e:
+        out["c5"] = {"unavailable": f"{type(e).__name__}: {e}"}
+    return out
+
+
+def ours_c1(capi, lib):
+    """configs[0] through the C ABI, CUDA events on the launching stream"""
+    import ctypes as C
+    import torch
+    n, xyz, table, dy = c1_inputs()
+    desc, n_entries = capi.make_grid_desc(device_scales=True)
+    d_xyz, d_table, d_dy = torch.from_numpy(xyz).cuda(), torch.from_numpy(table.view(np.int16)).cuda(), torch.from_numpy(dy.view(np.int16)).cuda()
+    d_out, d_grad = torch.zeros(n * 32, dtype=torch.int16, device="cuda"), torch.zeros(2 * n_entries, dtype=torch.int16, device="cuda")
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    fwd = lambda: capi.check(lib.ngp_hash_encode_fwd(s, p(d_xyz), 3, n, p(d_table), C.byref(desc), p(d_out), 32, None))
+    bwd = lambda: capi.check(lib.ngp_hash_encode_bwd(s, p(d_xyz), 3, n, p(d_dy), 32, C.byref(desc), p(d_grad), 1))
+    out = {"workload": C1_WORKLOAD}
+    for name, fn in (("fwd_us", fwd), ("bwd_us", bwd)):
+        for _ in range(10):
+            fn()
+        ms = []
+        for _ in range(100):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record(); b.synchronize()
+            ms.append(a.elapsed_time(b))
+        out[name] = float(np.median(ms)) * 1e3
+    out["algorithmic_GBs"] = {"fwd": n * 588 / out["fwd_us"] / 1e3, "bwd": (n * 588 + 4 * n_entries) / out["bwd_us"] / 1e3}
+    return out
+
+
+def ours_render_and_psnr(args, tb, pyngp, capi, lib, scene, world, rank, barrier):
+    """configs[3] + PSNR on the held-out poses, with the weights as they are after the timed training region"""
+    ogl = held_out_poses(scene)
+    tb.background_color = [0.0, 0.0, 0.0, 1.0]
+    tb.fov = scene.CAMERA_ANGLE_X
+    out = {}
+    if rank == 0:
+        imgs = []
+        for m in ogl:
+            tb.set_nerf_camera_matrix(m)
+            imgs.append(np.array(tb.render(args.res, args.res, 1, False)))
+        mean, per = psnr_db(imgs, ground_truth_linear(args, capi, scene, lib, ogl))
+        out["psnr_db"] = {"value": mean, "per_view": per, "at_step": int(tb.training_buffer.i_step), "views": f"{HELD_OUT} held-out {args.res}x{args.res} poses, spp 1"}
+    # tile-sharded frame: rank r marches the rows [r H / N, (r + 1) H / N) and nothing is exchanged
+    if world > 1:
+        tb.set_render_rows(round(rank * RENDER_H / world), round((rank + 1) * RENDER_H / world))
+    tb.set_nerf_camera_matrix(ogl[0])
+    tb.render_frames_ms(RENDER_W, RENDER_H, 1, True)                 # allocation + first touch
+    ms, e2e_ms = [], []
+    for rep in range(2):
+        for m in ogl:
+            tb.set_nerf_camera_matrix(m)
+            barrier()
+            t = tb.render_frames_ms(RENDER_W, RENDER_H, 1, True)
+            if world > 1:
+                import torch
+                import torch.distributed as dist
+                tt = torch.tensor([t], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                t = float(tt[0])
+            ms.append(t)
+    for m in ogl:                                                      # the call a user makes: device -> host copy of the frame (band) included
+        tb.set_nerf_camera_matrix(m)
+        barrier()
+        t0 = time.perf_counter()
+        band = tb.render_band(RENDER_W, RENDER_H, 1, True) if world > 1 else tb.render(RENDER_W, RENDER_H, 1, True)
+        e2e_ms.append((time.perf_counter() - t0) * 1e3)
+    tb.set_render_rows(0, -1)
+    frame_ms = float(np.mean(ms))
+    out["render"] = {"workload": f"configs[3]: {RENDER_W}x{RENDER_H} novel views, spp 1, {HELD_OUT} held-out poses" + (f", {world} row bands (one per GPU, no collective)" if world > 1 else ""),
+                     "mrays_per_s": RENDER_W * RENDER_H / frame_ms / 1e3, "ms_per_frame": frame_ms, "frames_timed": len(ms),
+                     "timing": "wall clock around render_frame (ray generation -> tonemap), device synchronised on both sides, max over ranks",
+                     "e2e_ms_per_frame_with_d2h": float(np.mean(e2e_ms)), "d2h_bytes_per_frame": int(np.asarray(band).nbytes)}
+    return out
+
+
+def ours_c5(args, pyngp, np_rgba8, ogl, scene):
+    """configs[4] on the same images: a second Testbed with the large-table cascaded model, bounded to a few train() calls"""
+    import tempfile
+    import torch
+    cfg = write_config(os.path.join(tempfile.mkdtemp(prefix="ngp_c5_"), "config.json"), **C5_EDITS)
+    tb = pyngp.Testbed()
+    tb.load_model_config(cfg)
+    tb.load_training_data_from_memory(np_rgba8, ogl, scene.CAMERA_ANGLE_X, 0.33, [0.5, 0.5, 0.5])
+    train_steps(tb, C5_WARMUP, C5_BATCH)
+    torch.cuda.synchronize()
+    samples, marched, rays, dev_ms = train_steps(tb, args.c5_steps, C5_BATCH)
+    return {"workload": C5_WORKLOAD, "ms_per_step": dev_ms / args.c5_steps, "samples_per_s": samples / (dev_ms * 1e-3), "steps": args.c5_steps, "warmup": C5_WARMUP,
+            "samples_marched_per_step": marched / args.c5_steps, "n_params": int(tb.n_params), "loss": tb.training_buffer.loss}
 
 
 def run_reference_cuda(args):
     """--impl reference, CUDA kind: rank 0 times the reference's own CUDA build on GPU 0"""
+    import shutil
     import torch
     pkg = importlib.import_module(PKG)
     capi, scene = pkg.capi, importlib.import_module(PKG + ".scene")
     lib = capi.load()
     torch.cuda.set_device(0)
     _, xf_np, fx, rgba8 = make_scene_on_device(args, capi, scene, lib)
-    clocks = ClockSampler(0)
-    clocks.start()
-    r = time_reference_cuda(args, capi, lib, xf_np, fx, rgba8, args.steps, args.warmup)
-    clk = clocks.stop()
-    if not isinstance(r, dict):
-        return None, r
-    out = {"impl": "reference", "reference_kind": "cuda: unmodified reference (Testbed::train, tiny-cuda-nn) compiled for sm_100 by oracle/build_ref.sh, run as oracle/_ref/ref_harness",
-           "metric": METRIC, "value": r["samples_per_s"], "unit": UNIT, "n_gpus": 1, "steps": int(r["steps"]), "warmup": int(r["warmup_steps"]),
-           "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-           "config": config_dict(args, 1), "clocks": clk,
-           "e2e": {"value": r["samples_per_s"] * r["ms_per_step"] / r["wall_ms_per_step"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 12,
-                   "wall_ms_per_step": r["wall_ms_per_step"]},
-           "samples_marched_per_step": r["marched_per_step"], "rays_per_step": r["rays_per_step"], "loss": r["loss"]}
-    return out, None
+    d = stage_reference_dataset(args, capi, lib, xf_np, fx, rgba8, scene)
+    del rgba8
+    try:
+        clocks = ClockSampler(0)
+        clocks.sample_now()
+        clocks.start()
+        r = time_reference_cuda(args, d, args.steps, args.warmup, extras=not args.no_extras)
+        clocks.sample_now()
+        clk = clocks.stop()
+        if not isinstance(r, dict):
+            return None, r
+        out = {"impl": "reference", "reference_kind": "cuda: unmodified reference (Testbed::train, tiny-cuda-nn) compiled for sm_100 by oracle/build_ref.sh, run as oracle/_ref/ref_harness",
+               "metric": METRIC, "value": r["samples_per_s"], "unit": UNIT, "n_gpus": 1, "steps": int(r["steps"]), "warmup": int(r["warmup_steps"]),
+               "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+               "config": config_dict(args, 1), "clocks": clk,
+               "e2e": {"value": r["samples_per_s"] * r["ms_per_step"] / r["wall_ms_per_step"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 12,
+                       "wall_ms_per_step": r["wall_ms_per_step"]},
+               "samples_marched_per_step": r["marched_per_step"], "rays_per_step": r["rays_per_step"], "loss": r["loss"]}
+        if not args.no_extras:
+            out.update(reference_extras(args, d, r, capi, lib, scene))
+        return out, None
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
 
 
 def run_reference(args):
