@@ -49,10 +49,7 @@ def parse():
     p.add_argument("--timeline", default=None, help="write a per-launch timeline (json per rank) of two further train() calls with the march pipelined")
     p.add_argument("--dp-mode", default="peer", choices=["peer", "nccl"],
                    help="N > 1: fused reduce-scatter + Adam + all-gather over NVLink peer memory (default), or NCCL all-reduce + replicated optimizer")
-    p.add_argument("--ref-cuda", action="store_true",
-                   help="also time the reference's own CUDA build (oracle/_ref/ref_harness) right after ours and add it as a `reference_cuda` object; "
-                        "off by default: the reference arm proper is `--impl reference`, the only other place this file executes oracle/")
-    p.add_argument("--no-ref-cuda", action="store_true", help="(default now; kept so older command lines still parse)")
+    p.add_argument("--no-ref-cuda", action="store_true", help="(kept so older command lines still parse: the reference's CUDA build is timed by --impl reference only)")
     p.add_argument("--reference-kind", default="auto", choices=["auto", "cuda", "cpu"],
                    help="--impl reference: the reference's CUDA build when oracle/_ref/ref_harness exists (auto/cuda), or the CPU oracle port")
     return p.parse_args()
@@ -488,8 +485,8 @@ def run_reference(args):
     if cuda_line is not None:
         # the CPU port is still reported beside it, on a bounded sample
         cb = pipeline.time_cpu_steps(n_steps=4, n_rays=2048, warmup=1, n_views=8, res=200, batch=args.batch)
-        cuda_line["cpu_baseline"] = {"value": cb["samples_per_s"], "unit": UNIT, "cores": cores, "kind": "port",
-                                     "sample": f"4 steps of 2048 rays ({cb['samples_per_step']:.0f} samples/step, {cb['seconds']:.1f} s) on 8 procedural views 200x200, analytic occupancy, same model"}
+        cuda_line["cpu_baseline"] = {"value": cb["samples_per_s"], "unit": UNIT, "cores": cores, "kind": "port", "workload": "reduced (see sample)",
+                                     "sample": f"REDUCED WORKLOAD: 4 steps of 2048 rays ({cb['samples_per_step']:.0f} samples/step, {cb['seconds']:.1f} s) on 8 procedural views 200x200, analytic occupancy, same model"}
         print(json.dumps(cuda_line), flush=True)
         return
     budget_s = 150.0
@@ -555,8 +552,7 @@ def run_ours(args):
     ogl, xf_np, fx, rgba8 = make_scene_on_device(args, capi, scene, lib)
     host_rgba8 = torch.empty(rgba8.shape, dtype=torch.uint8, pin_memory=True)
     host_rgba8.copy_(rgba8)
-    if not (args.gpus == 1 and args.ref_cuda):
-        del rgba8
+    del rgba8
     np_rgba8 = host_rgba8.numpy()
 
     tb = pyngp.Testbed()
@@ -620,6 +616,17 @@ def run_ours(args):
         st_timed = np.zeros((2, 4096), np.uint64)          # read now: the profiling region below leaves stamps of its own
         capi.check(lib.ngp_peer_stamps_read(st_timed.ctypes.data_as(C.c_void_p)))
 
+    # ---- the rest of BASELINE.json's metric, on the weights as the timed region left them: PSNR on held-out poses, configs[3] render ----
+    loss_after_timed = tb.training_buffer.loss
+    extras = {}
+    if not args.no_extras:
+        try:
+            extras = ours_render_and_psnr(args, tb, pyngp, capi, lib, scene, world, rank, barrier)
+        except Exception as e:
+            if world > 1:
+                raise                           # a rank that dropped out of the banded render would leave the others in a collective
+            extras = {"render": {"unavailable": f"{type(e).__name__}: {e}"}}
+
     # ---- per-kernel durations, live, with CUDA events on the launching stream (same workload, a further timed region) ----
     prof_steps = min(args.steps, 64)
     capi.check(lib.ngp_kernel_timing_enable(1, 64 * prof_steps + 4096))
@@ -667,6 +674,20 @@ def run_ours(args):
         return
 
     hbm_peak, tf_peak, peak_src = measured_peaks()
+    # measured ceilings of the L1TEX / L2 path ("L2 peak is not in MEASURED_PEAKS.json -> must be measured on the box"):
+    # coalesced 16-byte reads of a 32 MB L2-resident buffer, and scattered gathers / reductions with every lane on its own line
+    probe = {}
+    try:
+        scratch = torch.zeros(32 << 20, dtype=torch.uint8, device="cuda")
+        sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        for kind, key in ((0, "l2_stream_read_GBs"), (1, "scattered_gather_4B_G_per_s"), (2, "scattered_gather_16B_G_per_s"),
+                          (3, "scattered_red_f16x2_G_per_s"), (4, "scattered_red_v4_f16x2_G_per_s")):
+            val = C.c_double(0.0)
+            capi.check(lib.ngp_l2_probe(sp, kind, C.c_void_p(scratch.data_ptr()), scratch.numel(), 5, C.byref(val)))
+            probe[key] = val.value
+        del scratch
+    except Exception as e:
+        probe = {"unavailable": str(e)}
     total_kernel_ms = sum(v[0] for v in kt.values())
     # dominant kernel of the STEP: the march kernels run one step ahead on the look-ahead stream, underneath the others, so they
     # are listed in kernels_ms_per_step (this profiling region runs them serially) but cannot be the kernel that bounds the step
@@ -675,7 +696,7 @@ def run_ours(args):
     m, b, r = p_marched / prof_steps, p_samples / prof_steps, p_rays / prof_steps
     first = args.warmup + args.steps                                     # index of the first profiled step
     g = sum((1 << 22) if (first + k) < 256 else (1 << 21) for k in range(0, prof_steps, CALL_STEPS)) / prof_steps
-    work = kernel_work(name, m, b, r, tb.n_params, g)
+    work = kernel_work(name, m, b, r, tb.n_params, g, world, args.dp_mode == "peer")
     launches_per_step = k_n / prof_steps
     total_kernel_ms = sum(v[0] for v in on_path.values())
     roofline = {"kernel": name, "share_of_kernel_time": k_ms / total_kernel_ms, "avg_launch_us": k_ms / k_n * 1e3, "launches_per_step": launches_per_step}
@@ -683,8 +704,11 @@ def run_ours(args):
         bound, per_step = work
         per_launch = per_step / launches_per_step
         achieved = per_launch / (k_ms / k_n * 1e-3)
-        peak = hbm_peak if bound == "hbm" else tf_peak
-        achieved = achieved / 1e9 if bound == "hbm" else achieved / 1e12
+        l2_peak = probe.get("l2_stream_read_GBs")
+        if bound == "l2" and not l2_peak:
+            bound = "hbm"                       # the probe failed: fall back to the conservative denominator
+        peak = hbm_peak if bound == "hbm" else l2_peak if bound == "l2" else tf_peak
+        achieved = achieved / 1e12 if bound == "tensor" else achieved / 1e9
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
@@ -693,8 +717,14 @@ def run_ours(args):
             units = {"hash_encode_fwd_kernel": m + g, "hash_encode_bwd_kernel": b, "adam_ema_kernel": tb.n_params}.get(name)
             if t and units:
                 traffic = t["dram_bytes_per_unit"] * units / launches_per_step
-        roofline.update({"bound": bound, "achieved": achieved, "peak": peak, "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": achieved / peak,
+        roofline.update({"bound": bound, "achieved": achieved, "peak": peak, "unit": "TFLOP/s" if bound == "tensor" else "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "algorithmic_per_launch": per_launch})
+        if bound == "l2":
+            roofline["peak_source"] = "ngp_l2_probe kind 0 measured in this run: coalesced 16-byte reads of a 32 MB L2-resident buffer (MEASURED_PEAKS.json has no L2 figure)"
+            roofline["hbm"] = {"peak": hbm_peak, "frac": achieved / hbm_peak, "peak_source": peak_src,
+                               "note": "HBM copy peak for comparison; measured DRAM traffic (`traffic`) is a fraction of the algorithmic bytes: the table stays in L2"}
+        if name == "adam_ema_kernel" and world > 1 and args.dp_mode == "peer":
+            roofline["note"] = "fused exchange kernel (reduce-scatter + Adam + all-gather over NVLink peer memory): its duration includes the wait for the slowest rank's gradient flag"
     roofline["kernels_ms_per_step"] = {k: v[0] / prof_steps for k, v in sorted(kt.items(), key=lambda kv: -kv[1][0])}
 
     out = {"metric": METRIC, "value": samples / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -704,18 +734,13 @@ def run_ours(args):
                    "d2h_bytes_per_step": (3 * 4 * CALL_STEPS + 4) / CALL_STEPS, "wall_ms_per_step": wall / args.steps * 1e3, "dataset_upload_ms": t_upload * 1e3,
                    "host_enqueue_ms_per_step": enqueue_ms / args.steps},
            "roofline": roofline,
-           "samples_marched_per_step": marched / args.steps / max(world, 1), "rays_per_step": rays / args.steps / max(world, 1), "loss": tb.training_buffer.loss}
-    # ---- the encoder kernels against MEASURED ceilings of the L1TEX / L2 path (the table is L2-resident: SURVEY.md 8d) ----
+           "samples_marched_per_step": marched / args.steps / max(world, 1), "rays_per_step": rays / args.steps / max(world, 1),
+           "loss": loss_after_timed, "loss_scope": "rank 0's rays, last train() call of the timed region"}
+    out.update(extras)
+    # ---- the encoder kernels against the measured ceilings, access by access ----
     try:
-        scratch = torch.zeros(32 << 20, dtype=torch.uint8, device="cuda")
-        sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        probe = {}
-        for kind, key in ((0, "l2_stream_read_GBs"), (1, "scattered_gather_4B_G_per_s"), (2, "scattered_gather_16B_G_per_s"),
-                          (3, "scattered_red_f16x2_G_per_s"), (4, "scattered_red_v4_f16x2_G_per_s")):
-            val = C.c_double(0.0)
-            capi.check(lib.ngp_l2_probe(sp, kind, C.c_void_p(scratch.data_ptr()), scratch.numel(), 5, C.byref(val)))
-            probe[key] = val.value
-        del scratch
+        if "unavailable" in probe:
+            raise RuntimeError(probe["unavailable"])
         k = roofline["kernels_ms_per_step"]
         # accesses the kernels issue per point and level: 4 x-pairs, 3 of 4 served by one 16-byte access, the 4th by two 4-byte ones
         per_point = 16 * 5
@@ -735,17 +760,19 @@ def run_ours(args):
         out["l2_roofline"] = {"unavailable": str(e)}
     if peer_trace:
         out["peer_trace"] = peer_trace
-    if args.gpus == 1 and args.ref_cuda:
-        # the reference's own CUDA build on the same GPU, same scene, right after ours (reported, not part of any timed region)
-        r = time_reference_cuda(args, capi, lib, xf_np, fx, rgba8, args.steps, args.warmup)
-        out["reference_cuda"] = r if isinstance(r, dict) else {"unavailable": r}
-        if isinstance(r, dict):
-            out["reference_cuda"]["speedup"] = out["value"] / r["samples_per_s"]
+    if args.gpus == 1 and not args.no_extras:
+        for key, fn in (("c1", lambda: ours_c1(capi, lib)), ("c5", lambda: ours_c5(args, pyngp, np_rgba8, ogl, scene))):
+            try:
+                if key == "c5":
+                    del tb                      # the configs[1] model and its buffers make room for the 2^22 / 2^20 configuration
+                out[key] = fn()
+            except Exception as e:
+                out[key] = {"unavailable": f"{type(e).__name__}: {e}"}
     if args.gpus == 1 and not args.no_cpu_baseline:
         from oracle import pipeline                      # the CPU restatement, timed as the baseline only
         cb = pipeline.time_cpu_steps(n_steps=4, n_rays=2048, warmup=1, n_views=8, res=200, batch=args.batch)
-        out["cpu_baseline"] = {"value": cb["samples_per_s"], "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
-                               "sample": f"4 steps of 2048 rays ({cb['samples_per_step']:.0f} samples/step, {cb['seconds']:.1f} s) on 8 procedural views 200x200, analytic occupancy, same model"}
+        out["cpu_baseline"] = {"value": cb["samples_per_s"], "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port", "workload": "reduced (see sample)",
+                               "sample": f"REDUCED WORKLOAD: 4 steps of 2048 rays ({cb['samples_per_step']:.0f} samples/step, {cb['seconds']:.1f} s) on 8 procedural views 200x200, analytic occupancy, same model"}
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
