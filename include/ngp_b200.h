@@ -204,6 +204,18 @@ int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays
                         const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
                         uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,
                         const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, void* d_scan_ws, uint32_t* d_src_index);
+/* ngp_composite_train WITHOUT any allocation on either side: no counterpart in the reference -- added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Identical launches and results; the per-ray scratch (what d_scan_ws is above) lives in a file-scope `static __device__` array of
+ * the library, sized for NGP_COMPOSITE_STATIC_MAX_RAYS rays (1.5 MB, held by every GPU that loads the library until exit).  Returns
+ * -1 with a message when n_rays exceeds that maximum.  Calls no cudaMalloc / cudaFree / allocating routine.  The array is shared by
+ * all calls and keeps the last call's contents (nothing in it has to start at zero); calls that overlap on one GPU -- two streams,
+ * two threads -- race on it: serialise them, or use ngp_composite_train with separate workspaces. */
+#define NGP_COMPOSITE_STATIC_MAX_RAYS 65536u
+int ngp_composite_train_static(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
+                               const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
+                               uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,
+                               const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, uint32_t* d_src_index);
 /* fill_rollover_and_rescale + fill_rollover (tiny-cuda-nn/common_device.h:485-505; testbed.cu:398-404) */
 int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted,
                  uint32_t* d_src_index /* optional, rolled over like the coordinates */);

@@ -86,6 +86,7 @@ SIGNATURES = {
     "ngp_generate_coords_from_rays": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, u32, vp, vp, vp]),
     "ngp_composite_workspace_bytes": (sz, [u32]),
     "ngp_composite_train": (i32, [vp, C.POINTER(RenderCfg), u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, u64, u64, vp, vp, vp]),
+    "ngp_composite_train_static": (i32, [vp, C.POINTER(RenderCfg), u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, u64, u64, vp, vp]),
     "ngp_rollover": (i32, [vp, u32, vp, vp, u32, vp, vp]),
     "ngp_composite_infer": (i32, [vp, C.POINTER(RenderCfg), u32, vp, u32, u32, vp, vp, vp, vp, u32, i32, f32, f32, C.POINTER(f32), f32]),
     "ngp_compact_rays": (i32, [vp, u32, vp, vp, vp, vp, vp, vp, vp, vp, vp]),

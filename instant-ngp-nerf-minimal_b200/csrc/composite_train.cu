@@ -5,6 +5,7 @@
 // ~260 k busy lanes.  The compacted base of each ray is an exclusive scan in ray order (bit-reproducible) instead of one
 // global atomicAdd per ray.  HBM-bound: 12 B / marched sample in the forward launch, 72 B / trained sample in the backward one.
 #include "composite.cuh"
+#include <mutex>
 
 namespace ngp {
 
@@ -278,6 +279,44 @@ extern "C" int ngp_composite_train(void* stream, const ngp_render_cfg* cfg, uint
 		(const Coordinate*)d_coords, (Coordinate*)d_coords_compacted, (const __half*)d_rgbsigma, (__half*)d_dloss, padded_width, d_mean_density, rng, d_loss,
 		tmp, n_used, cbase, d_src_index));
 	return check_launch("composite_train");
+}
+
+// ---- no-allocation variant (no counterpart in the reference) ----
+// Same launches as ngp_composite_train, with the per-ray scratch in a file-scope device array instead of a caller-provided buffer,
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).  Every GPU that loads the library holds the
+// array (1.5 MB) until exit.  In host code the array's name is a host-side stand-in, not a device address: the address is looked
+// up once per device with cudaGetSymbolAddress and cached.  All calls share the array: calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned char g_composite_scratch[(size_t)NGP_COMPOSITE_STATIC_MAX_RAYS * (sizeof(RayTmp) + 8) + 256];
+
+static void* composite_scratch_address() {
+	static std::mutex lock;
+	static void* address[64] = {};
+	int dev = -1;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("ngp_composite_train_static: cudaGetDevice failed or device index above 63"); return nullptr; }
+	std::lock_guard<std::mutex> guard(lock);
+	if (!address[dev]) {
+		void* p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress(&p, g_composite_scratch);        // with `dev` current: this device's copy of the array
+		if (e != cudaSuccess || !p) { set_error("ngp_composite_train_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e)); return nullptr; }
+		address[dev] = p;
+	}
+	return address[dev];
+}
+
+extern "C" int ngp_composite_train_static(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, uint32_t max_compacted, const uint32_t* d_ray_counter,
+                                          const float* d_rays_rgba, uint32_t* d_numsteps, const float* d_coords, float* d_coords_compacted,
+                                          uint32_t* d_compacted_counter, const void* d_rgbsigma, void* d_dloss, uint32_t padded_width,
+                                          const float* d_mean_density, uint64_t rng_state, uint64_t rng_inc, float* d_loss, uint32_t* d_src_index) {
+	if (n_rays > NGP_COMPOSITE_STATIC_MAX_RAYS) {
+		set_error("ngp_composite_train_static: n_rays = %u exceeds the static scratch (NGP_COMPOSITE_STATIC_MAX_RAYS = %u); use ngp_composite_train with a caller-owned workspace", n_rays, NGP_COMPOSITE_STATIC_MAX_RAYS);
+		return -1;
+	}
+	static_assert(sizeof(g_composite_scratch) >= (size_t)NGP_COMPOSITE_STATIC_MAX_RAYS * (sizeof(RayTmp) + 8) + 256, "scratch covers the maximum");
+	void* ws = composite_scratch_address();
+	if (!ws) return -2;
+	// nothing in the scratch has to start at zero: composite_count_kernel writes every slot the later launches read
+	return ngp_composite_train(stream, cfg, n_rays, max_compacted, d_ray_counter, d_rays_rgba, d_numsteps, d_coords, d_coords_compacted, d_compacted_counter, d_rgbsigma,
+	                           d_dloss, padded_width, d_mean_density, rng_state, rng_inc, d_loss, ws, d_src_index);
 }
 
 extern "C" int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_counter, void* d_dloss, uint32_t padded_width, float* d_coords_compacted, uint32_t* d_src_index) {
