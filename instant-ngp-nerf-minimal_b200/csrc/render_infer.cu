@@ -41,8 +41,10 @@ __global__ void __launch_bounds__(128) composite_infer_kernel(
 				// through the density activation, the normal points towards decreasing density
 				const float k = -net_to_density_d(raw[3], c.density_activation);
 				const float nx = k * co.px, ny = k * co.py, nz = k * co.pz;
-				const float inv = 1.0f / sqrtf(nx * nx + ny * ny + nz * nz);
-				r = nx * inv; g = ny * inv; b = nz * inv;
+				// Eigen's normalized(): divide by the norm when the squared norm is positive, else leave the (zero) vector as it is
+				const float n2 = nx * nx + ny * ny + nz * nz;
+				r = nx; g = ny; b = nz;
+				if (n2 > 0.f) { const float nn = sqrtf(n2); r = nx / nn; g = ny / nn; b = nz / nn; }
 			}
 		}
 		l.x += r * w; l.y += g * w; l.z += b * w; l.w += w;
@@ -89,8 +91,9 @@ __global__ void shade_kernel(uint32_t n_hit_max, const uint32_t* __restrict__ n_
 	float4 t = rgba[i];
 	const RayPayload p = payloads[i];
 	if (render_mode == 2) {          // testbed.cu:463-465: accumulated normal -> unit length -> [0, 1], premultiplied
-		const float inv = 1.0f / sqrtf(t.x * t.x + t.y * t.y + t.z * t.z);
-		t.x = (0.5f * (t.x * inv) + 0.5f) * t.w; t.y = (0.5f * (t.y * inv) + 0.5f) * t.w; t.z = (0.5f * (t.z * inv) + 0.5f) * t.w;
+		const float n2 = t.x * t.x + t.y * t.y + t.z * t.z;      // Eigen's normalized(): a zero vector stays zero (no 0 / 0)
+		if (n2 > 0.f) { const float nn = sqrtf(n2); t.x /= nn; t.y /= nn; t.z /= nn; }
+		t.x = (0.5f * t.x + 0.5f) * t.w; t.y = (0.5f * t.y + 0.5f) * t.w; t.z = (0.5f * t.z + 0.5f) * t.w;
 	}
 	if (render_mode == 6) { const float col = (float)p.n_steps / 128; t = make_float4(col, col, col, 1.0f); }
 	if (!train_in_linear && render_mode == 1) { t.x = srgb_to_linear(t.x); t.y = srgb_to_linear(t.y); t.z = srgb_to_linear(t.z); }
