@@ -3,7 +3,8 @@
  * Drop-in boundary for the reference's internal/{sampler,network,render} modules and the tiny-cuda-nn
  * objects they call (file:line below are relative to the reference tree).  Plain pointers and sizes only:
  * every pointer named d_* is DEVICE memory owned by the caller, every call is asynchronous on `stream`
- * (a cudaStream_t passed as void*), nothing allocates, nothing synchronises with the host.
+ * (a cudaStream_t passed as void*), nothing allocates, nothing synchronises with the host (one set-up call,
+ * ngp_grid_desc_device_scales, waits for its own 128-byte result and says so).
  * Return value: 0 on success, <0 on error (message via ngp_last_error()).  There is no CPU fallback.
  */
 #ifndef NGP_B200_H
@@ -95,8 +96,9 @@ int ngp_l2_probe(void* stream, int kind, void* d_table, uint64_t table_bytes, ui
 uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, uint32_t log2_hashmap_size, uint32_t base_resolution, float per_level_scale);
 /* replaces desc->scales / resolutions by what the reference's kernels evaluate per thread ON THE DEVICE (grid.h:157-158: exp2f ->
  * MUFU.EX2, one FFMA): an ulp away from the host value on some levels.  Offsets are untouched (the reference sizes the levels on
- * the host, grid.h:497-510).  Allocates 64 bytes, launches one tiny kernel on the default stream and synchronises: call once. */
-int ngp_grid_desc_device_scales(ngp_grid_desc* desc, uint32_t base_resolution, float per_level_scale);
+ * the host, grid.h:497-510).  Set-up call: launches one tiny kernel on `stream` into d_scratch (NGP_MAX_LEVELS floats of device
+ * memory owned by the caller), copies the result back and WAITS for it (the one entry point that synchronises `stream`). */
+int ngp_grid_desc_device_scales(ngp_grid_desc* desc, uint32_t base_resolution, float per_level_scale, void* stream, float* d_scratch);
 /* replaces NGPNetwork::auto_determine_grid_parameters (internal/network/ngp_network.h:597-641) */
 float ngp_auto_per_level_scale(float desired_resolution, uint32_t base_resolution, uint32_t n_levels);
 
@@ -108,9 +110,6 @@ int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t stride_floats
  * then scatters w*dL/dy with warp-aggregated half2 atomics. */
 int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
                         const ngp_grid_desc* desc, void* d_grad, int zero_first);
-/* the same scatter restricted to the levels [level_begin, level_end), accumulating into d_grad (never zeroes it) */
-int ngp_hash_encode_bwd_levels(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
-                               const ngp_grid_desc* desc, void* d_grad, uint32_t level_begin, uint32_t level_end);
 
 /* ---- network ---------------------------------------------------------------------------------- */
 /* d_params: fp16 arena [NGP_MLP_PARAMS | grid table], reference order (ngp_network.h:496-541). */
@@ -138,17 +137,6 @@ int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const voi
 int ngp_network_train_reuse(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
                             const void* d_dloss, void* d_rgbsigma, void* d_grads, const void* d_encoded, uint32_t n_encoded /* = m; indices are clamped to it */,
                             const uint32_t* d_src_index, void* d_workspace, size_t workspace_bytes);
-/* ngp_network_train_reuse with control over the gradient arena and the encoder backward's schedule.
- * zero_first = 0: the caller guarantees the grid part of d_grads is already zero (ngp_optimizer_step_range leaves it so), which
- * saves a 24 MB memset and a launch boundary per step.
- * ev_fine_done (a cudaEvent_t, may be NULL): when given, the encoder backward runs as two launches -- levels [fine_level_begin, L)
- * first, then the event is recorded on the stream, then levels [0, fine_level_begin) -- so that an optimizer launch on another
- * stream can start on the fine levels' parameters early.  Measured on B200 this overlap LOSES 35 us per step (the optimizer's
- * 400 MB stream evicts the L2-resident gradient table the scatter depends on); the Testbed leaves it off. */
-int ngp_network_train_reuse_phased(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
-                                   const void* d_dloss, void* d_rgbsigma, void* d_grads, const void* d_encoded, uint32_t n_encoded,
-                                   const uint32_t* d_src_index, void* d_workspace, size_t workspace_bytes,
-                                   uint32_t fine_level_begin, void* ev_fine_done, int zero_first);
 /* the two MLPs alone on a precomputed encoding (tests, profiling): enc [n][32] fp16 */
 int ngp_mlp_inference(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, void* d_rgbsigma);
 int ngp_mlp_train(void* stream, const void* d_enc, const float* d_coords, uint32_t n, const void* d_mlp_params, const void* d_dloss,
@@ -240,12 +228,6 @@ int ngp_init_params(void* stream, uint64_t* rng_state, uint64_t rng_inc, uint64_
 /* Trainer::optimizer_step (trainer.h:198) -> ExponentialDecay -> Adam -> EMA, one fused pass.  step = Adam step count BEFORE this step. */
 int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, uint64_t n_params, uint64_t n_matrix_params, uint32_t step, float learning_rate,
                        float* d_w32, void* d_w16, const void* d_g16, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16);
-/* The same update for the parameters [begin, end) only (all pointers are the bases of the whole arenas; begin a multiple of 8).
- * Calls on disjoint ranges with the same step / learning rate compose to ngp_optimizer_step exactly (the update is elementwise),
- * so ranges whose gradients are final early can be stepped on another stream.  zero_gradients != 0: the consumed gradients are
- * overwritten with zero, leaving the arena ready for the next accumulation. */
-int ngp_optimizer_step_range(void* stream, const ngp_optimizer_cfg* cfg, uint64_t begin, uint64_t end, uint64_t n_matrix_params, uint32_t step, float learning_rate,
-                             float* d_w32, void* d_w16, void* d_g16, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16, int zero_gradients);
 /* ---- data-parallel optimizer over NVLink peer memory ------------------------------------------------
  * One process per GPU.  Instead of "all-reduce the gradient arena, then every rank runs the whole optimizer", rank r owns the
  * parameter range [shard_begin, shard_end): ONE kernel waits until every rank has published its gradients, sums the shard's

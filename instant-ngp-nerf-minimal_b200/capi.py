@@ -59,17 +59,15 @@ SIGNATURES = {
     "ngp_l2_probe": (i32, [vp, i32, vp, u64, u32, vp]),
     "ngp_grid_desc_init": (u32, [C.POINTER(GridDesc), u32, u32, u32, f32]),
     "ngp_auto_per_level_scale": (f32, [f32, u32, u32]),
-    "ngp_grid_desc_device_scales": (i32, [C.POINTER(GridDesc), u32, f32]),
+    "ngp_grid_desc_device_scales": (i32, [C.POINTER(GridDesc), u32, f32, vp, vp]),
     "ngp_hash_encode_fwd": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, u32, vp]),
     "ngp_hash_encode_bwd": (i32, [vp, vp, u32, u32, vp, u32, C.POINTER(GridDesc), vp, i32]),
-    "ngp_hash_encode_bwd_levels": (i32, [vp, vp, u32, u32, vp, u32, C.POINTER(GridDesc), vp, u32, u32]),
     "ngp_network_workspace_bytes": (sz, [u32]),
     "ngp_network_inference": (i32, [vp, vp, u32, vp, vp, C.POINTER(GridDesc), vp, vp, sz]),
     "ngp_network_density": (i32, [vp, vp, u32, u32, vp, C.POINTER(GridDesc), vp, vp, sz]),
     "ngp_network_input_gradient": (i32, [vp, vp, u32, vp, vp, C.POINTER(GridDesc), vp, sz]),
     "ngp_network_train": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, sz]),
     "ngp_network_train_reuse": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, u32, vp, vp, sz]),
-    "ngp_network_train_reuse_phased": (i32, [vp, vp, u32, vp, C.POINTER(GridDesc), vp, vp, vp, vp, u32, vp, vp, sz, u32, vp, i32]),
     "ngp_mlp_inference": (i32, [vp, vp, vp, u32, vp, vp]),
     "ngp_mlp_train": (i32, [vp, vp, vp, u32, vp, vp, vp, vp, vp]),
     "ngp_mark_untrained_grid": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), u32, vp, vp]),
@@ -95,7 +93,6 @@ SIGNATURES = {
     "ngp_tonemap": (i32, [vp, u32, f32, C.POINTER(f32), vp, i32, i32, i32, vp]),
     "ngp_init_params": (i32, [vp, C.POINTER(u64), u64, u64, vp, vp]),
     "ngp_optimizer_step": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u32, f32, vp, vp, vp, vp, vp, vp, vp]),
-    "ngp_optimizer_step_range": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u64, u32, f32, vp, vp, vp, vp, vp, vp, vp, i32]),
     "ngp_peer_publish_gradients": (i32, [vp, C.POINTER(PeerSet), u32]),
     "ngp_optimizer_step_sharded": (i32, [vp, C.POINTER(OptimizerCfg), u64, u64, u64, u32, f32, vp, vp, vp, vp, vp, C.POINTER(PeerSet), u32, vp]),
     "ngp_peer_wait_weights": (i32, [vp, C.POINTER(PeerSet), u32]),
@@ -146,7 +143,9 @@ def make_grid_desc(n_levels=16, log2_hashmap_size=19, base_resolution=16, per_le
     if n_entries == 0:
         raise NgpError(lib.ngp_last_error().decode())
     if device_scales:
-        check(lib.ngp_grid_desc_device_scales(C.byref(d), base_resolution, per_level_scale))
+        import torch                                     # device memory only: the scratch the set-up call writes its 32 scales to
+        scratch = torch.zeros(32, dtype=torch.float32, device="cuda")
+        check(lib.ngp_grid_desc_device_scales(C.byref(d), base_resolution, per_level_scale, None, C.c_void_p(scratch.data_ptr())))
     return d, n_entries
 
 

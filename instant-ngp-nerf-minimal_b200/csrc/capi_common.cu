@@ -30,8 +30,7 @@ static std::vector<TimedLaunch> g_pool;
 static size_t g_pool_used = 0;
 
 bool chained_launch_enabled() {
-	static const bool on = !(getenv("NGP_PDL") && getenv("NGP_PDL")[0] == '0');
-	return on && !g_timing;          // per-kernel timing wants each kernel alone between its two events
+	return !g_timing;          // per-kernel timing wants each kernel alone between its two events
 }
 
 KernelTimer::KernelTimer(const char* name, cudaStream_t s) : slot(-1), stream(s) {

@@ -32,7 +32,7 @@ struct KernelTimer {
 // calls chain_enter() as its FIRST statement: it blocks until the preceding grid has completed and its writes are visible,
 // then lets its own successor start launching.  Waiting before triggering keeps at most two grids in flight, and because a
 // grid only triggers after all its CTAs have passed the wait, completion is transitive along the chain.
-bool chained_launch_enabled();     // NGP_PDL=0 turns the attribute off (plain stream order)
+bool chained_launch_enabled();     // off while per-kernel timing is enabled (each kernel alone between its two events)
 template <typename... Exp, typename... Act>
 inline cudaError_t launch_chained(void (*kernel)(Exp...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Act&&... args) {
 	cudaLaunchConfig_t cfg = {};

@@ -43,11 +43,10 @@ __device__ __forceinline__ void pos_fract(float x, float scale, uint32_t& g, flo
 	w = p - f;
 }
 
-// WIDTH: 0 = one 4-byte gather per corner; 1 = x-adjacent corners share an aligned 8-byte load when the lower index is even;
-// 2 = they share an aligned 16-byte load whenever both fall into one group of four entries (3 cases out of 4).  The kernel is
-// bound by the tag stage of L1TEX -- one look-up per lane and instruction once every lane hits its own line -- so what counts
-// is the number of gather instructions per level (8 -> 6 -> 5), not the bytes they return.
-template <bool WRITE_INDICES, int WIDTH = 2>
+// x-adjacent corners share one aligned 16-byte load whenever both fall into one group of four entries (3 cases out of 4).  The kernel
+// is bound by the tag stage of L1TEX -- one look-up per lane and instruction once every lane hits its own line -- so what counts
+// is the number of gather instructions per level (8 with 4-byte loads, 6 with 8-byte pairs, 5 here), not the bytes they return.
+template <bool WRITE_INDICES>
 __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n, const uint32_t* __restrict__ n_valid,
 	const __half2* __restrict__ table, const __grid_constant__ ngp_grid_desc desc,
@@ -76,10 +75,7 @@ __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 		// gx ^ h and (gx+1) ^ h differ in bit 0 only when gx is even; dense: e and e+1).  One aligned 8-byte load then brings
 		// both, and only the other half of the lanes issue a second gather: a quarter fewer L1 wavefronts per level.
 		__half2 v[8];
-		if (WIDTH == 0) {
-			#pragma unroll
-			for (int c = 0; c < 8; ++c) v[c] = __ldg(grid + e[c]);
-		} else if (WIDTH == 2) {
+		{
 			uint4 q[4];
 			#pragma unroll
 			for (int c = 0; c < 8; c += 2) q[c >> 1] = __ldg(reinterpret_cast<const uint4*>(grid) + (e[c] >> 2));
@@ -94,17 +90,6 @@ __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 					v[c + 1] = *reinterpret_cast<const __half2*>(&b);
 				} else v[c + 1] = __ldg(grid + e[c + 1]);
 			}
-		} else {
-		uint2 pr[4];
-		#pragma unroll
-		for (int c = 0; c < 8; c += 2) pr[c >> 1] = __ldg(reinterpret_cast<const uint2*>(grid) + (e[c] >> 1));
-		#pragma unroll
-		for (int c = 0; c < 8; c += 2) {
-			const uint32_t lo = (e[c] & 1u) ? pr[c >> 1].y : pr[c >> 1].x, buddy = (e[c] & 1u) ? pr[c >> 1].x : pr[c >> 1].y;
-			v[c] = *reinterpret_cast<const __half2*>(&lo);
-			if (e[c + 1] == (e[c] ^ 1u)) v[c + 1] = *reinterpret_cast<const __half2*>(&buddy);
-			else v[c + 1] = __ldg(grid + e[c + 1]);
-		}
 		}
 		__half2 acc = __floats2half2_rn(0.f, 0.f);
 		#pragma unroll
@@ -121,96 +106,6 @@ __global__ void __launch_bounds__(256) hash_encode_fwd_kernel(
 		*reinterpret_cast<__half2*>(orow + 2 * l) = acc;
 	}
 }
-
-// segmented sum over runs of equal keys in neighbouring lanes; returns true on the first lane of each run (which then holds the run's sums)
-template <int N>
-__device__ __forceinline__ bool warp_run_sum(uint32_t key, uint32_t lane, float (&v)[N]) {
-	const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
-	const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0 || prev != key);
-	if (heads != 0xffffffffu) {
-		const uint32_t above = heads & ~((2u << lane) - 1u);           // heads strictly above this lane
-		const uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;   // last lane of this lane's run
-		#pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			float a[N];
-			#pragma unroll
-			for (int k = 0; k < N; ++k) a[k] = __shfl_down_sync(0xffffffffu, v[k], o);
-			if (lane + o <= end) {
-				#pragma unroll
-				for (int k = 0; k < N; ++k) v[k] += a[k];
-			}
-		}
-	}
-	return (heads >> lane) & 1u;
-}
-
-__device__ __forceinline__ void red_half2(__half2* p, float x, float y) { atomicAdd(p, __floats2half2_rn(x, y)); }
-// one 8-byte reduction onto two adjacent half2 entries (p 8-byte aligned): REDG.E.ADD.F16x4
-__device__ __forceinline__ void red_half2x2(__half2* p, float x0, float y0, float x1, float y1) {
-	const __half2 a = __floats2half2_rn(x0, y0), b = __floats2half2_rn(x1, y1);
-	asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" :: "l"(p), "r"(*reinterpret_cast<const uint32_t*>(&a)), "r"(*reinterpret_cast<const uint32_t*>(&b)) : "memory");
-}
-
-// Backward: warp = 32 consecutive samples, one level at a time.  Per corner pair along x: when the two entries are adjacent in
-// the table (lower index even, see the forward kernel) they leave as ONE 8-byte reduction.  Before that, equal targets in
-// neighbouring lanes (samples of one ray inside one cell) are summed in fp32 with a segmented shuffle reduction, so the
-// contended coarse levels issue one reduction per run instead of one per sample.
-__global__ void __launch_bounds__(256) hash_encode_bwd_kernel(
-	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
-	const __half* __restrict__ dy, uint32_t dy_stride, const __grid_constant__ ngp_grid_desc desc, __half2* __restrict__ grad,
-	uint32_t level_begin, uint32_t level_end)
-{
-	chain_enter();
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	const uint32_t lane = threadIdx.x & 31;
-	const bool valid = i < n;
-	const uint32_t ii = valid ? i : n - 1;
-	const float x = xyz[(size_t)ii * stride_floats + 0], y = xyz[(size_t)ii * stride_floats + 1], z = xyz[(size_t)ii * stride_floats + 2];
-	const __half* drow = dy + (size_t)ii * dy_stride;
-
-	for (uint32_t l = level_begin; l < level_end; ++l) {
-		const uint32_t off = desc.offsets[l], size = desc.offsets[l + 1] - off, res = desc.resolutions[l];
-		const float scale = desc.scales[l];
-		const bool hashed = level_is_hashed(size, res);
-		__half2* grid = grad + off;
-		uint32_t gx, gy, gz; float wx, wy, wz;
-		pos_fract(x, scale, gx, wx); pos_fract(y, scale, gy, wy); pos_fract(z, scale, gz, wz);
-		const float2 g = __half22float2(*reinterpret_cast<const __half2*>(drow + 2 * l));
-		#pragma unroll
-		for (int c = 0; c < 8; c += 2) {
-			// same product order as the forward pass: (wx' * wy') * wz'
-			const float w0 = ((1 - wx) * ((c & 2) ? wy : 1 - wy)) * ((c & 4) ? wz : 1 - wz);
-			const float w1 = (wx * ((c & 2) ? wy : 1 - wy)) * ((c & 4) ? wz : 1 - wz);
-			const uint32_t e0 = grid_index(size, res, hashed, gx, gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
-			const uint32_t e1 = grid_index(size, res, hashed, gx + 1, gy + ((c >> 1) & 1), gz + ((c >> 2) & 1));
-			const bool paired = e1 == (e0 ^ 1u);
-			// per-term fp16 rounding as in grid.h:303-306, then exact fp32 sums inside the warp
-			const float2 t0 = __half22float2(__floats2half2_rn(g.x * w0, g.y * w0)), t1 = __half22float2(__floats2half2_rn(g.x * w1, g.y * w1));
-			// round A: entry e0 of every lane, together with e1 where the two are adjacent
-			{
-				float v[4] = {t0.x, t0.y, paired ? t1.x : 0.f, paired ? t1.y : 0.f};
-				const uint32_t key = valid ? (e0 | (paired ? 0x80000000u : 0u)) : 0x7fffffffu - lane;
-				const bool head = warp_run_sum<4>(key, lane, v);
-				if (valid && head) {
-					if (paired) {
-						if (e0 & 1u) red_half2x2(grid + (e0 ^ 1u), v[2], v[3], v[0], v[1]);
-						else red_half2x2(grid + e0, v[0], v[1], v[2], v[3]);
-					} else {
-						red_half2(grid + e0, v[0], v[1]);
-					}
-				}
-			}
-			// round B: entry e1 of the lanes whose pair is not adjacent
-			if (__any_sync(0xffffffffu, valid && !paired)) {
-				float v[2] = {t1.x, t1.y};
-				const uint32_t key = (valid && !paired) ? e1 : 0x7fffffffu - lane;
-				const bool head = warp_run_sum<2>(key, lane, v);
-				if (valid && !paired && head) red_half2(grid + e1, v[0], v[1]);
-			}
-		}
-	}
-}
-
 
 // all 8 corner entries of one cell; same values as grid_index() corner by corner.  Hashed: the y and z products are formed once
 // and stepped by their primes.  Dense: one base index stepped by the strides, wrapped by a compare (the index of a point inside
@@ -249,13 +144,13 @@ __device__ __forceinline__ void red_h2x4(__half2* p, uint32_t a, uint32_t b, uin
 	asm volatile("red.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-// Backward, second generation.  Same mapping (thread = sample, warp = 32 consecutive samples of mostly one ray) and the same
+// Backward.  Same mapping (thread = sample, warp = 32 consecutive samples of mostly one ray) and the same
 // arithmetic per term (weight product order, fp16 rounding of every term as in grid.h:303-306), but the merge of equal targets
 // is keyed by the CELL: neighbouring lanes inside one cell share all 8 corners, so the run structure is found once per level
 // (3 shuffles + 1 ballot) instead of once per corner, the 16 partial sums of a run are reduced in fp32 with only as many
 // shuffle rounds as the longest run of the warp needs, and warps without any run (the fine levels) skip the merge altogether.
-// x-adjacent corner pairs whose entries are adjacent in memory leave as one 8-byte reduction.  The first-generation kernel
-// spent ~800 instructions per warp and level, most of them in eight corner-keyed run sums; it was issue-bound (72 %).
+// x-adjacent corner pairs whose entries are adjacent in memory leave as one 8- or 16-byte reduction.  (A first-generation kernel
+// keyed the merge per corner: ~800 instructions per warp and level, issue-bound at 72 %, 144.8 us against 78 us -- DESIGN.md 3.1.)
 template <bool QUADS>
 __global__ void __launch_bounds__(256) hash_encode_bwd_cell_kernel(
 	const float* __restrict__ xyz, uint32_t stride_floats, uint32_t n,
@@ -444,14 +339,14 @@ extern "C" uint32_t ngp_grid_desc_init(ngp_grid_desc* desc, uint32_t n_levels, u
 	return offset;
 }
 
-extern "C" int ngp_grid_desc_device_scales(ngp_grid_desc* desc, uint32_t base_resolution, float per_level_scale) {
+extern "C" int ngp_grid_desc_device_scales(ngp_grid_desc* desc, uint32_t base_resolution, float per_level_scale, void* stream, float* d_scratch) {
 	NGP_REQUIRE(desc && desc->n_levels >= 1 && desc->n_levels <= NGP_MAX_LEVELS, "bad descriptor");
-	float* d = nullptr;
-	if (cudaMalloc(&d, sizeof(float) * NGP_MAX_LEVELS) != cudaSuccess) { set_error("ngp_grid_desc_device_scales: cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError())); return -2; }
-	grid_scales_kernel<<<1, NGP_MAX_LEVELS>>>(desc->n_levels, std::log2(per_level_scale), base_resolution, d);
+	NGP_REQUIRE(d_scratch, "d_scratch (NGP_MAX_LEVELS floats of device memory) is required");
+	cudaStream_t s = (cudaStream_t)stream;
+	grid_scales_kernel<<<1, NGP_MAX_LEVELS, 0, s>>>(desc->n_levels, std::log2(per_level_scale), base_resolution, d_scratch);
 	float h[NGP_MAX_LEVELS];
-	const cudaError_t e = cudaMemcpy(h, d, sizeof(float) * NGP_MAX_LEVELS, cudaMemcpyDeviceToHost);
-	cudaFree(d);
+	cudaError_t e = cudaMemcpyAsync(h, d_scratch, sizeof(float) * NGP_MAX_LEVELS, cudaMemcpyDeviceToHost, s);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(s);          // set-up call: the one entry point that waits for its own result
 	if (e != cudaSuccess) { set_error("ngp_grid_desc_device_scales: %s", cudaGetErrorString(e)); return -2; }
 	for (uint32_t l = 0; l < desc->n_levels; ++l) {
 		desc->scales[l] = h[l];
@@ -467,8 +362,8 @@ extern "C" int ngp_hash_encode_fwd(void* stream, const float* d_xyz, uint32_t st
 	NGP_REQUIRE(out_stride >= 2 * desc->n_levels && out_stride % 2 == 0, "out_stride too small or odd");
 	if (n == 0) return 0;
 	const uint32_t grid = div_up(n, 256);
-	if (d_indices) NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<true, 2>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, d_indices));
-	else NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<false, 2>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	if (d_indices) NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<true>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, d_indices));
+	else NGP_LAUNCH("hash_encode_fwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_fwd_kernel<false>, grid, 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, nullptr, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
 	return check_launch("hash_encode_fwd");
 }
 
@@ -476,33 +371,26 @@ namespace ngp {
 int hash_encode_fwd_counted(cudaStream_t stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const uint32_t* d_n_valid,
                             const void* d_table, const ngp_grid_desc* desc, void* d_out, uint32_t out_stride) {
 	if (n == 0) return 0;
-	static const int width = getenv("NGP_HASH_WIDTH") ? atoi(getenv("NGP_HASH_WIDTH")) : 2;
 	// (an explicit L2 prefetch of the 24 MB table before this launch was measured: no change, the kernel is L1TEX-bound, not
 	// bound by its first-touch DRAM misses)
 	if (((uintptr_t)d_table & 15u) != 0) { set_error("hash_encode_fwd: d_table must be 16-byte aligned"); return -1; }
-	if (width == 2) NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, 2>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
-	else if (width == 1) NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, 1>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
-	else NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false, 0>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
+	NGP_LAUNCH("hash_encode_fwd_kernel", stream, launch_chained(hash_encode_fwd_kernel<false>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, d_n_valid, (const __half2*)d_table, *desc, (__half*)d_out, out_stride, nullptr));
 	return check_launch("hash_encode_fwd");
 }
 }
 
-extern "C" int ngp_hash_encode_bwd_levels(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
-                                          const ngp_grid_desc* desc, void* d_grad, uint32_t level_begin, uint32_t level_end) {
-	NGP_REQUIRE(d_xyz && d_dy && desc && d_grad, "null pointer");
-	NGP_REQUIRE(((uintptr_t)d_grad & 7u) == 0, "d_grad must be 8-byte aligned");
-	NGP_REQUIRE(level_begin <= level_end && level_end <= desc->n_levels, "bad level range");
+namespace ngp {
+// the scatter restricted to the levels [level_begin, level_end), accumulating into d_grad (never zeroes it)
+int hash_encode_bwd_levels(cudaStream_t stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
+                           const ngp_grid_desc* desc, void* d_grad, uint32_t level_begin, uint32_t level_end) {
+	if (((uintptr_t)d_grad & 7u) != 0) { set_error("hash_encode_bwd: d_grad must be 8-byte aligned"); return -1; }
+	if (!(level_begin <= level_end && level_end <= desc->n_levels)) { set_error("hash_encode_bwd: bad level range"); return -1; }
 	if (n == 0 || level_begin == level_end) return 0;
-	static const bool corner_keyed = getenv("NGP_HASH_BWD") && getenv("NGP_HASH_BWD")[0] == '1';       // first-generation kernel, for A/B runs
-	if (corner_keyed) NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_kernel, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
-	// 16-byte reductions (REDG.E.ADD.F16x8): 89 -> 78 us per step; NGP_HASH_BWD_QUADS=0 falls back to 8-byte pairs, also used when
-	// the caller's arena is only 8-byte aligned
-	static const bool quads_on = !(getenv("NGP_HASH_BWD_QUADS") && getenv("NGP_HASH_BWD_QUADS")[0] == '0');
-	const bool quads = quads_on && ((uintptr_t)d_grad & 15u) == 0;
-	if (corner_keyed) {}
-	else if (quads) NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_cell_kernel<true>, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
-	else NGP_LAUNCH("hash_encode_bwd_kernel", (cudaStream_t)stream, launch_chained(hash_encode_bwd_cell_kernel<false>, div_up(n, 256), 256, 0, (cudaStream_t)stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
+	// 16-byte reductions (REDG.E.ADD.F16x8) when the arena is 16-byte aligned, 8-byte pairs otherwise
+	if (((uintptr_t)d_grad & 15u) == 0) NGP_LAUNCH("hash_encode_bwd_kernel", stream, launch_chained(hash_encode_bwd_cell_kernel<true>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
+	else NGP_LAUNCH("hash_encode_bwd_kernel", stream, launch_chained(hash_encode_bwd_cell_kernel<false>, div_up(n, 256), 256, 0, stream, d_xyz, stride_floats, n, (const __half*)d_dy, dy_stride, *desc, (__half2*)d_grad, level_begin, level_end));
 	return check_launch("hash_encode_bwd");
+}
 }
 
 extern "C" int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t stride_floats, uint32_t n, const void* d_dy, uint32_t dy_stride,
@@ -512,5 +400,5 @@ extern "C" int ngp_hash_encode_bwd(void* stream, const float* d_xyz, uint32_t st
 		const int rc = zero_fill((cudaStream_t)stream, d_grad, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half));
 		if (rc) return rc;
 	}
-	return ngp_hash_encode_bwd_levels(stream, d_xyz, stride_floats, n, d_dy, dy_stride, desc, d_grad, 0, desc->n_levels);
+	return hash_encode_bwd_levels((cudaStream_t)stream, d_xyz, stride_floats, n, d_dy, dy_stride, desc, d_grad, 0, desc->n_levels);
 }

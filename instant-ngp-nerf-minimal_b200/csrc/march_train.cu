@@ -246,7 +246,7 @@ extern "C" int ngp_generate_training_samples(void* stream, const ngp_sampler_cfg
 	uint32_t* nwin_tmp = ridx_tmp + n_rays;
 	uint32_t* mask_tmp = nwin_tmp + n_rays;
 	// at most 4 CTAs (32 warps) per SM: the march is latency-bound and usually runs underneath another stream's kernels
-	static const uint32_t ctas_per_sm = getenv("NGP_MARCH_CTAS") ? (uint32_t)atoi(getenv("NGP_MARCH_CTAS")) : 4u;
+	const uint32_t ctas_per_sm = 4u;
 	const uint32_t grid = std::min(div_up(n_rays, 8), kNumSMs * ctas_per_sm);
 	NGP_LAUNCH("march_count_kernel", s, march_count_kernel<<<grid, 256, 0, s>>>(*cfg, *cam, n_rays, n_rays_shift, n_images, d_xforms, d_bitfield,
 		snap_to_pixel_centers, rng, n_tmp, d_per_ray_n, nwin_tmp, mask_tmp));

@@ -511,7 +511,7 @@ extern "C" int ngp_network_density(void* stream, const float* d_positions, uint3
 
 static int network_train_impl(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc, const void* d_dloss,
                               void* d_rgbsigma, void* d_grads, const void* d_encoded, uint32_t n_encoded, const uint32_t* d_src_index, void* d_workspace, size_t workspace_bytes,
-                              uint32_t fine_level_begin = 0, void* ev_fine_done = nullptr, int zero_first = 1) {
+                              int zero_first = 1) {
 	NGP_REQUIRE(d_coords && d_params && desc && d_dloss && d_grads && d_workspace, "null pointer");
 	NGP_REQUIRE(desc->n_levels == 16, "the fused network expects 16 levels x 2 features = 32 encoded dims");
 	NGP_REQUIRE(workspace_bytes >= ngp_network_workspace_bytes(n), "workspace too small");
@@ -530,29 +530,12 @@ static int network_train_impl(void* stream, const float* d_coords, uint32_t n, c
 	if (rc) return rc;
 	NGP_LAUNCH("wgrad_reduce_kernel", s, launch_chained(wgrad_reduce_kernel, div_up(NGP_MLP_PARAMS, 32), 256, 0, s, wgrad_slots, n_slots, (__half*)d_grads, NGP_MLP_PARAMS));
 	__half* grid_grads = (__half*)d_grads + NGP_MLP_PARAMS;
-	if (!ev_fine_done) return ngp_hash_encode_bwd(stream, d_coords, 7, n, denc, 32, desc, grid_grads, zero_first);
-	// two launches: the levels [fine_level_begin, L) first, an event, then the coarse rest
-	NGP_REQUIRE(fine_level_begin <= desc->n_levels, "fine_level_begin out of range");
-	if (zero_first && cudaMemsetAsync(grid_grads, 0, (size_t)desc->offsets[desc->n_levels] * 2 * sizeof(__half), s) != cudaSuccess) { set_error("network_train: memset failed"); return -2; }
-	rc = ngp_hash_encode_bwd_levels(stream, d_coords, 7, n, denc, 32, desc, grid_grads, fine_level_begin, desc->n_levels);
-	if (rc) return rc;
-	if (cudaEventRecord((cudaEvent_t)ev_fine_done, s) != cudaSuccess) { set_error("network_train: event record failed"); return -2; }
-	return ngp_hash_encode_bwd_levels(stream, d_coords, 7, n, denc, 32, desc, grid_grads, 0, fine_level_begin);
+	return ngp_hash_encode_bwd(stream, d_coords, 7, n, denc, 32, desc, grid_grads, zero_first);
 }
 
 extern "C" int ngp_network_train(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
                                  const void* d_dloss, void* d_rgbsigma, void* d_grads, void* d_workspace, size_t workspace_bytes) {
 	return network_train_impl(stream, d_coords, n, d_params, desc, d_dloss, d_rgbsigma, d_grads, nullptr, 0, nullptr, d_workspace, workspace_bytes);
-}
-
-extern "C" int ngp_network_train_reuse_phased(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,
-                                              const void* d_dloss, void* d_rgbsigma, void* d_grads, const void* d_encoded, uint32_t n_encoded, const uint32_t* d_src_index,
-                                              void* d_workspace, size_t workspace_bytes, uint32_t fine_level_begin, void* ev_fine_done, int zero_first) {
-	NGP_REQUIRE(d_encoded && d_src_index, "null pointer");
-	NGP_REQUIRE(n_encoded > 0, "n_encoded must be positive");
-	NGP_REQUIRE(d_encoded != d_workspace, "the training workspace must not alias the encodings it reads");
-	return network_train_impl(stream, d_coords, n, d_params, desc, d_dloss, d_rgbsigma, d_grads, d_encoded, n_encoded, d_src_index, d_workspace, workspace_bytes,
-	                          fine_level_begin, ev_fine_done, zero_first);
 }
 
 extern "C" int ngp_network_train_reuse(void* stream, const float* d_coords, uint32_t n, const void* d_params, const ngp_grid_desc* desc,

@@ -89,8 +89,8 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 // sharded step) and the last CTA to finish raises the "weights of this epoch have landed" flag at every rank.
 // PEER with WORLD > 0: the reduce-scatter is fused in -- the kernel first waits for every rank's "gradients complete" flag, then
 // each group of 8 gradients is summed straight out of all ranks' arenas (16-byte P2P loads over NVLink, fixed rank order, fp32,
-// rounded to fp16 exactly like the stand-alone peer_reduce_kernel it replaces) while the fp32 state streams from local HBM.
-template <bool PEER, bool ZERO_GRADS = false, int WORLD = 0>
+// rounded to fp16 once) while the fp32 state streams from local HBM.
+template <bool PEER, int WORLD = 0>
 __global__ void __launch_bounds__(256, 3) adam_ema_kernel(uint64_t begin, uint64_t n, uint64_t n_matrix, AdamHyper h, float* __restrict__ w32, __half* __restrict__ w16,
                                                         const __half* g16, float* __restrict__ m1, float* __restrict__ m2,
                                                         uint32_t* __restrict__ steps, __half* __restrict__ ema16, ngp_peer_set ps, uint32_t epoch,
@@ -129,10 +129,8 @@ __global__ void __launch_bounds__(256, 3) adam_ema_kernel(uint64_t begin, uint64
 			}
 			gp = pack8(sum);
 		} else {
-			gp = ZERO_GRADS ? reinterpret_cast<const uint4*>(g16)[q] : __ldg(reinterpret_cast<const uint4*>(g16) + q);
+			gp = __ldg(reinterpret_cast<const uint4*>(g16) + q);
 		}
-		// the consumer leaves the arena clean for the next backward pass (saves a 24 MB memset and a launch boundary per step)
-		if (ZERO_GRADS && ((gp.x | gp.y | gp.z | gp.w) != 0u)) reinterpret_cast<uint4*>(const_cast<__half*>(g16))[q] = make_uint4(0u, 0u, 0u, 0u);
 		const uint4 wp = reinterpret_cast<const uint4*>(w16)[q];
 		const uint4 ep = reinterpret_cast<const uint4*>(ema16)[q];
 		const bool any = i < n_matrix || ((gp.x | gp.y | gp.z | gp.w) & 0x7fff7fffu) != 0u;      // any gradient that is not +-0
@@ -192,7 +190,6 @@ __global__ void __launch_bounds__(256, 3) adam_ema_kernel(uint64_t begin, uint64
 		const uint64_t i = n8 * 8 + threadIdx.x;
 		__half wh = w16[i]; bool t; uint32_t cs = 0; float clr = 0.f;
 		adam_one(h, i < n_matrix, __half2float(g16[i]), w32[i], m1[i], m2[i], steps[i], wh, t, cs, clr);
-		if (ZERO_GRADS) const_cast<__half*>(g16)[i] = __float2half_rn(0.f);
 		w16[i] = wh;
 		ema16[i] = __float2half_rn((__half2float(ema16[i]) * h.ema_decay * h.deb_old + __half2float(wh) * (1 - h.ema_decay)) * h.deb_new);
 	}
@@ -217,33 +214,6 @@ __global__ void peer_wait_kernel(ngp_peer_set ps, uint32_t slot_base, uint32_t e
 	if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + slot_base + threadIdx.x) < epoch) __nanosleep(64); }
 	__syncwarp();
 	if (threadIdx.x == 0) g_peer_stamps[1][epoch & 4095u] = global_ns();
-}
-
-// Reduce-scatter half of the sharded step: waits for every rank's "gradients complete" flag, then sums this rank's shard out of
-// all arenas (P2P loads over NVLink, fixed rank order, fp32) and leaves the fp16 sum in the local arena.  Few registers and
-// 16-byte loads from every peer in flight per thread: the kernel exists to keep enough bytes in flight to cover NVLink latency.
-template <int WORLD>
-__global__ void __launch_bounds__(512) peer_reduce_kernel(uint64_t begin, uint64_t end, ngp_peer_set ps, uint32_t epoch) {
-	chain_enter();
-	if (threadIdx.x < ps.world) { while (ld_acquire_sys(ps.flags[ps.rank] + threadIdx.x) < epoch) __nanosleep(32); }
-	__syncthreads();
-	uint4* mine = reinterpret_cast<uint4*>(const_cast<void*>(ps.grads[ps.rank]));
-	for (uint64_t q = begin / 8 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < end / 8; q += (uint64_t)gridDim.x * blockDim.x) {
-		uint4 g[WORLD];
-		#pragma unroll
-		for (int p = 0; p < WORLD; ++p) if (p < (int)ps.world) g[p] = ld_peer16(reinterpret_cast<const uint4*>(ps.grads[p]) + q);
-		float sum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-		#pragma unroll
-		for (int p = 0; p < WORLD; ++p) {
-			if (p < (int)ps.world) {
-				float t[8];
-				unpack8(g[p], t);
-				#pragma unroll
-				for (int k = 0; k < 8; ++k) sum[k] += t[k];
-			}
-		}
-		mine[q] = pack8(sum);
-	}
 }
 
 } // namespace ngp
@@ -289,22 +259,6 @@ extern "C" int ngp_optimizer_step(void* stream, const ngp_optimizer_cfg* cfg, ui
 	return check_launch("optimizer_step");
 }
 
-extern "C" int ngp_optimizer_step_range(void* stream, const ngp_optimizer_cfg* cfg, uint64_t begin, uint64_t end, uint64_t n_matrix_params, uint32_t step, float learning_rate,
-                                        float* d_w32, void* d_w16, void* d_g16, float* d_m1, float* d_m2, uint32_t* d_param_steps, void* d_ema16, int zero_gradients) {
-	NGP_REQUIRE(cfg && d_w32 && d_w16 && d_g16 && d_m1 && d_m2 && d_param_steps && d_ema16, "null pointer");
-	NGP_REQUIRE(n_matrix_params % 8 == 0 && begin % 8 == 0 && begin <= end, "begin and n_matrix_params must be multiples of 8, begin <= end");
-	if (begin == end) return 0;
-	AdamHyper h;
-	fill_hyper(h, cfg, step, learning_rate);
-	cudaStream_t s = (cudaStream_t)stream;
-	const uint32_t grid = grid_for((end - begin) / 8 + 1, 256, 6);
-	if (zero_gradients) NGP_LAUNCH("adam_ema_kernel", s, launch_chained(adam_ema_kernel<false, true>, grid, 256, 0, s, begin, end, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
-		d_m1, d_m2, d_param_steps, (__half*)d_ema16, ngp_peer_set{}, 0, nullptr));
-	else NGP_LAUNCH("adam_ema_kernel", s, launch_chained(adam_ema_kernel<false, false>, grid, 256, 0, s, begin, end, n_matrix_params, h, d_w32, (__half*)d_w16, (const __half*)d_g16,
-		d_m1, d_m2, d_param_steps, (__half*)d_ema16, ngp_peer_set{}, 0, nullptr));
-	return check_launch("optimizer_step_range");
-}
-
 extern "C" int ngp_peer_stamps_read(uint64_t* host_out /* [2][4096] */) {
 	NGP_REQUIRE(host_out, "null pointer");
 	if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpyFromSymbol(host_out, g_peer_stamps, sizeof(unsigned long long) * 2 * 4096) != cudaSuccess) {
@@ -344,23 +298,16 @@ extern "C" int ngp_optimizer_step_sharded(void* stream, const ngp_optimizer_cfg*
 	cudaStream_t st = (cudaStream_t)stream;
 	__half* w16 = (__half*)peers->params[peers->rank];
 	const __half* g16 = (const __half*)peers->grads[peers->rank];
-	static const bool fused = !(getenv("NGP_PEER_FUSED") && getenv("NGP_PEER_FUSED")[0] == '0');     // 0: separate reduce kernel, for A/B runs
 	const uint32_t agrid = grid_for(groups ? groups : 1, 256, 6);
-	if (!fused) {
-		const uint32_t rgrid = grid_for(groups ? groups : 1, 512, 4);
-		if (peers->world <= 2) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<2>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
-		else if (peers->world <= 4) NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<4>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
-		else NGP_LAUNCH("peer_reduce_kernel", st, launch_chained(peer_reduce_kernel<8>, rgrid, 512, 0, st, shard_begin, shard_end, *peers, epoch));
-		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
-			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
-	} else if (peers->world <= 2) {
-		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, false, 2>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+	// (a separate reduce kernel followed by a plain sharded Adam was measured at 2 GPUs: 0.65 vs 0.625 ms/step fused -- DESIGN.md 7)
+	if (peers->world <= 2) {
+		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, 2>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
 			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
 	} else if (peers->world <= 4) {
-		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, false, 4>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, 4>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
 			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
 	} else {
-		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, false, 8>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
+		NGP_LAUNCH("adam_ema_kernel", st, launch_chained(adam_ema_kernel<true, 8>, agrid, 256, 0, st, shard_begin, shard_end, n_matrix_params, h, d_w32, w16, g16,
 			d_m1, d_m2, d_param_steps, (__half*)d_ema16, *peers, epoch, d_ticket));
 	}
 	return check_launch("optimizer_step_sharded");

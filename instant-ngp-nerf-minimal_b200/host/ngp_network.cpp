@@ -26,7 +26,8 @@ NGPNetwork::NGPNetwork(Json& config) {
 	m_n_grid_entries = ngp_grid_desc_init(&m_grid, n_levels, log2_hashmap_size, base_resolution, per_level_scale);
 	if (!m_n_grid_entries) throw std::runtime_error(ngp_last_error());
 	// the per-level scales the reference's kernels evaluate on the device (grid.h:157), not glibc's: an ulp apart on some levels
-	api_check(ngp_grid_desc_device_scales(&m_grid, base_resolution, per_level_scale));
+	DeviceBuffer<float> scratch(NGP_MAX_LEVELS);
+	api_check(ngp_grid_desc_device_scales(&m_grid, base_resolution, per_level_scale, nullptr, scratch.data()));
 
 	auto check_mlp = [](const Json& c, int hidden, const char* name) {
 		if (lower(c.value("otype", "FullyFusedMLP")) != "fullyfusedmlp" || c.value("n_neurons", 64) != 64 || c.value("n_hidden_layers", hidden) != hidden ||
@@ -74,15 +75,6 @@ void NGPNetwork::backward(cudaStream_t stream, const Coordinate* input, uint32_t
 	} else {
 		api_check(ngp_network_train(stream, (const float*)input, n, m_params, &m_grid, dL_doutput, out, m_gradients, m_train_workspace.data(), m_train_workspace.get_bytes()));
 	}
-	m_forward_output = nullptr;
-}
-
-void NGPNetwork::backward_phased(cudaStream_t stream, const Coordinate* input, uint32_t n, const precision_t* output, const precision_t* dL_doutput,
-                                 const uint32_t* src_index, uint32_t n_encoded, uint32_t fine_level_begin, cudaEvent_t fine_done, bool grads_clean) {
-	precision_t* out = m_forward_output == output ? m_forward_output : nullptr;
-	m_train_workspace.enlarge(ngp_network_workspace_bytes(n));
-	api_check(ngp_network_train_reuse_phased(stream, (const float*)input, n, m_params, &m_grid, dL_doutput, out, m_gradients, m_workspace.data(), n_encoded, src_index,
-	                                         m_train_workspace.data(), m_train_workspace.get_bytes(), fine_level_begin, (void*)fine_done, grads_clean ? 0 : 1));
 	m_forward_output = nullptr;
 }
 
@@ -140,16 +132,6 @@ void Trainer::optimizer_step(cudaStream_t stream, float loss_scale) {
 	api_check(ngp_optimizer_step(stream, &c, m_n, m_network->n_matrix_params(), m_step, m_opt.learning_rate * m_lr_factor, m_params_fp32.data(), m_params.data(),
 	                             m_grads.data(), m_m1.data(), m_m2.data(), m_param_steps.data(), m_ema.data()));
 	++m_step;
-}
-
-void Trainer::begin_step() {
-	if (m_opt.has_decay && m_step >= m_opt.decay_start && (m_step - m_opt.decay_start) % m_opt.decay_interval == 0) m_lr_factor *= m_opt.decay_base;
-}
-
-void Trainer::step_range(cudaStream_t stream, float loss_scale, size_t begin, size_t end) {
-	ngp_optimizer_cfg c{m_opt.learning_rate, m_opt.beta1, m_opt.beta2, m_opt.epsilon, m_opt.l2_reg, loss_scale, m_opt.has_ema ? m_opt.ema_decay : 0.0f};
-	api_check(ngp_optimizer_step_range(stream, &c, begin, end, m_network->n_matrix_params(), m_step, m_opt.learning_rate * m_lr_factor, m_params_fp32.data(), m_params.data(),
-	                                   m_grads.data(), m_m1.data(), m_m2.data(), m_param_steps.data(), m_ema.data(), 1));
 }
 
 void Trainer::set_shard(uint32_t rank, uint32_t world) {

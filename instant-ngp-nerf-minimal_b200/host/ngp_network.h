@@ -28,10 +28,6 @@ public:
 	// computed there are then gathered instead of recomputed (same values: the table has not changed in between).
 	void backward(cudaStream_t stream, const Coordinate* input, uint32_t n, const precision_t* output, const precision_t* dL_doutput,
 	              const uint32_t* src_index = nullptr, uint32_t n_encoded = 0);
-	// backward() with the encoder gradient in two phases (levels >= fine_level_begin first, then `fine_done` is recorded, then the
-	// coarse levels): lets the caller start the optimizer on the fine levels early.  grads_clean: the grid gradients are already zero.
-	void backward_phased(cudaStream_t stream, const Coordinate* input, uint32_t n, const precision_t* output, const precision_t* dL_doutput,
-	                     const uint32_t* src_index, uint32_t n_encoded, uint32_t fine_level_begin, cudaEvent_t fine_done, bool grads_clean);
 	// first parameter of grid level `level` in the arena
 	size_t level_param_begin(uint32_t level) const { return (size_t)NGP_MLP_PARAMS + (size_t)m_grid.offsets[level] * 2; }
 
@@ -78,11 +74,6 @@ public:
 	void initialize_params(cudaStream_t stream);
 	// Trainer::optimizer_step (trainer.h:198): ExponentialDecay -> Adam -> EMA in one fused launch
 	void optimizer_step(cudaStream_t stream, float loss_scale);
-	// the same step applied range by range: begin_step() once, any number of step_range() calls on disjoint ranges (they may go to
-	// different streams), end_step() once.  step_range() leaves the consumed gradients zeroed.
-	void begin_step();
-	void step_range(cudaStream_t stream, float loss_scale, size_t begin, size_t end);
-	void end_step() { ++m_step; }
 	// data parallel over peer memory: this rank updates only [shard_begin(), shard_end()) and stores the new weights into every rank's arena
 	void set_shard(uint32_t rank, uint32_t world);
 	size_t shard_size() const { return m_shard_size; }

@@ -38,11 +38,6 @@ Testbed::Testbed() {
 		NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_march_ready[k], cudaEventDisableTiming));
 		NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_slot_free[k], cudaEventDisableTiming));
 	}
-	NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_opt_stream, cudaStreamNonBlocking, prio_hi));
-	NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_fine_grads, cudaEventDisableTiming));
-	NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_fine_adam, cudaEventDisableTiming));
-	if (const char* e = getenv("NGP_FINE_LEVEL_BEGIN")) m_fine_level_begin = (uint32_t)atoi(e);
-	if (const char* e = getenv("NGP_ZERO_IN_ADAM")) m_optimizer_zeroes_gradients = e[0] != '0';
 	NGP_CUDA_CHECK(cudaMallocHost((void**)&m_host_counter, 64 * sizeof(uint32_t)));
 	m_training_buffer.loss_sum.resize(1024);
 	m_training_buffer.loss_sum.memset(0);
@@ -62,8 +57,6 @@ Testbed::~Testbed() {
 	for (auto& e : m_ev) if (e) cudaEventDestroy(e);
 	for (cudaEvent_t e : {m_ev_march_go, m_ev_march_ready[0], m_ev_march_ready[1], m_ev_slot_free[0], m_ev_slot_free[1]}) if (e) cudaEventDestroy(e);
 	if (m_march_stream) cudaStreamDestroy(m_march_stream);
-	for (cudaEvent_t e : {m_ev_fine_grads, m_ev_fine_adam}) if (e) cudaEventDestroy(e);
-	if (m_opt_stream) cudaStreamDestroy(m_opt_stream);
 	if (m_host_counter) cudaFreeHost(m_host_counter);
 	if (m_stream) cudaStreamDestroy(m_stream);
 }
@@ -93,7 +86,6 @@ void Testbed::load_model_config_json(const Json& config) {
 	m_render = std::make_shared<RayMarcher>(m_model_config["render"]);
 	m_loss_type = string_to_loss_type(m_model_config["loss"].str());
 	m_trainer = std::make_shared<Trainer>(m_network, OptimizerConfig::from_json(m_model_config["optimizer"]), m_seed, m_stream);
-	m_grid_grads_clean = false;
 	m_train_envmap = m_model_config.contains("envmap") ? m_model_config["envmap"].value("train", false) : false;
 	if (m_train_envmap) {
 		// testbed.cu:83-90.  All buffers start at zero (trainable_buffer.h:45-55), so an untrained map changes nothing.

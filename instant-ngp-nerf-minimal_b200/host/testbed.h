@@ -158,17 +158,7 @@ private:
 	cudaEvent_t m_ev[3] = {nullptr, nullptr, nullptr};
 public:
 	bool m_pipeline_march = true;      // false: issue the march on the main stream (serial schedule; used when timing kernels one by one)
-	// single GPU, experiment (default off = 0): the optimizer steps the fine grid levels (>= m_fine_level_begin) on m_opt_stream while
-	// the encoder backward is still scattering the coarse levels.  Measured slower on B200 (0.550 vs 0.514 ms/step): the optimizer's
-	// stream through L2 evicts the gradient table the scatter's atomics live in.
-	uint32_t m_fine_level_begin = 0;
-	// experiment (default off): the optimizer zeroes the gradients it consumes instead of a 24 MB memset before the encoder backward.
-	// Measured slower (0.560 vs 0.514 ms/step): the memset doubles as the L2 prefetch of the table the scatter's atomics hit.
-	bool m_optimizer_zeroes_gradients = false;
 private:
-	cudaStream_t m_opt_stream = nullptr;
-	cudaEvent_t m_ev_fine_grads = nullptr, m_ev_fine_adam = nullptr;
-	bool m_grid_grads_clean = false;
 	std::chrono::steady_clock::time_point m_enqueue_start;
 	cudaStream_t m_march_stream = nullptr;
 	cudaEvent_t m_ev_march_go = nullptr, m_ev_march_ready[2] = {nullptr, nullptr}, m_ev_slot_free[2] = {nullptr, nullptr};

@@ -87,8 +87,6 @@ void Testbed::train_nerf(uint32_t target_batch_size, uint32_t n_training_steps, 
 		learn_step(slot, target_batch_size, n_rays, rng_step, tb.n_coords_counter.data() + 2 * i, tb.n_compacted_coords_counter.data() + i,
 		           tb.loss.data() + (size_t)n_rays * i, stream);
 		NGP_CUDA_CHECK(cudaEventRecord(m_ev_slot_free[slot], stream));
-		static const bool sync_each_step = getenv("NGP_SYNC_EACH_STEP") != nullptr;     // experiment switch
-		if (sync_each_step) NGP_CUDA_CHECK(cudaStreamSynchronize(stream));
 		rng_step.advance();
 		++tb.i_step;
 	}
@@ -179,35 +177,6 @@ void Testbed::learn_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_r
 	// 5./6. forward + backward on the compacted batch (one fused launch chain).  The compacted samples are a subset of the ones
 	//       step 2 encoded with the same table, so their encodings are gathered from there instead of being computed again.
 	m_network->forward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data());
-	const uint32_t n_levels = m_network->grid().n_levels;
-	if (m_dp_world == 1 && m_fine_level_begin > 0 && m_fine_level_begin < n_levels) {
-		// single GPU: encoder backward in two phases; the optimizer steps the fine levels' parameters (HBM-bound) on m_opt_stream
-		// underneath the coarse levels' scatter (atomic-bound), then the rest on the main stream.  The update is elementwise, so the
-		// result is the one of a single optimizer launch.  The optimizer also zeroes what it consumed: no memset per step.
-		m_network->backward_phased(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data(), tb.dloss_drgbsigma.data(),
-		                           tb.compacted_src_index.data(), max_inference, m_fine_level_begin, m_ev_fine_grads, m_grid_grads_clean);
-		const size_t split = m_network->level_param_begin(m_fine_level_begin);
-		m_trainer->begin_step();
-		NGP_CUDA_CHECK(cudaStreamWaitEvent(m_opt_stream, m_ev_fine_grads, 0));
-		m_trainer->step_range(m_opt_stream, LOSS_SCALE, split, m_trainer->n_params());
-		NGP_CUDA_CHECK(cudaEventRecord(m_ev_fine_adam, m_opt_stream));
-		m_trainer->step_range(stream, LOSS_SCALE, 0, split);
-		m_trainer->end_step();
-		NGP_CUDA_CHECK(cudaStreamWaitEvent(stream, m_ev_fine_adam, 0));
-		m_grid_grads_clean = true;
-		return;
-	}
-	if (m_dp_world == 1 && m_optimizer_zeroes_gradients) {
-		// single GPU: the optimizer zeroes the gradients it consumes, so the encoder backward needs no memset (after the first step)
-		m_network->backward_phased(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data(), tb.dloss_drgbsigma.data(),
-		                           tb.compacted_src_index.data(), max_inference, 0, nullptr, m_grid_grads_clean);
-		m_trainer->begin_step();
-		m_trainer->step_range(stream, LOSS_SCALE, 0, m_trainer->n_params());
-		m_trainer->end_step();
-		m_grid_grads_clean = true;
-		return;
-	}
-	m_grid_grads_clean = false;
 	m_network->backward(stream, tb.coords_compacted.data(), target_batch_size, tb.rgbsigma.data(), tb.dloss_drgbsigma.data(),
 	                    tb.compacted_src_index.data(), max_inference);
 	if (m_peer_enabled) {

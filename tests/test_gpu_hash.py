@@ -158,34 +158,3 @@ def test_hash_encode_bwd_accumulates_when_not_zeroed(capi, orc):
     a, b = G.host(g1, np.float16).astype(np.float32), G.host(g2, np.float16).astype(np.float32)
     fine = slice(int(L.offsets[8]) * 2, None)   # few collisions: 2x within fp16 rounding
     assert np.allclose(b[fine], 2 * a[fine], rtol=2e-3, atol=1e-6)
-
-
-@pytest.mark.parametrize("split", [0, 5, 8, 16])
-def test_hash_encode_bwd_levels_partition_the_full_scatter(capi, orc, split):
-    """ngp_hash_encode_bwd_levels: levels [split, 16) then [0, split) into one zeroed arena == the full scatter.  Levels write
-    disjoint parts of the arena; the results agree within the fp16 rounding of the order-dependent atomic sums; a range never
-    touches another level's entries."""
-    import gpuutil as G
-    import torch
-    lib = capi.load()
-    n = 6000
-    L, xyz, _ = _inputs(orc, n, 7, 5, 1.0)
-    dy = (rng_uniform((n, 32), 9, -1, 1) * np.float32(2 ** -7)).astype(np.float16)
-    d, _ = capi.make_grid_desc()
-    dx, ddy = G.dev(xyz), G.dev(dy.view(np.uint16))
-    full, parts, only = G.zeros(L.n_params, torch.int16), G.zeros(L.n_params, torch.int16), G.zeros(L.n_params, torch.int16)
-    capi.check(lib.ngp_hash_encode_bwd(G.stream(), G.p(dx), 7, n, G.p(ddy), 32, C.byref(d), G.p(full), 1))
-    capi.check(lib.ngp_hash_encode_bwd_levels(G.stream(), G.p(dx), 7, n, G.p(ddy), 32, C.byref(d), G.p(parts), split, 16))
-    capi.check(lib.ngp_hash_encode_bwd_levels(G.stream(), G.p(dx), 7, n, G.p(ddy), 32, C.byref(d), G.p(only), split, 16))
-    capi.check(lib.ngp_hash_encode_bwd_levels(G.stream(), G.p(dx), 7, n, G.p(ddy), 32, C.byref(d), G.p(parts), 0, split))
-    G.sync()
-    a, b, c = (G.host(t, np.float16).astype(np.float32) for t in (full, parts, only))
-    cut = int(L.offsets[split]) * 2
-    assert not c[:cut].any(), "a level range wrote below its first level"
-    differ = (c[cut:] != 0) != (a[cut:] != 0)      # an order-dependent fp16 sum may cancel to exactly 0 in one run only
-    assert np.all(np.maximum(np.abs(c[cut:][differ]), np.abs(a[cut:][differ])) <= 2e-5), "a level range missed entries of its levels"
-    assert differ.sum() <= 1e-4 * max(1, int((a[cut:] != 0).sum()))
-    fine = int(L.offsets[10]) * 2
-    assert np.allclose(a[fine:], b[fine:], rtol=2e-3, atol=1e-6)
-    assert np.allclose(a, b, rtol=1e-2, atol=2e-5)
-    assert lib.ngp_hash_encode_bwd_levels(G.stream(), G.p(dx), 7, n, G.p(ddy), 32, C.byref(d), G.p(parts), 9, 8) != 0      # begin > end is refused
