@@ -185,7 +185,8 @@ def kernel_work(name, m, b, r, p, g=0.0, world=1, peer=False):
         "hash_encode_fwd_kernel": ("l2", (m + g) * 588),                  # the marched samples + the refresh positions; the batch reuses pass 1
         "hash_encode_bwd_kernel": ("l2", b * 588 + 2 * (p - 10240)),
         "adam_ema_kernel": ("hbm", p * 42),
-        "mlp_kernel": ("tensor", m * 18816 + b * 54400 + g * 6144),       # inference launch + training launch + density-only refresh
+        "mlp_kernel": ("tensor", b * 54400),                              # training launch: forward + dgrad + wgrad on the compacted batch
+        "mlp_fwd_kernel": ("tensor", m * 18816 + g * 6144),               # inference launch on the marched samples + density-only refresh
     }
     return table.get(name)
 

@@ -382,6 +382,174 @@ __global__ void __launch_bounds__(128, MODE == MODE_TRAIN ? 2 : 3) mlp_kernel(
 	if (threadIdx.x < 32) tmem_dealloc(tm, kTmemCols);
 }
 
+// =====================================================================================================
+// Forward-only kernel (inference on the marched samples, density on the occupancy-refresh positions): activations never leave
+// tensor memory.
+//
+//   * one persistent CTA per SM holds kFwdSlots independent tile slots of 128 samples, one warpgroup (4 warps) per slot; the slots
+//     share the 20 KB of weights in shared memory and the 512 TMEM columns (128 per slot) and never meet at a CTA-wide barrier;
+//   * the A operand of every layer comes from TENSOR MEMORY: a thread reads its accumulator row (tcgen05.ld), applies ReLU, rounds
+//     to fp16, packs two values per 32-bit column and writes the row back with tcgen05.st -- no shared-memory round trip, no
+//     generic->async proxy fence, no shared-memory bandwidth spent on activations (the weights are the only shared-memory
+//     operand).  Even the encoded position (64 B / sample = 16 packed columns) goes global -> registers -> TMEM;
+//   * per slot two 64-column halves ping-pong: layer k reads A from the low columns of one half and accumulates into the other;
+//   * per layer a slot synchronises with a 128-thread named barrier (A written), its first thread issues the MMAs and commits to
+//     the slot's mbarrier, the warpgroup sleeps on it (try_wait: hardware sleep, ~60 cycles wake-up).  (A dedicated MMA warp that
+//     polled the slots' "A written" mbarriers was measured first: mbarrier.test_wait costs ~150 cycles a probe, a layer step took
+//     2 100 cycles and the kernel was slower than the one it replaces.)
+// =====================================================================================================
+constexpr uint32_t kFwdSlots = 4;
+constexpr uint32_t kFwdThreads = kFwdSlots * 128;
+
+// round to fp16 first, then one max.f16x2 with zero: 2 instructions per pair instead of 3 (rounding is monotonic, so the result equals
+// rounding the fp32 ReLU)
+__device__ __forceinline__ uint32_t relu_pack(uint32_t a, uint32_t b) {
+	const __half2 h = __hmax2(__floats2half2_rn(__uint_as_float(a), __uint_as_float(b)), __floats2half2_rn(0.f, 0.f));
+	return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ void slot_barrier(uint32_t slot) { asm volatile("bar.sync %0, 128;" :: "r"(slot + 1) : "memory"); }
+
+// accumulator columns [src, src + 64) of this thread's lane -> ReLU -> fp16 pairs -> columns [dst, dst + 32)
+__device__ __forceinline__ void relu_row_to_tmem(uint32_t src, uint32_t dst) {
+	uint32_t r[64], q[32];
+	tmem_ld32_nowait(src, r);
+	tmem_ld32_nowait(src + 32, r + 32);
+	tmem_ld_wait();
+	tmem_ld_pin(r); tmem_ld_pin(r + 16); tmem_ld_pin(r + 32); tmem_ld_pin(r + 48);
+	#pragma unroll
+	for (int i = 0; i < 32; ++i) q[i] = relu_pack(r[2 * i], r[2 * i + 1]);
+	tmem_st16(dst, q);
+	tmem_st16(dst + 16, q + 16);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(
+	const __half* __restrict__ enc, const float* __restrict__ coords, uint32_t coord_stride, uint32_t n, const uint32_t* __restrict__ n_valid,
+	const __half* __restrict__ weights, __half* __restrict__ out)
+{
+	extern __shared__ __align__(1024) uint8_t smem[];
+	constexpr uint32_t kCtrl = Smem::WEND;            // [0,4) tmem base; from +16: one mbarrier ("accumulator complete") per slot
+	const uint32_t sbase = smem_u32(smem);
+	const uint32_t warp = threadIdx.x >> 5;
+	const uint32_t slot = warp >> 2, row = threadIdx.x & 127;
+	const uint32_t acc_ready = sbase + kCtrl + 16 + slot * 8;
+
+	if (row == 0) { mbar_init(acc_ready, 1); fence_mbar_init(); }
+	if (warp == 0) tmem_alloc(sbase + kCtrl, 512);
+	chain_enter();
+	stage_weights(weights + kW0, smem, Smem::W0, 64, 32);
+	stage_weights(weights + kW1, smem, Smem::W1, 16, 64);
+	if (MODE != MODE_DENSITY) {
+		stage_weights(weights + kV0, smem, Smem::V0, 64, 32);
+		stage_weights(weights + kV1, smem, Smem::V1, 64, 64);
+		stage_weights(weights + kV2, smem, Smem::V2, 16, 64);
+	}
+	fence_proxy_async();                               // the weights are read by the tensor core (async proxy)
+	fence_before_sync();
+	__syncthreads();
+	fence_after_sync();
+	const uint32_t tm = *reinterpret_cast<const uint32_t*>(smem + kCtrl);
+
+	const uint32_t n_limit = n_valid ? min(*n_valid, n) : n;
+	const uint32_t n_tiles = (n_limit + 127) / 128;
+	const uint32_t tile_stride = gridDim.x * kFwdSlots;
+	constexpr uint32_t I_128x64 = instr_desc(128, 64, 0, 0), I_128x16 = instr_desc(128, 16, 0, 0), I_128x8 = instr_desc(128, 8, 0, 0);
+
+	const uint32_t mlo = tm + slot * 128, mhi = mlo + 64;                 // the slot's two halves as the MMA addresses them (lane 0)
+	const uint32_t lo = mlo + ((row & ~31u) << 16), hi = lo + 64;         // ... and as this thread's warp does (its 32 lanes)
+	uint32_t parity = 0;
+	// this warpgroup's TMEM stores are complete and ordered before the MMAs its first thread issues; then everyone sleeps on the commit
+	auto run_layer = [&](uint32_t d, uint32_t idesc, uint32_t a, uint32_t w_off, uint32_t F) {
+		tmem_st_wait();
+		fence_before_sync();
+		slot_barrier(slot);
+		if (row == 0) {
+			fence_after_sync();
+			gemm_ts(d, idesc, a, k_major(sbase + w_off, F), F / 16, 0);
+			mma_commit(acc_ready);
+		}
+		mbar_wait(acc_ready, parity);
+		parity ^= 1;
+		fence_after_sync();
+	};
+
+	struct In { uint32_t e[16]; float dx, dy, dz; };
+	auto load_tile = [&](uint32_t tile, In& t) {
+		const uint32_t s = tile * 128 + row;
+		const bool valid = s < n_limit;
+		const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)s * 32);
+		#pragma unroll
+		for (int c = 0; c < 4; ++c) {
+			const uint4 q = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+			t.e[4 * c] = q.x; t.e[4 * c + 1] = q.y; t.e[4 * c + 2] = q.z; t.e[4 * c + 3] = q.w;
+		}
+		t.dx = t.dy = t.dz = 0.f;
+		if (MODE != MODE_DENSITY && valid) { const float* cp = coords + (size_t)s * coord_stride + 4; t.dx = cp[0]; t.dy = cp[1]; t.dz = cp[2]; }
+	};
+	uint32_t tile = blockIdx.x * kFwdSlots + slot;
+	In nxt;
+	if (tile < n_tiles) load_tile(tile, nxt);
+	for (; tile < n_tiles; tile += tile_stride) {
+		const uint32_t s = tile * 128 + row;
+		const bool valid = s < n_limit;
+		const In cur = nxt;
+		// the encoded position is already fp16 pairs in feature order: 16 packed columns, straight into the A operand of layer 0
+		tmem_st16(lo, cur.e);
+		if (tile + tile_stride < n_tiles) load_tile(tile + tile_stride, nxt);
+		run_layer(mhi, I_128x64, mlo, Smem::W0, 32);                       // h = W0 e
+		relu_row_to_tmem(hi, hi);
+		run_layer(mlo, I_128x16, mhi, Smem::W1, 64);                       // o = W1 h (16 outputs, no activation)
+		uint32_t r[16];
+		tmem_ld16_nowait(lo, r);
+		tmem_ld_wait();
+		tmem_ld_pin(r);
+		if (MODE == MODE_DENSITY) {
+			if (valid) {
+				uint4 o0, o1;
+				o0.x = pack2(__uint_as_float(r[0]), __uint_as_float(r[1])); o0.y = pack2(__uint_as_float(r[2]), __uint_as_float(r[3]));
+				o0.z = pack2(__uint_as_float(r[4]), __uint_as_float(r[5])); o0.w = pack2(__uint_as_float(r[6]), __uint_as_float(r[7]));
+				o1.x = pack2(__uint_as_float(r[8]), __uint_as_float(r[9])); o1.y = pack2(__uint_as_float(r[10]), __uint_as_float(r[11]));
+				o1.z = pack2(__uint_as_float(r[12]), __uint_as_float(r[13])); o1.w = pack2(__uint_as_float(r[14]), __uint_as_float(r[15]));
+				reinterpret_cast<uint4*>(out + (size_t)s * 16)[0] = o0;
+				reinterpret_cast<uint4*>(out + (size_t)s * 16)[1] = o1;
+			}
+			continue;
+		}
+		const float sigma_raw = __half2float(__float2half_rn(__uint_as_float(r[0])));
+		{
+			uint32_t x[16];
+			#pragma unroll
+			for (int i = 0; i < 8; ++i) x[i] = pack2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+			float sh[16];
+			if (valid) {
+				sh4(cur.dx, cur.dy, cur.dz, sh);
+			} else {
+				#pragma unroll
+				for (int i = 0; i < 16; ++i) sh[i] = 0.f;
+			}
+			#pragma unroll
+			for (int i = 0; i < 8; ++i) x[8 + i] = pack2(sh[2 * i], sh[2 * i + 1]);
+			tmem_st16(lo, x);                                              // rgb-network input [density_out(16) | SH(16)]
+		}
+		run_layer(mhi, I_128x64, mlo, Smem::V0, 32);                       // h1 = V0 x
+		relu_row_to_tmem(hi, hi);
+		run_layer(mlo, I_128x64, mhi, Smem::V1, 64);                       // h2 = V1 h1
+		relu_row_to_tmem(lo, lo);
+		run_layer(mhi, I_128x8, mlo, Smem::V2, 64);                        // c = V2 h2 (3 of the 8 computed outputs are used)
+		uint32_t c[8];
+		tmem_ld8_nowait(hi, c);
+		tmem_ld_wait();
+		tmem_ld_pin8(c);
+		if (valid) {
+			uint2 o; o.x = pack2(__uint_as_float(c[0]), __uint_as_float(c[1])); o.y = pack2(__uint_as_float(c[2]), sigma_raw);
+			*reinterpret_cast<uint2*>(out + (size_t)s * 4) = o;
+		}
+	}
+	fence_before_sync();
+	__syncthreads();
+	if (warp == 0) tmem_dealloc(tm, 512);
+}
+
 } // namespace ngp
 
 // =====================================================================================================
@@ -418,6 +586,23 @@ template <int MODE>
 static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords, uint32_t coord_stride, uint32_t n, const uint32_t* n_valid,
                       const void* weights, const void* dloss, void* out, void* denc, float* wgrad, float* wgrad_partials = nullptr, uint32_t* grid_out = nullptr,
                       const uint32_t* enc_rows = nullptr, uint32_t n_enc_rows = 0) {
+	if (MODE != MODE_TRAIN) {
+		// forward only: the warp-specialised kernel with activations in tensor memory, one persistent CTA per SM
+		constexpr uint32_t fwd_smem = Smem::WEND + 256;
+		static bool fwd_configured = false;
+		if (!fwd_configured) {
+			if (cudaFuncSetAttribute(mlp_fwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, fwd_smem) != cudaSuccess) {
+				set_error("mlp: cannot reserve %u bytes of shared memory: %s", fwd_smem, cudaGetErrorString(cudaGetLastError())); return -2;
+			}
+			fwd_configured = true;
+		}
+		const uint32_t groups = div_up(div_up(n, 128), kFwdSlots);
+		const uint32_t fwd_grid = groups < kNumSMs ? groups : kNumSMs;
+		NGP_LAUNCH("mlp_fwd_kernel", stream, launch_chained(mlp_fwd_kernel<MODE>, fwd_grid, kFwdThreads, fwd_smem, stream, (const __half*)enc, coords, coord_stride, n, n_valid,
+			(const __half*)weights, (__half*)out));
+		if (grid_out) *grid_out = fwd_grid;
+		return check_launch("mlp_fwd_kernel");
+	}
 	constexpr uint32_t smem = (MODE == MODE_TRAIN ? Smem::TRAIN_END : Smem::INFER_END) + Smem::CTRL;
 	constexpr uint32_t ctas_per_sm = MODE == MODE_TRAIN ? 2 : 3;
 	static bool configured = false;
