@@ -3,11 +3,10 @@
 // CUTLASS weight-gradient GEMMs and the two FullLayer dgrad GEMMs (:845-897), the SH encoding kernel
 // (encodings/spherical_harmonics.h:48) and NGPNetwork's glue kernels (internal/network/ngp_network.h:44-127).
 //
-// One CTA (4 warps) owns a tile of 128 samples: thread t owns sample t for loads/epilogues, thread 0 issues the MMAs.
-// Weights (20 KB) stay in shared memory for the CTA lifetime; activations pass layer to layer TMEM -> registers -> SMEM
-// and never visit HBM.  In training the same tile runs forward AND backward: dgrad uses the resident weights as MN-major
-// operands, wgrad (dW = dY^T X, K = 128 samples per tile) accumulates in TMEM across all tiles of the persistent CTA
-// and is flushed once with fp32 atomics -- no split-K workspaces, no stored activations.
+// Two kernels (see their headers below): mlp_fwd_kernel (inference / density: activations never leave tensor memory) and
+// mlp_train_kernel (forward + dgrad chain through tensor memory, weight gradients resident in TMEM for the CTA's lifetime).
+// Both are persistent, one CTA per SM, with several independent 128-sample tile slots in flight; the weights (20 KB) stay in
+// shared memory; activations never visit HBM; no split-K workspaces, no stored activations.
 #include "common.cuh"
 #include "tcgen05.cuh"
 
@@ -21,17 +20,9 @@ enum { MODE_INFER = 0, MODE_TRAIN = 1, MODE_DENSITY = 2 };
 constexpr uint32_t kW0 = 0, kW1 = 2048, kV0 = 3072, kV1 = 5120, kV2 = 9216;
 
 struct Smem {
-	// weights, core-matrix tiled, rows = output neuron, F = fan-in
+	// weights, core-matrix tiled, rows = output neuron, F = fan-in (the only shared-memory operand of the chain MMAs)
 	static constexpr uint32_t W0 = 0, W1 = 4096, V0 = 6144, V1 = 10240, V2 = 18432, WEND = 20480;
-	// activations, rows = sample
-	static constexpr uint32_t E = WEND, H = E + 8192, X = H + 16384, H1 = X + 8192;
-	static constexpr uint32_t INFER_END = H1 + 16384;                  // H2 reuses H in inference
-	static constexpr uint32_t H2 = INFER_END, GA = H2 + 16384, G16 = GA + 16384, TRAIN_END = G16 + 4096;
-	static constexpr uint32_t CTRL = 64;                               // mbarrier + tmem base, placed after the buffers
 };
-
-// TMEM columns: [0,64) working accumulator; wgrad accumulators (M = 64 rows) follow
-constexpr uint32_t kTmemWork = 0, kTmemW0 = 64, kTmemW1 = 96, kTmemV0 = 112, kTmemV1 = 144, kTmemV2 = 208;
 
 __device__ __forceinline__ void stage_weights(const __half* __restrict__ w, uint8_t* smem, uint32_t off, uint32_t rows, uint32_t F) {
 	// 16-byte chunks: chunk c of row r -> tiled position
@@ -75,28 +66,6 @@ __device__ __forceinline__ void sh4(float dx, float dy, float dz, float* out) {
 	out[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
 }
 
-struct Pipe {
-	uint32_t bar, parity, tmem;
-	// all threads: publish SMEM writes to the async proxy, order prior TMEM reads, meet
-	__device__ __forceinline__ void publish() { fence_proxy_async(); fence_before_sync(); __syncthreads(); }
-	// thread 0 after issuing: commit; everyone: wait for completion
-	__device__ __forceinline__ void commit_and_wait() {
-		if (threadIdx.x == 0) mma_commit(bar);
-		wait();
-	}
-	// the issuing thread has already committed (possibly with more MMAs queued behind the commit)
-	__device__ __forceinline__ void wait() {
-		__syncwarp();
-		mbar_wait(bar, parity);
-		parity ^= 1;
-		fence_after_sync();
-	}
-};
-
-// the global-memory inputs of one tile row, fetched one tile ahead so that their latency (two dependent loads for a reused
-// encoding row) hides under the current tile's layers instead of heading its serial chain
-struct TileIn { uint4 e[4]; float dx, dy, dz; uint2 dl; };
-
 // read this thread's row: n16 groups of 16 fp32 columns starting at column col
 template <int N16>
 __device__ __forceinline__ void read_row(uint32_t tmem, uint32_t col, float* v) {
@@ -110,276 +79,6 @@ __device__ __forceinline__ void read_row(uint32_t tmem, uint32_t col, float* v) 
 	for (int g = 0; g < N16; ++g) tmem_ld_pin(r + g * 16);
 	#pragma unroll
 	for (int i = 0; i < N16 * 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// zero the gradient where the forward activation (fp16, this thread's row in buf) was not positive
-__device__ __forceinline__ void relu_mask64(const uint8_t* smem, uint32_t buf, uint32_t row, float* g) {
-	#pragma unroll
-	for (int c = 0; c < 8; ++c) {
-		const uint4 a = *reinterpret_cast<const uint4*>(smem + buf + tile_off(row, c, 64));
-		const uint32_t w[4] = {a.x, a.y, a.z, a.w};
-		#pragma unroll
-		for (int i = 0; i < 4; ++i) {
-			const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
-			if (!(f.x > 0.f)) g[c * 8 + 2 * i] = 0.f;
-			if (!(f.y > 0.f)) g[c * 8 + 2 * i + 1] = 0.f;
-		}
-	}
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(128, MODE == MODE_TRAIN ? 2 : 3) mlp_kernel(
-	const __half* __restrict__ enc, const float* __restrict__ coords, uint32_t coord_stride, uint32_t n, const uint32_t* __restrict__ n_valid,
-	const __half* __restrict__ weights, const __half* __restrict__ dloss, __half* __restrict__ out, __half* __restrict__ denc, float* __restrict__ wgrad,
-	float* __restrict__ wgrad_partials, const uint32_t* __restrict__ enc_rows, uint32_t n_enc_rows)
-{
-	extern __shared__ __align__(1024) uint8_t smem[];
-	constexpr uint32_t kEnd = MODE == MODE_TRAIN ? Smem::TRAIN_END : Smem::INFER_END;
-	constexpr uint32_t kH2 = MODE == MODE_TRAIN ? Smem::H2 : Smem::H;
-	constexpr uint32_t kTmemCols = MODE == MODE_TRAIN ? 256 : 64;
-	const uint32_t sbase = smem_u32(smem);
-	uint32_t* ctrl = reinterpret_cast<uint32_t*>(smem + kEnd);   // [0..1] mbarrier, [2] tmem base, [4..5] second mbarrier (weight-gradient MMAs)
-	const uint32_t row = threadIdx.x;
-
-	// barrier and TMEM set-up touch no global memory: they run while the previous kernel of the chain is still draining
-	if (threadIdx.x == 0) { mbar_init(sbase + kEnd, 1); mbar_init(sbase + kEnd + 16, 1); fence_mbar_init(); }
-	if (threadIdx.x < 32) tmem_alloc(sbase + kEnd + 8, kTmemCols);
-	chain_enter();
-	stage_weights(weights + kW0, smem, Smem::W0, 64, 32);
-	stage_weights(weights + kW1, smem, Smem::W1, 16, 64);
-	if (MODE != MODE_DENSITY) {
-		stage_weights(weights + kV0, smem, Smem::V0, 64, 32);
-		stage_weights(weights + kV1, smem, Smem::V1, 64, 64);
-		stage_weights(weights + kV2, smem, Smem::V2, 16, 64);
-	}
-	fence_before_sync();
-	__syncthreads();
-	fence_after_sync();
-	Pipe pipe; pipe.bar = sbase + kEnd; pipe.parity = 0; pipe.tmem = ctrl[2];
-	const uint32_t tm = pipe.tmem;
-
-	constexpr uint32_t I_128x64 = instr_desc(128, 64, 0, 0), I_128x16 = instr_desc(128, 16, 0, 0);
-	constexpr uint32_t I_d64 = instr_desc(128, 64, 0, 1), I_d32 = instr_desc(128, 32, 0, 1);          // dgrad: B = W as MN-major
-	constexpr uint32_t I_w64 = instr_desc(64, 64, 1, 1), I_w32 = instr_desc(64, 32, 1, 1), I_w16 = instr_desc(64, 16, 1, 1);
-
-	const uint32_t n_limit = n_valid ? min(*n_valid, n) : n;
-	const uint32_t n_tiles = (n_limit + 127) / 128;
-	uint32_t wg_acc = 0;   // 0 for the CTA's first tile, 1 afterwards
-	uint32_t wg_parity = 0;
-
-	auto load_tile = [&](uint32_t tile, TileIn& t) {
-		const uint32_t s = tile * 128 + row;
-		const bool valid = s < n_limit;
-		const uint32_t enc_row = (MODE == MODE_TRAIN && enc_rows && valid) ? min(__ldg(enc_rows + s), n_enc_rows - 1u) : s;   // reuse of the inference pass's encodings
-		const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)enc_row * 32);
-		#pragma unroll
-		for (int c = 0; c < 4; ++c) t.e[c] = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
-		t.dx = t.dy = t.dz = 0.f;
-		if (MODE != MODE_DENSITY && valid) {
-			const float* cp = coords + (size_t)s * coord_stride + 4;
-			t.dx = cp[0]; t.dy = cp[1]; t.dz = cp[2];
-		}
-		t.dl = make_uint2(0u, 0u);
-		// dloss == nullptr: "input gradient" mode (tiny-cuda-nn/object.h:126-150) -- the loss gradient is one-hot on sigma_raw with the
-		// reference's backprop scale 128 (fp16 0x5800), zero on r, g, b
-		if (MODE == MODE_TRAIN && valid) t.dl = dloss ? __ldg(reinterpret_cast<const uint2*>(dloss + (size_t)s * 4)) : make_uint2(0u, 0x58000000u);
-	};
-	TileIn nxt;
-	if (blockIdx.x < n_tiles) load_tile(blockIdx.x, nxt);
-
-	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-		const uint32_t s = tile * 128 + row;
-		const bool valid = s < n_limit;
-		const TileIn cur = nxt;
-
-		// ---- stage the encoded positions (64 B / sample) and the SH of the direction --------------
-		{
-			#pragma unroll
-			for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(smem + Smem::E + tile_off(row, c, 32)) = cur.e[c];
-			if (MODE != MODE_DENSITY) {
-				float sh[16];
-				if (valid) {
-					sh4(cur.dx, cur.dy, cur.dz, sh);
-				} else {
-					#pragma unroll
-					for (int i = 0; i < 16; ++i) sh[i] = 0.f;
-				}
-				store_chunk(smem, Smem::X, 32, row, 2, sh, false);
-				store_chunk(smem, Smem::X, 32, row, 3, sh + 8, false);
-			}
-		}
-		pipe.publish();
-		if (tile + gridDim.x < n_tiles) load_tile(tile + gridDim.x, nxt);
-
-		float v[64];
-		// ---- density net layer 0: h = relu(W0 e) ---------------------------------------------------
-		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x64, k_major(sbase + Smem::E, 32), k_major(sbase + Smem::W0, 32), 2, 0); }
-		pipe.commit_and_wait();
-		read_row<4>(tm, kTmemWork, v);
-		#pragma unroll
-		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::H, 64, row, c, v + 8 * c, true);
-		pipe.publish();
-		// ---- density net layer 1: o = W1 h (16 outputs, no activation) -------------------------------
-		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x16, k_major(sbase + Smem::H, 64), k_major(sbase + Smem::W1, 64), 4, 0); }
-		pipe.commit_and_wait();
-		read_row<1>(tm, kTmemWork, v);
-		if (MODE == MODE_DENSITY) {
-			if (valid) {
-				uint4 o0, o1;
-				o0.x = pack2(v[0], v[1]); o0.y = pack2(v[2], v[3]); o0.z = pack2(v[4], v[5]); o0.w = pack2(v[6], v[7]);
-				o1.x = pack2(v[8], v[9]); o1.y = pack2(v[10], v[11]); o1.z = pack2(v[12], v[13]); o1.w = pack2(v[14], v[15]);
-				reinterpret_cast<uint4*>(out + (size_t)s * 16)[0] = o0;
-				reinterpret_cast<uint4*>(out + (size_t)s * 16)[1] = o1;
-			}
-			fence_before_sync();
-			__syncthreads();
-			continue;
-		}
-		const float sigma_raw = __half2float(__float2half_rn(v[0]));
-		store_chunk(smem, Smem::X, 32, row, 0, v, false);
-		store_chunk(smem, Smem::X, 32, row, 1, v + 8, false);
-		pipe.publish();
-		// ---- rgb net: h1 = relu(V0 x), h2 = relu(V1 h1), c = V2 h2 ---------------------------------
-		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x64, k_major(sbase + Smem::X, 32), k_major(sbase + Smem::V0, 32), 2, 0); }
-		pipe.commit_and_wait();
-		read_row<4>(tm, kTmemWork, v);
-		#pragma unroll
-		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::H1, 64, row, c, v + 8 * c, true);
-		pipe.publish();
-		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x64, k_major(sbase + Smem::H1, 64), k_major(sbase + Smem::V1, 64), 4, 0); }
-		pipe.commit_and_wait();
-		read_row<4>(tm, kTmemWork, v);
-		#pragma unroll
-		for (int c = 0; c < 8; ++c) store_chunk(smem, kH2, 64, row, c, v + 8 * c, true);
-		pipe.publish();
-		if (threadIdx.x == 0) { fence_after_sync(); gemm(tm + kTmemWork, I_128x16, k_major(sbase + kH2, 64), k_major(sbase + Smem::V2, 64), 4, 0); }
-		pipe.commit_and_wait();
-		read_row<1>(tm, kTmemWork, v);
-		if (valid && out) {
-			uint2 o; o.x = pack2(v[0], v[1]); o.y = pack2(v[2], sigma_raw);
-			*reinterpret_cast<uint2*>(out + (size_t)s * 4) = o;
-		}
-		if (MODE == MODE_INFER) { fence_before_sync(); __syncthreads(); continue; }
-
-		// ======================= backward (MODE_TRAIN) ==============================================
-		float dsigma = 0.f;
-		{
-			float dc[16];
-			#pragma unroll
-			for (int i = 0; i < 16; ++i) dc[i] = 0.f;
-			if (valid) {
-				const uint2 d = cur.dl;
-				const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&d.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&d.y));
-				dc[0] = a.x; dc[1] = a.y; dc[2] = b.x; dsigma = b.y;
-			}
-			store_chunk(smem, Smem::G16, 16, row, 0, dc, false);
-			store_chunk(smem, Smem::G16, 16, row, 1, dc + 8, false);
-		}
-		pipe.publish();
-		// dV2^T[64][16] += H2^T dc ; dh2 = dc V2
-		if (threadIdx.x == 0) {
-			fence_after_sync();
-			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::G16, 16), mn_major(sbase + Smem::V2, 64), 1, 0);
-			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
-			gemm(tm + kTmemV2, I_w16, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
-		}
-		pipe.wait();
-		read_row<4>(tm, kTmemWork, v);
-		relu_mask64(smem, kH2, row, v);
-		#pragma unroll
-		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::GA, 64, row, c, v + 8 * c, false);
-		pipe.publish();
-		// dV1[64][64] += dh2^T H1 ; dh1 = dh2 V1
-		if (threadIdx.x == 0) {
-			fence_after_sync();
-			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::V1, 64), 4, 0);
-			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
-			gemm(tm + kTmemV1, I_w64, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::H1, 64), 8, wg_acc);
-		}
-		pipe.wait();
-		read_row<4>(tm, kTmemWork, v);
-		relu_mask64(smem, Smem::H1, row, v);
-		#pragma unroll
-		for (int c = 0; c < 8; ++c) store_chunk(smem, kH2, 64, row, c, v + 8 * c, false);   // dh1 takes H2's place
-		pipe.publish();
-		// dV0[64][32] += dh1^T x ; dx = dh1 V0
-		if (threadIdx.x == 0) {
-			fence_after_sync();
-			gemm(tm + kTmemWork, I_d32, k_major(sbase + kH2, 64), mn_major(sbase + Smem::V0, 32), 4, 0);
-			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
-			gemm(tm + kTmemV0, I_w32, mn_major(sbase + kH2, 64), mn_major(sbase + Smem::X, 32), 8, wg_acc);
-		}
-		pipe.wait();
-		read_row<1>(tm, kTmemWork, v);      // only dL/d(density_out[0..16)) is needed; the SH half has no parameters
-		v[0] = __half2float(__float2half_rn(v[0])) + dsigma;   // ngp_network.h:119-126
-		store_chunk(smem, Smem::G16, 16, row, 0, v, false);
-		store_chunk(smem, Smem::G16, 16, row, 1, v + 8, false);
-		pipe.publish();
-		// dW1^T[64][16] += H^T do ; dh = do W1
-		if (threadIdx.x == 0) {
-			fence_after_sync();
-			gemm(tm + kTmemWork, I_d64, k_major(sbase + Smem::G16, 16), mn_major(sbase + Smem::W1, 64), 1, 0);
-			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
-			gemm(tm + kTmemW1, I_w16, mn_major(sbase + Smem::H, 64), mn_major(sbase + Smem::G16, 16), 8, wg_acc);
-		}
-		pipe.wait();
-		read_row<4>(tm, kTmemWork, v);
-		relu_mask64(smem, Smem::H, row, v);
-		#pragma unroll
-		for (int c = 0; c < 8; ++c) store_chunk(smem, Smem::GA, 64, row, c, v + 8 * c, false);
-		pipe.publish();
-		// dW0[64][32] += dh^T e ; de = dh W0
-		if (threadIdx.x == 0) {
-			fence_after_sync();
-			gemm(tm + kTmemWork, I_d32, k_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::W0, 32), 4, 0);
-			mma_commit(pipe.bar);          // the epilogue waits for the dgrad only; the weight-gradient MMAs run underneath it
-			gemm(tm + kTmemW0, I_w32, mn_major(sbase + Smem::GA, 64), mn_major(sbase + Smem::E, 32), 8, wg_acc);
-			mma_commit(sbase + kEnd + 16);   // second barrier: every weight-gradient MMA of this tile has read its operands
-		}
-		pipe.wait();
-		read_row<2>(tm, kTmemWork, v);
-		if (valid && denc) {
-			uint4* dst = reinterpret_cast<uint4*>(denc + (size_t)s * 32);
-			#pragma unroll
-			for (int c = 0; c < 4; ++c) {
-				uint4 o; o.x = pack2(v[8 * c], v[8 * c + 1]); o.y = pack2(v[8 * c + 2], v[8 * c + 3]); o.z = pack2(v[8 * c + 4], v[8 * c + 5]); o.w = pack2(v[8 * c + 6], v[8 * c + 7]);
-				dst[c] = o;
-			}
-		}
-		wg_acc = 1;
-		// the next tile's staging overwrites E / X / H..., which the trailing weight-gradient MMAs may still be reading
-		__syncwarp();
-		mbar_wait(sbase + kEnd + 16, wg_parity);
-		wg_parity ^= 1;
-		fence_before_sync();
-		__syncthreads();
-	}
-
-	// ---- flush the weight-gradient accumulators (M = 64: row m sits in TMEM lane 32*(m/16) + m%16) ------
-	// wgrad_partials != nullptr: this CTA owns one [NGP_MLP_PARAMS] fp32 slot and stores plainly (a small second kernel sums
-	// the slots in a fixed order); otherwise fp32 atomics into wgrad (the stand-alone ngp_mlp_train entry point).
-	if (MODE == MODE_TRAIN && wg_acc) {
-		fence_after_sync();
-		const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, m = warp * 16 + lane;
-		float v[64];
-		if (wgrad_partials) {
-			float* slot = wgrad_partials + (size_t)blockIdx.x * NGP_MLP_PARAMS;
-			read_row<2>(tm, kTmemW0, v);      if (lane < 16) for (int k = 0; k < 32; k += 4) *reinterpret_cast<float4*>(slot + kW0 + m * 32 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
-			read_row<1>(tm, kTmemW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) slot[kW1 + o * 64 + m] = v[o];
-			read_row<2>(tm, kTmemV0, v);      if (lane < 16) for (int k = 0; k < 32; k += 4) *reinterpret_cast<float4*>(slot + kV0 + m * 32 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
-			read_row<4>(tm, kTmemV1, v);      if (lane < 16) for (int k = 0; k < 64; k += 4) *reinterpret_cast<float4*>(slot + kV1 + m * 64 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
-			read_row<1>(tm, kTmemV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) slot[kV2 + o * 64 + m] = v[o];
-		} else {
-			read_row<2>(tm, kTmemW0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kW0 + m * 32 + k, v[k]);
-			read_row<1>(tm, kTmemW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kW1 + o * 64 + m, v[o]);
-			read_row<2>(tm, kTmemV0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kV0 + m * 32 + k, v[k]);
-			read_row<4>(tm, kTmemV1, v);      if (lane < 16) for (int k = 0; k < 64; ++k) atomicAdd(wgrad + kV1 + m * 64 + k, v[k]);
-			read_row<1>(tm, kTmemV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kV2 + o * 64 + m, v[o]);
-		}
-	}
-	fence_before_sync();
-	__syncthreads();
-	if (threadIdx.x < 32) tmem_dealloc(tm, kTmemCols);
 }
 
 // =====================================================================================================
@@ -550,6 +249,351 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(
 	if (warp == 0) tmem_dealloc(tm, 512);
 }
 
+// =====================================================================================================
+// Training kernel: forward + backward (dgrad and wgrad) of both networks on one tile of 128 samples per slot.
+//
+//   * one persistent CTA per SM, kTrainSlots = 3 independent tile slots (one warpgroup each) + one weight-gradient warp;
+//   * the CHAIN (5 forward layers, 5 dgrad layers: each needs the previous one's result) runs like the forward-only kernel:
+//     the A operand of every chain MMA is written to TENSOR MEMORY by the epilogue (tcgen05.st) and read from there, so the
+//     critical path of a layer is  accumulator -> registers -> TMEM -> next MMA  with one 128-thread named barrier;
+//   * the SAME packed registers are then stored to shared memory -- off the critical path, while the chain MMA already runs -- as
+//     the operands of the weight-gradient GEMMs (dW = dY^T X, K = 128 samples, both operands MN-major views of sample-major
+//     buffers).  A dedicated thread issues all weight-gradient MMAs of the CTA (one issuer: the accumulators, resident in TMEM
+//     for the CTA's lifetime, are shared by the three slots) as the slots hand their operand pairs over through mbarriers;
+//   * per-slot shared memory is 68 KB: the five activations a tile needs until its backward pass (E, H, X, H1, H2: 64 KB) and
+//     dL/dc (4 KB); every other gradient overwrites an activation whose weight-gradient GEMM has completed (dh2 and dh take
+//     H2's place, dh1 takes H1's, dL/d(density_out) takes dL/dc's) -- which is what lets THREE tiles be in flight per SM
+//     instead of two (20 + 3 x 68 = 224 KB);
+//   * TMEM: per slot 96 columns (A operand 32 | accumulator 64), weight-gradient accumulators 160 columns: 448 of 512.
+// =====================================================================================================
+constexpr uint32_t kTrainSlots = 3;
+constexpr uint32_t kTrainThreads = kTrainSlots * 128 + 32;
+
+struct TrainSmem {
+	static constexpr uint32_t E = 0, H = 8192, X = 24576, H1 = 32768, H2 = 49152, G16 = 65536, SLOT = 69632;
+	static constexpr uint32_t SLOT0 = Smem::WEND, CTRL = SLOT0 + kTrainSlots * SLOT, END = CTRL + 256;
+};
+constexpr uint32_t kTrainWg = kTrainSlots * 96;       // first weight-gradient accumulator column
+constexpr uint32_t kWgW0 = kTrainWg, kWgW1 = kTrainWg + 32, kWgV0 = kTrainWg + 48, kWgV1 = kTrainWg + 80, kWgV2 = kTrainWg + 144;
+
+// this thread's row of `n_chunks` 16-byte chunks (8 fp16 features each, already packed) into a core-matrix tiled buffer
+template <int N_CHUNKS>
+__device__ __forceinline__ void store_row_packed(uint8_t* smem, uint32_t buf, uint32_t F, uint32_t row, const uint32_t* q) {
+	#pragma unroll
+	for (int c = 0; c < N_CHUNKS; ++c) *reinterpret_cast<uint4*>(smem + buf + tile_off(row, c, F)) = make_uint4(q[4 * c], q[4 * c + 1], q[4 * c + 2], q[4 * c + 3]);
+}
+
+// accumulator columns [src, src + 64) -> fp16 pairs q[32]; RELU: max with zero; else: zero where the forward activation (this
+// thread's row of the 64-wide buffer `act`) was not positive
+template <bool RELU>
+__device__ __forceinline__ void row64_to_packed(uint32_t src, uint32_t* q, const uint8_t* smem = nullptr, uint32_t act = 0, uint32_t row = 0) {
+	uint32_t r[64];
+	tmem_ld32_nowait(src, r);
+	tmem_ld32_nowait(src + 32, r + 32);
+	tmem_ld_wait();
+	tmem_ld_pin(r); tmem_ld_pin(r + 16); tmem_ld_pin(r + 32); tmem_ld_pin(r + 48);
+	if (RELU) {
+		#pragma unroll
+		for (int i = 0; i < 32; ++i) q[i] = relu_pack(r[2 * i], r[2 * i + 1]);
+	} else {
+		const __half2 zero = __floats2half2_rn(0.f, 0.f);
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			const uint4 a = *reinterpret_cast<const uint4*>(smem + act + tile_off(row, c, 64));
+			const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+			#pragma unroll
+			for (int i = 0; i < 4; ++i) {
+				const __half2 g = __floats2half2_rn(__uint_as_float(r[8 * c + 2 * i]), __uint_as_float(r[8 * c + 2 * i + 1]));
+				const __half2 m = __hmul2(g, __hgt2(*reinterpret_cast<const __half2*>(&w[i]), zero));      // gradient x (activation > 0)
+				q[4 * c + i] = *reinterpret_cast<const uint32_t*>(&m);
+			}
+		}
+	}
+}
+
+__global__ void __launch_bounds__(kTrainThreads, 1) mlp_train_kernel(
+	const __half* __restrict__ enc, const float* __restrict__ coords, uint32_t coord_stride, uint32_t n, const uint32_t* __restrict__ n_valid,
+	const __half* __restrict__ weights, const __half* __restrict__ dloss, __half* __restrict__ out, __half* __restrict__ denc, float* __restrict__ wgrad,
+	float* __restrict__ wgrad_partials, const uint32_t* __restrict__ enc_rows, uint32_t n_enc_rows)
+{
+	extern __shared__ __align__(1024) uint8_t smem[];
+	using TS = TrainSmem;
+	const uint32_t sbase = smem_u32(smem);
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const bool wg_warp = warp == kTrainSlots * 4;
+	// control block: [0,4) tmem base; barriers (8 B each) from +16: acc_ready[slot], wg_ready[slot], wg_done[slot]
+	auto bar_acc = [&](uint32_t s) { return sbase + TS::CTRL + 16 + s * 8; };
+	auto bar_wg_ready = [&](uint32_t s) { return sbase + TS::CTRL + 16 + (kTrainSlots + s) * 8; };
+	auto bar_wg_done = [&](uint32_t s) { return sbase + TS::CTRL + 16 + (2 * kTrainSlots + s) * 8; };
+
+	if (threadIdx.x == kTrainSlots * 128) {
+		for (uint32_t s = 0; s < kTrainSlots; ++s) { mbar_init(bar_acc(s), 1); mbar_init(bar_wg_ready(s), 4); mbar_init(bar_wg_done(s), 1); }
+		fence_mbar_init();
+	}
+	if (wg_warp) tmem_alloc(sbase + TS::CTRL, 512);
+	chain_enter();
+	stage_weights(weights + kW0, smem, Smem::W0, 64, 32);
+	stage_weights(weights + kW1, smem, Smem::W1, 16, 64);
+	stage_weights(weights + kV0, smem, Smem::V0, 64, 32);
+	stage_weights(weights + kV1, smem, Smem::V1, 64, 64);
+	stage_weights(weights + kV2, smem, Smem::V2, 16, 64);
+	fence_proxy_async();
+	fence_before_sync();
+	__syncthreads();
+	fence_after_sync();
+	const uint32_t tm = *reinterpret_cast<const uint32_t*>(smem + TS::CTRL);
+
+	const uint32_t n_limit = n_valid ? min(*n_valid, n) : n;
+	const uint32_t n_tiles = (n_limit + 127) / 128;
+	const uint32_t tile_stride = gridDim.x * kTrainSlots;
+
+	if (wg_warp) {
+		// ---------------------------------------------------------------------------------------------------------------
+		// weight-gradient issuer: per tile round five jobs (V2, V1, V0, W1, W0) for each slot in turn; every job waits for the slot's
+		// operand pair ("wg_ready": the gradient has been stored and fenced by all four warps), issues dW += dY^T X (M = 64,
+		// K = 128 samples) and commits to the slot's "wg_done", which the slot waits on before it reuses either buffer
+		// ---------------------------------------------------------------------------------------------------------------
+		if (lane == 0) {
+			constexpr uint32_t I_w64 = instr_desc(64, 64, 1, 1), I_w32 = instr_desc(64, 32, 1, 1), I_w16 = instr_desc(64, 16, 1, 1);
+			// FIXED order (tile round, job, slot): every accumulator sums its tiles in the same order whatever the timing, so the weight
+			// gradients are deterministic; the slots run the same sequence side by side, so waiting in order costs little
+			uint32_t parity = 0, started = 0;                                      // started: bit k = accumulator k holds a sum
+			for (uint32_t base = blockIdx.x * kTrainSlots; base < n_tiles; base += tile_stride) {
+				#pragma unroll 1
+				for (uint32_t job = 0; job < 5; ++job) {
+					#pragma unroll
+					for (uint32_t s = 0; s < kTrainSlots; ++s) {
+						if (base + s >= n_tiles) continue;
+						mbar_wait(bar_wg_ready(s), parity);
+						fence_after_sync();
+						const uint32_t b = sbase + TS::SLOT0 + s * TS::SLOT;
+						const uint32_t acc = (started >> job) & 1u;
+						switch (job) {
+							case 0: gemm(tm + kWgV2, I_w16, mn_major(b + TS::H2, 64), mn_major(b + TS::G16, 16), 8, acc); break;      // dV2^T[64][16] += H2^T dc
+							case 1: gemm(tm + kWgV1, I_w64, mn_major(b + TS::H2, 64), mn_major(b + TS::H1, 64), 8, acc); break;       // dV1[64][64]  += dh2^T H1   (dh2 in H2's place)
+							case 2: gemm(tm + kWgV0, I_w32, mn_major(b + TS::H1, 64), mn_major(b + TS::X, 32), 8, acc); break;        // dV0[64][32]  += dh1^T x    (dh1 in H1's place)
+							case 3: gemm(tm + kWgW1, I_w16, mn_major(b + TS::H, 64), mn_major(b + TS::G16, 16), 8, acc); break;       // dW1^T[64][16] += H^T do    (do in dc's place)
+							default: gemm(tm + kWgW0, I_w32, mn_major(b + TS::H2, 64), mn_major(b + TS::E, 32), 8, acc); break;       // dW0[64][32]  += dh^T e     (dh in H2's place)
+						}
+						mma_commit(bar_wg_done(s));
+						started |= 1u << job;
+					}
+					parity ^= 1;                                                   // every slot's hand-over barrier completes one phase per job
+				}
+			}
+		}
+		__syncwarp();
+	} else {
+		const uint32_t slot = warp >> 2, row = threadIdx.x & 127;
+		const uint32_t acc_ready = bar_acc(slot), wg_ready = bar_wg_ready(slot), wg_done = bar_wg_done(slot);
+		const uint32_t sb = TS::SLOT0 + slot * TS::SLOT;                      // this slot's buffers (byte offset in smem[])
+		const uint32_t mA = tm + slot * 96, mD = mA + 32;                      // A operand / accumulator columns as the MMA addresses them
+		const uint32_t tA = mA + ((row & ~31u) << 16), tD = tA + 32;           // ... and as this thread's warp does (its 32 lanes)
+		uint32_t parity = 0, wg_parity = 0;
+		constexpr uint32_t I_128x64 = instr_desc(128, 64, 0, 0), I_128x16 = instr_desc(128, 16, 0, 0);
+		constexpr uint32_t I_d64 = instr_desc(128, 64, 0, 1), I_d32 = instr_desc(128, 32, 0, 1), I_d16 = instr_desc(128, 16, 0, 1);   // dgrad: B = W as MN-major
+
+		// chain step, part 1: the A operand (this warpgroup's TMEM stores) is complete -> the slot's first thread issues the layer
+		auto issue = [&](uint32_t idesc, Operand b, uint32_t nk) {
+			tmem_st_wait();
+			fence_before_sync();
+			slot_barrier(slot);
+			if (row == 0) {
+				fence_after_sync();
+				gemm_ts(mD, idesc, mA, b, nk, 0);
+				mma_commit(acc_ready);
+			}
+		};
+		// chain step, part 2: sleep until the accumulator is complete
+		auto acquire = [&]() { mbar_wait(acc_ready, parity); parity ^= 1; fence_after_sync(); };
+		// the shared-memory stores of this thread are visible to the tensor core; the fourth warp's arrival releases the weight-gradient job
+		auto hand_over = [&]() { fence_proxy_async(); __syncwarp(); if (lane == 0) mbar_arrive(wg_ready); };
+		auto wait_wgrad = [&]() { mbar_wait(wg_done, wg_parity); wg_parity ^= 1; };
+
+		struct In { uint32_t e[16]; float dx, dy, dz; uint2 dl; };
+		auto load_tile = [&](uint32_t tile, In& t) {
+			const uint32_t s = tile * 128 + row;
+			const bool valid = s < n_limit;
+			const uint32_t enc_row = (enc_rows && valid) ? min(__ldg(enc_rows + s), n_enc_rows - 1u) : s;       // reuse of the inference pass's encodings
+			const uint4* src = reinterpret_cast<const uint4*>(enc + (size_t)enc_row * 32);
+			#pragma unroll
+			for (int c = 0; c < 4; ++c) {
+				const uint4 v = valid ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+				t.e[4 * c] = v.x; t.e[4 * c + 1] = v.y; t.e[4 * c + 2] = v.z; t.e[4 * c + 3] = v.w;
+			}
+			t.dx = t.dy = t.dz = 0.f;
+			if (valid) { const float* cp = coords + (size_t)s * coord_stride + 4; t.dx = cp[0]; t.dy = cp[1]; t.dz = cp[2]; }
+			// dloss == nullptr: "input gradient" mode (tiny-cuda-nn/object.h:126-150) -- the loss gradient is one-hot on sigma_raw with the
+			// reference's backprop scale 128 (fp16 0x5800), zero on r, g, b
+			t.dl = make_uint2(0u, 0u);
+			if (valid) t.dl = dloss ? __ldg(reinterpret_cast<const uint2*>(dloss + (size_t)s * 4)) : make_uint2(0u, 0x58000000u);
+		};
+		uint32_t tile = blockIdx.x * kTrainSlots + slot;
+		In nxt;
+		if (tile < n_tiles) load_tile(tile, nxt);
+		for (; tile < n_tiles; tile += tile_stride) {
+			const uint32_t s = tile * 128 + row;
+			const bool valid = s < n_limit;
+			const In cur = nxt;
+			uint32_t q[32];
+			// ================= forward =================
+			tmem_st16(tA, cur.e);
+			issue(I_128x64, k_major(sbase + Smem::W0, 32), 2);                                       // h = W0 e
+			store_row_packed<4>(smem, sb + TS::E, 32, row, cur.e);
+			if (tile + tile_stride < n_tiles) load_tile(tile + tile_stride, nxt);
+			acquire();
+			row64_to_packed<true>(tD, q);
+			tmem_st16(tA, q); tmem_st16(tA + 16, q + 16);
+			issue(I_128x16, k_major(sbase + Smem::W1, 64), 4);                                       // o = W1 h
+			store_row_packed<8>(smem, sb + TS::H, 64, row, q);
+			acquire();
+			float sigma_raw;
+			{
+				uint32_t r[16];
+				tmem_ld16_nowait(tD, r);
+				tmem_ld_wait();
+				tmem_ld_pin(r);
+				sigma_raw = __half2float(__float2half_rn(__uint_as_float(r[0])));
+				#pragma unroll
+				for (int i = 0; i < 8; ++i) q[i] = pack2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+				float sh[16];
+				if (valid) {
+					sh4(cur.dx, cur.dy, cur.dz, sh);
+				} else {
+					#pragma unroll
+					for (int i = 0; i < 16; ++i) sh[i] = 0.f;
+				}
+				#pragma unroll
+				for (int i = 0; i < 8; ++i) q[8 + i] = pack2(sh[2 * i], sh[2 * i + 1]);
+			}
+			tmem_st16(tA, q);
+			issue(I_128x64, k_major(sbase + Smem::V0, 32), 2);                                       // h1 = V0 [o | sh]
+			store_row_packed<4>(smem, sb + TS::X, 32, row, q);
+			acquire();
+			row64_to_packed<true>(tD, q);
+			tmem_st16(tA, q); tmem_st16(tA + 16, q + 16);
+			issue(I_128x64, k_major(sbase + Smem::V1, 64), 4);                                       // h2 = V1 h1
+			store_row_packed<8>(smem, sb + TS::H1, 64, row, q);
+			acquire();
+			row64_to_packed<true>(tD, q);
+			tmem_st16(tA, q); tmem_st16(tA + 16, q + 16);
+			issue(I_128x16, k_major(sbase + Smem::V2, 64), 4);                                       // c = V2 h2
+			store_row_packed<8>(smem, sb + TS::H2, 64, row, q);
+			acquire();
+			float dsigma = 0.f;
+			{
+				uint32_t c[8];
+				tmem_ld8_nowait(tD, c);
+				tmem_ld_wait();
+				tmem_ld_pin8(c);
+				if (valid && out) {
+					uint2 o; o.x = pack2(__uint_as_float(c[0]), __uint_as_float(c[1])); o.y = pack2(__uint_as_float(c[2]), sigma_raw);
+					*reinterpret_cast<uint2*>(out + (size_t)s * 4) = o;
+				}
+				// ================= backward =================
+				// dL/dc: r, g, b from the loss; the 13 padding outputs get no gradient
+				const __half2 hi = *reinterpret_cast<const __half2*>(&cur.dl.y);
+				dsigma = __half2float(__high2half(hi));
+				const __half2 b0 = __halves2half2(__low2half(hi), __float2half_rn(0.f));
+				#pragma unroll
+				for (int i = 0; i < 8; ++i) q[i] = 0u;
+				q[0] = cur.dl.x; q[1] = *reinterpret_cast<const uint32_t*>(&b0);
+			}
+			tmem_st8(tA, q);
+			issue(I_d64, mn_major(sbase + Smem::V2, 64), 1);                                         // dh2 = dc V2
+			store_row_packed<2>(smem, sb + TS::G16, 16, row, q);
+			hand_over();                                                                             // job V2: (H2, dc)
+			acquire();
+			row64_to_packed<false>(tD, q, smem, sb + TS::H2, row);                                   // x relu'(h2)
+			tmem_st16(tA, q); tmem_st16(tA + 16, q + 16);
+			issue(I_d64, mn_major(sbase + Smem::V1, 64), 4);                                         // dh1 = dh2 V1
+			wait_wgrad();                                                                            // job V2 has read H2 ...
+			store_row_packed<8>(smem, sb + TS::H2, 64, row, q);                                    // ... whose place dh2 takes
+			hand_over();                                                                             // job V1: (dh2, H1)
+			acquire();
+			row64_to_packed<false>(tD, q, smem, sb + TS::H1, row);                                   // x relu'(h1)
+			tmem_st16(tA, q); tmem_st16(tA + 16, q + 16);
+			issue(I_d16, mn_major(sbase + Smem::V0, 32), 4);                                         // dx[0..16) = dh1 V0[:, 0..16): the SH half has no parameters
+			wait_wgrad();                                                                            // job V1 has read H1 (and dh2)
+			store_row_packed<8>(smem, sb + TS::H1, 64, row, q);                                    // dh1 takes H1's place
+			hand_over();                                                                             // job V0: (dh1, x)
+			acquire();
+			{
+				uint32_t r[16];
+				tmem_ld16_nowait(tD, r);
+				tmem_ld_wait();
+				tmem_ld_pin(r);
+				float v0 = __half2float(__float2half_rn(__uint_as_float(r[0]))) + dsigma;              // ngp_network.h:119-126
+				q[0] = pack2(v0, __uint_as_float(r[1]));
+				#pragma unroll
+				for (int i = 1; i < 8; ++i) q[i] = pack2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+			}
+			tmem_st8(tA, q);
+			issue(I_d64, mn_major(sbase + Smem::W1, 64), 1);                                         // dh = do W1
+			store_row_packed<2>(smem, sb + TS::G16, 16, row, q);                                   // do takes dc's place (job V2 is long complete)
+			wait_wgrad();                                                                            // job V0 has been taken: the hand-over barrier never runs a phase ahead of its reader
+			hand_over();                                                                             // job W1: (H, do)
+			acquire();
+			row64_to_packed<false>(tD, q, smem, sb + TS::H, row);                                    // x relu'(h)
+			tmem_st16(tA, q); tmem_st16(tA + 16, q + 16);
+			issue(I_d32, mn_major(sbase + Smem::W0, 32), 4);                                         // de = dh W0
+			store_row_packed<8>(smem, sb + TS::H2, 64, row, q);                                    // dh takes dh2's place (job V1 is complete)
+			wait_wgrad();                                                                            // job W1 has been taken
+			hand_over();                                                                             // job W0: (dh, e)
+			acquire();
+			{
+				uint32_t r[32];
+				tmem_ld32_nowait(tD, r);
+				tmem_ld_wait();
+				tmem_ld_pin(r); tmem_ld_pin(r + 16);
+				if (valid && denc) {
+					uint4* dst = reinterpret_cast<uint4*>(denc + (size_t)s * 32);
+					#pragma unroll
+					for (int c = 0; c < 4; ++c) {
+						uint4 o;
+						o.x = pack2(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1])); o.y = pack2(__uint_as_float(r[8 * c + 2]), __uint_as_float(r[8 * c + 3]));
+						o.z = pack2(__uint_as_float(r[8 * c + 4]), __uint_as_float(r[8 * c + 5])); o.w = pack2(__uint_as_float(r[8 * c + 6]), __uint_as_float(r[8 * c + 7]));
+						dst[c] = o;
+					}
+				}
+			}
+			// the next tile overwrites E (and the flush reads the accumulators): job W0 must be complete
+			wait_wgrad();
+		}
+	}
+
+	// ---- flush the weight-gradient accumulators (M = 64: row m sits in TMEM lane 32*(m/16) + m%16) ------
+	// wgrad_partials != nullptr: this CTA owns one [NGP_MLP_PARAMS] fp32 slot and stores plainly (a small second kernel sums
+	// the slots in a fixed order); otherwise fp32 atomics into wgrad (the stand-alone ngp_mlp_train entry point).
+	fence_before_sync();
+	__syncthreads();
+	fence_after_sync();
+	if (blockIdx.x * kTrainSlots >= n_tiles) {
+		// no tile (a device-side count shrank the batch): this CTA's slot still takes part in the fixed-order sum
+		if (wgrad_partials) for (uint32_t i = threadIdx.x; i < NGP_MLP_PARAMS; i += blockDim.x) wgrad_partials[(size_t)blockIdx.x * NGP_MLP_PARAMS + i] = 0.f;
+	} else if (warp < 4) {
+		const uint32_t m = warp * 16 + lane;
+		float v[64];
+		if (wgrad_partials) {
+			float* slot_out = wgrad_partials + (size_t)blockIdx.x * NGP_MLP_PARAMS;
+			read_row<2>(tm, kWgW0, v);      if (lane < 16) for (int k = 0; k < 32; k += 4) *reinterpret_cast<float4*>(slot_out + kW0 + m * 32 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+			read_row<1>(tm, kWgW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) slot_out[kW1 + o * 64 + m] = v[o];
+			read_row<2>(tm, kWgV0, v);      if (lane < 16) for (int k = 0; k < 32; k += 4) *reinterpret_cast<float4*>(slot_out + kV0 + m * 32 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+			read_row<4>(tm, kWgV1, v);      if (lane < 16) for (int k = 0; k < 64; k += 4) *reinterpret_cast<float4*>(slot_out + kV1 + m * 64 + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+			read_row<1>(tm, kWgV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) slot_out[kV2 + o * 64 + m] = v[o];
+		} else {
+			read_row<2>(tm, kWgW0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kW0 + m * 32 + k, v[k]);
+			read_row<1>(tm, kWgW1, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kW1 + o * 64 + m, v[o]);
+			read_row<2>(tm, kWgV0, v);      if (lane < 16) for (int k = 0; k < 32; ++k) atomicAdd(wgrad + kV0 + m * 32 + k, v[k]);
+			read_row<4>(tm, kWgV1, v);      if (lane < 16) for (int k = 0; k < 64; ++k) atomicAdd(wgrad + kV1 + m * 64 + k, v[k]);
+			read_row<1>(tm, kWgV2, v);      if (lane < 16) for (int o = 0; o < 16; ++o) atomicAdd(wgrad + kV2 + o * 64 + m, v[o]);
+		}
+	}
+	fence_before_sync();
+	__syncthreads();
+	if (wg_warp) tmem_dealloc(tm, 512);
+}
+
 } // namespace ngp
 
 // =====================================================================================================
@@ -603,18 +647,17 @@ static int launch_mlp(cudaStream_t stream, const void* enc, const float* coords,
 		if (grid_out) *grid_out = fwd_grid;
 		return check_launch("mlp_fwd_kernel");
 	}
-	constexpr uint32_t smem = (MODE == MODE_TRAIN ? Smem::TRAIN_END : Smem::INFER_END) + Smem::CTRL;
-	constexpr uint32_t ctas_per_sm = MODE == MODE_TRAIN ? 2 : 3;
-	static bool configured = false;
-	if (!configured) {
-		if (cudaFuncSetAttribute(mlp_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
-			set_error("mlp: cannot reserve %u bytes of shared memory: %s", smem, cudaGetErrorString(cudaGetLastError())); return -2;
+	// training: forward + backward, three tile slots per persistent CTA
+	static bool train_configured = false;
+	if (!train_configured) {
+		if (cudaFuncSetAttribute(mlp_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TrainSmem::END) != cudaSuccess) {
+			set_error("mlp: cannot reserve %u bytes of shared memory: %s", TrainSmem::END, cudaGetErrorString(cudaGetLastError())); return -2;
 		}
-		configured = true;
+		train_configured = true;
 	}
-	const uint32_t n_tiles = div_up(n, 128);
-	const uint32_t grid = n_tiles < kNumSMs * ctas_per_sm ? n_tiles : kNumSMs * ctas_per_sm;
-	NGP_LAUNCH("mlp_kernel", stream, launch_chained(mlp_kernel<MODE>, grid, 128, smem, stream, (const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
+	const uint32_t groups = div_up(div_up(n, 128), kTrainSlots);
+	const uint32_t grid = groups < kNumSMs ? groups : kNumSMs;
+	NGP_LAUNCH("mlp_kernel", stream, launch_chained(mlp_train_kernel, grid, kTrainThreads, TrainSmem::END, stream, (const __half*)enc, coords, coord_stride, n, n_valid, (const __half*)weights,
 		(const __half*)dloss, (__half*)out, (__half*)denc, wgrad, wgrad_partials, enc_rows, n_enc_rows));
 	if (grid_out) *grid_out = grid;
 	return check_launch("mlp_kernel");
