@@ -154,6 +154,18 @@ int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cfg, uint32_t
  * plain order is written. */
 int ngp_generate_grid_samples_sorted(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
                                      const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices);
+/* One rank's share of ngp_generate_grid_samples_sorted under data parallelism: only the samples whose first candidate cell lies in
+ * part `part` of `n_parts` contiguous Morton-cell ranges are written, into the SAME slots of d_positions / d_indices the full
+ * call would use; *slot_begin / *slot_end (host) receive that contiguous slot range, so the density pass and the splat run on
+ * [slot_begin, slot_end) alone.  The union over the parts is the full call's output, bit for bit. */
+int ngp_generate_grid_samples_sorted_part(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
+                                          const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices,
+                                          uint32_t part, uint32_t n_parts, uint32_t* slot_begin, uint32_t* slot_end);
+/* update_grid (:705-735) in its two halves, for callers that put an exchange between them (max over ranks of d_grid_current):
+ * splat_grid_samples_nerf_max_nearest_neighbor (:107-132) WITHOUT the memset, then ema_grid_samples_nerf (:134-158) */
+int ngp_splat_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,
+                   int density_activation, float* d_grid_current);
+int ngp_ema_grid(void* stream, const ngp_sampler_cfg* cfg, float decay, const float* d_grid_current, float* d_grid);
 /* update_grid (:705-735): memset current, splat max, decay max */
 int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,
                     int density_activation, float decay, float* d_grid_current, float* d_grid);

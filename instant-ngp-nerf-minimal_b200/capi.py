@@ -73,6 +73,9 @@ SIGNATURES = {
     "ngp_mark_untrained_grid": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), u32, vp, vp]),
     "ngp_generate_grid_samples": (i32, [vp, C.POINTER(SamplerCfg), u32, u64, u64, u32, vp, f32, vp, vp]),
     "ngp_generate_grid_samples_sorted": (i32, [vp, C.POINTER(SamplerCfg), u32, u64, u64, u32, vp, f32, vp, vp]),
+    "ngp_generate_grid_samples_sorted_part": (i32, [vp, C.POINTER(SamplerCfg), u32, u64, u64, u32, vp, f32, vp, vp, u32, u32, C.POINTER(u32), C.POINTER(u32)]),
+    "ngp_splat_grid": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, vp, u32, i32, vp]),
+    "ngp_ema_grid": (i32, [vp, C.POINTER(SamplerCfg), f32, vp, vp]),
     "ngp_update_grid": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, vp, u32, i32, f32, vp, vp]),
     "ngp_update_grid_bitfield": (i32, [vp, C.POINTER(SamplerCfg), vp, f32, vp, vp]),
     "ngp_scan_workspace_bytes": (sz, [u32]),

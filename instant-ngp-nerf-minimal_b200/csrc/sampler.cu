@@ -60,9 +60,9 @@ __device__ __forceinline__ void grid_sample_one(const ngp_sampler_cfg& c, uint32
 	*idx_out = idx;
 }
 
-__global__ void generate_grid_samples_kernel(ngp_sampler_cfg c, uint32_t n, Pcg32 rng0, uint32_t step, const float* __restrict__ grid_in, float thresh,
+__global__ void generate_grid_samples_kernel(ngp_sampler_cfg c, uint32_t n, uint32_t i_begin, uint32_t i_end, Pcg32 rng0, uint32_t step, const float* __restrict__ grid_in, float thresh,
                                              float* __restrict__ out_pos, uint32_t* __restrict__ out_idx) {
-	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+	for (uint32_t i = i_begin + blockIdx.x * blockDim.x + threadIdx.x; i < i_end; i += gridDim.x * blockDim.x)
 		grid_sample_one(c, i, n, rng0, step, grid_in, thresh, out_pos + (size_t)i * 3, out_idx + i);
 }
 
@@ -91,10 +91,10 @@ __host__ __device__ inline uint64_t count_below(uint64_t M, uint64_t C, uint64_t
 // encodes 32 Morton-adjacent cells instead of 32 cells spread over the whole volume: the hash-grid gathers of the coarse
 // levels hit L1 instead of L2.  The multiset of (position, index) pairs equals generate_grid_samples_kernel's.
 __global__ void __launch_bounds__(256) generate_grid_samples_sorted_kernel(ngp_sampler_cfg c, uint32_t n, Pcg32 rng0, uint32_t step, uint32_t alpha, uint32_t beta, uint32_t chunk,
-                                                                            const float* __restrict__ grid_in, float thresh, float* __restrict__ out_pos, uint32_t* __restrict__ out_idx) {
+                                                                            uint32_t first_block, const float* __restrict__ grid_in, float thresh, float* __restrict__ out_pos, uint32_t* __restrict__ out_idx) {
 	const uint32_t cells = c.grid_size * c.grid_size * c.grid_size, mask = cells - 1;
 	const uint32_t K = n / cells, R = n % cells;
-	const uint32_t m_begin = blockIdx.x * chunk, m_end = min(m_begin + chunk, cells);      // chunk and cells are multiples of 256
+	const uint32_t m_begin = (first_block + blockIdx.x) * chunk, m_end = min(m_begin + chunk, cells);      // chunk and cells are multiples of 256
 	if (m_begin >= cells) return;
 	__shared__ uint32_t warp_tot[8];
 	__shared__ uint64_t fs[2];
@@ -204,25 +204,62 @@ extern "C" int ngp_generate_grid_samples(void* stream, const ngp_sampler_cfg* cf
 	NGP_REQUIRE(cfg && d_grid && d_positions && d_indices, "null pointer");
 	if (n == 0) return 0;
 	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
-	NGP_LAUNCH("generate_grid_samples_kernel", (cudaStream_t)stream, generate_grid_samples_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, d_grid, thresh, d_positions, d_indices));
+	NGP_LAUNCH("generate_grid_samples_kernel", (cudaStream_t)stream, generate_grid_samples_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n, 0, n, rng, step, d_grid, thresh, d_positions, d_indices));
 	return check_launch("generate_grid_samples");
+}
+
+extern "C" int ngp_generate_grid_samples_sorted_part(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
+                                                     const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices,
+                                                     uint32_t part, uint32_t n_parts, uint32_t* slot_begin, uint32_t* slot_end) {
+	NGP_REQUIRE(cfg && d_grid && d_positions && d_indices, "null pointer");
+	NGP_REQUIRE(n_parts >= 1 && part < n_parts, "bad part");
+	uint32_t lo = 0, hi = 0;
+	if (slot_begin) *slot_begin = 0;
+	if (slot_end) *slot_end = 0;
+	if (n == 0) return 0;
+	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
+	const uint32_t cells = cfg->grid_size * cfg->grid_size * cfg->grid_size;
+	if ((cells & (cells - 1)) != 0 || cells < 256) {         // the inversion needs a power-of-two cell count: plain order otherwise
+		lo = (uint32_t)((uint64_t)n * part / n_parts); hi = (uint32_t)((uint64_t)n * (part + 1) / n_parts);
+		if (hi > lo) NGP_LAUNCH("generate_grid_samples_kernel", (cudaStream_t)stream, generate_grid_samples_kernel<<<grid_for(hi - lo, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n, lo, hi, rng, step, d_grid, thresh, d_positions, d_indices));
+	} else {
+		uint32_t inv = kCellMul;                             // Newton: the inverse of an odd number modulo 2^32
+		for (int k = 0; k < 5; ++k) inv *= 2u - kCellMul * inv;
+		const uint32_t mask = cells - 1;
+		const uint32_t alpha = inv & mask, beta = (0u - inv * kCellAdd - step * n) & mask;
+		const uint32_t chunk = div_up(div_up(cells, 256), kNumSMs * 4) * 256;        // one resident wave of CTAs, each walks a contiguous run of cells
+		const uint32_t n_blocks = div_up(cells, chunk);
+		const uint32_t b0 = (uint32_t)((uint64_t)n_blocks * part / n_parts), b1 = (uint32_t)((uint64_t)n_blocks * (part + 1) / n_parts);
+		// samples whose first candidate cell is below m: the kernel's own closed form, on the host
+		const uint32_t K = n / cells, R = n % cells;
+		auto below = [&](uint64_t m) -> uint64_t { m = m < cells ? m : cells; return m * K + (R ? m + floor_sum(m, cells, alpha, beta) - floor_sum(m, cells, alpha, (uint64_t)beta + cells - R) : 0); };
+		lo = (uint32_t)below((uint64_t)b0 * chunk); hi = (uint32_t)below((uint64_t)b1 * chunk);
+		if (b1 > b0) NGP_LAUNCH("generate_grid_samples_sorted_kernel", (cudaStream_t)stream, generate_grid_samples_sorted_kernel<<<b1 - b0, 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, alpha, beta, chunk, b0, d_grid, thresh, d_positions, d_indices));
+	}
+	if (slot_begin) *slot_begin = lo;
+	if (slot_end) *slot_end = hi;
+	return check_launch("generate_grid_samples_sorted_part");
 }
 
 extern "C" int ngp_generate_grid_samples_sorted(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, uint64_t rng_state, uint64_t rng_inc, uint32_t step,
                                                 const float* d_grid, float thresh, float* d_positions, uint32_t* d_indices) {
-	NGP_REQUIRE(cfg && d_grid && d_positions && d_indices, "null pointer");
-	if (n == 0) return 0;
-	const uint32_t cells = cfg->grid_size * cfg->grid_size * cfg->grid_size;
-	if ((cells & (cells - 1)) != 0 || cells < 256)          // the inversion needs a power-of-two cell count: plain order otherwise
-		return ngp_generate_grid_samples(stream, cfg, n, rng_state, rng_inc, step, d_grid, thresh, d_positions, d_indices);
-	Pcg32 rng; rng.state = rng_state; rng.inc = rng_inc;
-	uint32_t inv = kCellMul;                                 // Newton: the inverse of an odd number modulo 2^32
-	for (int k = 0; k < 5; ++k) inv *= 2u - kCellMul * inv;
-	const uint32_t mask = cells - 1;
-	const uint32_t alpha = inv & mask, beta = (0u - inv * kCellAdd - step * n) & mask;
-	const uint32_t chunk = div_up(div_up(cells, 256), kNumSMs * 4) * 256;        // one resident wave of CTAs, each walks a contiguous run of cells
-	NGP_LAUNCH("generate_grid_samples_sorted_kernel", (cudaStream_t)stream, generate_grid_samples_sorted_kernel<<<div_up(cells, chunk), 256, 0, (cudaStream_t)stream>>>(*cfg, n, rng, step, alpha, beta, chunk, d_grid, thresh, d_positions, d_indices));
-	return check_launch("generate_grid_samples_sorted");
+	return ngp_generate_grid_samples_sorted_part(stream, cfg, n, rng_state, rng_inc, step, d_grid, thresh, d_positions, d_indices, 0, 1, nullptr, nullptr);
+}
+
+extern "C" int ngp_splat_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,
+                              int density_activation, float* d_grid_current) {
+	NGP_REQUIRE(cfg && d_indices && d_density && d_grid_current, "null pointer");
+	cudaStream_t s = (cudaStream_t)stream;
+	if (n) NGP_LAUNCH("splat_grid_kernel", s, splat_grid_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, d_indices, (const __half*)d_density, density_stride, density_activation, cfg->min_step, d_grid_current));
+	return check_launch("splat_grid");
+}
+
+extern "C" int ngp_ema_grid(void* stream, const ngp_sampler_cfg* cfg, float decay, const float* d_grid_current, float* d_grid) {
+	NGP_REQUIRE(cfg && d_grid_current && d_grid, "null pointer");
+	const uint32_t total = cfg->grid_size * cfg->grid_size * cfg->grid_size * cfg->n_cascades;
+	cudaStream_t s = (cudaStream_t)stream;
+	NGP_LAUNCH("ema_grid_kernel", s, ema_grid_kernel<<<grid_for(total, 256), 256, 0, s>>>(total, d_grid_current, decay, d_grid));
+	return check_launch("ema_grid");
 }
 
 extern "C" int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const uint32_t* d_indices, const void* d_density, uint32_t density_stride,

@@ -49,18 +49,23 @@ void OccupancySampler::init(uint32_t n_images, const int image_resolution[2], co
 }
 
 void OccupancySampler::sample_positions_from_grid(uint32_t n_uniform_positions, uint32_t n_nonuniform_positions, DeviceBuffer<Position>& grid_positions,
-                                                  DeviceBuffer<uint32_t>& grid_indices, cudaStream_t stream) {
+                                                  DeviceBuffer<uint32_t>& grid_indices, cudaStream_t stream, uint32_t part, uint32_t n_parts, SlotRange* ranges) {
 	const uint32_t n_total = n_uniform_positions + n_nonuniform_positions;
 	grid_positions.enlarge(n_total);
 	grid_indices.enlarge(n_total);
 	const ngp_sampler_cfg c = cfg();
-	// Morton-ordered emission: the same samples as the reference's kernel, in an order the hash-grid gathers like (see ngp_b200.h)
-	api_check(ngp_generate_grid_samples_sorted(stream, &c, n_uniform_positions, rng.state, rng.inc, i_step, density_grid.data(), -0.01f,
-	                                           (float*)grid_positions.data(), grid_indices.data()));
+	SlotRange r[2] = {};
+	// Morton-ordered emission: the same samples as the reference's kernel, in an order the hash-grid gathers like (see ngp_b200.h).
+	// With n_parts > 1 this rank writes (and later evaluates) only its contiguous share of each of the two sample sets.
+	api_check(ngp_generate_grid_samples_sorted_part(stream, &c, n_uniform_positions, rng.state, rng.inc, i_step, density_grid.data(), -0.01f,
+	                                                (float*)grid_positions.data(), grid_indices.data(), part, n_parts, &r[0].begin, &r[0].end));
 	rng.advance();
-	api_check(ngp_generate_grid_samples_sorted(stream, &c, n_nonuniform_positions, rng.state, rng.inc, i_step, density_grid.data(), min_optical_thickness,
-	                                           (float*)(grid_positions.data() + n_uniform_positions), grid_indices.data() + n_uniform_positions));
+	api_check(ngp_generate_grid_samples_sorted_part(stream, &c, n_nonuniform_positions, rng.state, rng.inc, i_step, density_grid.data(), min_optical_thickness,
+	                                                (float*)(grid_positions.data() + n_uniform_positions), grid_indices.data() + n_uniform_positions,
+	                                                part, n_parts, &r[1].begin, &r[1].end));
 	rng.advance();
+	r[1].begin += n_uniform_positions; r[1].end += n_uniform_positions;
+	if (ranges) { ranges[0] = r[0]; ranges[1] = r[1]; }
 }
 
 void OccupancySampler::update_grid(uint32_t n_total_positions, uint32_t padded_output_width, const DeviceBuffer<precision_t>& grid_densities,
@@ -68,6 +73,24 @@ void OccupancySampler::update_grid(uint32_t n_total_positions, uint32_t padded_o
 	const ngp_sampler_cfg c = cfg();
 	api_check(ngp_update_grid(stream, &c, n_total_positions, grid_indices.data(), grid_densities.data(), padded_output_width, (int)density_activation,
 	                          ema_decay, density_grid_current.data(), density_grid.data()));
+	++i_step;
+}
+
+// update_grid in its two halves (data parallel: the ranks' partial maxima are combined between them)
+void OccupancySampler::splat_grid(const SlotRange* ranges, uint32_t n_ranges, uint32_t padded_output_width, const DeviceBuffer<precision_t>& grid_densities,
+                                  const DeviceBuffer<uint32_t>& grid_indices, EActivation density_activation, cudaStream_t stream) {
+	const ngp_sampler_cfg c = cfg();
+	density_grid_current.memset(0, stream);
+	for (uint32_t k = 0; k < n_ranges; ++k)
+		if (ranges[k].end > ranges[k].begin)
+			api_check(ngp_splat_grid(stream, &c, ranges[k].end - ranges[k].begin, grid_indices.data() + ranges[k].begin,
+			                         grid_densities.data() + (size_t)ranges[k].begin * padded_output_width, padded_output_width, (int)density_activation,
+			                         density_grid_current.data()));
+}
+
+void OccupancySampler::ema_grid(cudaStream_t stream) {
+	const ngp_sampler_cfg c = cfg();
+	api_check(ngp_ema_grid(stream, &c, ema_decay, density_grid_current.data(), density_grid.data()));
 	++i_step;
 }
 

@@ -9,6 +9,7 @@ namespace ngp {
 struct NeRFSynthetic;
 
 struct BoundingBox { float min[3], max[3]; };
+struct SlotRange { uint32_t begin = 0, end = 0; };          // [begin, end) of the grid-sample arrays
 
 class OccupancySampler {
 public:
@@ -18,11 +19,16 @@ public:
 	void init(uint32_t n_images, const int image_resolution[2], const float focal_length[2], const float principal_point[2],
 	          const DeviceBuffer<Mat34>& camera_matrices, default_rng_t& rng, cudaStream_t stream);
 	// :660-703
+	// part / n_parts (data parallel): write only this rank's share; ranges[2] receives the slots written (uniform set, non-uniform set)
 	void sample_positions_from_grid(uint32_t n_uniform_positions, uint32_t n_nonuniform_positions, DeviceBuffer<Position>& grid_positions,
-	                                DeviceBuffer<uint32_t>& grid_indices, cudaStream_t stream);
+	                                DeviceBuffer<uint32_t>& grid_indices, cudaStream_t stream, uint32_t part = 0, uint32_t n_parts = 1, SlotRange* ranges = nullptr);
 	// :705-735
 	void update_grid(uint32_t n_total_positions, uint32_t padded_output_width, const DeviceBuffer<precision_t>& grid_densities,
 	                 const DeviceBuffer<uint32_t>& grid_indices, EActivation density_activation, cudaStream_t stream);
+	// the two halves of update_grid, for an exchange (max over ranks of density_grid_current) between them
+	void splat_grid(const SlotRange* ranges, uint32_t n_ranges, uint32_t padded_output_width, const DeviceBuffer<precision_t>& grid_densities,
+	                const DeviceBuffer<uint32_t>& grid_indices, EActivation density_activation, cudaStream_t stream);
+	void ema_grid(cudaStream_t stream);
 	// :737-760
 	void update_grid_bitfield(cudaStream_t stream);
 	// :762-811.  scan_ws: scratch for the ordered compaction (sized by the callee)

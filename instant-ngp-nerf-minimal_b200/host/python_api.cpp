@@ -129,6 +129,7 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readwrite("color_space", &Testbed::m_color_space)
 		.def_readonly("training_buffer", &Testbed::m_training_buffer)
 		.def_readonly("rendering_buffer", &Testbed::m_rendering_buffer)
+		.def_readwrite("shard_grid_refresh", &Testbed::m_shard_grid_refresh, "data parallel: shard the occupancy-grid refresh over the ranks (default on; off = every rank refreshes everything)")
 		.def_readwrite("pipeline_march", &Testbed::m_pipeline_march, "march step i+1 on a second stream underneath step i (default on)")
 		.def_property("fov", &Testbed::fov, &Testbed::set_fov)
 		.def_property("fov_xy",

@@ -157,6 +157,7 @@ public:
 private:
 	cudaEvent_t m_ev[3] = {nullptr, nullptr, nullptr};
 public:
+	bool m_shard_grid_refresh = true;  // world > 1: each rank refreshes 1/world of the occupancy samples, one allreduce(max) combines them (false: replicated)
 	bool m_pipeline_march = true;      // false: issue the march on the main stream (serial schedule; used when timing kernels one by one)
 private:
 	std::chrono::steady_clock::time_point m_enqueue_start;

@@ -19,18 +19,36 @@ void Testbed::train(uint32_t n_training_steps, uint32_t target_batch_size) {
 	train_nerf(target_batch_size, n_training_steps, m_stream);
 }
 
-// testbed.cu:193-229
+// testbed.cu:193-229.  Data parallel (world > 1): every rank holds the same weights and the same density grid, so the refresh is
+// SHARDED instead of replicated -- rank r generates, evaluates and splats only its contiguous 1/world of the sample slots, the
+// partial maxima (density_grid_current, non-negative floats) are combined with one ncclAllReduce(max), and the decay + bitfield
+// run everywhere on identical input.  max is exact and order-free: the grid is bit-identical to the replicated refresh.
 void Testbed::train_prep_nerf(uint32_t, uint32_t, cudaStream_t stream) {
 	const uint32_t n_total_elements = m_sampler->n_total_elements;
 	const uint32_t n_uniform_positions = m_training_buffer.i_step >= 256 ? n_total_elements / 4 : n_total_elements;
 	const uint32_t n_nonuniform_positions = m_training_buffer.i_step >= 256 ? n_total_elements / 4 : 0;
 	const uint32_t n_total_positions = n_uniform_positions + n_nonuniform_positions;
-	m_sampler->sample_positions_from_grid(n_uniform_positions, n_nonuniform_positions, m_training_buffer.grid_positions, m_training_buffer.grid_indices, stream);
 	const uint32_t padded_output_width = m_network->padded_density_output_width();
 	m_training_buffer.rgbsigma.enlarge((size_t)padded_output_width * n_total_positions);
-	m_network->density(stream, (const float*)m_training_buffer.grid_positions.data(), sizeof(Position) / sizeof(float), n_total_positions,
-	                   m_training_buffer.rgbsigma.data(), false);
-	m_sampler->update_grid(n_total_positions, padded_output_width, m_training_buffer.rgbsigma, m_training_buffer.grid_indices, m_density_activation, stream);
+	if (m_dp_world > 1 && m_shard_grid_refresh) {
+		SlotRange ranges[2];
+		m_sampler->sample_positions_from_grid(n_uniform_positions, n_nonuniform_positions, m_training_buffer.grid_positions, m_training_buffer.grid_indices, stream,
+		                                      (uint32_t)m_dp_rank, (uint32_t)m_dp_world, ranges);
+		for (const SlotRange& r : ranges)
+			if (r.end > r.begin)
+				m_network->density(stream, (const float*)(m_training_buffer.grid_positions.data() + r.begin), sizeof(Position) / sizeof(float), r.end - r.begin,
+				                   m_training_buffer.rgbsigma.data() + (size_t)r.begin * padded_output_width, false);
+		m_sampler->splat_grid(ranges, 2, padded_output_width, m_training_buffer.rgbsigma, m_training_buffer.grid_indices, m_density_activation, stream);
+		const ncclResult_t rc = ncclAllReduce(m_sampler->density_grid_current.data(), m_sampler->density_grid_current.data(), n_total_elements, ncclFloat, ncclMax,
+		                                      (ncclComm_t)m_nccl_comm, stream);
+		if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce(max) of the density grid failed: ") + ncclGetErrorString(rc));
+		m_sampler->ema_grid(stream);
+	} else {
+		m_sampler->sample_positions_from_grid(n_uniform_positions, n_nonuniform_positions, m_training_buffer.grid_positions, m_training_buffer.grid_indices, stream);
+		m_network->density(stream, (const float*)m_training_buffer.grid_positions.data(), sizeof(Position) / sizeof(float), n_total_positions,
+		                   m_training_buffer.rgbsigma.data(), false);
+		m_sampler->update_grid(n_total_positions, padded_output_width, m_training_buffer.rgbsigma, m_training_buffer.grid_indices, m_density_activation, stream);
+	}
 	m_sampler->update_grid_bitfield(stream);
 }
 

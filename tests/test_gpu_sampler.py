@@ -94,6 +94,68 @@ def test_generate_grid_samples_sorted_is_a_permutation_in_cell_order(capi, orc, 
         assert np.array_equal(ri, bi) and np.array_equal(rp, bp)
 
 
+@pytest.mark.parametrize("n_mult,n_parts,thresh,step", [(0.25, 2, -0.01, 300), (0.25, 8, 0.01, 301), (1.0, 3, -0.01, 16), (0.37, 5, 0.01, 7), (0.0001, 8, -0.01, 2)])
+def test_grid_sample_parts_tile_the_full_call(capi, orc, n_mult, n_parts, thresh, step):
+    """ngp_generate_grid_samples_sorted_part (the sharded occupancy refresh of the data-parallel path): the parts write disjoint,
+    contiguous slot ranges that tile [0, n), and their union is the full call's output bit for bit."""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg = capi.make_sampler_cfg(1)
+    cells = 128 ** 3
+    grid = make_density_grid()
+    rng = orc.Pcg32(17)
+    n = int(round(n_mult * cells))
+    d_grid = G.dev(grid)
+    full_pos, full_idx = G.zeros(n * 3, torch.float32), G.zeros(n, torch.int32)
+    capi.check(lib.ngp_generate_grid_samples_sorted(G.stream(), C.byref(cfg), n, rng.state, rng.inc, step, G.p(d_grid), thresh, G.p(full_pos), G.p(full_idx)))
+    G.sync()
+    want_pos, want_idx = G.host(full_pos).view(np.uint32).reshape(n, 3), G.host(full_idx, np.uint32)
+    cursor = 0
+    for part in range(n_parts):
+        pos, idx = G.dev(np.full(n * 3, np.nan, np.float32)), G.dev(np.full(n, 0xFFFFFFFF, np.uint32))
+        lo, hi = C.c_uint32(123), C.c_uint32(456)
+        capi.check(lib.ngp_generate_grid_samples_sorted_part(G.stream(), C.byref(cfg), n, rng.state, rng.inc, step, G.p(d_grid), thresh, G.p(pos), G.p(idx),
+                                                             part, n_parts, C.byref(lo), C.byref(hi)))
+        G.sync()
+        assert lo.value == cursor and hi.value >= lo.value, (part, lo.value, hi.value, cursor)
+        cursor = hi.value
+        got_pos, got_idx = G.host(pos).view(np.uint32).reshape(n, 3), G.host(idx, np.uint32)
+        assert np.array_equal(got_idx[lo.value:hi.value], want_idx[lo.value:hi.value]) and np.array_equal(got_pos[lo.value:hi.value], want_pos[lo.value:hi.value])
+        untouched = np.ones(n, bool)
+        untouched[lo.value:hi.value] = False
+        assert (got_idx[untouched] == 0xFFFFFFFF).all(), "a part wrote outside the slot range it reported"
+    assert cursor == n
+    assert lib.ngp_generate_grid_samples_sorted_part(G.stream(), C.byref(cfg), n, rng.state, rng.inc, step, G.p(d_grid), thresh, G.p(full_pos), G.p(full_idx), 3, 3, None, None) != 0
+
+
+def test_splat_then_ema_equals_update_grid_and_partial_maxima_combine(capi, orc):
+    """ngp_splat_grid + ngp_ema_grid are ngp_update_grid's two halves; splatting two halves of the samples into separate grids and
+    taking the element-wise max (what the all-reduce between the halves does) gives the same grid bit for bit."""
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg = capi.make_sampler_cfg(1)
+    grid = make_density_grid()
+    n = 300001
+    g = np.random.Generator(np.random.PCG64(5))
+    indices = g.integers(0, grid.size, n).astype(np.uint32)
+    density = (g.random((n, 16), dtype=np.float32) * 8 - 6).astype(np.float16)
+    d_idx, d_den = G.dev(indices), G.dev(density)
+    want_grid, want_cur = G.dev(grid), G.zeros(grid.size, torch.float32)
+    capi.check(lib.ngp_update_grid(G.stream(), C.byref(cfg), n, G.p(d_idx), G.p(d_den), 16, 3, 0.95, G.p(want_cur), G.p(want_grid)))
+    cur_a, cur_b, got_grid = G.zeros(grid.size, torch.float32), G.zeros(grid.size, torch.float32), G.dev(grid)
+    cut = 123457
+    capi.check(lib.ngp_splat_grid(G.stream(), C.byref(cfg), cut, G.p(d_idx), G.p(d_den), 16, 3, G.p(cur_a)))
+    capi.check(lib.ngp_splat_grid(G.stream(), C.byref(cfg), n - cut, C.c_void_p(d_idx.data_ptr() + 4 * cut), C.c_void_p(d_den.data_ptr() + 32 * cut), 16, 3, G.p(cur_b)))
+    G.sync()
+    combined = torch.maximum(cur_a, cur_b)
+    capi.check(lib.ngp_ema_grid(G.stream(), C.byref(cfg), 0.95, G.p(combined), G.p(got_grid)))
+    G.sync()
+    assert np.array_equal(G.host(combined).view(np.uint32), G.host(want_cur).view(np.uint32))
+    assert np.array_equal(G.host(got_grid).view(np.uint32), G.host(want_grid).view(np.uint32))
+
+
 def test_update_grid_and_bitfield_match_oracle(capi, orc):
     import gpuutil as G
     import torch
