@@ -4,6 +4,8 @@
 // memory so the render loop needs no host round trip per iteration (the reference syncs every iteration, testbed.cu:540).
 #include "march.cuh"
 #include "composite.cuh"
+#include <algorithm>
+#include <atomic>
 
 namespace ngp {
 
@@ -38,24 +40,9 @@ __host__ __device__ inline float ld_random_val(uint32_t index, uint32_t seed, ui
 
 struct CamMat { float m[12]; };
 
-// one 8-point window of a ray's stepping lattice for an octet of lanes (see generate_coords_from_rays_kernel below)
-__device__ __forceinline__ float octet_lattice(float t_base, uint32_t sub, uint32_t shift, uint32_t gmask, const ngp_sampler_cfg& c, bool const_dt, float& t_next_base) {
-	if (const_dt) {
-		const float dt0 = calc_dt(t_base, c);
-		const float dtq = (t_base + dt0) - t_base;
-		const float cand = __fmaf_rn((float)sub, dtq, t_base), next = __fmaf_rn((float)(sub + 1), dtq, t_base);
-		if ((__ballot_sync(gmask, cand + dt0 == next) & gmask) == gmask) { t_next_base = __shfl_sync(gmask, next, shift + 7); return cand; }
-	}
-	float t = t_base, my_t = t_base;
-	#pragma unroll
-	for (int s = 0; s < 8; ++s) { if (s == (int)sub) my_t = t; t += calc_dt(t, c); }
-	t_next_base = t;
-	return my_t;
-}
-
-// One thread per pixel: ray set-up, then the skip to the first occupied cell (advance_pos_nerf).  An 8-lanes-per-pixel variant of
-// this kernel was measured 6x slower (1.2 -> 7.1 ms at 1080p): the skip crosses about one voxel per 8-point window, so the
-// rounds do not shrink while the thread count grows 8x.
+// One thread per pixel: ray set-up, then the skip to the first occupied cell (advance_pos_nerf) with the closed-form hop of
+// lattice_hop.h.  An 8-lanes-per-pixel variant of this kernel was measured 6x slower (1.2 -> 7.1 ms at 1080p): the skip crosses
+// about one voxel per 8-point window, so the rounds do not shrink while the thread count grows 8x.
 __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
                                                         uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads,
                                                         uint32_t first_pixel, uint32_t n, const __half* __restrict__ envmap, int env_res_x, int env_res_y,
@@ -91,77 +78,176 @@ __global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_c
 		dt = calc_dt(t, c);
 		const uint32_t mip = mip_from_dt(dt, pos, c);
 		if (grid_occupied(pos, bits, mip, c.grid_size)) break;
-		t = advance_to_next_voxel(t, c, pos, d, idir, c.grid_size >> mip);
+		t = advance_to_next_voxel_fast(t, c, c.cone_angle == 0.f, pos, d, idir, c.grid_size >> mip);
 	}
 	p.t = t;
 	payloads[slot] = p;
 }
 
-// 8 lanes per ray ("octet"): the ray's stepping lattice (see march_train.cu) is taken 8 points at a time, every lane evaluates
-// one point (position, cascade, occupancy bit, exit distance of its voxel), and an octet-local ballot replays the reference's
-// sequential control flow: occupied visited points become samples, an empty visited point skips to the first lattice point
-// behind its voxel.  Sample positions, step counts and the stored ray parameter are bit-identical to the thread-per-ray loop,
-// but the 8 Coordinates of a ray leave as one contiguous 224-byte store, four rays share a warp instead of 32 (the reference's
-// loop lengths differ wildly from ray to ray), and empty space is crossed 8 lattice points per round.
-__global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_sampler_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr, uint32_t n_steps,
-                                                                         const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads, Coordinate* __restrict__ coords) {
-	const uint32_t n_rays = n_rays_ptr ? min(*n_rays_ptr, n_rays_max) : n_rays_max;
-	const uint32_t lane = threadIdx.x & 31, sub = lane & 7, shift = lane & 24;
-	const uint32_t gmask = 0xffu << shift;
-	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-	if (i >= n_rays) return;                                   // the whole octet leaves together
-	RayPayload& p = payloads[i];
-	if (!p.alive) return;
-	const V3 o = {p.ox, p.oy, p.oz}, d = {p.dx, p.dy, p.dz}, idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
-	float t_base = p.t, skip_target = -INFINITY;
-	uint32_t j = 0;
-	if (n_steps == 0) { if (sub == 0) p.n_steps = 0; return; }
-	const bool const_dt = c.cone_angle == 0.f;
-	for (uint32_t window = 0; window < (1u << 18); ++window) {
-		float t_next_base;
-		const float my_t = octet_lattice(t_base, sub, shift, gmask, c, const_dt, t_next_base);
-		const V3 pos = ray_at(o, d, my_t);
-		const bool inside = aabb_contains(c, pos);
-		const float dt = calc_dt(my_t, c);
-		bool occ = false;
-		float t_target = 0.f;
-		if (inside) {
-			const uint32_t mip = mip_from_dt(dt, pos, c);
-			occ = grid_occupied(pos, bits, mip, c.grid_size);
-			if (!occ) t_target = my_t + distance_to_next_voxel(pos, d, idir, c.grid_size >> mip);
-		}
-		const uint32_t inside_mask = (__ballot_sync(gmask, inside) >> shift) & 0xffu;
-		const uint32_t run_mask = (__ballot_sync(gmask, inside && occ) >> shift) & 0xffu;
-		uint32_t q0 = 0;
-		while (q0 < 8) {
-			const uint32_t cand = (__ballot_sync(gmask, sub >= q0 && !(my_t < skip_target)) >> shift) & 0xffu;
-			if (!cand) break;                                      // the rest of the window is stepped over; the target carries on
-			const uint32_t q = (uint32_t)__ffs(cand) - 1u;
-			if (!((inside_mask >> q) & 1u)) {                      // the ray left the box: n_steps = samples so far, t stays (:581-584)
-				if (sub == 0) p.n_steps = j;
-				return;
-			}
-			if ((run_mask >> q) & 1u) {
-				const uint32_t rest = (~run_mask & 0xffu) >> q;    // bit 0 is clear
-				const uint32_t run = rest ? (uint32_t)__ffs(rest) - 1u : 8u - q;
-				const uint32_t take = min(run, n_steps - j);
-				if (sub >= q && sub < q + take) coords[(size_t)i * n_steps + j + (sub - q)] = make_coord(pos, d, dt, c);
-				j += take;
-				if (j >= n_steps) {                                // t after the last sample is the next lattice point
-					const float t_after = __shfl_sync(gmask, my_t, shift + ((q + take) & 7u));
-					if (sub == 0) { p.t = q + take < 8 ? t_after : t_next_base; p.n_steps = n_steps; }
-					return;
-				}
-				q0 = q + run;
-				skip_target = -INFINITY;
-			} else {
-				skip_target = __shfl_sync(gmask, t_target, shift + q);
-				q0 = q + 1;
-			}
-		}
-		t_base = t_next_base;
+// The reference's per-ray loop (generate_coords_from_rays_regularly_kernel, occupancy_sampler.cu:552-601) on persistent warps that
+// REFILL: a lane whose ray is finished takes the next unprocessed ray, so a warp is not held up by its longest ray.
+//   * ncu on the thread-per-ray form of this loop (profiles/r02_render.md): 8.1 of 32 lanes active -- rays of one warp need between 4
+//     and a few hundred loop iterations per round (empty voxels to cross between samples) and the short ones idle.
+//   * rays are dealt out dynamically: a warp draws blocks of 32 ray indices from one device-wide counter (one atomic per 32 rays)
+//     and hands them to its idle lanes in index order; the last warp to leave resets the counter for the next launch.
+//   * one loop iteration = one visited lattice point: ray_at, cascade, occupancy bit, then either a sample or the empty-voxel hop in
+//     closed form (lattice_hop.h).  make_coord's per-ray parts are hoisted; a Coordinate leaves as 8-byte stores where aligned.
+// Sample positions, step counts and the stored ray parameter are bit-identical to the reference loop (the visiting order of a ray's
+// lattice points is the reference's; only which lane works on which ray differs).
+constexpr uint32_t kGenQueues = 64;
+__device__ uint32_t g_gen_queue[kGenQueues * 2];       // per launch slot: [0] next ray index, [1] warps that have left
+
+struct MarchRay {
+	V3 o, d, idir, half_sign;          // half_sign = 0.5 * copysign(1, d): distance_to_next_voxel's per-axis constant
+	float cdx, cdy, cdz, t;
+	ngp_lattice lat;                   // closed-form stepping constants of the binade t is in (lattice_hop.h)
+	uint32_t index, j;
+};
+
+// a Coordinate (28 bytes, 4-byte aligned) as 8-byte stores where the alignment allows
+__device__ __forceinline__ void store_coordinate(Coordinate* dst, float px, float py, float pz, float dt, float dx, float dy, float dz) {
+	float* f = reinterpret_cast<float*>(dst);
+	if ((reinterpret_cast<uintptr_t>(f) & 7u) == 0) {
+		reinterpret_cast<float2*>(f)[0] = make_float2(px, py); reinterpret_cast<float2*>(f)[1] = make_float2(pz, dt);
+		reinterpret_cast<float2*>(f)[2] = make_float2(dx, dy); f[6] = dz;
+	} else {
+		f[0] = px; reinterpret_cast<float2*>(f + 1)[0] = make_float2(py, pz); reinterpret_cast<float2*>(f + 1)[1] = make_float2(dt, dx);
+		reinterpret_cast<float2*>(f + 1)[2] = make_float2(dy, dz);
 	}
-	if (sub == 0) { p.t = t_base; p.n_steps = j; }                 // unreachable for sane cameras (2 M lattice points)
+}
+
+// mip_from_dt (occupancy_sampler.cu:225-240) with frexp's exponent read from the float's bits: frexpf(m) = (f, e) with
+// e = biased exponent - 126 for normal m and e = 0 for m == 0; subnormal m gives e <= -126 either way, clamped to cascade 0
+__device__ __forceinline__ int exponent_of(float m) { return m == 0.f ? 0 : (int)(__float_as_uint(m) >> 23 & 0xffu) - 126; }
+__device__ __forceinline__ uint32_t mip_at(float dt, V3 p, const ngp_sampler_cfg& c) {
+	const float m = fmaxf(fmaxf(fabsf(p.x - 0.5f), fabsf(p.y - 0.5f)), fabsf(p.z - 0.5f));
+	const int mip = min((int)c.n_cascades - 1, max(0, exponent_of(m) + 1));
+	dt *= (float)(2 * c.grid_size);
+	if (dt < 1.f) return (uint32_t)mip;
+	return (uint32_t)min((int)c.n_cascades - 1, max(exponent_of(dt), mip));
+}
+
+// occupancy bit of the cell around p in cascade mip; the Morton interleave comes from a 256-entry shared table when the grid is
+// small enough (every grid the configurations use)
+__device__ __forceinline__ bool occupied_at(V3 p, uint32_t mip, uint32_t G, const uint32_t* __restrict__ spread, const uint8_t* __restrict__ bits) {
+	const float s = __uint_as_float((127u - mip) << 23), g = (float)G;          // scalbnf(1, -mip)
+	const int ix = min(max((int)(((p.x - 0.5f) * s + 0.5f) * g), 0), (int)G - 1);
+	const int iy = min(max((int)(((p.y - 0.5f) * s + 0.5f) * g), 0), (int)G - 1);
+	const int iz = min(max((int)(((p.z - 0.5f) * s + 0.5f) * g), 0), (int)G - 1);
+	const uint32_t idx = spread ? (spread[ix] | (spread[iy] << 1) | (spread[iz] << 2)) : morton3D(ix, iy, iz);
+	return __ldg(bits + idx / 8 + (size_t)(G * G * G) * mip / 8) & (1u << (idx % 8));
+}
+
+__global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_sampler_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr,
+                                                                         uint32_t n_steps_arg, const uint32_t* __restrict__ n_steps_ptr, uint32_t queue_slot,
+                                                                         const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads, Coordinate* __restrict__ coords) {
+	__shared__ uint32_t spread_table[256];
+	const uint32_t* spread = nullptr;
+	if (c.grid_size <= 256) {
+		spread_table[threadIdx.x] = morton3D(threadIdx.x, 0, 0);
+		__syncthreads();
+		spread = spread_table;
+	}
+	const uint32_t n_rays = n_rays_ptr ? min(*n_rays_ptr, n_rays_max) : n_rays_max;
+	const uint32_t n_steps = n_steps_ptr ? *n_steps_ptr : n_steps_arg;
+	const uint32_t lane = threadIdx.x & 31, lt_mask = (1u << lane) - 1u;
+	uint32_t* queue = g_gen_queue + 2 * queue_slot;
+	const bool const_dt = c.cone_angle == 0.f;
+	const float diag = c.aabb_max - c.aabb_min;
+	int diag_exp;
+	const bool diag_pow2 = frexpf(diag, &diag_exp) == 0.5f;      // then x / diag == x * (1 / diag) exactly
+	const float inv_diag = 1.0f / diag;
+	const float wdt_const = warp_dt(c.min_step, c);
+	const bool res_pow2 = (c.grid_size & (c.grid_size - 1u)) == 0u;
+	const uint32_t log2_grid = 31u - (uint32_t)__clz((int)c.grid_size);
+
+	MarchRay r;
+	bool have = false, drained = false;
+	uint32_t wnext = 0, wend = 0;                                  // this warp's private block of ray indices (warp-uniform)
+	while (true) {
+		// Refill in batches: the set-up of a ray (payload load, three reciprocals) runs with only the idle lanes active, so it waits
+		// until a quarter of the warp is idle -- or nothing is left to wait for
+		const uint32_t need = __ballot_sync(0xffffffffu, !have);
+		if (__popc(need) >= 8 || (need && drained)) {
+			if (wnext >= wend && !drained) {
+				uint32_t b = 0;
+				if (lane == 0) b = atomicAdd(queue, 32u);
+				b = __shfl_sync(0xffffffffu, b, 0);
+				if (b >= n_rays) { drained = true; wnext = wend = 0; }
+				else { wnext = b; wend = min(b + 32u, n_rays); }
+			}
+			if (wnext < wend) {
+				const uint32_t cand = wnext + __popc(need & lt_mask);
+				wnext += __popc(need);
+				if (!have && cand < wend) {
+					const uint2* src = reinterpret_cast<const uint2*>(payloads + cand);      // 40-byte records, 8-byte aligned
+					const uint2 w0 = src[0], w1 = src[1], w2 = src[2], w3 = src[3], w4 = src[4];
+					if (w0.x) {                                    // alive
+						if (n_steps == 0) payloads[cand].n_steps = 0;
+						else {
+							r.o = {__uint_as_float(w0.y), __uint_as_float(w1.x), __uint_as_float(w1.y)};
+							r.d = {__uint_as_float(w2.x), __uint_as_float(w2.y), __uint_as_float(w3.x)};
+							r.idir = {1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z};
+							r.half_sign = {0.5f * copysignf(1.f, r.d.x), 0.5f * copysignf(1.f, r.d.y), 0.5f * copysignf(1.f, r.d.z)};
+							r.cdx = (r.d.x + 1.f) * 0.5f; r.cdy = (r.d.y + 1.f) * 0.5f; r.cdz = (r.d.z + 1.f) * 0.5f;
+							r.t = __uint_as_float(w4.x); r.index = cand; r.j = 0;
+							ngp_lattice_enter(&r.lat, r.t, c.min_step, const_dt);
+							have = true;
+						}
+					}
+				}
+			} else if (drained && need == 0xffffffffu) break;
+		}
+		if (have) {
+			const V3 pos = ray_at(r.o, r.d, r.t);
+			if (!aabb_contains(c, pos)) {                          // the ray left the box: n_steps = samples so far, t stays (:581-584)
+				payloads[r.index].n_steps = r.j;
+				have = false;
+			} else {
+				const float dt = calc_dt(r.t, c);
+				const uint32_t mip = mip_at(dt, pos, c);
+				if (occupied_at(pos, mip, c.grid_size, spread, bits)) {
+					float px, py, pz;
+					if (diag_pow2) { px = (pos.x - c.aabb_min) * inv_diag; py = (pos.y - c.aabb_min) * inv_diag; pz = (pos.z - c.aabb_min) * inv_diag; }
+					else { px = (pos.x - c.aabb_min) / diag; py = (pos.y - c.aabb_min) / diag; pz = (pos.z - c.aabb_min) / diag; }
+					float wdt = wdt_const;
+					if (!const_dt) wdt = warp_dt(dt, c);
+					store_coordinate(coords + (size_t)r.index * n_steps + r.j, px, py, pz, wdt, r.cdx, r.cdy, r.cdz);
+					++r.j;
+					r.t += dt;
+					if (r.j >= n_steps) {
+						payloads[r.index].t = r.t; payloads[r.index].n_steps = n_steps;
+						have = false;
+					} else if (!(r.t < r.lat.top)) ngp_lattice_enter(&r.lat, r.t, c.min_step, const_dt);
+				} else {
+					// advance_to_next_voxel (:284-294): distance to the cell's exit, then the first lattice point at or behind it
+					const uint32_t res = c.grid_size >> mip;
+					const float rr = (float)res;
+					const float qx = rr * pos.x, qy = rr * pos.y, qz = rr * pos.z;
+					const float tx = (floorf(qx + 0.5f + r.half_sign.x) - qx) * r.idir.x;
+					const float ty = (floorf(qy + 0.5f + r.half_sign.y) - qy) * r.idir.y;
+					const float tz = (floorf(qz + 0.5f + r.half_sign.z) - qz) * r.idir.z;
+					const float tmin = fminf(fminf(tx, ty), tz);
+					const float dist = fmaxf(res_pow2 ? tmin * __uint_as_float((127u - (log2_grid - mip)) << 23) : tmin / rr, 0.0f);     // a power of two divides exactly
+					const float t_target = r.t + dist;
+					float hopped;
+					if (ngp_lattice_hop_cached(&r.lat, r.t, t_target, &hopped)) r.t = hopped;
+					else {
+						float t = r.t;
+						do { t += calc_dt(t, c); } while (t < t_target);
+						r.t = t;
+						ngp_lattice_enter(&r.lat, r.t, c.min_step, const_dt);
+					}
+				}
+			}
+		}
+	}
+	// the last warp out re-arms the queue for the next launch that uses this slot
+	if (lane == 0) {
+		__threadfence();
+		const uint32_t total_warps = gridDim.x * (blockDim.x >> 5);
+		if (atomicAdd(queue + 1, 1u) == total_warps - 1u) { queue[0] = 0; queue[1] = 0; __threadfence(); }
+	}
 }
 
 } // namespace ngp
@@ -208,10 +294,22 @@ extern "C" int ngp_init_rays(void* stream, const ngp_sampler_cfg* cfg, const ngp
 	return ngp_init_rays_rows(stream, cfg, cam, camera_matrix_host, spp, snap_to_pixel_centers, d_bitfield, d_payloads, 0, (uint32_t)cam->height);
 }
 
-extern "C" int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps,
-                                             const uint8_t* d_bitfield, void* d_payloads, float* d_coords) {
+static int generate_coords_impl(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, const uint32_t* d_n_steps,
+                                const uint8_t* d_bitfield, void* d_payloads, float* d_coords) {
 	NGP_REQUIRE(cfg && d_bitfield && d_payloads && d_coords, "null pointer");
 	if (n_rays == 0) return 0;
-	NGP_LAUNCH("generate_coords_from_rays_kernel", (cudaStream_t)stream, generate_coords_from_rays_kernel<<<div_up((uint64_t)n_rays * 8, 256), 256, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, d_bitfield, (RayPayload*)d_payloads, (Coordinate*)d_coords));
+	// launches take turns on kGenQueues work counters, so launches that overlap on the device (other streams) do not share one
+	static std::atomic<uint32_t> turn{0};
+	const uint32_t slot = turn.fetch_add(1) % kGenQueues;
+	// Persistent warps that refill.  A round is over when its longest ray is (some rays cross tens of empty voxels between samples),
+	// so the warps are kept FEW and full: about 8 rays per lane lets the refill even out the rest, while one warp per ray-lane
+	// (ncu, profiles/r02_render.md) spent 2/3 of its issue slots on warps holding one or two unfinished rays.
+	const uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)kNumSMs * 2, std::max<uint64_t>(div_up(n_rays, 2048), std::min<uint64_t>(div_up(n_rays, 256), kNumSMs)));
+	NGP_LAUNCH("generate_coords_from_rays_kernel", (cudaStream_t)stream, generate_coords_from_rays_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, d_n_steps, slot, d_bitfield, (RayPayload*)d_payloads, (Coordinate*)d_coords));
 	return check_launch("generate_coords_from_rays");
+}
+
+extern "C" int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps,
+                                             const uint8_t* d_bitfield, void* d_payloads, float* d_coords) {
+	return generate_coords_impl(stream, cfg, n_rays, d_n_rays, n_steps, nullptr, d_bitfield, d_payloads, d_coords);
 }
