@@ -38,6 +38,9 @@ typedef struct ngp_sampler_cfg {
 	float    min_step, max_step;     /* sqrt3/max_steps, sqrt3*2^(C-1)/grid_size */
 	float    near_distance;          /* 0.2 */
 	uint32_t keep_empty_rays;        /* train_envmap (occupancy_sampler.cu:408): training rays without a single sample stay in the ray list */
+	const uint8_t* coarse_bitfield;  /* optional (may be NULL): one bit per 8x8x8 block of cells, set when any cell of the block is occupied
+	                                    (ngp_build_coarse_bitfield).  The inference march crosses an empty block in one hop when it can
+	                                    prove the landing point is the one the cell-by-cell march reaches; results are identical. */
 } ngp_sampler_cfg;
 
 /* Pinhole camera set (internal/dataset/nerf_synthetic.h; xforms 3x4 column-major, 12 floats each). */
@@ -171,6 +174,11 @@ int ngp_update_grid(void* stream, const ngp_sampler_cfg* cfg, uint32_t n, const 
                     int density_activation, float decay, float* d_grid_current, float* d_grid);
 /* update_grid_bitfield (:737-760): mean of cascade 0 -> d_mean[0] (d_mean: 1 result + 128 floats of scratch), bits, max-pool */
 int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg, const float* d_grid, float min_optical_thickness, float* d_mean, uint8_t* d_bitfield);
+/* One bit per 8x8x8 block of cells (Morton order: block = cell index >> 9), cascades one after the other; d_coarse holds
+ * ngp_coarse_bitfield_bytes(cfg) bytes.  grid_size must be a power of two >= 32.  No counterpart in the reference (which visits
+ * every empty cell); see ngp_sampler_cfg.coarse_bitfield. */
+size_t ngp_coarse_bitfield_bytes(const ngp_sampler_cfg* cfg);
+int ngp_build_coarse_bitfield(void* stream, const ngp_sampler_cfg* cfg, const uint8_t* d_bitfield, uint8_t* d_coarse);
 /* sample_coords_from_dataset -> generate_training_samples_nerf (:310-449).  Compaction is in ray order (deterministic).
  * d_counters: [0] rays kept, [1] samples counted (overwritten).  d_scan_ws: >= ngp_scan_workspace_bytes(n_rays) bytes of scratch. */
 size_t ngp_scan_workspace_bytes(uint32_t n);
@@ -223,6 +231,23 @@ int ngp_rollover(void* stream, uint32_t batch, const uint32_t* d_compacted_count
 int ngp_composite_infer(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t n_steps_offset,
                         void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
                         float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale);
+/* Device-driven render loop.  Testbed::render_frame (testbed.cu:521-575) decides every round on the HOST how many steps to take
+ * (n_steps = clamp(n_pixels / n_alive, MIN, MAX)) and so synchronises once per round; here the decision is a one-thread kernel and
+ * the march / network / compositing launches read the round's counts from device memory, so a caller enqueues any number of rounds
+ * and reads the live-ray count back when it likes.  d_ctl: NGP_RENDER_CTL_WORDS uint32, zeroed before round 0:
+ *   [0],[1] live rays (ping-pong: the compaction of round r takes its input count from [r & 1] -- pass NULL in round 0 -- and must
+ *           be given d_ctl + ((r + 1) & 1) as its live-ray counter),  [2] steps of the round,  [3] samples of the round
+ *           (d_n_valid of ngp_network_inference),  [4] i_steps_offset.
+ * Call order per round r: ngp_compact_rays, ngp_render_round, ngp_generate_coords_from_rays_dev, ngp_network_inference,
+ * ngp_composite_infer_dev.  tail_steps > max_steps lets late rounds (batch below a quarter of the frame) take up to tail_steps
+ * steps: fewer, fuller rounds; a ray's samples and their compositing order -- the image -- do not depend on the grouping. */
+#define NGP_RENDER_CTL_WORDS 8
+int ngp_render_round(void* stream, uint32_t* d_ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter);
+int ngp_generate_coords_from_rays_dev(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round,
+                                      const uint8_t* d_bitfield, void* d_payloads, float* d_coords);
+int ngp_composite_infer_dev(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round,
+                            void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
+                            float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale);
 /* compact_rays_kernel (testbed.cu:423-446) with warp-aggregated reservation; counters: [0] alive, [1] hit */
 int ngp_compact_rays(void* stream, uint32_t n_rays, const uint32_t* d_n_rays, const void* d_src_payloads, const float* d_src_rgba,
                      void* d_dst_payloads, float* d_dst_rgba, void* d_hit_payloads, float* d_hit_rgba, uint32_t* d_n_alive, uint32_t* d_n_hit);

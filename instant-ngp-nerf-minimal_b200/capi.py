@@ -22,7 +22,7 @@ class GridDesc(C.Structure):
 
 class SamplerCfg(C.Structure):
     _fields_ = [("aabb_min", f32), ("aabb_max", f32), ("grid_size", u32), ("n_cascades", u32), ("max_steps", u32),
-                ("cone_angle", f32), ("min_step", f32), ("max_step", f32), ("near_distance", f32), ("keep_empty_rays", u32)]
+                ("cone_angle", f32), ("min_step", f32), ("max_step", f32), ("near_distance", f32), ("keep_empty_rays", u32), ("coarse_bitfield", vp)]
 
 
 class CameraCfg(C.Structure):
@@ -77,6 +77,8 @@ SIGNATURES = {
     "ngp_splat_grid": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, vp, u32, i32, vp]),
     "ngp_ema_grid": (i32, [vp, C.POINTER(SamplerCfg), f32, vp, vp]),
     "ngp_update_grid": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, vp, u32, i32, f32, vp, vp]),
+    "ngp_coarse_bitfield_bytes": (C.c_size_t, [C.POINTER(SamplerCfg)]),
+    "ngp_build_coarse_bitfield": (i32, [vp, C.POINTER(SamplerCfg), vp, vp]),
     "ngp_update_grid_bitfield": (i32, [vp, C.POINTER(SamplerCfg), vp, f32, vp, vp]),
     "ngp_scan_workspace_bytes": (sz, [u32]),
     "ngp_generate_training_samples": (i32, [vp, C.POINTER(SamplerCfg), C.POINTER(CameraCfg), u32, u32, u32, u32, vp, vp, vp, i32, u64, u64,
@@ -90,6 +92,9 @@ SIGNATURES = {
     "ngp_composite_train_static": (i32, [vp, C.POINTER(RenderCfg), u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, u64, u64, vp, vp]),
     "ngp_rollover": (i32, [vp, u32, vp, vp, u32, vp, vp]),
     "ngp_composite_infer": (i32, [vp, C.POINTER(RenderCfg), u32, vp, u32, u32, vp, vp, vp, vp, u32, i32, f32, f32, C.POINTER(f32), f32]),
+    "ngp_composite_infer_dev": (i32, [vp, C.POINTER(RenderCfg), u32, vp, u32, vp, vp, vp, vp, u32, i32, f32, f32, C.POINTER(f32), f32]),
+    "ngp_render_round": (i32, [vp, vp, u32, u32, u32, u32, u32, u32]),
+    "ngp_generate_coords_from_rays_dev": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, u32, vp, vp, vp]),
     "ngp_compact_rays": (i32, [vp, u32, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "ngp_shade": (i32, [vp, u32, vp, vp, vp, vp, i32, i32]),
     "ngp_accumulate": (i32, [vp, u32, vp, vp, f32, i32]),

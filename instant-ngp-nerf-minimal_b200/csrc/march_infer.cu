@@ -40,50 +40,6 @@ __host__ __device__ inline float ld_random_val(uint32_t index, uint32_t seed, ui
 
 struct CamMat { float m[12]; };
 
-// One thread per pixel: ray set-up, then the skip to the first occupied cell (advance_pos_nerf) with the closed-form hop of
-// lattice_hop.h.  An 8-lanes-per-pixel variant of this kernel was measured 6x slower (1.2 -> 7.1 ms at 1080p): the skip crosses
-// about one voxel per 8-point window, so the rounds do not shrink while the thread count grows 8x.
-__global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
-                                                        uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads,
-                                                        uint32_t first_pixel, uint32_t n, const __half* __restrict__ envmap, int env_res_x, int env_res_y,
-                                                        float4* __restrict__ frame) {
-	// tile-sharded rendering: the launch covers the n pixels from first_pixel on (whole rows); every quantity that depends on the
-	// pixel -- the ray, the jitter seed, the scatter target -- uses the GLOBAL pixel index, so a band is bit-identical to the same
-	// rows of the full frame; only the slot in the payload array is band-relative
-	const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-	if (slot >= n) return;
-	const uint32_t idx = first_pixel + slot;
-	const uint32_t x = idx % cam.width, y = idx / cam.width;
-	V3 o, d;
-	make_ray(cam_matrix.m, ((float)x + offx) / (float)cam.width, ((float)y + offy) / (float)cam.height, cam, o, d);
-	if (envmap) {            // occupancy_sampler.cu:500-502: every pixel starts from the environment map seen along its ray
-		float ev[4];
-		read_envmap(envmap, env_res_x, env_res_y, d.x, d.y, d.z, ev);
-		frame[idx] = make_float4(ev[0], ev[1], ev[2], ev[3]);
-	}
-	float t = fmaxf(ray_intersect_tmin(c, o, d), 0.05f) + 1e-6f;
-	RayPayload p;
-	p.ox = o.x; p.oy = o.y; p.oz = o.z; p.dx = d.x; p.dy = d.y; p.dz = d.z; p.idx = idx; p.n_steps = 0; p.t = t; p.alive = 1;
-	if (!aabb_contains(c, ray_at(o, d, t))) {
-		p.alive = 0; p.dx = p.dy = p.dz = 0.f; p.t = 0.f; p.idx = 0;
-		payloads[slot] = p;
-		return;
-	}
-	const V3 idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
-	float dt = calc_dt(t, c);
-	t = __fmaf_rn(ld_random_val(spp, idx * 786433u, 0), dt, t);
-	V3 pos;
-	while (true) {
-		if (!aabb_contains(c, pos = ray_at(o, d, t))) { p.alive = 0; break; }
-		dt = calc_dt(t, c);
-		const uint32_t mip = mip_from_dt(dt, pos, c);
-		if (grid_occupied(pos, bits, mip, c.grid_size)) break;
-		t = advance_to_next_voxel_fast(t, c, c.cone_angle == 0.f, pos, d, idir, c.grid_size >> mip);
-	}
-	p.t = t;
-	payloads[slot] = p;
-}
-
 // The reference's per-ray loop (generate_coords_from_rays_regularly_kernel, occupancy_sampler.cu:552-601) on persistent warps that
 // REFILL: a lane whose ray is finished takes the next unprocessed ray, so a warp is not held up by its longest ray.
 //   * ncu on the thread-per-ray form of this loop (profiles/r02_render.md): 8.1 of 32 lanes active -- rays of one warp need between 4
@@ -101,7 +57,7 @@ struct MarchRay {
 	V3 o, d, idir, half_sign;          // half_sign = 0.5 * copysign(1, d): distance_to_next_voxel's per-axis constant
 	float cdx, cdy, cdz, t;
 	ngp_lattice lat;                   // closed-form stepping constants of the binade t is in (lattice_hop.h)
-	uint32_t index, j;
+	uint32_t index, j, known_cell;
 };
 
 // a Coordinate (28 bytes, 4-byte aligned) as 8-byte stores where the alignment allows
@@ -127,15 +83,80 @@ __device__ __forceinline__ uint32_t mip_at(float dt, V3 p, const ngp_sampler_cfg
 	return (uint32_t)min((int)c.n_cascades - 1, max(exponent_of(dt), mip));
 }
 
-// occupancy bit of the cell around p in cascade mip; the Morton interleave comes from a 256-entry shared table when the grid is
-// small enough (every grid the configurations use)
-__device__ __forceinline__ bool occupied_at(V3 p, uint32_t mip, uint32_t G, const uint32_t* __restrict__ spread, const uint8_t* __restrict__ bits) {
+// the cell around p in cascade mip: its coordinates in cells (float, before truncation), its Morton index and its occupancy bit.
+// The Morton interleave comes from a 256-entry shared table when the grid is small enough (every grid the configurations use).
+// `known` (optional): packed coordinates of a cell already known to be OCCUPIED (the previous sample's); a probe that lands in it
+// again -- about four of five samples do -- skips the table look-ups and the bitfield load.  0xffffffff = none.
+struct CellProbe { float gx, gy, gz; uint32_t idx; bool occupied; };
+__device__ __forceinline__ CellProbe probe_cell(V3 p, uint32_t mip, uint32_t G, const uint32_t* __restrict__ spread, const uint8_t* __restrict__ bits, uint32_t* known = nullptr) {
 	const float s = __uint_as_float((127u - mip) << 23), g = (float)G;          // scalbnf(1, -mip)
-	const int ix = min(max((int)(((p.x - 0.5f) * s + 0.5f) * g), 0), (int)G - 1);
-	const int iy = min(max((int)(((p.y - 0.5f) * s + 0.5f) * g), 0), (int)G - 1);
-	const int iz = min(max((int)(((p.z - 0.5f) * s + 0.5f) * g), 0), (int)G - 1);
-	const uint32_t idx = spread ? (spread[ix] | (spread[iy] << 1) | (spread[iz] << 2)) : morton3D(ix, iy, iz);
-	return __ldg(bits + idx / 8 + (size_t)(G * G * G) * mip / 8) & (1u << (idx % 8));
+	CellProbe cp;
+	cp.gx = ((p.x - 0.5f) * s + 0.5f) * g; cp.gy = ((p.y - 0.5f) * s + 0.5f) * g; cp.gz = ((p.z - 0.5f) * s + 0.5f) * g;
+	const int ix = min(max((int)cp.gx, 0), (int)G - 1), iy = min(max((int)cp.gy, 0), (int)G - 1), iz = min(max((int)cp.gz, 0), (int)G - 1);
+	const uint32_t key = known && G <= 512 ? ((uint32_t)ix | ((uint32_t)iy << 9) | ((uint32_t)iz << 18) | (mip << 27)) : 0xffffffffu;
+	if (known && key == *known && key != 0xffffffffu) { cp.idx = 0; cp.occupied = true; return cp; }
+	cp.idx = spread ? (spread[ix] | (spread[iy] << 1) | (spread[iz] << 2)) : morton3D(ix, iy, iz);
+	cp.occupied = __ldg(bits + cp.idx / 8 + (size_t)(G * G * G) * mip / 8) & (1u << (cp.idx % 8));
+	if (known) *known = cp.occupied ? key : 0xffffffffu;
+	return cp;
+}
+
+// Crossing a whole empty 8x8x8 block of cells in one hop, with the reference's result.
+//
+// The reference visits (about) one lattice point per empty cell: from a visited point v it goes to the first lattice point at or
+// behind  tau = fl(v.t + exit distance of v's cell).  tau differs from the true time e at which the ray crosses that cell face by a
+// rounding error |tau - e| <= delta, so whenever no lattice point lies within delta of e the landing point is L(e), the first
+// lattice point behind e -- whatever v was.  Now let e* be the time the ray leaves the block B around the current point, all of B
+// empty.  The reference's last visited point before e* sits in some (empty) cell of B; if its own hop aims at a face before e* it
+// nevertheless lands behind e* (it is the LAST point before e*), so no lattice point lies between its target and e*, and its landing
+// point is L(e*) again.  Hence, if no lattice point lies within delta + delta' of our own estimate of e* (delta' its error), hopping
+// straight to L(e*) reproduces a point the reference visits, and every point it visited in between lay in empty cells: the march
+// continues from identical state.  Otherwise the hop is declined and the cell-by-cell march goes on (it re-tries in the next cell).
+//   delta, delta' <= 2 ulp(box coordinate) |1 / d_axis| + ulp(t) each (position fma, the products with 1/d, the sum with t); the
+//   margin used is 8 (ulp(coordinate) |1 / d_axis| + ulp(t)) plus 1e-3 of a step.
+// Needs the constant-step lattice (L.inv_dtq != 0) and stays inside its binade; blocks never straddle a cascade shell (shell faces
+// are at multiples of 8 cells for grid_size >= 32).
+__device__ __forceinline__ bool coarse_hop(const ngp_sampler_cfg& c, const ngp_lattice& L, float& t, const CellProbe& cp, uint32_t mip, V3 d, V3 idir, float coord_ulp) {
+	if (!c.coarse_bitfield || L.inv_dtq == 0.f) return false;
+	const uint32_t G = c.grid_size, block = cp.idx >> 9;
+	if (__ldg(c.coarse_bitfield + (size_t)(G * G * G / 4096) * mip + (block >> 3)) & (1u << (block & 7u))) return false;
+	if (!(cp.gx >= 0.f && cp.gx < (float)G && cp.gy >= 0.f && cp.gy < (float)G && cp.gz >= 0.f && cp.gz < (float)G)) return false;
+	// exit of the block, in cells along each axis, as a time
+	const float bx = floorf(cp.gx * 0.125f) * 8.f, by = floorf(cp.gy * 0.125f) * 8.f, bz = floorf(cp.gz * 0.125f) * 8.f;
+	const float tx = d.x > 0.f ? (bx + 8.f - cp.gx) * idir.x : d.x < 0.f ? (bx - cp.gx) * idir.x : INFINITY;
+	const float ty = d.y > 0.f ? (by + 8.f - cp.gy) * idir.y : d.y < 0.f ? (by - cp.gy) * idir.y : INFINITY;
+	const float tz = d.z > 0.f ? (bz + 8.f - cp.gz) * idir.z : d.z < 0.f ? (bz - cp.gz) * idir.z : INFINITY;
+	float tmin = tx, ia = fabsf(idir.x);
+	if (ty < tmin) { tmin = ty; ia = fabsf(idir.y); }
+	if (tz < tmin) { tmin = tz; ia = fabsf(idir.z); }
+	const float dist = tmin * (__uint_as_float((127u + mip) << 23) / (float)G);      // cells -> world units: 2^mip / G (exact: G is a power of two)
+	if (!(dist > 0.f) || !(dist < 1.0e30f)) return false;
+	const float x = dist * L.inv_dtq, fl = floorf(x), fr = x - fl;
+	const float margin = 8.f * (coord_ulp * ia + L.top * 5.9604645e-8f) * L.inv_dtq + 1.0e-3f;
+	if (!(fr > margin && fr < 1.f - margin) || !(fl < 8388607.f)) return false;
+	const float tc = fmaf(fl + 1.f, L.dtq, t);
+	if (!(tc < L.top)) return false;
+	t = tc;
+	return true;
+}
+
+// advance_to_next_voxel (occupancy_sampler.cu:284-294): distance to the cell's exit, then the first lattice point at or behind it --
+// in closed form where lattice_hop.h can prove it, else with the reference's loop
+__device__ __forceinline__ void cell_hop(const ngp_sampler_cfg& c, ngp_lattice& L, float& t, V3 pos, V3 idir, V3 half_sign, uint32_t mip, bool const_dt) {
+	const uint32_t res = c.grid_size >> mip;
+	const float rr = (float)res;
+	const float qx = rr * pos.x, qy = rr * pos.y, qz = rr * pos.z;
+	const float tx = (floorf(qx + 0.5f + half_sign.x) - qx) * idir.x;
+	const float ty = (floorf(qy + 0.5f + half_sign.y) - qy) * idir.y;
+	const float tz = (floorf(qz + 0.5f + half_sign.z) - qz) * idir.z;
+	const float tmin = fminf(fminf(tx, ty), tz);
+	// t / res as a multiplication when res is a power of two (exact)
+	const float dist = fmaxf((res & (res - 1u)) == 0u ? tmin * __uint_as_float((127u - (31u - (uint32_t)__clz((int)res))) << 23) : tmin / rr, 0.0f);
+	const float t_target = t + dist;
+	float hopped;
+	if (ngp_lattice_hop_cached(&L, t, t_target, &hopped)) { t = hopped; return; }
+	do { t += calc_dt(t, c); } while (t < t_target);
+	ngp_lattice_enter(&L, t, c.min_step, const_dt);
 }
 
 __global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_sampler_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr,
@@ -157,9 +178,9 @@ __global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_samp
 	int diag_exp;
 	const bool diag_pow2 = frexpf(diag, &diag_exp) == 0.5f;      // then x / diag == x * (1 / diag) exactly
 	const float inv_diag = 1.0f / diag;
-	const float wdt_const = warp_dt(c.min_step, c);
-	const bool res_pow2 = (c.grid_size & (c.grid_size - 1u)) == 0u;
-	const uint32_t log2_grid = 31u - (uint32_t)__clz((int)c.grid_size);
+	float wdt_const = warp_dt(c.min_step, c);
+	asm volatile("" : "+f"(wdt_const));                            // keep the division out of the loop (nvcc folds it back into the sample path otherwise)
+	const float coord_ulp = ngp_binade_top(fmaxf(fmaxf(fabsf(c.aabb_min), fabsf(c.aabb_max)), 1.f)) * 5.9604645e-8f;
 
 	MarchRay r;
 	bool have = false, drained = false;
@@ -190,7 +211,7 @@ __global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_samp
 							r.idir = {1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z};
 							r.half_sign = {0.5f * copysignf(1.f, r.d.x), 0.5f * copysignf(1.f, r.d.y), 0.5f * copysignf(1.f, r.d.z)};
 							r.cdx = (r.d.x + 1.f) * 0.5f; r.cdy = (r.d.y + 1.f) * 0.5f; r.cdz = (r.d.z + 1.f) * 0.5f;
-							r.t = __uint_as_float(w4.x); r.index = cand; r.j = 0;
+							r.t = __uint_as_float(w4.x); r.index = cand; r.j = 0; r.known_cell = 0xffffffffu;
 							ngp_lattice_enter(&r.lat, r.t, c.min_step, const_dt);
 							have = true;
 						}
@@ -206,7 +227,8 @@ __global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_samp
 			} else {
 				const float dt = calc_dt(r.t, c);
 				const uint32_t mip = mip_at(dt, pos, c);
-				if (occupied_at(pos, mip, c.grid_size, spread, bits)) {
+				const CellProbe cp = probe_cell(pos, mip, c.grid_size, spread, bits, &r.known_cell);
+				if (cp.occupied) {
 					float px, py, pz;
 					if (diag_pow2) { px = (pos.x - c.aabb_min) * inv_diag; py = (pos.y - c.aabb_min) * inv_diag; pz = (pos.z - c.aabb_min) * inv_diag; }
 					else { px = (pos.x - c.aabb_min) / diag; py = (pos.y - c.aabb_min) / diag; pz = (pos.z - c.aabb_min) / diag; }
@@ -219,25 +241,8 @@ __global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_samp
 						payloads[r.index].t = r.t; payloads[r.index].n_steps = n_steps;
 						have = false;
 					} else if (!(r.t < r.lat.top)) ngp_lattice_enter(&r.lat, r.t, c.min_step, const_dt);
-				} else {
-					// advance_to_next_voxel (:284-294): distance to the cell's exit, then the first lattice point at or behind it
-					const uint32_t res = c.grid_size >> mip;
-					const float rr = (float)res;
-					const float qx = rr * pos.x, qy = rr * pos.y, qz = rr * pos.z;
-					const float tx = (floorf(qx + 0.5f + r.half_sign.x) - qx) * r.idir.x;
-					const float ty = (floorf(qy + 0.5f + r.half_sign.y) - qy) * r.idir.y;
-					const float tz = (floorf(qz + 0.5f + r.half_sign.z) - qz) * r.idir.z;
-					const float tmin = fminf(fminf(tx, ty), tz);
-					const float dist = fmaxf(res_pow2 ? tmin * __uint_as_float((127u - (log2_grid - mip)) << 23) : tmin / rr, 0.0f);     // a power of two divides exactly
-					const float t_target = r.t + dist;
-					float hopped;
-					if (ngp_lattice_hop_cached(&r.lat, r.t, t_target, &hopped)) r.t = hopped;
-					else {
-						float t = r.t;
-						do { t += calc_dt(t, c); } while (t < t_target);
-						r.t = t;
-						ngp_lattice_enter(&r.lat, r.t, c.min_step, const_dt);
-					}
+				} else if (!coarse_hop(c, r.lat, r.t, cp, mip, r.d, r.idir, coord_ulp)) {
+					cell_hop(c, r.lat, r.t, pos, r.idir, r.half_sign, mip, const_dt);
 				}
 			}
 		}
@@ -248,6 +253,56 @@ __global__ void __launch_bounds__(256) generate_coords_from_rays_kernel(ngp_samp
 		const uint32_t total_warps = gridDim.x * (blockDim.x >> 5);
 		if (atomicAdd(queue + 1, 1u) == total_warps - 1u) { queue[0] = 0; queue[1] = 0; __threadfence(); }
 	}
+}
+
+// One thread per pixel: ray set-up, then the skip to the first occupied cell (advance_pos_nerf) with the closed-form hop of
+// lattice_hop.h and whole empty blocks crossed at once (coarse_hop).  An 8-lanes-per-pixel variant of this kernel was measured 6x slower (1.2 -> 7.1 ms at 1080p): the skip crosses
+// about one voxel per 8-point window, so the rounds do not shrink while the thread count grows 8x.
+__global__ void __launch_bounds__(128) init_rays_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam, CamMat cam_matrix, float offx, float offy,
+                                                        uint32_t spp, const uint8_t* __restrict__ bits, RayPayload* __restrict__ payloads,
+                                                        uint32_t first_pixel, uint32_t n, const __half* __restrict__ envmap, int env_res_x, int env_res_y,
+                                                        float4* __restrict__ frame) {
+	// tile-sharded rendering: the launch covers the n pixels from first_pixel on (whole rows); every quantity that depends on the
+	// pixel -- the ray, the jitter seed, the scatter target -- uses the GLOBAL pixel index, so a band is bit-identical to the same
+	// rows of the full frame; only the slot in the payload array is band-relative
+	const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+	if (slot >= n) return;
+	const uint32_t idx = first_pixel + slot;
+	const uint32_t x = idx % cam.width, y = idx / cam.width;
+	V3 o, d;
+	make_ray(cam_matrix.m, ((float)x + offx) / (float)cam.width, ((float)y + offy) / (float)cam.height, cam, o, d);
+	if (envmap) {            // occupancy_sampler.cu:500-502: every pixel starts from the environment map seen along its ray
+		float ev[4];
+		read_envmap(envmap, env_res_x, env_res_y, d.x, d.y, d.z, ev);
+		frame[idx] = make_float4(ev[0], ev[1], ev[2], ev[3]);
+	}
+	float t = fmaxf(ray_intersect_tmin(c, o, d), 0.05f) + 1e-6f;
+	RayPayload p;
+	p.ox = o.x; p.oy = o.y; p.oz = o.z; p.dx = d.x; p.dy = d.y; p.dz = d.z; p.idx = idx; p.n_steps = 0; p.t = t; p.alive = 1;
+	if (!aabb_contains(c, ray_at(o, d, t))) {
+		p.alive = 0; p.dx = p.dy = p.dz = 0.f; p.t = 0.f; p.idx = 0;
+		payloads[slot] = p;
+		return;
+	}
+	const V3 idir = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
+	const V3 half_sign = {0.5f * copysignf(1.f, d.x), 0.5f * copysignf(1.f, d.y), 0.5f * copysignf(1.f, d.z)};
+	const bool const_dt = c.cone_angle == 0.f;
+	const float coord_ulp = ngp_binade_top(fmaxf(fmaxf(fabsf(c.aabb_min), fabsf(c.aabb_max)), 1.f)) * 5.9604645e-8f;
+	float dt = calc_dt(t, c);
+	t = __fmaf_rn(ld_random_val(spp, idx * 786433u, 0), dt, t);
+	ngp_lattice lat;
+	ngp_lattice_enter(&lat, t, c.min_step, const_dt);
+	while (true) {
+		const V3 pos = ray_at(o, d, t);
+		if (!aabb_contains(c, pos)) { p.alive = 0; break; }
+		dt = calc_dt(t, c);
+		const uint32_t mip = mip_at(dt, pos, c);
+		const CellProbe cp = probe_cell(pos, mip, c.grid_size, nullptr, bits);
+		if (cp.occupied) break;
+		if (!coarse_hop(c, lat, t, cp, mip, d, idir, coord_ulp)) cell_hop(c, lat, t, pos, idir, half_sign, mip, const_dt);
+	}
+	p.t = t;
+	payloads[slot] = p;
 }
 
 } // namespace ngp
@@ -312,4 +367,10 @@ static int generate_coords_impl(void* stream, const ngp_sampler_cfg* cfg, uint32
 extern "C" int ngp_generate_coords_from_rays(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps,
                                              const uint8_t* d_bitfield, void* d_payloads, float* d_coords) {
 	return generate_coords_impl(stream, cfg, n_rays, d_n_rays, n_steps, nullptr, d_bitfield, d_payloads, d_coords);
+}
+
+extern "C" int ngp_generate_coords_from_rays_dev(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round,
+                                                 const uint8_t* d_bitfield, void* d_payloads, float* d_coords) {
+	NGP_REQUIRE(d_ctl, "null pointer");
+	return generate_coords_impl(stream, cfg, n_rays_bound, d_ctl + ((round + 1) & 1), 0, d_ctl + 2, d_bitfield, d_payloads, d_coords);
 }

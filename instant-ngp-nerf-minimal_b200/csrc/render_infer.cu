@@ -8,11 +8,14 @@
 namespace ngp {
 
 __global__ void __launch_bounds__(128) composite_infer_kernel(
-	ngp_render_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr, uint32_t n_steps, uint32_t n_steps_offset,
+	ngp_render_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr, uint32_t n_steps_arg, uint32_t n_steps_offset_arg,
+	const uint32_t* __restrict__ n_steps_ptr, const uint32_t* __restrict__ n_steps_offset_ptr,
 	RayPayload* __restrict__ payloads, float4* __restrict__ rgba, const Coordinate* __restrict__ coords, const __half* __restrict__ net_out,
 	uint32_t padded_width, int render_mode, float aabb_min, float aabb_max, float fwd_x, float fwd_y, float fwd_z, float depth_scale)
 {
 	const uint32_t n_rays = n_rays_ptr ? min(*n_rays_ptr, n_rays_max) : n_rays_max;
+	const uint32_t n_steps = n_steps_ptr ? *n_steps_ptr : n_steps_arg;
+	const uint32_t n_steps_offset = n_steps_offset_ptr ? *n_steps_offset_ptr : n_steps_offset_arg;
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_rays) return;
 	RayPayload& p = payloads[i];
@@ -83,6 +86,28 @@ __global__ void __launch_bounds__(256) compact_rays_kernel(
 	else if (hit) { const uint32_t d = hbase + __popc(hm & below); hit_p[d] = p; hit_c[d] = col; }
 }
 
+// Round control of the device-driven render loop (the host loop of testbed.cu:521-575, one thread): after the compaction of round
+// `round` it turns the live-ray count into the round's step count and sample count, keeps the running samples-per-ray offset and
+// re-arms the counter the next compaction will fill.
+//   ctl[0], ctl[1]: live rays, ping-pong (round r's compaction reads [r & 1] -- round 0 the pixel count -- and fills [(r + 1) & 1])
+//   ctl[2] n_steps of this round, ctl[3] samples of this round, ctl[4] i_steps_offset (1 + samples per live ray so far)
+__global__ void render_round_kernel(uint32_t* __restrict__ ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter) {
+	uint32_t offset = round == 0 ? 1u : ctl[4] + ctl[2];             // the previous round composited ctl[2] samples per live ray
+	uint32_t n_alive = ctl[(round + 1) & 1];
+	if (offset >= march_iter) n_alive = 0;                           // `while (n_alive > 0 && i_steps_offset < MARCH_ITER)`
+	uint32_t n_steps = 0;
+	if (n_alive) {
+		n_steps = min(max(n_pixels / n_alive, min_steps), max_steps);
+		// Our own extension of the schedule, not of the result (a ray's samples and their compositing order do not depend on how
+		// they are grouped into rounds): once the batch has shrunk below a quarter of the frame, rounds are latency bound, so more
+		// steps are taken per round and fewer rounds are needed.
+		if (tail_steps > n_steps) n_steps = max(n_steps, min(tail_steps, n_pixels / (4u * n_alive)));
+	}
+	ctl[(round + 1) & 1] = n_alive;
+	ctl[round & 1] = 0;
+	ctl[2] = n_steps; ctl[3] = n_alive * n_steps; ctl[4] = offset;
+}
+
 __global__ void shade_kernel(uint32_t n_hit_max, const uint32_t* __restrict__ n_hit_ptr, const float4* __restrict__ rgba, const RayPayload* __restrict__ payloads,
                              float4* __restrict__ frame, int render_mode, int train_in_linear) {
 	const uint32_t n_hit = n_hit_ptr ? min(*n_hit_ptr, n_hit_max) : n_hit_max;
@@ -150,15 +175,39 @@ __global__ void tonemap_kernel(uint32_t n, float exposure, float4 bg_in, const f
 
 using namespace ngp;
 
-extern "C" int ngp_composite_infer(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t n_steps_offset,
-                                   void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
-                                   float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale) {
+static int composite_infer_impl(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t n_steps_offset,
+                                const uint32_t* d_n_steps, const uint32_t* d_n_steps_offset,
+                                void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
+                                float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale) {
 	NGP_REQUIRE(cfg && d_payloads && d_rgba && d_coords && d_rgbsigma && camera_fwd_host, "null pointer");
 	if (n_rays == 0) return 0;
-	NGP_LAUNCH("composite_infer_kernel", (cudaStream_t)stream, composite_infer_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, n_steps_offset, (RayPayload*)d_payloads,
+	NGP_LAUNCH("composite_infer_kernel", (cudaStream_t)stream, composite_infer_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, n_steps_offset,
+		d_n_steps, d_n_steps_offset, (RayPayload*)d_payloads,
 		(float4*)d_rgba, (const Coordinate*)d_coords, (const __half*)d_rgbsigma, padded_width, render_mode, aabb_min, aabb_max,
 		camera_fwd_host[0], camera_fwd_host[1], camera_fwd_host[2], depth_scale));
 	return check_launch("composite_infer");
+}
+
+extern "C" int ngp_composite_infer(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t n_steps_offset,
+                                   void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
+                                   float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale) {
+	return composite_infer_impl(stream, cfg, n_rays, d_n_rays, n_steps, n_steps_offset, nullptr, nullptr, d_payloads, d_rgba, d_coords, d_rgbsigma, padded_width, render_mode,
+	                            aabb_min, aabb_max, camera_fwd_host, depth_scale);
+}
+
+extern "C" int ngp_composite_infer_dev(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round,
+                                       void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
+                                       float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale) {
+	NGP_REQUIRE(d_ctl, "null pointer");
+	return composite_infer_impl(stream, cfg, n_rays_bound, d_ctl + ((round + 1) & 1), 0, 0, d_ctl + 2, d_ctl + 4, d_payloads, d_rgba, d_coords, d_rgbsigma, padded_width,
+	                            render_mode, aabb_min, aabb_max, camera_fwd_host, depth_scale);
+}
+
+extern "C" int ngp_render_round(void* stream, uint32_t* d_ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter) {
+	NGP_REQUIRE(d_ctl, "null pointer");
+	NGP_REQUIRE(min_steps >= 1 && max_steps >= min_steps, "bad step limits");
+	NGP_LAUNCH("render_round_kernel", (cudaStream_t)stream, render_round_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(d_ctl, round, n_pixels, min_steps, max_steps, tail_steps, march_iter));
+	return check_launch("render_round");
 }
 
 extern "C" int ngp_compact_rays(void* stream, uint32_t n_rays, const uint32_t* d_n_rays, const void* d_src_payloads, const float* d_src_rgba,

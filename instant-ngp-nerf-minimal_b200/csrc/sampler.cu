@@ -188,6 +188,21 @@ __global__ void bitfield_max_pool_kernel(uint32_t n, uint32_t G, const uint8_t* 
 	}
 }
 
+// one thread per output byte = 8 blocks of 512 cells = 8 x 64 bytes of the cell bitfield
+__global__ void coarse_bitfield_kernel(uint32_t n_bytes, const uint4* __restrict__ bits, uint8_t* __restrict__ coarse) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_bytes) return;
+	uint32_t out = 0;
+	#pragma unroll
+	for (uint32_t b = 0; b < 8; ++b) {
+		uint32_t any = 0;
+		#pragma unroll
+		for (uint32_t q = 0; q < 4; ++q) { const uint4 v = bits[((size_t)i * 8 + b) * 4 + q]; any |= v.x | v.y | v.z | v.w; }
+		if (any) out |= 1u << b;
+	}
+	coarse[i] = (uint8_t)out;
+}
+
 } // namespace ngp
 
 using namespace ngp;
@@ -285,4 +300,20 @@ extern "C" int ngp_update_grid_bitfield(void* stream, const ngp_sampler_cfg* cfg
 	for (uint32_t level = 1; level < cfg->n_cascades; ++level)
 		NGP_LAUNCH("bitfield_max_pool_kernel", s, bitfield_max_pool_kernel<<<grid_for(cells / 64, 256), 256, 0, s>>>(cells / 64, G, d_bitfield + (size_t)cells * (level - 1) / 8, d_bitfield + (size_t)cells * level / 8));
 	return check_launch("update_grid_bitfield");
+}
+
+extern "C" size_t ngp_coarse_bitfield_bytes(const ngp_sampler_cfg* cfg) {
+	if (!cfg) return 0;
+	return (size_t)cfg->grid_size * cfg->grid_size * cfg->grid_size / 4096 * cfg->n_cascades;
+}
+
+extern "C" int ngp_build_coarse_bitfield(void* stream, const ngp_sampler_cfg* cfg, const uint8_t* d_bitfield, uint8_t* d_coarse) {
+	NGP_REQUIRE(cfg && d_bitfield && d_coarse, "null pointer");
+	const uint32_t G = cfg->grid_size;
+	NGP_REQUIRE((G & (G - 1)) == 0 && G >= 32, "the coarse bitfield needs grid_size to be a power of two >= 32");
+	NGP_REQUIRE(((uintptr_t)d_bitfield & 15) == 0, "the cell bitfield must be 16-byte aligned");
+	const uint32_t n_bytes = (uint32_t)ngp_coarse_bitfield_bytes(cfg);
+	cudaStream_t s = (cudaStream_t)stream;
+	NGP_LAUNCH("coarse_bitfield_kernel", s, coarse_bitfield_kernel<<<div_up(n_bytes, 128), 128, 0, s>>>(n_bytes, (const uint4*)d_bitfield, d_coarse));
+	return check_launch("build_coarse_bitfield");
 }

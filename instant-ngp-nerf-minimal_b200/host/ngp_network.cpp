@@ -55,11 +55,11 @@ void NGPNetwork::density(cudaStream_t stream, const float* positions, uint32_t s
 	                              m_workspace.data(), m_workspace.get_bytes()));
 }
 
-void NGPNetwork::input_gradient(cudaStream_t stream, uint32_t dim, Coordinate* input_and_output, uint32_t n) {
+void NGPNetwork::input_gradient(cudaStream_t stream, uint32_t dim, Coordinate* input_and_output, uint32_t n, const uint32_t* d_n_valid) {
 	if (dim >= padded_output_width()) throw std::runtime_error("Invalid dimension to compute the input gradient for.");
 	if (dim != 3) throw std::runtime_error("input_gradient: only the density output (dim 3) is implemented");
 	m_train_workspace.enlarge(ngp_network_workspace_bytes(n));
-	api_check(ngp_network_input_gradient(stream, (float*)input_and_output, n, nullptr, m_inference_params, &m_grid, m_train_workspace.data(), m_train_workspace.get_bytes()));
+	api_check(ngp_network_input_gradient(stream, (float*)input_and_output, n, d_n_valid, m_inference_params, &m_grid, m_train_workspace.data(), m_train_workspace.get_bytes()));
 }
 
 void NGPNetwork::forward(cudaStream_t, const Coordinate*, uint32_t, precision_t* output) { m_forward_output = output; }

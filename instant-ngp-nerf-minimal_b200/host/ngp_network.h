@@ -20,7 +20,7 @@ public:
 	void density(cudaStream_t stream, const float* positions, uint32_t stride, uint32_t n, precision_t* output, bool use_inference_matrices = true);
 	// tiny-cuda-nn/object.h:126-150 as Testbed calls it (testbed.cu:558-560): d output[dim] / d input written over the inputs, with
 	// the inference weights; only dim == 3 (sigma_raw, what RenderMode::Normals needs) is implemented
-	void input_gradient(cudaStream_t stream, uint32_t dim, Coordinate* input_and_output, uint32_t n);
+	void input_gradient(cudaStream_t stream, uint32_t dim, Coordinate* input_and_output, uint32_t n, const uint32_t* d_n_valid = nullptr);
 	// ngp_network.h:325-398 / 400-494.  forward() only notes its arguments: the fused kernel recomputes the activations in
 	// shared memory during backward() instead of storing them in HBM, and writes `output` there.
 	void forward(cudaStream_t stream, const Coordinate* input, uint32_t n, precision_t* output);

@@ -19,6 +19,10 @@ OccupancySampler::OccupancySampler(const Json& config) {
 	density_grid_mean.resize(256);
 	density_grid_bitfield.resize(n_total_elements / 8);
 	density_grid_current.memset(0); density_grid.memset(0); density_grid_mean.memset(0); density_grid_bitfield.memset(0);
+	if ((n_grid_size & (n_grid_size - 1)) == 0 && n_grid_size >= 32) {
+		density_grid_coarse.resize(n_total_elements / 4096);
+		density_grid_coarse.memset(0);
+	}
 	n_max_steps = (uint32_t)config.value("maximum_marching_steps", 1024);
 	cone_angle_constant = config.value("cone_angle_constant", 0.f);
 	const float sqrt3 = 1.73205080757f;
@@ -36,6 +40,7 @@ ngp_sampler_cfg OccupancySampler::cfg() const {
 	c.aabb_min = aabb.min[0]; c.aabb_max = aabb.max[0];
 	c.grid_size = n_grid_size; c.n_cascades = n_cascades; c.max_steps = n_max_steps;
 	c.cone_angle = cone_angle_constant; c.min_step = min_cone_stepsize; c.max_step = max_cone_stepsize; c.near_distance = near_distance;
+	c.coarse_bitfield = coarse_skip && density_grid_coarse.size() ? density_grid_coarse.data() : nullptr;
 	return c;
 }
 
@@ -97,6 +102,7 @@ void OccupancySampler::ema_grid(cudaStream_t stream) {
 void OccupancySampler::update_grid_bitfield(cudaStream_t stream) {
 	const ngp_sampler_cfg c = cfg();
 	api_check(ngp_update_grid_bitfield(stream, &c, density_grid.data(), min_optical_thickness, density_grid_mean.data(), density_grid_bitfield.data()));
+	if (density_grid_coarse.size()) api_check(ngp_build_coarse_bitfield(stream, &c, density_grid_bitfield.data(), density_grid_coarse.data()));
 }
 
 void OccupancySampler::sample_coords_from_dataset(uint32_t n_rays, uint32_t n_rays_shift, uint32_t n_coords, const NeRFSynthetic& dataset, bool train_envmap,
@@ -135,6 +141,12 @@ void OccupancySampler::generate_coords_from_rays(uint32_t n_rays, const uint32_t
                                                  DeviceBuffer<Coordinate>& coords, cudaStream_t stream) {
 	const ngp_sampler_cfg c = cfg();
 	api_check(ngp_generate_coords_from_rays(stream, &c, n_rays, d_n_rays, n_steps, density_grid_bitfield.data(), payloads.data(), (float*)coords.data()));
+}
+
+void OccupancySampler::generate_coords_from_rays_dev(uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round, DeviceBuffer<RayPayload>& payloads,
+                                                     DeviceBuffer<Coordinate>& coords, cudaStream_t stream) {
+	const ngp_sampler_cfg c = cfg();
+	api_check(ngp_generate_coords_from_rays_dev(stream, &c, n_rays_bound, d_ctl, round, density_grid_bitfield.data(), payloads.data(), (float*)coords.data()));
 }
 
 } // namespace ngp

@@ -45,6 +45,10 @@ public:
 	void generate_coords_from_rays(uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, DeviceBuffer<RayPayload>& payloads,
 	                               DeviceBuffer<Coordinate>& coords, cudaStream_t stream);
 
+	// device-driven render loop: live-ray count and step count come from the control block (include/ngp_b200.h)
+	void generate_coords_from_rays_dev(uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round, DeviceBuffer<RayPayload>& payloads,
+	                                   DeviceBuffer<Coordinate>& coords, cudaStream_t stream);
+
 	ngp_sampler_cfg cfg() const;
 
 public:
@@ -54,6 +58,8 @@ public:
 	float ema_decay;
 	DeviceBuffer<float> density_grid_current, density_grid, density_grid_mean;
 	DeviceBuffer<uint8_t> density_grid_bitfield;
+	DeviceBuffer<uint8_t> density_grid_coarse;       // one bit per 8x8x8 block of cells (ngp_build_coarse_bitfield); empty when the grid is too small
+	bool coarse_skip = true;                         // hand it to the inference march (identical results, fewer visited cells)
 	uint32_t n_max_steps;
 	float cone_angle_constant, min_cone_stepsize, max_cone_stepsize, near_distance, far_distance;
 	bool snap_to_pixel_centers_in_training, snap_to_pixel_centers_in_rendering;

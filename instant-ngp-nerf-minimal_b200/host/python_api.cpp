@@ -130,6 +130,8 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readonly("training_buffer", &Testbed::m_training_buffer)
 		.def_readonly("rendering_buffer", &Testbed::m_rendering_buffer)
 		.def_readwrite("shard_grid_refresh", &Testbed::m_shard_grid_refresh, "data parallel: shard the occupancy-grid refresh over the ranks (default on; off = every rank refreshes everything)")
+		.def_property("coarse_skip", [](const Testbed& t) { return t.coarse_skip(); }, [](Testbed& t, bool v) { t.set_coarse_skip(v); },
+		              "inference march crosses empty 8x8x8 blocks of the occupancy grid in one hop (default on; results are identical either way)")
 		.def_readwrite("pipeline_march", &Testbed::m_pipeline_march, "march step i+1 on a second stream underneath step i (default on)")
 		.def_property("fov", &Testbed::fov, &Testbed::set_fov)
 		.def_property("fov_xy",
@@ -189,6 +191,11 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_property("principal_point",
 			[](const Testbed::RenderingBuffer& r) { return std::vector<float>{r.principal_point[0], r.principal_point[1]}; },
 			[](Testbed::RenderingBuffer& r, const py::object& v) { to_vec(v, r.principal_point, 2, "principal_point"); })
+		.def_readwrite("device_loop", &Testbed::RenderingBuffer::device_loop, "render rounds decided on the device, the live-ray count read back every ROUNDS_PER_READBACK rounds (default on; off: one host synchronisation per round like the reference)")
+		.def_readwrite("ROUNDS_PER_READBACK", &Testbed::RenderingBuffer::ROUNDS_PER_READBACK)
+		.def_readwrite("TAIL_STEPS", &Testbed::RenderingBuffer::TAIL_STEPS, "late rounds (batch below a quarter of the frame) take up to this many steps; <= MAX_STEPS_INBETWEEN_COMPACTION switches it off")
+		.def_readonly("rounds_last_frame", &Testbed::RenderingBuffer::rounds_last_frame)
+		.def_readonly("readbacks_last_frame", &Testbed::RenderingBuffer::readbacks_last_frame)
 		.def_readwrite("MIN_STEPS_INBETWEEN_COMPACTION", &Testbed::RenderingBuffer::MIN_STEPS_INBETWEEN_COMPACTION)
 		.def_readwrite("MAX_STEPS_INBETWEEN_COMPACTION", &Testbed::RenderingBuffer::MAX_STEPS_INBETWEEN_COMPACTION)
 		;

@@ -41,6 +41,11 @@ public:
 	                      const DeviceBuffer<precision_t>& rgbsigma, uint32_t padded_output_width, EActivation density_activation, EActivation rgb_activation,
 	                      ERenderMode render_mode, const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const Mat34& camera_matrix,
 	                      float depth_scale, cudaStream_t stream);
+	// the same with the round's counts read from the device control block of the device-driven render loop (include/ngp_b200.h)
+	void volume_rendering_dev(uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,
+	                          const DeviceBuffer<precision_t>& rgbsigma, uint32_t padded_output_width, EActivation density_activation, EActivation rgb_activation,
+	                          ERenderMode render_mode, const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const Mat34& camera_matrix,
+	                          float depth_scale, cudaStream_t stream);
 
 public:
 	bool train_with_random_bg_color;

@@ -66,6 +66,8 @@ public:
 	// instead of NCCL all-reduce + replicated optimizer.  Collective: every rank must call it.
 	void set_data_parallel(int rank, int world_size, void* nccl_comm, bool peer_memory = false);
 	bool peer_memory_enabled() const { return m_peer_enabled; }
+	bool coarse_skip() const { return m_sampler ? m_sampler->coarse_skip : true; }
+	void set_coarse_skip(bool v) { if (!m_sampler) throw std::runtime_error("coarse_skip: load_model_config first"); m_sampler->coarse_skip = v; }
 	// all-gather of sharded optimizer state (collective; needed before a snapshot with serialize_optimizer in peer mode)
 	void gather_optimizer_state();
 	precision_t* gradients() const { return m_trainer->gradients(); }
@@ -150,8 +152,14 @@ public:
 		DeviceBuffer<uint32_t> n_alive_counter{64};
 		DeviceBuffer<Coordinate> coords;
 		DeviceBuffer<precision_t> rgbsigma;
+		DeviceBuffer<uint32_t> round_ctl{NGP_RENDER_CTL_WORDS};
 		uint32_t MIN_STEPS_INBETWEEN_COMPACTION = 1;
 		uint32_t MAX_STEPS_INBETWEEN_COMPACTION = 8;
+		// Not in the reference: how the rounds are scheduled (the image does not depend on it).
+		bool device_loop = true;              // rounds decided on the device, live-ray count read back every ROUNDS_PER_READBACK rounds (false: testbed.cu's loop, one sync per round)
+		uint32_t ROUNDS_PER_READBACK = 8;
+		uint32_t TAIL_STEPS = 32;             // late rounds (batch below a quarter of the frame) take up to this many steps (<= MAX...: off)
+		uint32_t rounds_last_frame = 0, readbacks_last_frame = 0;
 	} m_rendering_buffer;
 
 private:

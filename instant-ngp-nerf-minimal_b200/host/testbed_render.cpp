@@ -34,9 +34,49 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 	NGP_CUDA_CHECK(cudaMemsetAsync(rb.rays[0].rgba.data(), 0, (size_t)std::max(n_pixels, 1u) * 4 * sizeof(float), m_stream));
 	NGP_CUDA_CHECK(cudaMemsetAsync(rb.n_hit_counter.data(), 0, sizeof(uint32_t), m_stream));
 
+	if (rb.device_loop) {
+		// Rounds are decided on the device (ngp_render_round): compaction, the step-count decision, march, network and compositing of
+		// ROUNDS_PER_READBACK rounds are enqueued back to back, then the live-ray count comes back once.  Rounds enqueued after the
+		// last ray died find a zero count and do nothing.  The launch bounds shrink with every read-back.
+		const uint32_t tail_steps = std::min<uint32_t>(std::max(rb.TAIL_STEPS, rb.MAX_STEPS_INBETWEEN_COMPACTION), 64u);
+		rb.coords.enlarge((size_t)next_multiple(std::max(n_pixels, 1u), BATCH_SIZE_MULTIPLE) * std::max(rb.MAX_STEPS_INBETWEEN_COMPACTION, 1u));
+		uint32_t* ctl = rb.round_ctl.data();
+		NGP_CUDA_CHECK(cudaMemsetAsync(ctl, 0, sizeof(uint32_t) * NGP_RENDER_CTL_WORDS, m_stream));
+		uint32_t bound = n_pixels, round = 0;
+		rb.rounds_last_frame = rb.readbacks_last_frame = 0;
+		const uint32_t per_batch = std::max(rb.ROUNDS_PER_READBACK, 1u);
+		while (bound > 0) {
+			// samples of a round: n_alive * clamp(n_pixels / n_alive, MIN, MAX) <= max(n_pixels, bound * MIN); the tail rule stays below a quarter of the frame
+			const uint32_t sample_bound = next_multiple(std::max(n_pixels, bound * rb.MIN_STEPS_INBETWEEN_COMPACTION), BATCH_SIZE_MULTIPLE);
+			rb.coords.enlarge(sample_bound);
+			rb.rgbsigma.enlarge((size_t)sample_bound * padded_output_width);
+			for (uint32_t k = 0; k < per_batch; ++k, ++round) {
+				RaysSoA& rays_previous = rb.rays[round % 2];
+				RaysSoA& rays_current = rb.rays[(round + 1) % 2];
+				api_check(ngp_compact_rays(m_stream, bound, round == 0 ? nullptr : ctl + (round & 1), rays_previous.payload.data(), rays_previous.rgba.data(),
+				                           rays_current.payload.data(), rays_current.rgba.data(), rb.rays_hit.payload.data(), rb.rays_hit.rgba.data(),
+				                           ctl + ((round + 1) & 1), rb.n_hit_counter.data()));
+				api_check(ngp_render_round(m_stream, ctl, round, n_pixels, rb.MIN_STEPS_INBETWEEN_COMPACTION, rb.MAX_STEPS_INBETWEEN_COMPACTION, tail_steps, MARCH_ITER));
+				m_sampler->generate_coords_from_rays_dev(bound, ctl, round, rays_current.payload, rb.coords, m_stream);
+				m_network->inference_mixed_precision(m_stream, rb.coords.data(), sample_bound, ctl + 3, rb.rgbsigma.data(), true);
+				if (render_mode == ERenderMode::Normals) m_network->input_gradient(m_stream, 3, rb.coords.data(), sample_bound, ctl + 3);   // testbed.cu:558-560
+				m_render->volume_rendering_dev(bound, ctl, round, rays_current, rb.coords, rb.rgbsigma, padded_output_width, m_density_activation, m_rgb_activation,
+				                               render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix, 1.f / m_scene_scale, m_stream);
+			}
+			// live rays after the batch's last compaction (some of them may have been finished by its compositing: the next
+			// compaction sorts that out), still an upper bound for everything that follows
+			NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter, ctl + (round & 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
+			NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 2, ctl + 4, sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
+			NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+			++rb.readbacks_last_frame;
+			bound = m_host_counter[2] >= MARCH_ITER ? 0 : m_host_counter[0];
+		}
+		rb.rounds_last_frame = round;
+	} else {
 	uint32_t i_steps_offset = 1;
 	uint32_t double_buffer_index = 0;
 	uint32_t n_alive = n_pixels;
+	rb.rounds_last_frame = rb.readbacks_last_frame = 0;
 	while (n_alive > 0 && i_steps_offset < MARCH_ITER) {
 		RaysSoA& rays_previous = rb.rays[double_buffer_index % 2];
 		RaysSoA& rays_current = rb.rays[(double_buffer_index + 1) % 2];
@@ -47,8 +87,10 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 		                           rb.rays_hit.payload.data(), rb.rays_hit.rgba.data(), rb.n_alive_counter.data(), rb.n_hit_counter.data()));
 		NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter, rb.n_alive_counter.data(), sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
 		NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
+		++rb.readbacks_last_frame;
 		n_alive = m_host_counter[0];
 		if (n_alive == 0) break;
+		++rb.rounds_last_frame;
 
 		const uint32_t n_steps = std::min(std::max(n_pixels / n_alive, rb.MIN_STEPS_INBETWEEN_COMPACTION), rb.MAX_STEPS_INBETWEEN_COMPACTION);
 		m_sampler->generate_coords_from_rays(n_alive, nullptr, n_steps, rays_current.payload, rb.coords, m_stream);
@@ -59,6 +101,7 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 		                           m_rgb_activation, render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix,
 		                           1.f / m_scene_scale, m_stream);
 		i_steps_offset += n_steps;
+	}
 	}
 
 	NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 1, rb.n_hit_counter.data(), sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));

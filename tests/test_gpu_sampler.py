@@ -272,8 +272,32 @@ def test_generate_training_samples_keeps_empty_rays_for_the_envmap(capi, orc):
     assert np.all(np.abs(np.linalg.norm(b["rays"][~full][:, 3:], axis=1) - 1) < 1e-5), "empty rays still carry their direction"
 
 
-@pytest.mark.parametrize("spp,n_steps", [(0, 1), (3, 8)])
-def test_inference_rays_and_coords_match_oracle(capi, orc, spp, n_steps):
+def test_coarse_bitfield_is_the_or_over_blocks_of_512_cells(capi, orc):
+    import gpuutil as G
+    import torch
+    lib = capi.load()
+    cfg = capi.make_sampler_cfg(4)                      # 3 cascades
+    g = np.random.Generator(np.random.PCG64(4))
+    n_bytes = 128 ** 3 // 8 * 3
+    bits = np.zeros(n_bytes, np.uint8)
+    hot = g.integers(0, n_bytes, 700)
+    bits[hot] = (1 << g.integers(0, 8, 700)).astype(np.uint8)
+    assert lib.ngp_coarse_bitfield_bytes(C.byref(cfg)) == n_bytes // 512
+    d_coarse = G.dev(np.full(n_bytes // 512, 0xAA, np.uint8))
+    capi.check(lib.ngp_build_coarse_bitfield(G.stream(), C.byref(cfg), G.p(G.dev(bits)), G.p(d_coarse)))
+    G.sync()
+    want = np.packbits(bits.reshape(-1, 64).any(axis=1), bitorder="little")
+    assert np.array_equal(G.host(d_coarse, np.uint8), want) and want.any() and not want.all()
+    bad = capi.make_sampler_cfg(1, grid_size=16)
+    assert lib.ngp_build_coarse_bitfield(G.stream(), C.byref(bad), G.p(d_coarse), G.p(d_coarse)) != 0
+
+
+@pytest.mark.parametrize("coarse", [False, True])
+@pytest.mark.parametrize("spp,n_steps", [(0, 1), (3, 8), (1, 64)])
+def test_inference_rays_and_coords_match_oracle(capi, orc, spp, n_steps, coarse):
+    """coarse: with ngp_sampler_cfg.coarse_bitfield set the march crosses whole empty 8x8x8 blocks in one hop where it can prove the
+    landing point -- payloads and samples must still be bit-exact against the oracle's cell-by-cell march (the test grid is
+    blocky at exactly that granularity and 92 % empty, so the block hops carry most of the march)"""
     import gpuutil as G
     import torch
     lib = capi.load()
@@ -285,6 +309,10 @@ def test_inference_rays_and_coords_match_oracle(capi, orc, spp, n_steps):
     cam = _cam(capi, W, H, fx)
     payloads = G.zeros(W * H * 10, torch.int32)
     d_bits = G.dev(bits)
+    if coarse:
+        d_coarse = G.zeros(lib.ngp_coarse_bitfield_bytes(C.byref(cfg)), torch.uint8)
+        capi.check(lib.ngp_build_coarse_bitfield(G.stream(), C.byref(cfg), G.p(d_bits), G.p(d_coarse)))
+        cfg.coarse_bitfield = d_coarse.data_ptr()
     cm = (C.c_float * 12)(*cam_m.tolist())
     capi.check(lib.ngp_init_rays(G.stream(), C.byref(cfg), C.byref(cam), cm, spp, 1, G.p(d_bits), G.p(payloads)))
     G.sync()

@@ -117,6 +117,53 @@ def test_render_row_bands_are_bit_identical_to_the_full_frame(pyngp):
     assert np.array_equal(again.view(np.uint32), full.view(np.uint32)), "rendering is deterministic"
 
 
+def test_block_skipping_march_renders_the_identical_image(pyngp):
+    """Testbed.coarse_skip: the inference march crosses empty 8x8x8 blocks of the occupancy grid in one hop (csrc/march_infer.cu
+    coarse_hop); with it and without it every pixel of every render mode is the same bit pattern"""
+    tb, _ = _trained(pyngp)
+    tb.background_color = [0, 0, 0, 1]
+    assert tb.coarse_skip
+    for view, (w, h) in [(3, (400, 240)), (11, (256, 256))]:
+        tb.set_camera_to_training_view(view)
+        for mode in (pyngp.RenderMode.Shade, pyngp.RenderMode.Depth, pyngp.RenderMode.Cost):
+            tb.rendering_buffer.render_mode = mode
+            tb.coarse_skip = True
+            fast = np.array(tb.render(w, h, 1, False))
+            tb.coarse_skip = False
+            plain = np.array(tb.render(w, h, 1, False))
+            tb.coarse_skip = True
+            assert np.array_equal(fast.view(np.uint32), plain.view(np.uint32)), (view, mode)
+    tb.rendering_buffer.render_mode = pyngp.RenderMode.Shade
+
+
+def test_device_driven_render_loop_gives_the_identical_image(pyngp):
+    """rendering_buffer.device_loop: the rounds of Testbed::render_frame (testbed.cu:521-575) decided by a kernel instead of the host,
+    with late rounds taking more steps (TAIL_STEPS).  Against the host loop with the reference's schedule: same bits in every
+    pixel, all render modes (Cost shows the per-ray step counter the rounds hand on), far fewer host synchronisations."""
+    tb, _ = _trained(pyngp)
+    tb.background_color = [0, 0, 0, 1]
+    rb = tb.rendering_buffer
+    assert rb.device_loop
+    tb.set_camera_to_training_view(5)
+    w, h = 384, 216
+    for mode in (pyngp.RenderMode.Shade, pyngp.RenderMode.Normals, pyngp.RenderMode.Depth, pyngp.RenderMode.Cost):
+        rb.render_mode = mode
+        rb.device_loop = False
+        want = np.array(tb.render(w, h, 1, False))
+        host_rounds, host_syncs = rb.rounds_last_frame, rb.readbacks_last_frame
+        for tail, per_batch in ((32, 8), (8, 3), (64, 1)):
+            rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK = True, tail, per_batch
+            got = np.array(tb.render(w, h, 1, False))
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (mode, tail, per_batch)
+            if (tail, per_batch) == (32, 8):
+                assert rb.readbacks_last_frame * 3 < host_syncs, (rb.readbacks_last_frame, host_syncs)
+            if tail == 8:
+                assert rb.rounds_last_frame >= host_rounds          # the reference's schedule, plus the empty rounds of the last batch
+    rb.render_mode = pyngp.RenderMode.Shade
+    rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK = True, 32, 8
+    assert want[..., 3].max() > 0.5
+
+
 def test_render_modes_and_tonemap_curves(pyngp):
     tb, _ = _trained(pyngp)
     tb.set_camera_to_training_view(0)
