@@ -46,8 +46,11 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 		rb.rounds_last_frame = rb.readbacks_last_frame = 0;
 		const uint32_t per_batch = std::max(rb.ROUNDS_PER_READBACK, 1u);
 		while (bound > 0) {
-			// samples of a round: n_alive * clamp(n_pixels / n_alive, MIN, MAX) <= max(n_pixels, bound * MIN); the tail rule stays below a quarter of the frame
-			const uint32_t sample_bound = next_multiple(std::max(n_pixels, bound * rb.MIN_STEPS_INBETWEEN_COMPACTION), BATCH_SIZE_MULTIPLE);
+			// samples of a round: n_alive * clamp(n_pixels / n_alive, MIN, MAX) <= max(min(n_pixels, bound * MAX), bound * MIN); the tail
+			// rule stays below a quarter of the frame
+			const uint64_t by_rule = std::max<uint64_t>(std::min<uint64_t>(n_pixels, (uint64_t)bound * rb.MAX_STEPS_INBETWEEN_COMPACTION), (uint64_t)bound * rb.MIN_STEPS_INBETWEEN_COMPACTION);
+			const uint64_t by_tail = tail_steps > rb.MAX_STEPS_INBETWEEN_COMPACTION ? std::min<uint64_t>(n_pixels / 4, (uint64_t)bound * tail_steps) : 0;
+			const uint32_t sample_bound = next_multiple((uint32_t)std::max<uint64_t>(std::max(by_rule, by_tail), 1), BATCH_SIZE_MULTIPLE);
 			rb.coords.enlarge(sample_bound);
 			rb.rgbsigma.enlarge((size_t)sample_bound * padded_output_width);
 			for (uint32_t k = 0; k < per_batch; ++k, ++round) {
