@@ -43,10 +43,12 @@ NGPNetwork::NGPNetwork(Json& config) {
 
 void NGPNetwork::ensure_workspace(uint32_t n) { m_workspace.enlarge(ngp_network_workspace_bytes(n)); }
 
-void NGPNetwork::inference_mixed_precision(cudaStream_t stream, const Coordinate* input, uint32_t n, const uint32_t* d_n_valid, precision_t* output, bool use_inference_matrices) {
-	ensure_workspace(n);
+void NGPNetwork::inference_mixed_precision(cudaStream_t stream, const Coordinate* input, uint32_t n, const uint32_t* d_n_valid, precision_t* output, bool use_inference_matrices,
+                                           DeviceBuffer<uint8_t>* workspace) {
+	DeviceBuffer<uint8_t>& ws = workspace ? *workspace : m_workspace;
+	ws.enlarge(ngp_network_workspace_bytes(n));
 	api_check(ngp_network_inference(stream, (const float*)input, n, d_n_valid, use_inference_matrices ? m_inference_params : m_params, &m_grid, output,
-	                                m_workspace.data(), m_workspace.get_bytes()));
+	                                ws.data(), ws.get_bytes()));
 }
 
 void NGPNetwork::density(cudaStream_t stream, const float* positions, uint32_t stride, uint32_t n, precision_t* output, bool use_inference_matrices) {

@@ -15,7 +15,7 @@ public:
 	void set_params(precision_t* params, precision_t* inference_params, precision_t* gradients) { m_params = params; m_inference_params = inference_params; m_gradients = gradients; }
 
 	// ngp_network.h:217-284.  input: Coordinate[n]; output: [n][4] fp16.  d_n_valid (optional) = device-side element count.
-	void inference_mixed_precision(cudaStream_t stream, const Coordinate* input, uint32_t n, const uint32_t* d_n_valid, precision_t* output, bool use_inference_matrices = true);
+	void inference_mixed_precision(cudaStream_t stream, const Coordinate* input, uint32_t n, const uint32_t* d_n_valid, precision_t* output, bool use_inference_matrices = true, DeviceBuffer<uint8_t>* workspace = nullptr);   // workspace: the caller's own scratch (concurrent calls on several streams); default: the network's
 	// ngp_network.h:286-307.  input: positions with the given float stride; output [n][16] fp16
 	void density(cudaStream_t stream, const float* positions, uint32_t stride, uint32_t n, precision_t* output, bool use_inference_matrices = true);
 	// tiny-cuda-nn/object.h:126-150 as Testbed calls it (testbed.cu:558-560): d output[dim] / d input written over the inputs, with

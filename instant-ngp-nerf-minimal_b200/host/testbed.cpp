@@ -33,6 +33,11 @@ Testbed::Testbed() {
 	NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_stream, cudaStreamNonBlocking, prio_hi));
 	for (auto& e : m_ev) NGP_CUDA_CHECK(cudaEventCreate(&e));
 	NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_march_stream, cudaStreamNonBlocking, prio_lo));
+	for (int b = 0; b < 2; ++b) {
+		NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_band_stream[b], cudaStreamNonBlocking, prio_hi));
+		NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_band_done[b], cudaEventDisableTiming));
+	}
+	NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_frame_cleared, cudaEventDisableTiming));
 	NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_march_go, cudaEventDisableTiming));
 	for (int k = 0; k < 2; ++k) {
 		NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_march_ready[k], cudaEventDisableTiming));
@@ -57,6 +62,8 @@ Testbed::~Testbed() {
 	for (auto& e : m_ev) if (e) cudaEventDestroy(e);
 	for (cudaEvent_t e : {m_ev_march_go, m_ev_march_ready[0], m_ev_march_ready[1], m_ev_slot_free[0], m_ev_slot_free[1]}) if (e) cudaEventDestroy(e);
 	if (m_march_stream) cudaStreamDestroy(m_march_stream);
+	for (int b = 0; b < 2; ++b) { if (m_band_stream[b]) cudaStreamDestroy(m_band_stream[b]); if (m_ev_band_done[b]) cudaEventDestroy(m_ev_band_done[b]); }
+	if (m_ev_frame_cleared) cudaEventDestroy(m_ev_frame_cleared);
 	if (m_host_counter) cudaFreeHost(m_host_counter);
 	if (m_stream) cudaStreamDestroy(m_stream);
 }

@@ -152,7 +152,14 @@ public:
 		DeviceBuffer<uint32_t> n_alive_counter{64};
 		DeviceBuffer<Coordinate> coords;
 		DeviceBuffer<precision_t> rgbsigma;
-		DeviceBuffer<uint32_t> round_ctl{NGP_RENDER_CTL_WORDS};
+		// device-driven loop: the frame is marched as up to two row bands on two streams at once (one band's march and compositing
+		// run under the other band's network kernels); every band owns its ray lists, sample buffers, counters and network scratch
+		struct Band {
+			RaysSoA rays[2]; RaysSoA rays_hit;
+			DeviceBuffer<uint32_t> n_hit_counter{1}, round_ctl{NGP_RENDER_CTL_WORDS};
+			DeviceBuffer<Coordinate> coords; DeviceBuffer<precision_t> rgbsigma; DeviceBuffer<uint8_t> workspace;
+		} band[2];
+		uint32_t CONCURRENT_BANDS = 2;
 		uint32_t MIN_STEPS_INBETWEEN_COMPACTION = 1;
 		uint32_t MAX_STEPS_INBETWEEN_COMPACTION = 8;
 		// Not in the reference: how the rounds are scheduled (the image does not depend on it).
@@ -170,6 +177,8 @@ public:
 private:
 	std::chrono::steady_clock::time_point m_enqueue_start;
 	cudaStream_t m_march_stream = nullptr;
+	cudaStream_t m_band_stream[2] = {nullptr, nullptr};
+	cudaEvent_t m_ev_frame_cleared = nullptr, m_ev_band_done[2] = {nullptr, nullptr};
 	cudaEvent_t m_ev_march_go = nullptr, m_ev_march_ready[2] = {nullptr, nullptr}, m_ev_slot_free[2] = {nullptr, nullptr};
 	void march_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_rays_per_batch, uint32_t n_rays_total, default_rng_t rng, uint32_t* counters, cudaStream_t stream);
 	void learn_step(uint32_t slot, uint32_t target_batch_size, uint32_t n_rays_per_batch, default_rng_t rng, uint32_t* counters, uint32_t* compacted_counter, float* loss,

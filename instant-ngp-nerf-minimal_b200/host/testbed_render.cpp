@@ -18,64 +18,112 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 	const ERenderMode render_mode = rb.render_mode;
 	const uint32_t padded_output_width = m_network->padded_output_width();
 
+	render_buffer.set_rows(row_begin, row_end);
+	render_buffer.clear_frame_buffer(m_stream);
+	(void)n_frame_pixels;
+
+	if (rb.device_loop) {
+		// Rounds are decided on the device (ngp_render_round): compaction, the step-count decision, march, network and compositing of
+		// ROUNDS_PER_READBACK rounds are enqueued back to back, then the live-ray count comes back once.  Rounds enqueued after the
+		// last ray died find a zero count and do nothing.  The launch bounds shrink with every read-back.
+		// The rows are split into up to two bands that are marched CONCURRENTLY on two streams: the march and the compositing of a
+		// round are latency bound and leave most of an SM idle, the network kernels in between are throughput bound, so one band's
+		// march runs under the other band's encoder.  (Measured: 15.4 -> 14.9 ms per 1080p frame -- less than the idle slots
+		// suggest: the march waits on the same L1TEX path the encoder saturates.  Staggering the bands by one march made no difference.)  A band is bit-identical to the same rows of a single-pass frame (the ray, its
+		// jitter seed and its scatter target use the global pixel index; the grouping of a ray's samples into rounds does not matter).
+		const uint32_t tail_steps = std::min<uint32_t>(std::max(rb.TAIL_STEPS, rb.MAX_STEPS_INBETWEEN_COMPACTION), 64u);
+		const uint32_t per_batch = std::max(rb.ROUNDS_PER_READBACK, 1u);
+		const int n_rows = row_end - row_begin;
+		// (Normals needs the network's training scratch, which exists once: one band)
+		const int n_bands = (rb.CONCURRENT_BANDS >= 2 && n_rows >= 2 && render_mode != ERenderMode::Normals) ? 2 : 1;
+		struct BandRun { int r0, r1; uint32_t n_pixels, bound, round; cudaStream_t stream; };
+		BandRun run[2];
+		if (n_bands > 1) NGP_CUDA_CHECK(cudaEventRecord(m_ev_frame_cleared, m_stream));
+		for (int b = 0; b < n_bands; ++b) {
+			BandRun& u = run[b];
+			auto& bd = rb.band[b];
+			u.r0 = row_begin + (int)((int64_t)n_rows * b / n_bands); u.r1 = row_begin + (int)((int64_t)n_rows * (b + 1) / n_bands);
+			u.n_pixels = (uint32_t)(resolution[0] * (u.r1 - u.r0)); u.bound = u.n_pixels; u.round = 0;
+			u.stream = n_bands > 1 ? m_band_stream[b] : m_stream;
+			if (n_bands > 1) NGP_CUDA_CHECK(cudaStreamWaitEvent(u.stream, m_ev_frame_cleared, 0));
+			const uint32_t n_elements = next_multiple(std::max(u.n_pixels, 1u), BATCH_SIZE_MULTIPLE);
+			bd.rays[0].enlarge(n_elements); bd.rays[1].enlarge(n_elements); bd.rays_hit.enlarge(n_elements);
+			m_sampler->generate_rays_from_camera_matrix(resolution, focal_length, rb.principal_point, camera_matrix, render_buffer.spp(), bd.rays[0].payload, u.stream,
+			                                            u.r0, u.r1, m_train_envmap ? m_envmap.params_inference() : nullptr, m_envmap.resolution,
+			                                            m_train_envmap ? render_buffer.frame_buffer() : nullptr);      // testbed.cu:506-512
+			NGP_CUDA_CHECK(cudaMemsetAsync(bd.rays[0].rgba.data(), 0, (size_t)std::max(u.n_pixels, 1u) * 4 * sizeof(float), u.stream));
+			NGP_CUDA_CHECK(cudaMemsetAsync(bd.n_hit_counter.data(), 0, sizeof(uint32_t), u.stream));
+			NGP_CUDA_CHECK(cudaMemsetAsync(bd.round_ctl.data(), 0, sizeof(uint32_t) * NGP_RENDER_CTL_WORDS, u.stream));
+		}
+		rb.rounds_last_frame = rb.readbacks_last_frame = 0;
+		while (true) {
+			bool any = false;
+			for (int b = 0; b < n_bands; ++b) {
+				BandRun& u = run[b];
+				if (u.bound == 0) continue;
+				any = true;
+				auto& bd = rb.band[b];
+				uint32_t* ctl = bd.round_ctl.data();
+				// samples of a round: n_alive * clamp(n_pixels / n_alive, MIN, MAX) <= max(min(n_pixels, bound * MAX), bound * MIN); the tail
+				// rule stays below a quarter of the band
+				const uint64_t by_rule = std::max<uint64_t>(std::min<uint64_t>(u.n_pixels, (uint64_t)u.bound * rb.MAX_STEPS_INBETWEEN_COMPACTION), (uint64_t)u.bound * rb.MIN_STEPS_INBETWEEN_COMPACTION);
+				const uint64_t by_tail = tail_steps > rb.MAX_STEPS_INBETWEEN_COMPACTION ? std::min<uint64_t>(u.n_pixels / 4, (uint64_t)u.bound * tail_steps) : 0;
+				const uint32_t sample_bound = next_multiple((uint32_t)std::max<uint64_t>(std::max(by_rule, by_tail), 1), BATCH_SIZE_MULTIPLE);
+				bd.coords.enlarge(sample_bound);
+				bd.rgbsigma.enlarge((size_t)sample_bound * padded_output_width);
+				for (uint32_t k = 0; k < per_batch; ++k, ++u.round) {
+					const uint32_t round = u.round;
+					RaysSoA& rays_previous = bd.rays[round % 2];
+					RaysSoA& rays_current = bd.rays[(round + 1) % 2];
+					api_check(ngp_compact_rays(u.stream, u.bound, round == 0 ? nullptr : ctl + (round & 1), rays_previous.payload.data(), rays_previous.rgba.data(),
+					                           rays_current.payload.data(), rays_current.rgba.data(), bd.rays_hit.payload.data(), bd.rays_hit.rgba.data(),
+					                           ctl + ((round + 1) & 1), bd.n_hit_counter.data()));
+					api_check(ngp_render_round(u.stream, ctl, round, u.n_pixels, rb.MIN_STEPS_INBETWEEN_COMPACTION, rb.MAX_STEPS_INBETWEEN_COMPACTION, tail_steps, MARCH_ITER));
+					m_sampler->generate_coords_from_rays_dev(u.bound, ctl, round, rays_current.payload, bd.coords, u.stream);
+					// rendering uses the EMA weights (use_inference_matrices = true, testbed.cu:556)
+					m_network->inference_mixed_precision(u.stream, bd.coords.data(), sample_bound, ctl + 3, bd.rgbsigma.data(), true, n_bands > 1 ? &bd.workspace : nullptr);
+					if (render_mode == ERenderMode::Normals) m_network->input_gradient(u.stream, 3, bd.coords.data(), sample_bound, ctl + 3);   // testbed.cu:558-560
+					m_render->volume_rendering_dev(u.bound, ctl, round, rays_current, bd.coords, bd.rgbsigma, padded_output_width, m_density_activation, m_rgb_activation,
+					                               render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix, 1.f / m_scene_scale, u.stream);
+				}
+				// live rays after the batch's last compaction (some may have been finished by its compositing: the next compaction sorts
+				// that out), still an upper bound for everything that follows
+				NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 8 * b, ctl + (u.round & 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, u.stream));
+				NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 8 * b + 1, ctl + 4, sizeof(uint32_t), cudaMemcpyDeviceToHost, u.stream));
+			}
+			if (!any) break;
+			++rb.readbacks_last_frame;
+			for (int b = 0; b < n_bands; ++b) {
+				BandRun& u = run[b];
+				if (u.bound == 0) continue;
+				NGP_CUDA_CHECK(cudaStreamSynchronize(u.stream));
+				u.bound = m_host_counter[8 * b + 1] >= MARCH_ITER ? 0 : m_host_counter[8 * b];
+			}
+		}
+		for (int b = 0; b < n_bands; ++b) {
+			auto& bd = rb.band[b];
+			rb.rounds_last_frame = std::max(rb.rounds_last_frame, run[b].round);
+			// the hit count stays on the device: no read-back before the shade
+			api_check(ngp_shade(run[b].stream, std::max(run[b].n_pixels, 1u), bd.n_hit_counter.data(), bd.rays_hit.rgba.data(), bd.rays_hit.payload.data(),
+			                    render_buffer.frame_buffer(), (int)render_mode, m_render->train_in_linear_color ? 1 : 0));
+			if (n_bands > 1) {
+				NGP_CUDA_CHECK(cudaEventRecord(m_ev_band_done[b], run[b].stream));
+				NGP_CUDA_CHECK(cudaStreamWaitEvent(m_stream, m_ev_band_done[b], 0));
+			}
+		}
+	} else {
 	{
 		const uint32_t n_elements = next_multiple(std::max(n_pixels, 1u), BATCH_SIZE_MULTIPLE);
 		rb.rays[0].enlarge(n_elements); rb.rays[1].enlarge(n_elements); rb.rays_hit.enlarge(n_elements);
 		rb.coords.enlarge((size_t)n_elements * rb.MAX_STEPS_INBETWEEN_COMPACTION);
 		rb.rgbsigma.enlarge((size_t)n_elements * rb.MAX_STEPS_INBETWEEN_COMPACTION * padded_output_width);
 	}
-
-	render_buffer.set_rows(row_begin, row_end);
-	render_buffer.clear_frame_buffer(m_stream);
-	(void)n_frame_pixels;
 	m_sampler->generate_rays_from_camera_matrix(resolution, focal_length, rb.principal_point, camera_matrix, render_buffer.spp(), rb.rays[0].payload, m_stream,
 	                                            row_begin, row_end, m_train_envmap ? m_envmap.params_inference() : nullptr, m_envmap.resolution,
 	                                            m_train_envmap ? render_buffer.frame_buffer() : nullptr);      // testbed.cu:506-512
 	NGP_CUDA_CHECK(cudaMemsetAsync(rb.rays[0].rgba.data(), 0, (size_t)std::max(n_pixels, 1u) * 4 * sizeof(float), m_stream));
 	NGP_CUDA_CHECK(cudaMemsetAsync(rb.n_hit_counter.data(), 0, sizeof(uint32_t), m_stream));
 
-	if (rb.device_loop) {
-		// Rounds are decided on the device (ngp_render_round): compaction, the step-count decision, march, network and compositing of
-		// ROUNDS_PER_READBACK rounds are enqueued back to back, then the live-ray count comes back once.  Rounds enqueued after the
-		// last ray died find a zero count and do nothing.  The launch bounds shrink with every read-back.
-		const uint32_t tail_steps = std::min<uint32_t>(std::max(rb.TAIL_STEPS, rb.MAX_STEPS_INBETWEEN_COMPACTION), 64u);
-		rb.coords.enlarge((size_t)next_multiple(std::max(n_pixels, 1u), BATCH_SIZE_MULTIPLE) * std::max(rb.MAX_STEPS_INBETWEEN_COMPACTION, 1u));
-		uint32_t* ctl = rb.round_ctl.data();
-		NGP_CUDA_CHECK(cudaMemsetAsync(ctl, 0, sizeof(uint32_t) * NGP_RENDER_CTL_WORDS, m_stream));
-		uint32_t bound = n_pixels, round = 0;
-		rb.rounds_last_frame = rb.readbacks_last_frame = 0;
-		const uint32_t per_batch = std::max(rb.ROUNDS_PER_READBACK, 1u);
-		while (bound > 0) {
-			// samples of a round: n_alive * clamp(n_pixels / n_alive, MIN, MAX) <= max(min(n_pixels, bound * MAX), bound * MIN); the tail
-			// rule stays below a quarter of the frame
-			const uint64_t by_rule = std::max<uint64_t>(std::min<uint64_t>(n_pixels, (uint64_t)bound * rb.MAX_STEPS_INBETWEEN_COMPACTION), (uint64_t)bound * rb.MIN_STEPS_INBETWEEN_COMPACTION);
-			const uint64_t by_tail = tail_steps > rb.MAX_STEPS_INBETWEEN_COMPACTION ? std::min<uint64_t>(n_pixels / 4, (uint64_t)bound * tail_steps) : 0;
-			const uint32_t sample_bound = next_multiple((uint32_t)std::max<uint64_t>(std::max(by_rule, by_tail), 1), BATCH_SIZE_MULTIPLE);
-			rb.coords.enlarge(sample_bound);
-			rb.rgbsigma.enlarge((size_t)sample_bound * padded_output_width);
-			for (uint32_t k = 0; k < per_batch; ++k, ++round) {
-				RaysSoA& rays_previous = rb.rays[round % 2];
-				RaysSoA& rays_current = rb.rays[(round + 1) % 2];
-				api_check(ngp_compact_rays(m_stream, bound, round == 0 ? nullptr : ctl + (round & 1), rays_previous.payload.data(), rays_previous.rgba.data(),
-				                           rays_current.payload.data(), rays_current.rgba.data(), rb.rays_hit.payload.data(), rb.rays_hit.rgba.data(),
-				                           ctl + ((round + 1) & 1), rb.n_hit_counter.data()));
-				api_check(ngp_render_round(m_stream, ctl, round, n_pixels, rb.MIN_STEPS_INBETWEEN_COMPACTION, rb.MAX_STEPS_INBETWEEN_COMPACTION, tail_steps, MARCH_ITER));
-				m_sampler->generate_coords_from_rays_dev(bound, ctl, round, rays_current.payload, rb.coords, m_stream);
-				m_network->inference_mixed_precision(m_stream, rb.coords.data(), sample_bound, ctl + 3, rb.rgbsigma.data(), true);
-				if (render_mode == ERenderMode::Normals) m_network->input_gradient(m_stream, 3, rb.coords.data(), sample_bound, ctl + 3);   // testbed.cu:558-560
-				m_render->volume_rendering_dev(bound, ctl, round, rays_current, rb.coords, rb.rgbsigma, padded_output_width, m_density_activation, m_rgb_activation,
-				                               render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix, 1.f / m_scene_scale, m_stream);
-			}
-			// live rays after the batch's last compaction (some of them may have been finished by its compositing: the next
-			// compaction sorts that out), still an upper bound for everything that follows
-			NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter, ctl + (round & 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
-			NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 2, ctl + 4, sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
-			NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
-			++rb.readbacks_last_frame;
-			bound = m_host_counter[2] >= MARCH_ITER ? 0 : m_host_counter[0];
-		}
-		rb.rounds_last_frame = round;
-	} else {
 	uint32_t i_steps_offset = 1;
 	uint32_t double_buffer_index = 0;
 	uint32_t n_alive = n_pixels;
@@ -105,13 +153,13 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 		                           1.f / m_scene_scale, m_stream);
 		i_steps_offset += n_steps;
 	}
-	}
 
 	NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 1, rb.n_hit_counter.data(), sizeof(uint32_t), cudaMemcpyDeviceToHost, m_stream));
 	NGP_CUDA_CHECK(cudaStreamSynchronize(m_stream));
 	const uint32_t n_hit = m_host_counter[1];
 	api_check(ngp_shade(m_stream, n_hit, nullptr, rb.rays_hit.rgba.data(), rb.rays_hit.payload.data(), render_buffer.frame_buffer(), (int)render_mode,
 	                    m_render->train_in_linear_color ? 1 : 0));
+	}
 
 	render_buffer.set_color_space(m_color_space);
 	render_buffer.set_tonemap_curve(rb.tonemap_curve);

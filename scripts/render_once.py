@@ -27,6 +27,8 @@ def main():
     tb.load_snapshot(snap)
     tb.set_camera_to_training_view(3)
     tb.background_color = [0, 0, 0, 1]
+    if os.environ.get("NGP_BANDS"):
+        tb.rendering_buffer.CONCURRENT_BANDS = int(os.environ["NGP_BANDS"])
     for _ in range(frames):
         t0 = time.perf_counter()
         ms = tb.render_frames_ms(w, h, 1, True)

@@ -151,16 +151,16 @@ def test_device_driven_render_loop_gives_the_identical_image(pyngp):
         rb.device_loop = False
         want = np.array(tb.render(w, h, 1, False))
         host_rounds, host_syncs = rb.rounds_last_frame, rb.readbacks_last_frame
-        for tail, per_batch in ((32, 8), (8, 3), (64, 1)):
-            rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK = True, tail, per_batch
+        for tail, per_batch, bands in ((32, 8, 2), (32, 8, 1), (8, 3, 1), (64, 1, 2)):
+            rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS = True, tail, per_batch, bands
             got = np.array(tb.render(w, h, 1, False))
-            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (mode, tail, per_batch)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (mode, tail, per_batch, bands)
             if (tail, per_batch) == (32, 8):
                 assert rb.readbacks_last_frame * 3 < host_syncs, (rb.readbacks_last_frame, host_syncs)
             if tail == 8:
                 assert rb.rounds_last_frame >= host_rounds          # the reference's schedule, plus the empty rounds of the last batch
     rb.render_mode = pyngp.RenderMode.Shade
-    rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK = True, 32, 8
+    rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS = True, 32, 8, 2
     assert want[..., 3].max() > 0.5
 
 
