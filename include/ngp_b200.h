@@ -239,10 +239,14 @@ int ngp_composite_infer(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays
  *           be given d_ctl + ((r + 1) & 1) as its live-ray counter),  [2] steps of the round,  [3] samples of the round
  *           (d_n_valid of ngp_network_inference),  [4] i_steps_offset.
  * Call order per round r: ngp_compact_rays, ngp_render_round, ngp_generate_coords_from_rays_dev, ngp_network_inference,
- * ngp_composite_infer_dev.  tail_steps > max_steps lets late rounds (batch below a quarter of the frame) take up to tail_steps
- * steps: fewer, fuller rounds; a ray's samples and their compositing order -- the image -- do not depend on the grouping. */
+ * ngp_composite_infer_dev.  The step count is clamp(max(n_pixels, min_batch) / n_alive, min_steps, max_steps) -- min_batch = 0 is
+ * the reference's rule; a positive value keeps small frames and row bands from taking one step per round --, and tail_steps >
+ * max_steps lets late rounds (batch below a quarter of that) take up to tail_steps steps: fewer, fuller rounds.  A ray's samples
+ * and their compositing order -- the image -- do not depend on the grouping.  Samples per round <= max(min(max(n_pixels, min_batch),
+ * bound * max_steps), bound * min_steps, min(max(n_pixels, min_batch) / 4, bound * tail_steps)) for a live-ray bound `bound`. */
 #define NGP_RENDER_CTL_WORDS 8
-int ngp_render_round(void* stream, uint32_t* d_ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter);
+int ngp_render_round(void* stream, uint32_t* d_ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter,
+                     uint32_t min_batch);
 int ngp_generate_coords_from_rays_dev(void* stream, const ngp_sampler_cfg* cfg, uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round,
                                       const uint8_t* d_bitfield, void* d_payloads, float* d_coords);
 int ngp_composite_infer_dev(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round,

@@ -91,17 +91,20 @@ __global__ void __launch_bounds__(256) compact_rays_kernel(
 // re-arms the counter the next compaction will fill.
 //   ctl[0], ctl[1]: live rays, ping-pong (round r's compaction reads [r & 1] -- round 0 the pixel count -- and fills [(r + 1) & 1])
 //   ctl[2] n_steps of this round, ctl[3] samples of this round, ctl[4] i_steps_offset (1 + samples per live ray so far)
-__global__ void render_round_kernel(uint32_t* __restrict__ ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter) {
+__global__ void render_round_kernel(uint32_t* __restrict__ ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter,
+                                    uint32_t min_batch) {
 	uint32_t offset = round == 0 ? 1u : ctl[4] + ctl[2];             // the previous round composited ctl[2] samples per live ray
 	uint32_t n_alive = ctl[(round + 1) & 1];
 	if (offset >= march_iter) n_alive = 0;                           // `while (n_alive > 0 && i_steps_offset < MARCH_ITER)`
 	uint32_t n_steps = 0;
 	if (n_alive) {
-		n_steps = min(max(n_pixels / n_alive, min_steps), max_steps);
-		// Our own extension of the schedule, not of the result (a ray's samples and their compositing order do not depend on how
-		// they are grouped into rounds): once the batch has shrunk below a quarter of the frame, rounds are latency bound, so more
-		// steps are taken per round and fewer rounds are needed.
-		if (tail_steps > n_steps) n_steps = max(n_steps, min(tail_steps, n_pixels / (4u * n_alive)));
+		// Our own extensions of the schedule, not of the result (a ray's samples and their compositing order do not depend on how
+		// they are grouped into rounds).  (1) The reference aims at one sample per PIXEL and round, which starves small frames and
+		// row bands (a 135-row band of a 1080p frame took 72 one-step rounds): the batch it aims at is at least min_batch samples.
+		// (2) Once the batch has shrunk below a quarter of that, rounds are latency bound, so more steps are taken per round.
+		const uint32_t batch = max(n_pixels, min_batch);
+		n_steps = min(max(batch / n_alive, min_steps), max_steps);
+		if (tail_steps > n_steps) n_steps = max(n_steps, min(tail_steps, batch / (4u * n_alive)));
 	}
 	ctl[(round + 1) & 1] = n_alive;
 	ctl[round & 1] = 0;
@@ -203,10 +206,11 @@ extern "C" int ngp_composite_infer_dev(void* stream, const ngp_render_cfg* cfg, 
 	                            render_mode, aabb_min, aabb_max, camera_fwd_host, depth_scale);
 }
 
-extern "C" int ngp_render_round(void* stream, uint32_t* d_ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter) {
+extern "C" int ngp_render_round(void* stream, uint32_t* d_ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter,
+                                uint32_t min_batch) {
 	NGP_REQUIRE(d_ctl, "null pointer");
 	NGP_REQUIRE(min_steps >= 1 && max_steps >= min_steps, "bad step limits");
-	NGP_LAUNCH("render_round_kernel", (cudaStream_t)stream, render_round_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(d_ctl, round, n_pixels, min_steps, max_steps, tail_steps, march_iter));
+	NGP_LAUNCH("render_round_kernel", (cudaStream_t)stream, render_round_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(d_ctl, round, n_pixels, min_steps, max_steps, tail_steps, march_iter, min_batch));
 	return check_launch("render_round");
 }
 

@@ -193,6 +193,8 @@ PYBIND11_MODULE(pyngp, m) {
 			[](Testbed::RenderingBuffer& r, const py::object& v) { to_vec(v, r.principal_point, 2, "principal_point"); })
 		.def_readwrite("device_loop", &Testbed::RenderingBuffer::device_loop, "render rounds decided on the device, the live-ray count read back every ROUNDS_PER_READBACK rounds (default on; off: one host synchronisation per round like the reference)")
 		.def_readwrite("CONCURRENT_BANDS", &Testbed::RenderingBuffer::CONCURRENT_BANDS, "device loop: 2 = march the frame as two row bands on two streams at once (default), 1 = one pass")
+		.def_readwrite("CONCURRENT_BANDS_MIN_PIXELS", &Testbed::RenderingBuffer::CONCURRENT_BANDS_MIN_PIXELS)
+		.def_readwrite("MIN_BATCH_SAMPLES", &Testbed::RenderingBuffer::MIN_BATCH_SAMPLES, "device loop: a round's step count aims at max(pixels, this) samples (0 = the reference's rule)")
 		.def_readwrite("ROUNDS_PER_READBACK", &Testbed::RenderingBuffer::ROUNDS_PER_READBACK)
 		.def_readwrite("TAIL_STEPS", &Testbed::RenderingBuffer::TAIL_STEPS, "late rounds (batch below a quarter of the frame) take up to this many steps; <= MAX_STEPS_INBETWEEN_COMPACTION switches it off")
 		.def_readonly("rounds_last_frame", &Testbed::RenderingBuffer::rounds_last_frame)

@@ -159,12 +159,14 @@ public:
 			DeviceBuffer<uint32_t> n_hit_counter{1}, round_ctl{NGP_RENDER_CTL_WORDS};
 			DeviceBuffer<Coordinate> coords; DeviceBuffer<precision_t> rgbsigma; DeviceBuffer<uint8_t> workspace;
 		} band[2];
-		uint32_t CONCURRENT_BANDS = 2;
+		uint32_t CONCURRENT_BANDS = 2;         // ... when the frame (or band) has at least CONCURRENT_BANDS_MIN_PIXELS pixels: below that the rounds are latency bound and two streams only add launches
+		uint32_t CONCURRENT_BANDS_MIN_PIXELS = 1u << 20;
 		uint32_t MIN_STEPS_INBETWEEN_COMPACTION = 1;
 		uint32_t MAX_STEPS_INBETWEEN_COMPACTION = 8;
 		// Not in the reference: how the rounds are scheduled (the image does not depend on it).
 		bool device_loop = true;              // rounds decided on the device, live-ray count read back every ROUNDS_PER_READBACK rounds (false: testbed.cu's loop, one sync per round)
 		uint32_t ROUNDS_PER_READBACK = 8;
+		uint32_t MIN_BATCH_SAMPLES = 1u << 21; // the step count of a round aims at max(pixels, this) samples (0: the reference's rule, one sample per pixel)
 		uint32_t TAIL_STEPS = 32;             // late rounds (batch below a quarter of the frame) take up to this many steps (<= MAX...: off)
 		uint32_t rounds_last_frame = 0, readbacks_last_frame = 0;
 	} m_rendering_buffer;

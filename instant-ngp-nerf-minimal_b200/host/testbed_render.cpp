@@ -35,7 +35,7 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 		const uint32_t per_batch = std::max(rb.ROUNDS_PER_READBACK, 1u);
 		const int n_rows = row_end - row_begin;
 		// (Normals needs the network's training scratch, which exists once: one band)
-		const int n_bands = (rb.CONCURRENT_BANDS >= 2 && n_rows >= 2 && render_mode != ERenderMode::Normals) ? 2 : 1;
+		const int n_bands = (rb.CONCURRENT_BANDS >= 2 && n_rows >= 2 && n_pixels >= rb.CONCURRENT_BANDS_MIN_PIXELS && render_mode != ERenderMode::Normals) ? 2 : 1;
 		struct BandRun { int r0, r1; uint32_t n_pixels, bound, round; cudaStream_t stream; };
 		BandRun run[2];
 		if (n_bands > 1) NGP_CUDA_CHECK(cudaEventRecord(m_ev_frame_cleared, m_stream));
@@ -66,8 +66,9 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 				uint32_t* ctl = bd.round_ctl.data();
 				// samples of a round: n_alive * clamp(n_pixels / n_alive, MIN, MAX) <= max(min(n_pixels, bound * MAX), bound * MIN); the tail
 				// rule stays below a quarter of the band
-				const uint64_t by_rule = std::max<uint64_t>(std::min<uint64_t>(u.n_pixels, (uint64_t)u.bound * rb.MAX_STEPS_INBETWEEN_COMPACTION), (uint64_t)u.bound * rb.MIN_STEPS_INBETWEEN_COMPACTION);
-				const uint64_t by_tail = tail_steps > rb.MAX_STEPS_INBETWEEN_COMPACTION ? std::min<uint64_t>(u.n_pixels / 4, (uint64_t)u.bound * tail_steps) : 0;
+				const uint64_t batch = std::max(u.n_pixels, rb.MIN_BATCH_SAMPLES);
+				const uint64_t by_rule = std::max<uint64_t>(std::min<uint64_t>(batch, (uint64_t)u.bound * rb.MAX_STEPS_INBETWEEN_COMPACTION), (uint64_t)u.bound * rb.MIN_STEPS_INBETWEEN_COMPACTION);
+				const uint64_t by_tail = tail_steps > rb.MAX_STEPS_INBETWEEN_COMPACTION ? std::min<uint64_t>(batch / 4, (uint64_t)u.bound * tail_steps) : 0;
 				const uint32_t sample_bound = next_multiple((uint32_t)std::max<uint64_t>(std::max(by_rule, by_tail), 1), BATCH_SIZE_MULTIPLE);
 				bd.coords.enlarge(sample_bound);
 				bd.rgbsigma.enlarge((size_t)sample_bound * padded_output_width);
@@ -78,7 +79,7 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 					api_check(ngp_compact_rays(u.stream, u.bound, round == 0 ? nullptr : ctl + (round & 1), rays_previous.payload.data(), rays_previous.rgba.data(),
 					                           rays_current.payload.data(), rays_current.rgba.data(), bd.rays_hit.payload.data(), bd.rays_hit.rgba.data(),
 					                           ctl + ((round + 1) & 1), bd.n_hit_counter.data()));
-					api_check(ngp_render_round(u.stream, ctl, round, u.n_pixels, rb.MIN_STEPS_INBETWEEN_COMPACTION, rb.MAX_STEPS_INBETWEEN_COMPACTION, tail_steps, MARCH_ITER));
+					api_check(ngp_render_round(u.stream, ctl, round, u.n_pixels, rb.MIN_STEPS_INBETWEEN_COMPACTION, rb.MAX_STEPS_INBETWEEN_COMPACTION, tail_steps, MARCH_ITER, rb.MIN_BATCH_SAMPLES));
 					m_sampler->generate_coords_from_rays_dev(u.bound, ctl, round, rays_current.payload, bd.coords, u.stream);
 					// rendering uses the EMA weights (use_inference_matrices = true, testbed.cu:556)
 					m_network->inference_mixed_precision(u.stream, bd.coords.data(), sample_bound, ctl + 3, bd.rgbsigma.data(), true, n_bands > 1 ? &bd.workspace : nullptr);

@@ -29,10 +29,14 @@ def main():
     tb.background_color = [0, 0, 0, 1]
     if os.environ.get("NGP_BANDS"):
         tb.rendering_buffer.CONCURRENT_BANDS = int(os.environ["NGP_BANDS"])
+    if os.environ.get("NGP_ROWS"):
+        r0, r1 = (int(x) for x in os.environ["NGP_ROWS"].split(":"))
+        tb.set_render_rows(r0, r1)
     for _ in range(frames):
         t0 = time.perf_counter()
         ms = tb.render_frames_ms(w, h, 1, True)
-        print(f"{w}x{h}: {ms:.2f} ms ({time.perf_counter() - t0:.4f} s wall)")
+        rb = tb.rendering_buffer
+        print(f"{w}x{h}: {ms:.2f} ms ({time.perf_counter() - t0:.4f} s wall), {rb.rounds_last_frame} rounds, {rb.readbacks_last_frame} read-backs")
 
 
 if __name__ == "__main__":

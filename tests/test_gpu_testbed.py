@@ -144,6 +144,7 @@ def test_device_driven_render_loop_gives_the_identical_image(pyngp):
     tb.background_color = [0, 0, 0, 1]
     rb = tb.rendering_buffer
     assert rb.device_loop
+    rb.CONCURRENT_BANDS_MIN_PIXELS = 0                    # the test frames are small: let the two-stream path run on them
     tb.set_camera_to_training_view(5)
     w, h = 384, 216
     for mode in (pyngp.RenderMode.Shade, pyngp.RenderMode.Normals, pyngp.RenderMode.Depth, pyngp.RenderMode.Cost):
@@ -151,16 +152,17 @@ def test_device_driven_render_loop_gives_the_identical_image(pyngp):
         rb.device_loop = False
         want = np.array(tb.render(w, h, 1, False))
         host_rounds, host_syncs = rb.rounds_last_frame, rb.readbacks_last_frame
-        for tail, per_batch, bands in ((32, 8, 2), (32, 8, 1), (8, 3, 1), (64, 1, 2)):
-            rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS = True, tail, per_batch, bands
+        for tail, per_batch, bands, min_batch in ((32, 8, 2, 1 << 21), (32, 8, 1, 0), (8, 3, 1, 0), (64, 1, 2, 1 << 18)):
+            rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS, rb.MIN_BATCH_SAMPLES = True, tail, per_batch, bands, min_batch
             got = np.array(tb.render(w, h, 1, False))
-            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (mode, tail, per_batch, bands)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (mode, tail, per_batch, bands, min_batch)
             if (tail, per_batch) == (32, 8):
                 assert rb.readbacks_last_frame * 3 < host_syncs, (rb.readbacks_last_frame, host_syncs)
             if tail == 8:
                 assert rb.rounds_last_frame >= host_rounds          # the reference's schedule, plus the empty rounds of the last batch
     rb.render_mode = pyngp.RenderMode.Shade
-    rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS = True, 32, 8, 2
+    rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS, rb.MIN_BATCH_SAMPLES = True, 32, 8, 2, 1 << 21
+    rb.CONCURRENT_BANDS_MIN_PIXELS = 1 << 20
     assert want[..., 3].max() > 0.5
 
 
