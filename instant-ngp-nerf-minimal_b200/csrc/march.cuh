@@ -72,34 +72,6 @@ __device__ __forceinline__ float distance_to_next_voxel(V3 pos, V3 dir, V3 idir,
 	return fmaxf(t / r, 0.0f);
 }
 
-__device__ __forceinline__ float advance_to_next_voxel(float t, const ngp_sampler_cfg& c, V3 pos, V3 dir, V3 idir, uint32_t res) {
-	const float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
-	do { t += calc_dt(t, c); } while (t < t_target);
-	return t;
-}
-
-// The same hop with the closed form of lattice_hop.h when the step is constant (cone_angle 0) and, for a power-of-two grid, the two
-// divisions by the resolution written as exact multiplications.  Bit-identical to advance_to_next_voxel by construction: the
-// closed form either reproduces the loop or declines.
-__device__ __forceinline__ float advance_to_next_voxel_fast(float t, const ngp_sampler_cfg& c, bool const_dt, V3 pos, V3 dir, V3 idir, uint32_t res) {
-	float dist;
-	if ((res & (res - 1u)) == 0u) {
-		const float r = (float)res, ir = 1.0f / r;            // exact: r is a power of two
-		const float px = r * pos.x, py = r * pos.y, pz = r * pos.z;
-		const float tx = (floorf(px + 0.5f + 0.5f * copysignf(1.f, dir.x)) - px) * idir.x;
-		const float ty = (floorf(py + 0.5f + 0.5f * copysignf(1.f, dir.y)) - py) * idir.y;
-		const float tz = (floorf(pz + 0.5f + 0.5f * copysignf(1.f, dir.z)) - pz) * idir.z;
-		dist = fmaxf(fminf(fminf(tx, ty), tz) * ir, 0.0f);
-	} else {
-		dist = distance_to_next_voxel(pos, dir, idir, res);
-	}
-	const float t_target = t + dist;
-	float hopped;
-	if (const_dt && ngp_lattice_hop(t, t_target, c.min_step, &hopped)) return hopped;
-	do { t += calc_dt(t, c); } while (t < t_target);
-	return t;
-}
-
 __device__ __forceinline__ V3 ray_at(V3 o, V3 d, float t) { return {__fmaf_rn(t, d.x, o.x), __fmaf_rn(t, d.y, o.y), __fmaf_rn(t, d.z, o.z)}; }
 
 __device__ __forceinline__ float warp_dt(float dt, const ngp_sampler_cfg& c) {
