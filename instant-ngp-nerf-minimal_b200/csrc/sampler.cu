@@ -33,30 +33,52 @@ __global__ void mark_untrained_grid_kernel(ngp_sampler_cfg c, ngp_camera_cfg cam
 	}
 }
 
+// pcg32 skip-ahead through a table: entry k holds the affine map of 2^k steps (state -> state * mult + plus), so advancing by delta
+// is one 64-bit multiply-add per SET bit of delta instead of the two to four multiplies per bit of Pcg32::advance's square-and-
+// multiply loop (350 of the ~1 200 instructions a refresh sample cost, ncu).  Powers of one affine map commute: the state reached
+// is the same 64-bit integer.
+struct PcgJump { uint64_t mult[32], plus[32]; };
+__device__ __forceinline__ void pcg_jump_table_build(PcgJump& t, uint64_t inc) {      // one thread
+	uint64_t m = 0x5851f42d4c957f2dULL, p = inc;
+	for (int k = 0; k < 32; ++k) { t.mult[k] = m; t.plus[k] = p; p = (m + 1) * p; m *= m; }
+}
+__device__ __forceinline__ void pcg_jump(Pcg32& rng, const PcgJump& t, uint32_t delta) {
+	uint64_t st = rng.state;
+	while (delta) { const int k = __ffs((int)delta) - 1; delta &= delta - 1u; st = st * t.mult[k] + t.plus[k]; }
+	rng.state = st;
+}
+
 // sample i of generate_grid_samples_nerf_nonuniform (occupancy_sampler.cu:63-105): cascade from the first random number, up to 10
-// pseudo-random cells until one is above the threshold, a uniform position inside the cell that was kept
+// pseudo-random cells until one is above the threshold, a uniform position inside the cell that was kept.  jump (optional): the
+// skip-ahead table of rng0's stream; i * 4 must then fit 32 bits.
 __device__ __forceinline__ void grid_sample_one(const ngp_sampler_cfg& c, uint32_t i, uint32_t n, const Pcg32& rng0, uint32_t step, const float* __restrict__ grid_in,
-                                                float thresh, float* __restrict__ pos_out, uint32_t* __restrict__ idx_out) {
+                                                float thresh, float* __restrict__ pos_out, uint32_t* __restrict__ idx_out, const PcgJump* jump = nullptr) {
 	const uint32_t G = c.grid_size, cells = G * G * G;
+	const bool cells_pow2 = (cells & (cells - 1u)) == 0u;
 	Pcg32 rng = rng0;
-	rng.advance((uint64_t)i * 4);
+	if (jump) pcg_jump(rng, *jump, i * 4u); else rng.advance((uint64_t)i * 4);
 	const uint32_t level = (uint32_t)(rng.next_float() * (float)c.n_cascades) % c.n_cascades;
-	uint32_t idx = 0;
+	uint32_t pos_idx = 0;
 	for (uint32_t j = 0; j < 10; ++j) {
-		idx = ((i + step * n) * kCellMul + j * 19349663u + kCellAdd) % cells;
-		idx += level * cells;
-		if (grid_in[idx] > thresh) break;
+		const uint32_t h = (i + step * n) * kCellMul + j * 19349663u + kCellAdd;
+		pos_idx = cells_pow2 ? (h & (cells - 1u)) : (h % cells);
+		if (grid_in[pos_idx + level * cells] > thresh) break;
 	}
-	const uint32_t pos_idx = idx % cells;
+	const uint32_t idx = pos_idx + level * cells;
 	const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
 	const float rx = rng.next_float(), ry = rng.next_float(), rz = rng.next_float();
 	const float s = scalbnf(1.0f, (int)level), g = (float)G, diag = c.aabb_max - c.aabb_min;
-	const float px = (((float)x + rx) / g - 0.5f) * s + 0.5f;
-	const float py = (((float)y + ry) / g - 0.5f) * s + 0.5f;
-	const float pz = (((float)z + rz) / g - 0.5f) * s + 0.5f;
-	pos_out[0] = (px - c.aabb_min) / diag;
-	pos_out[1] = (py - c.aabb_min) / diag;
-	pos_out[2] = (pz - c.aabb_min) / diag;
+	// divisions by powers of two as multiplications by their reciprocals: the same float, bit for bit
+	int e;
+	const bool g_pow2 = (G & (G - 1u)) == 0u, diag_pow2 = frexpf(diag, &e) == 0.5f;
+	const float ig = 1.0f / g, idiag = 1.0f / diag;
+	const float qx = g_pow2 ? ((float)x + rx) * ig : ((float)x + rx) / g;
+	const float qy = g_pow2 ? ((float)y + ry) * ig : ((float)y + ry) / g;
+	const float qz = g_pow2 ? ((float)z + rz) * ig : ((float)z + rz) / g;
+	const float px = (qx - 0.5f) * s + 0.5f, py = (qy - 0.5f) * s + 0.5f, pz = (qz - 0.5f) * s + 0.5f;
+	pos_out[0] = diag_pow2 ? (px - c.aabb_min) * idiag : (px - c.aabb_min) / diag;
+	pos_out[1] = diag_pow2 ? (py - c.aabb_min) * idiag : (py - c.aabb_min) / diag;
+	pos_out[2] = diag_pow2 ? (pz - c.aabb_min) * idiag : (pz - c.aabb_min) / diag;
 	*idx_out = idx;
 }
 
@@ -98,8 +120,11 @@ __global__ void __launch_bounds__(256) generate_grid_samples_sorted_kernel(ngp_s
 	if (m_begin >= cells) return;
 	__shared__ uint32_t warp_tot[8];
 	__shared__ uint64_t fs[2];
+	__shared__ PcgJump jump;
 	// one closed-form prefix per CTA (the 64-bit divisions of floor_sum are slow: two lanes of different warps take one sum each)
 	if (R && (threadIdx.x == 0 || threadIdx.x == 32)) fs[threadIdx.x >> 5] = floor_sum(m_begin, cells, alpha, threadIdx.x ? (uint64_t)beta + cells - R : (uint64_t)beta);
+	if (threadIdx.x == 64) pcg_jump_table_build(jump, rng0.inc);
+	const bool use_jump = n <= (1u << 30);                                              // i * 4 fits 32 bits
 	__syncthreads();
 	uint64_t base = (uint64_t)m_begin * K + (R ? m_begin + fs[0] - fs[1] : 0);
 	for (uint32_t m0 = m_begin; m0 < m_end; m0 += 256) {
@@ -116,7 +141,7 @@ __global__ void __launch_bounds__(256) generate_grid_samples_sorted_kernel(ngp_s
 		for (uint32_t w = 0; w < 8; ++w) { const uint32_t v = warp_tot[w]; total += v; if (w < (threadIdx.x >> 5)) before += v; }
 		const uint64_t slot0 = base + before + incl - cnt;
 		for (uint32_t r = 0; r < cnt; ++r)
-			grid_sample_one(c, i0 + r * cells, n, rng0, step, grid_in, thresh, out_pos + (slot0 + r) * 3, out_idx + slot0 + r);
+			grid_sample_one(c, i0 + r * cells, n, rng0, step, grid_in, thresh, out_pos + (slot0 + r) * 3, out_idx + slot0 + r, use_jump ? &jump : nullptr);
 		base += total;
 	}
 }
