@@ -252,6 +252,13 @@ int ngp_generate_coords_from_rays_dev(void* stream, const ngp_sampler_cfg* cfg, 
 int ngp_composite_infer_dev(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round,
                             void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
                             float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale);
+/* ngp_composite_infer_dev followed by the compaction of the NEXT round in the same launch: after its compositing a live ray moves to
+ * d_next_*, a finished one with alpha > 0.001 to the hit list, and the live count of round + 1 accumulates in d_ctl[round & 1] (the
+ * counter ngp_render_round(round) has cleared) -- so only round 0 of a frame needs ngp_compact_rays. */
+int ngp_composite_infer_compact_dev(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays_bound, uint32_t* d_ctl, uint32_t round,
+                                    void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
+                                    float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale,
+                                    void* d_next_payloads, float* d_next_rgba, void* d_hit_payloads, float* d_hit_rgba, uint32_t* d_n_hit);
 /* compact_rays_kernel (testbed.cu:423-446) with warp-aggregated reservation; counters: [0] alive, [1] hit */
 int ngp_compact_rays(void* stream, uint32_t n_rays, const uint32_t* d_n_rays, const void* d_src_payloads, const float* d_src_rgba,
                      void* d_dst_payloads, float* d_dst_rgba, void* d_hit_payloads, float* d_hit_rgba, uint32_t* d_n_alive, uint32_t* d_n_hit);

@@ -93,6 +93,7 @@ SIGNATURES = {
     "ngp_rollover": (i32, [vp, u32, vp, vp, u32, vp, vp]),
     "ngp_composite_infer": (i32, [vp, C.POINTER(RenderCfg), u32, vp, u32, u32, vp, vp, vp, vp, u32, i32, f32, f32, C.POINTER(f32), f32]),
     "ngp_composite_infer_dev": (i32, [vp, C.POINTER(RenderCfg), u32, vp, u32, vp, vp, vp, vp, u32, i32, f32, f32, C.POINTER(f32), f32]),
+    "ngp_composite_infer_compact_dev": (i32, [vp, C.POINTER(RenderCfg), u32, vp, u32, vp, vp, vp, vp, u32, i32, f32, f32, C.POINTER(f32), f32, vp, vp, vp, vp, vp]),
     "ngp_render_round": (i32, [vp, vp, u32, u32, u32, u32, u32, u32, u32]),
     "ngp_generate_coords_from_rays_dev": (i32, [vp, C.POINTER(SamplerCfg), u32, vp, u32, vp, vp, vp]),
     "ngp_compact_rays": (i32, [vp, u32, vp, vp, vp, vp, vp, vp, vp, vp, vp]),

@@ -7,21 +7,29 @@
 
 namespace ngp {
 
+// where the fused variant sends a ray after its compositing: alive -> the next ping-pong buffer, finished with alpha > 0.001 -> the hit
+// list (compact_rays_kernel's rule, testbed.cu:423-446), so the next round needs no compaction launch of its own
+struct CompactTargets { RayPayload* dst_p; float4* dst_c; RayPayload* hit_p; float4* hit_c; uint32_t* n_alive; uint32_t* n_hit; };
+
+template <bool COMPACT>
 __global__ void __launch_bounds__(128) composite_infer_kernel(
 	ngp_render_cfg c, uint32_t n_rays_max, const uint32_t* __restrict__ n_rays_ptr, uint32_t n_steps_arg, uint32_t n_steps_offset_arg,
 	const uint32_t* __restrict__ n_steps_ptr, const uint32_t* __restrict__ n_steps_offset_ptr,
 	RayPayload* __restrict__ payloads, float4* __restrict__ rgba, const Coordinate* __restrict__ coords, const __half* __restrict__ net_out,
-	uint32_t padded_width, int render_mode, float aabb_min, float aabb_max, float fwd_x, float fwd_y, float fwd_z, float depth_scale)
+	uint32_t padded_width, int render_mode, float aabb_min, float aabb_max, float fwd_x, float fwd_y, float fwd_z, float depth_scale, CompactTargets ct)
 {
 	const uint32_t n_rays = n_rays_ptr ? min(*n_rays_ptr, n_rays_max) : n_rays_max;
 	const uint32_t n_steps = n_steps_ptr ? *n_steps_ptr : n_steps_arg;
 	const uint32_t n_steps_offset = n_steps_offset_ptr ? *n_steps_offset_ptr : n_steps_offset_arg;
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_rays) return;
-	RayPayload& p = payloads[i];
-	if (!p.alive) return;
-	float4 l = rgba[i];
-	const uint32_t steps = p.n_steps;
+	if (!COMPACT && i >= n_rays) return;
+	const bool in_range = i < n_rays;
+	RayPayload p;
+	float4 l = make_float4(0.f, 0.f, 0.f, 0.f);
+	if (in_range) { p = payloads[i]; l = rgba[i]; } else { p.alive = 0; p.n_steps = 0; }
+	if (!COMPACT && !p.alive) return;
+	const bool was_alive = in_range && p.alive;
+	const uint32_t steps = was_alive ? p.n_steps : 0u;
 	uint32_t j = 0;
 	for (; j < steps; ++j) {
 		const Coordinate co = coords[(size_t)i * n_steps + j];
@@ -53,8 +61,26 @@ __global__ void __launch_bounds__(128) composite_infer_kernel(
 		l.x += r * w; l.y += g * w; l.z += b * w; l.w += w;
 		if (l.w > (1.0f - c.transmittance_threshold)) break;
 	}
-	if (j < n_steps) { p.alive = 0; p.n_steps = j + n_steps_offset; }
-	rgba[i] = l;
+	if (was_alive && j < n_steps) { p.alive = 0; p.n_steps = j + n_steps_offset; }
+	if (!COMPACT) {
+		payloads[i].alive = p.alive; payloads[i].n_steps = p.n_steps;
+		rgba[i] = l;
+		return;
+	}
+	// compaction, warp-aggregated: one atomicAdd per warp and list
+	const uint32_t lane = threadIdx.x & 31;
+	const bool alive = was_alive && p.alive != 0;
+	const bool hit = in_range && !alive && l.w > 0.001f;
+	const uint32_t am = __ballot_sync(0xffffffffu, alive), hm = __ballot_sync(0xffffffffu, hit);
+	uint32_t abase = 0, hbase = 0;
+	if (lane == 0) {
+		if (am) abase = atomicAdd(ct.n_alive, __popc(am));
+		if (hm) hbase = atomicAdd(ct.n_hit, __popc(hm));
+	}
+	abase = __shfl_sync(0xffffffffu, abase, 0); hbase = __shfl_sync(0xffffffffu, hbase, 0);
+	const uint32_t below = (1u << lane) - 1u;
+	if (alive) { const uint32_t d = abase + __popc(am & below); ct.dst_p[d] = p; ct.dst_c[d] = l; }
+	else if (hit) { const uint32_t d = hbase + __popc(hm & below); ct.hit_p[d] = p; ct.hit_c[d] = l; }
 }
 
 // alive -> next ping-pong buffer, finished with alpha > 0.001 -> hit list.  Warp-aggregated: one atomicAdd per warp per
@@ -181,13 +207,19 @@ using namespace ngp;
 static int composite_infer_impl(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays, const uint32_t* d_n_rays, uint32_t n_steps, uint32_t n_steps_offset,
                                 const uint32_t* d_n_steps, const uint32_t* d_n_steps_offset,
                                 void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
-                                float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale) {
+                                float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale, const CompactTargets* ct = nullptr) {
 	NGP_REQUIRE(cfg && d_payloads && d_rgba && d_coords && d_rgbsigma && camera_fwd_host, "null pointer");
 	if (n_rays == 0) return 0;
-	NGP_LAUNCH("composite_infer_kernel", (cudaStream_t)stream, composite_infer_kernel<<<div_up(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(*cfg, n_rays, d_n_rays, n_steps, n_steps_offset,
-		d_n_steps, d_n_steps_offset, (RayPayload*)d_payloads,
-		(float4*)d_rgba, (const Coordinate*)d_coords, (const __half*)d_rgbsigma, padded_width, render_mode, aabb_min, aabb_max,
-		camera_fwd_host[0], camera_fwd_host[1], camera_fwd_host[2], depth_scale));
+	cudaStream_t s = (cudaStream_t)stream;
+	if (ct) {
+		NGP_LAUNCH("composite_infer_kernel", s, composite_infer_kernel<true><<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, n_rays, d_n_rays, n_steps, n_steps_offset,
+			d_n_steps, d_n_steps_offset, (RayPayload*)d_payloads, (float4*)d_rgba, (const Coordinate*)d_coords, (const __half*)d_rgbsigma, padded_width, render_mode,
+			aabb_min, aabb_max, camera_fwd_host[0], camera_fwd_host[1], camera_fwd_host[2], depth_scale, *ct));
+	} else {
+		NGP_LAUNCH("composite_infer_kernel", s, composite_infer_kernel<false><<<div_up(n_rays, 128), 128, 0, s>>>(*cfg, n_rays, d_n_rays, n_steps, n_steps_offset,
+			d_n_steps, d_n_steps_offset, (RayPayload*)d_payloads, (float4*)d_rgba, (const Coordinate*)d_coords, (const __half*)d_rgbsigma, padded_width, render_mode,
+			aabb_min, aabb_max, camera_fwd_host[0], camera_fwd_host[1], camera_fwd_host[2], depth_scale, CompactTargets{}));
+	}
 	return check_launch("composite_infer");
 }
 
@@ -204,6 +236,18 @@ extern "C" int ngp_composite_infer_dev(void* stream, const ngp_render_cfg* cfg, 
 	NGP_REQUIRE(d_ctl, "null pointer");
 	return composite_infer_impl(stream, cfg, n_rays_bound, d_ctl + ((round + 1) & 1), 0, 0, d_ctl + 2, d_ctl + 4, d_payloads, d_rgba, d_coords, d_rgbsigma, padded_width,
 	                            render_mode, aabb_min, aabb_max, camera_fwd_host, depth_scale);
+}
+
+extern "C" int ngp_composite_infer_compact_dev(void* stream, const ngp_render_cfg* cfg, uint32_t n_rays_bound, uint32_t* d_ctl, uint32_t round,
+                                               void* d_payloads, float* d_rgba, const float* d_coords, const void* d_rgbsigma, uint32_t padded_width, int render_mode,
+                                               float aabb_min, float aabb_max, const float* camera_fwd_host, float depth_scale,
+                                               void* d_next_payloads, float* d_next_rgba, void* d_hit_payloads, float* d_hit_rgba, uint32_t* d_n_hit) {
+	NGP_REQUIRE(d_ctl && d_next_payloads && d_next_rgba && d_hit_payloads && d_hit_rgba && d_n_hit, "null pointer");
+	// the live rays of round + 1 are counted where that round's compaction would have counted them: d_ctl[(round + 2) & 1],
+	// which ngp_render_round(round) has cleared
+	const CompactTargets ct{(RayPayload*)d_next_payloads, (float4*)d_next_rgba, (RayPayload*)d_hit_payloads, (float4*)d_hit_rgba, d_ctl + (round & 1), d_n_hit};
+	return composite_infer_impl(stream, cfg, n_rays_bound, d_ctl + ((round + 1) & 1), 0, 0, d_ctl + 2, d_ctl + 4, d_payloads, d_rgba, d_coords, d_rgbsigma, padded_width,
+	                            render_mode, aabb_min, aabb_max, camera_fwd_host, depth_scale, &ct);
 }
 
 extern "C" int ngp_render_round(void* stream, uint32_t* d_ctl, uint32_t round, uint32_t n_pixels, uint32_t min_steps, uint32_t max_steps, uint32_t tail_steps, uint32_t march_iter,

@@ -195,6 +195,7 @@ PYBIND11_MODULE(pyngp, m) {
 		.def_readwrite("CONCURRENT_BANDS", &Testbed::RenderingBuffer::CONCURRENT_BANDS, "device loop: 2 = march the frame as two row bands on two streams at once (default), 1 = one pass")
 		.def_readwrite("CONCURRENT_BANDS_MIN_PIXELS", &Testbed::RenderingBuffer::CONCURRENT_BANDS_MIN_PIXELS)
 		.def_readwrite("MIN_BATCH_SAMPLES", &Testbed::RenderingBuffer::MIN_BATCH_SAMPLES, "device loop: a round's step count aims at max(pixels, this) samples (0 = the reference's rule)")
+		.def_readwrite("fused_compaction", &Testbed::RenderingBuffer::fused_compaction, "device loop: compositing and the next round's compaction in one launch (default on)")
 		.def_readwrite("ROUNDS_PER_READBACK", &Testbed::RenderingBuffer::ROUNDS_PER_READBACK)
 		.def_readwrite("TAIL_STEPS", &Testbed::RenderingBuffer::TAIL_STEPS, "late rounds (batch below a quarter of the frame) take up to this many steps; <= MAX_STEPS_INBETWEEN_COMPACTION switches it off")
 		.def_readonly("rounds_last_frame", &Testbed::RenderingBuffer::rounds_last_frame)

@@ -50,16 +50,22 @@ void RayMarcher::volume_rendering(uint32_t n_rays, const uint32_t* d_n_rays, uin
 	                              rgbsigma.data(), padded_output_width, (int)render_mode, aabb.min[0], aabb.max[0], fwd, depth_scale));
 }
 
-void RayMarcher::volume_rendering_dev(uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,
+void RayMarcher::volume_rendering_dev(uint32_t n_rays_bound, uint32_t* d_ctl, uint32_t round, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,
                                       const DeviceBuffer<precision_t>& rgbsigma, uint32_t padded_output_width, EActivation density_activation, EActivation rgb_activation,
                                       ERenderMode render_mode, const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const Mat34& camera_matrix,
-                                      float depth_scale, cudaStream_t stream)
+                                      float depth_scale, cudaStream_t stream, RaysSoA* next, RaysSoA* hit, uint32_t* d_n_hit)
 {
 	ngp_render_cfg c{};
 	c.n_cascades = n_cascades; c.min_step = min_cone_stepsize;
 	c.rgb_activation = (int)rgb_activation; c.density_activation = (int)density_activation;
 	c.transmittance_threshold = transmittance_threshold;
 	const float fwd[3] = {camera_matrix.at(0, 2), camera_matrix.at(1, 2), camera_matrix.at(2, 2)};
+	if (next && hit && d_n_hit) {
+		api_check(ngp_composite_infer_compact_dev(stream, &c, n_rays_bound, d_ctl, round, rays.payload.data(), rays.rgba.data(), (const float*)coords.data(),
+		                                          rgbsigma.data(), padded_output_width, (int)render_mode, aabb.min[0], aabb.max[0], fwd, depth_scale,
+		                                          next->payload.data(), next->rgba.data(), hit->payload.data(), hit->rgba.data(), d_n_hit));
+		return;
+	}
 	api_check(ngp_composite_infer_dev(stream, &c, n_rays_bound, d_ctl, round, rays.payload.data(), rays.rgba.data(), (const float*)coords.data(),
 	                                  rgbsigma.data(), padded_output_width, (int)render_mode, aabb.min[0], aabb.max[0], fwd, depth_scale));
 }

@@ -42,10 +42,12 @@ public:
 	                      ERenderMode render_mode, const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const Mat34& camera_matrix,
 	                      float depth_scale, cudaStream_t stream);
 	// the same with the round's counts read from the device control block of the device-driven render loop (include/ngp_b200.h)
-	void volume_rendering_dev(uint32_t n_rays_bound, const uint32_t* d_ctl, uint32_t round, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,
+	// next / hit (optional, together): the launch also compacts -- live rays go to `next`, finished ones to the hit list -- so the
+	// following round needs no compaction launch (ngp_composite_infer_compact_dev)
+	void volume_rendering_dev(uint32_t n_rays_bound, uint32_t* d_ctl, uint32_t round, RaysSoA& rays, const DeviceBuffer<Coordinate>& coords,
 	                          const DeviceBuffer<precision_t>& rgbsigma, uint32_t padded_output_width, EActivation density_activation, EActivation rgb_activation,
 	                          ERenderMode render_mode, const BoundingBox& aabb, uint32_t n_cascades, float min_cone_stepsize, const Mat34& camera_matrix,
-	                          float depth_scale, cudaStream_t stream);
+	                          float depth_scale, cudaStream_t stream, RaysSoA* next = nullptr, RaysSoA* hit = nullptr, uint32_t* d_n_hit = nullptr);
 
 public:
 	bool train_with_random_bg_color;

@@ -165,6 +165,7 @@ public:
 		uint32_t MAX_STEPS_INBETWEEN_COMPACTION = 8;
 		// Not in the reference: how the rounds are scheduled (the image does not depend on it).
 		bool device_loop = true;              // rounds decided on the device, live-ray count read back every ROUNDS_PER_READBACK rounds (false: testbed.cu's loop, one sync per round)
+		bool fused_compaction = true;         // device loop: the compositing launch also sorts its rays into the next round's buffer / the hit list
 		uint32_t ROUNDS_PER_READBACK = 8;
 		uint32_t MIN_BATCH_SAMPLES = 1u << 21; // the step count of a round aims at max(pixels, this) samples (0: the reference's rule, one sample per pixel)
 		uint32_t TAIL_STEPS = 32;             // late rounds (batch below a quarter of the frame) take up to this many steps (<= MAX...: off)

@@ -76,20 +76,26 @@ void Testbed::render_frame(const Mat34& camera_matrix, CudaRenderBuffer& render_
 					const uint32_t round = u.round;
 					RaysSoA& rays_previous = bd.rays[round % 2];
 					RaysSoA& rays_current = bd.rays[(round + 1) % 2];
-					api_check(ngp_compact_rays(u.stream, u.bound, round == 0 ? nullptr : ctl + (round & 1), rays_previous.payload.data(), rays_previous.rgba.data(),
-					                           rays_current.payload.data(), rays_current.rgba.data(), bd.rays_hit.payload.data(), bd.rays_hit.rgba.data(),
-					                           ctl + ((round + 1) & 1), bd.n_hit_counter.data()));
+					// only the frame's first round compacts in a launch of its own (the rays the set-up left alive); afterwards the
+					// compositing of round r - 1 has already sorted its rays into this round's buffer and the hit list
+					if (round == 0 || !rb.fused_compaction)
+						api_check(ngp_compact_rays(u.stream, u.bound, round == 0 ? nullptr : ctl + (round & 1), rays_previous.payload.data(), rays_previous.rgba.data(),
+						                           rays_current.payload.data(), rays_current.rgba.data(), bd.rays_hit.payload.data(), bd.rays_hit.rgba.data(),
+						                           ctl + ((round + 1) & 1), bd.n_hit_counter.data()));
 					api_check(ngp_render_round(u.stream, ctl, round, u.n_pixels, rb.MIN_STEPS_INBETWEEN_COMPACTION, rb.MAX_STEPS_INBETWEEN_COMPACTION, tail_steps, MARCH_ITER, rb.MIN_BATCH_SAMPLES));
 					m_sampler->generate_coords_from_rays_dev(u.bound, ctl, round, rays_current.payload, bd.coords, u.stream);
 					// rendering uses the EMA weights (use_inference_matrices = true, testbed.cu:556)
 					m_network->inference_mixed_precision(u.stream, bd.coords.data(), sample_bound, ctl + 3, bd.rgbsigma.data(), true, n_bands > 1 ? &bd.workspace : nullptr);
 					if (render_mode == ERenderMode::Normals) m_network->input_gradient(u.stream, 3, bd.coords.data(), sample_bound, ctl + 3);   // testbed.cu:558-560
 					m_render->volume_rendering_dev(u.bound, ctl, round, rays_current, bd.coords, bd.rgbsigma, padded_output_width, m_density_activation, m_rgb_activation,
-					                               render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix, 1.f / m_scene_scale, u.stream);
+					                               render_mode, m_sampler->aabb, m_sampler->n_cascades, m_sampler->min_cone_stepsize, camera_matrix, 1.f / m_scene_scale, u.stream,
+					                               rb.fused_compaction ? &rays_previous : nullptr, rb.fused_compaction ? &bd.rays_hit : nullptr,
+					                               rb.fused_compaction ? bd.n_hit_counter.data() : nullptr);
 				}
 				// live rays after the batch's last compaction (some may have been finished by its compositing: the next compaction sorts
 				// that out), still an upper bound for everything that follows
-				NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 8 * b, ctl + (u.round & 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, u.stream));
+				// (with the fused compaction the newest count is the one the last compositing left for the next round)
+				NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 8 * b, ctl + ((u.round + (rb.fused_compaction ? 1u : 0u)) & 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, u.stream));
 				NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counter + 8 * b + 1, ctl + 4, sizeof(uint32_t), cudaMemcpyDeviceToHost, u.stream));
 			}
 			if (!any) break;

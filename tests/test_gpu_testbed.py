@@ -152,8 +152,9 @@ def test_device_driven_render_loop_gives_the_identical_image(pyngp):
         rb.device_loop = False
         want = np.array(tb.render(w, h, 1, False))
         host_rounds, host_syncs = rb.rounds_last_frame, rb.readbacks_last_frame
-        for tail, per_batch, bands, min_batch in ((32, 8, 2, 1 << 21), (32, 8, 1, 0), (8, 3, 1, 0), (64, 1, 2, 1 << 18)):
+        for tail, per_batch, bands, min_batch, fused in ((32, 8, 2, 1 << 21, True), (32, 8, 1, 0, False), (8, 3, 1, 0, True), (64, 1, 2, 1 << 18, False)):
             rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS, rb.MIN_BATCH_SAMPLES = True, tail, per_batch, bands, min_batch
+            rb.fused_compaction = fused
             got = np.array(tb.render(w, h, 1, False))
             assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (mode, tail, per_batch, bands, min_batch)
             if (tail, per_batch) == (32, 8):
@@ -163,6 +164,7 @@ def test_device_driven_render_loop_gives_the_identical_image(pyngp):
     rb.render_mode = pyngp.RenderMode.Shade
     rb.device_loop, rb.TAIL_STEPS, rb.ROUNDS_PER_READBACK, rb.CONCURRENT_BANDS, rb.MIN_BATCH_SAMPLES = True, 32, 8, 2, 1 << 21
     rb.CONCURRENT_BANDS_MIN_PIXELS = 1 << 20
+    rb.fused_compaction = True
     assert want[..., 3].max() > 0.5
 
 
